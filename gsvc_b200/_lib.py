@@ -1,0 +1,99 @@
+"""ctypes binding of libgs2d.so (include/gs2d.h).  No fallback of any kind: if the library
+is missing or the device is not sm_100, every entry point raises."""
+from __future__ import annotations
+
+import ctypes
+import os
+from ctypes import POINTER, Structure, c_char_p, c_float, c_int, c_size_t, c_void_p
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "lib", "libgs2d.so")
+
+GS2D_OK = 0
+
+
+class StateLayout(Structure):
+    """mirror of gs2d_state_layout (include/gs2d.h)"""
+
+    _fields_ = [
+        ("total_bytes", c_size_t),
+        ("off_status", c_size_t),
+        ("off_tile_bins", c_size_t),
+        ("off_ids_sorted", c_size_t),
+        ("off_keys_sorted", c_size_t),
+        ("off_packed", c_size_t),
+        ("off_scratch", c_size_t),
+        ("zero_begin", c_size_t),
+        ("zero_bytes", c_size_t),
+        ("key_bits", c_int),
+        ("sort_passes", c_int),
+    ]
+
+
+_P = c_void_p
+_SIGNATURES = {
+    "gs2d_version": (c_int, []),
+    "gs2d_last_error": (c_char_p, []),
+    "gs2d_device_arch": (c_int, [c_int]),
+    "gs2d_project_chol_fwd": (c_int, [c_int, _P, _P, c_int, c_int, c_int, c_int, c_float, _P, _P, _P, _P, _P, _P]),
+    "gs2d_project_scalerot_fwd": (c_int, [c_int, _P, _P, _P, c_int, c_int, c_int, c_int, c_float, _P, _P, _P, _P, _P, _P]),
+    "gs2d_project_chol_bwd": (c_int, [c_int, _P, c_int, c_int, _P, _P, _P, c_int, _P, c_int, _P, _P, _P, _P]),
+    "gs2d_project_scalerot_bwd": (c_int, [c_int, _P, _P, c_int, c_int, _P, _P, _P, c_int, _P, c_int, _P, _P, _P, _P, _P]),
+    "gs2d_cov2d_bounds": (c_int, [c_int, _P, _P, _P, _P]),
+    "gs2d_scan_scratch_bytes": (c_size_t, [c_int]),
+    "gs2d_cumsum_tiles_hit": (c_int, [c_int, _P, _P, _P, _P, _P, c_size_t, _P]),
+    "gs2d_map_intersects": (c_int, [c_int, c_int, _P, _P, _P, _P, c_int, c_int, _P, _P, _P]),
+    "gs2d_sort_scratch_bytes": (c_size_t, [c_int]),
+    "gs2d_sort_pairs": (c_int, [c_int, _P, _P, _P, _P, c_int, c_int, _P, c_size_t, _P]),
+    "gs2d_tile_bin_edges": (c_int, [c_int, _P, _P, c_int, _P]),
+    "gs2d_state_layout_for": (c_int, [c_int, c_int, c_int, c_int, POINTER(StateLayout)]),
+    "gs2d_rasterize_sum_fwd": (c_int, [c_int, _P, _P, _P, _P, _P, _P, _P, c_int, c_int, c_int, _P, c_size_t, _P, _P, _P, _P, _P]),
+    "gs2d_raster_binned_scratch_bytes": (c_size_t, [c_int]),
+    "gs2d_rasterize_sum_fwd_binned": (c_int, [c_int, c_int, _P, _P, _P, _P, _P, _P, c_int, c_int, _P, _P, _P, _P, c_size_t, _P]),
+    "gs2d_rasterize_sum_bwd": (c_int, [c_int, c_int, c_int, c_int, _P, c_size_t, _P, _P, _P, _P]),
+    "gs2d_rasterize_sum_bwd_binned": (c_int, [c_int, c_int, _P, _P, _P, _P, _P, _P, c_int, c_int, _P, _P, _P, _P, c_size_t, _P]),
+}
+
+_lib = None
+_arch_ok: dict = {}
+
+
+def exported_symbols():
+    """every symbol include/gs2d.h declares (used by the CPU load test)"""
+    return sorted(_SIGNATURES)
+
+
+def load() -> ctypes.CDLL:
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise RuntimeError(
+                f"gsvc_b200: {LIB_PATH} is missing -- build it with `python -m gsvc_b200.build` "
+                "(there is no CPU or PyTorch fallback)"
+            )
+        lib = ctypes.CDLL(LIB_PATH)
+        for name, (res, args) in _SIGNATURES.items():
+            fn = getattr(lib, name)   # AttributeError if the .so lacks a declared symbol
+            fn.restype = res
+            fn.argtypes = args
+        _lib = lib
+    return _lib
+
+
+def check(rc: int, what: str = "") -> None:
+    if rc != GS2D_OK:
+        msg = load().gs2d_last_error().decode("utf-8", "replace")
+        raise RuntimeError(f"gs2d {what} failed (code {rc}): {msg}")
+
+
+def require_device(index: int) -> None:
+    """The kernels are sm_100a only; refuse anything else loudly (no dispatch, no fallback)."""
+    ok = _arch_ok.get(index)
+    if ok is None:
+        arch = load().gs2d_device_arch(int(index))
+        ok = arch == 100
+        _arch_ok[index] = ok
+        if not ok:
+            raise RuntimeError(f"gsvc_b200 needs an sm_100 (B200) device, cuda:{index} reports sm_{arch}")
+    elif not ok:
+        raise RuntimeError(f"gsvc_b200 needs an sm_100 (B200) device, cuda:{index} is not")

@@ -1,0 +1,276 @@
+// raster.cu -- accumulated-sum rasteriser, forward and backward.
+// Reference: rasterize_forward_sum forward.cu:512-627 (host bindings.cu:400-469),
+//            rasterize_backward_sum_kernel backward.cu:696-862 (host bindings.cu:706-779).
+//
+// Forward: one CTA per 16x16 tile, one thread per pixel.  The tile's batch (at most the
+// first 256 sorted entries -- the reference renders only batch 0) is one
+// contiguous run of 48-byte packed records, staged into shared memory with 16-byte
+// cp.async.  Each warp owns two pixel rows; 32 lanes test 32 records' row ranges at once
+// and the warp only evaluates the records whose conservative rectangle touches its rows
+// (warp-cooperative early-out; rejected pixels could not pass the alpha test, so the
+// result is unchanged).
+//
+// Backward: one warp per sorted (tile, Gaussian) pair; lanes sweep the pair's pixel
+// rectangle, keep nine partial sums in registers, and one 14-shuffle transposed butterfly
+// leaves one total per lane group; the pair then issues a single coalesced reduction
+// (8 lanes, consecutive floats) plus one for opacity -- one atomic transaction per
+// Gaussian per tile, where the reference issues 9 atomicAdd per warp per Gaussian.
+#include "gs2d_internal.h"
+#include "gs2d_math.cuh"
+
+namespace gs2d {
+
+__device__ __forceinline__ void cp_async16(void* smem, const void* gmem) {
+    const unsigned sa = (unsigned)__cvta_generic_to_shared(smem);
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(sa), "l"(gmem) : "memory");
+}
+__device__ __forceinline__ void cp_async_wait_all() {
+    asm volatile("cp.async.commit_group;\ncp.async.wait_group 0;" ::: "memory");
+}
+
+// ------------------------------------------------------------------------------------------
+// forward
+// ------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(GS2D_TILE_PIX)
+k_raster_fwd(int W, int H, int tx, const int32_t* __restrict__ tile_bins, const float4* __restrict__ packed,
+             float* __restrict__ out_img, float* __restrict__ final_Ts, int32_t* __restrict__ final_idx) {
+    __shared__ float4 sq[GS2D_MAX_PER_TILE * 3];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int t = blockIdx.y * tx + blockIdx.x;
+    const int2 range = reinterpret_cast<const int2*>(tile_bins)[t];
+    const int lo = range.x;
+    const int nb = max(0, min(range.y - range.x, GS2D_MAX_PER_TILE));
+
+    const float4* src = packed + 3 * (size_t)lo;
+    for (int i = tid; i < nb * 3; i += GS2D_TILE_PIX) cp_async16(&sq[i], src + i);
+    cp_async_wait_all();
+    __syncthreads();
+
+    const int lx = tid & 15, ly = tid >> 4;   // warp w owns rows 2w, 2w+1 of the tile
+    const int px_i = blockIdx.x * GS2D_TILE + lx, py_i = blockIdx.y * GS2D_TILE + ly;
+    const bool inside = px_i < W && py_i < H;
+    const float px = (float)px_i, py = (float)py_i;
+    const int row_lo = 2 * warp, row_hi = 2 * warp + 1;
+
+    float3 pix = make_float3(0.f, 0.f, 0.f);
+    int cur_idx = 0;
+    for (int c = 0; c < nb; c += 32) {
+        const int k_lane = c + lane;
+        bool touch = false;
+        if (k_lane < nb) {
+            const uint32_t rect = __float_as_uint(sq[3 * k_lane + 1].z);
+            const int y0 = (rect >> 16) & 255, y1 = rect >> 24;
+            touch = (y1 >= row_lo) && (y0 <= row_hi);
+        }
+        unsigned m = __ballot_sync(0xffffffffu, touch);
+        while (m) {
+            const int k = c + __ffs(m) - 1;
+            m &= m - 1;
+            const float4 q0 = sq[3 * k];       // x, y, conic.x, conic.y
+            const float4 q1 = sq[3 * k + 1];   // conic.z, opacity, rect, id
+            const float dx = subf(q0.x, px), dy = subf(q0.y, py);
+            const float sigma = gauss_sigma(dx, dy, q0.z, q0.w, q1.x);
+            const float alpha = minf(mulf(q1.y, gauss_vis(sigma)), 1.f);
+            if (inside && gauss_pass(sigma, alpha)) {
+                const float4 q2 = sq[3 * k + 2];   // r, g, b, tile
+                pix.x = fmaf_(alpha, q2.x, pix.x);
+                pix.y = fmaf_(alpha, q2.y, pix.y);
+                pix.z = fmaf_(alpha, q2.z, pix.z);
+                cur_idx = lo + k;
+            }
+        }
+    }
+    if (inside) {
+        const size_t p = (size_t)py_i * W + px_i;
+        out_img[3 * p] = pix.x; out_img[3 * p + 1] = pix.y; out_img[3 * p + 2] = pix.z;
+        if (final_idx) final_idx[p] = cur_idx;
+        if (final_Ts) final_Ts[p] = 1.f;   // constant in the sum variant (forward.cu:557, 618)
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// backward
+// ------------------------------------------------------------------------------------------
+// Sum 8 per-lane values over the warp with 9 shuffles: after the call, the total of v[j]
+// is held by the lanes whose (lane >> 2) == j.
+__device__ __forceinline__ float warp_reduce8_transposed(float (&v)[8], int lane) {
+    const bool b4 = lane & 16, b3 = lane & 8, b2 = lane & 4;
+    float w[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        const float send = b4 ? v[k] : v[4 + k];
+        const float keep = b4 ? v[4 + k] : v[k];
+        w[k] = keep + __shfl_xor_sync(0xffffffffu, send, 16);
+    }
+    float u[2];
+#pragma unroll
+    for (int k = 0; k < 2; ++k) {
+        const float send = b3 ? w[k] : w[2 + k];
+        const float keep = b3 ? w[2 + k] : w[k];
+        u[k] = keep + __shfl_xor_sync(0xffffffffu, send, 8);
+    }
+    const float send = b2 ? u[0] : u[1];
+    const float keep = b2 ? u[1] : u[0];
+    float r = keep + __shfl_xor_sync(0xffffffffu, send, 4);
+    r += __shfl_xor_sync(0xffffffffu, r, 2);
+    r += __shfl_xor_sync(0xffffffffu, r, 1);
+    return r;
+}
+
+constexpr int kBwdThreads = 256;
+
+__global__ void __launch_bounds__(kBwdThreads)
+k_raster_bwd(const int32_t* __restrict__ n_dev, int n_static, int W, int tx, const int32_t* __restrict__ tile_bins,
+             const float4* __restrict__ packed, const int32_t* __restrict__ final_idx,
+             const float* __restrict__ v_out, float* __restrict__ grads) {
+    const int n = n_dev ? *n_dev : n_static;
+    const int lane = threadIdx.x & 31;
+    const int i = blockIdx.x * (kBwdThreads / 32) + (threadIdx.x >> 5);   // sorted index of this warp's pair
+    if (i >= n) return;
+    const float4 q1 = packed[3 * (size_t)i + 1];
+    const uint32_t rect = __float_as_uint(q1.z);
+    const int rx0 = rect & 255, rx1 = (rect >> 8) & 255, ry0 = (rect >> 16) & 255, ry1 = rect >> 24;
+    if (ry1 < ry0) return;                              // no pixel of this tile can pass
+    const float4 q2 = packed[3 * (size_t)i + 2];
+    const int t = (int)__float_as_uint(q2.w);
+    if (i - tile_bins[2 * t] >= GS2D_MAX_PER_TILE) return;   // never rendered, final_idx < i
+    const float4 q0 = packed[3 * (size_t)i];
+    const float gx = q0.x, gy = q0.y, cx = q0.z, cy = q0.w, cz = q1.x, opac = q1.y;
+    const int ox = (t % tx) * GS2D_TILE, oy = (t / tx) * GS2D_TILE;
+    const int w = rx1 - rx0 + 1, area = w * (ry1 - ry0 + 1);
+    const float inv_w = 1.f / (float)w;
+
+    float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    float acc_op = 0.f;
+    for (int p = lane; p < area; p += 32) {
+        const int ry = (int)(((float)p + 0.5f) * inv_w);
+        const int px_i = ox + rx0 + (p - ry * w), py_i = oy + ry0 + ry;
+        const size_t pid = (size_t)py_i * W + px_i;
+        if (i > final_idx[pid]) continue;              // backward.cu:784-787
+        const float dx = subf(gx, (float)px_i), dy = subf(gy, (float)py_i);
+        const float sigma = gauss_sigma(dx, dy, cx, cy, cz);
+        const float vis = gauss_vis(sigma);
+        const float alpha = minf(mulf(opac, vis), 1.f);
+        if (!gauss_pass(sigma, alpha)) continue;
+        const float vr = v_out[3 * pid], vg = v_out[3 * pid + 1], vb = v_out[3 * pid + 2];
+        const float v_alpha = q2.x * vr + q2.y * vg + q2.z * vb;       // backward.cu:821-825
+        const float v_sigma = -opac * vis * v_alpha;                    // :827
+        acc[0] += v_sigma * (cx * dx + cy * dy);                        // v_xy     :831-832
+        acc[1] += v_sigma * (cy * dx + cz * dy);
+        const float hs = 0.5f * v_sigma;
+        acc[2] += hs * dx * dx;                                         // v_conic  :828-830
+        acc[3] += hs * dx * dy;
+        acc[4] += hs * dy * dy;
+        acc[5] += alpha * vr;                                           // v_rgb    :817
+        acc[6] += alpha * vg;
+        acc[7] += alpha * vb;
+        acc_op += vis * v_alpha;                                        // v_opacity :833
+    }
+    const float tot = warp_reduce8_transposed(acc, lane);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) acc_op += __shfl_xor_sync(0xffffffffu, acc_op, o);
+    const int g = __float_as_int(q1.w);
+    float* row = grads + (size_t)g * 12;
+    if ((lane & 3) == 0) {
+        if (tot != 0.f) atomicAdd(row + (lane >> 2), tot);   // 8 lanes, 8 consecutive floats: one transaction
+    } else if (lane == 1) {
+        if (acc_op != 0.f) atomicAdd(row + 8, acc_op);
+    }
+}
+
+static size_t align256(size_t v) { return (v + 255) / 256 * 256; }
+
+}  // namespace gs2d
+
+using namespace gs2d;
+
+extern "C" {
+
+int gs2d_rasterize_sum_fwd(int n, const float* xys, const float* depths, const int32_t* radii, const float* conics,
+                           const int32_t* num_tiles_hit, const float* colors, const float* opacities, int img_h,
+                           int img_w, int cap, void* state, size_t state_bytes, float* out_img, int32_t* final_idx,
+                           int32_t* status_host, gs2d_event_t scan_done, gs2d_stream_t stream) {
+    GS2D_REQUIRE(n >= 0 && img_h > 0 && img_w > 0 && cap > 0, "rasterize_sum_fwd: bad sizes");
+    const int tx = div_up(img_w, GS2D_TILE), ty = div_up(img_h, GS2D_TILE);
+    StateOffsets so;
+    int rc = compute_state_offsets(n, cap, tx, ty, &so);
+    if (rc != GS2D_OK) return rc;
+    GS2D_REQUIRE(state_bytes >= so.pub.total_bytes, "rasterize_sum_fwd: state buffer too small");
+    GS2D_REQUIRE(((uintptr_t)state & 255) == 0, "rasterize_sum_fwd: state buffer must be 256-byte aligned");
+    cudaStream_t s = (cudaStream_t)stream;
+    char* st = (char*)state;
+    rc = launch_bin_and_pack(n, xys, depths, radii, num_tiles_hit, conics, colors, opacities, img_h, img_w, cap, so,
+                             st, status_host, (cudaEvent_t)scan_done, s);
+    if (rc != GS2D_OK) return rc;
+    k_raster_fwd<<<dim3(tx, ty), GS2D_TILE_PIX, 0, s>>>(img_w, img_h, tx, (const int32_t*)(st + so.pub.off_tile_bins),
+                                                        (const float4*)(st + so.pub.off_packed), out_img, nullptr,
+                                                        final_idx);
+    GS2D_CHECK_LAUNCH("raster_fwd");
+    return GS2D_OK;
+}
+
+size_t gs2d_raster_binned_scratch_bytes(int num_intersects) {
+    return align256((size_t)(num_intersects > 0 ? num_intersects : 1) * 3 * sizeof(float4));
+}
+
+int gs2d_rasterize_sum_fwd_binned(int n, int num_intersects, const int32_t* ids_sorted, const int32_t* tile_bins,
+                                  const float* xys, const float* conics, const float* colors, const float* opacities,
+                                  int img_h, int img_w, float* out_img, float* final_Ts, int32_t* final_idx,
+                                  void* scratch, size_t scratch_bytes, gs2d_stream_t stream) {
+    GS2D_REQUIRE(n >= 0 && num_intersects >= 0 && img_h > 0 && img_w > 0, "rasterize_sum_fwd_binned: bad sizes");
+    GS2D_REQUIRE(scratch_bytes >= gs2d_raster_binned_scratch_bytes(num_intersects),
+                 "rasterize_sum_fwd_binned: scratch too small");
+    const int tx = div_up(img_w, GS2D_TILE), ty = div_up(img_h, GS2D_TILE);
+    cudaStream_t s = (cudaStream_t)stream;
+    int rc = launch_pack_binned(num_intersects, ids_sorted, tile_bins, tx * ty, xys, conics, colors, opacities, img_h,
+                                img_w, (float4*)scratch, s);
+    if (rc != GS2D_OK) return rc;
+    k_raster_fwd<<<dim3(tx, ty), GS2D_TILE_PIX, 0, s>>>(img_w, img_h, tx, tile_bins, (const float4*)scratch, out_img,
+                                                        final_Ts, final_idx);
+    GS2D_CHECK_LAUNCH("raster_fwd_binned");
+    return GS2D_OK;
+}
+
+int gs2d_rasterize_sum_bwd(int n, int img_h, int img_w, int cap, const void* state, size_t state_bytes,
+                           const int32_t* final_idx, const float* v_out, float* grads, gs2d_stream_t stream) {
+    GS2D_REQUIRE(n >= 0 && img_h > 0 && img_w > 0 && cap > 0, "rasterize_sum_bwd: bad sizes");
+    const int tx = div_up(img_w, GS2D_TILE), ty = div_up(img_h, GS2D_TILE);
+    StateOffsets so;
+    const int rc = compute_state_offsets(n, cap, tx, ty, &so);
+    if (rc != GS2D_OK) return rc;
+    GS2D_REQUIRE(state_bytes >= so.pub.total_bytes, "rasterize_sum_bwd: state buffer too small");
+    cudaStream_t s = (cudaStream_t)stream;
+    const char* st = (const char*)state;
+    if (n == 0) return GS2D_OK;
+    GS2D_CHECK_CUDA(cudaMemsetAsync(grads, 0, (size_t)n * 12 * sizeof(float), s));
+    k_raster_bwd<<<div_up(cap, kBwdThreads / 32), kBwdThreads, 0, s>>>(
+        (const int32_t*)(st + so.pub.off_status) + 3, 0, img_w, tx, (const int32_t*)(st + so.pub.off_tile_bins),
+        (const float4*)(st + so.pub.off_packed), final_idx, v_out, grads);
+    GS2D_CHECK_LAUNCH("raster_bwd");
+    return GS2D_OK;
+}
+
+int gs2d_rasterize_sum_bwd_binned(int n, int num_intersects, const int32_t* ids_sorted, const int32_t* tile_bins,
+                                  const float* xys, const float* conics, const float* colors, const float* opacities,
+                                  int img_h, int img_w, const int32_t* final_idx, const float* v_out, float* grads,
+                                  void* scratch, size_t scratch_bytes, gs2d_stream_t stream) {
+    GS2D_REQUIRE(n >= 0 && num_intersects >= 0 && img_h > 0 && img_w > 0, "rasterize_sum_bwd_binned: bad sizes");
+    GS2D_REQUIRE(scratch_bytes >= gs2d_raster_binned_scratch_bytes(num_intersects),
+                 "rasterize_sum_bwd_binned: scratch too small");
+    const int tx = div_up(img_w, GS2D_TILE), ty = div_up(img_h, GS2D_TILE);
+    cudaStream_t s = (cudaStream_t)stream;
+    if (n == 0) return GS2D_OK;
+    GS2D_CHECK_CUDA(cudaMemsetAsync(grads, 0, (size_t)n * 12 * sizeof(float), s));
+    if (num_intersects == 0) return GS2D_OK;
+    // entries that belong to no tile range keep an all-zero record: opacity 0 never passes the alpha test
+    GS2D_CHECK_CUDA(cudaMemsetAsync(scratch, 0, gs2d_raster_binned_scratch_bytes(num_intersects), s));
+    int rc = launch_pack_binned(num_intersects, ids_sorted, tile_bins, tx * ty, xys, conics, colors, opacities, img_h,
+                                img_w, (float4*)scratch, s);
+    if (rc != GS2D_OK) return rc;
+    k_raster_bwd<<<div_up(num_intersects, kBwdThreads / 32), kBwdThreads, 0, s>>>(
+        nullptr, num_intersects, img_w, tx, tile_bins, (const float4*)scratch, final_idx, v_out, grads);
+    GS2D_CHECK_LAUNCH("raster_bwd_binned");
+    return GS2D_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,148 @@
+/*
+ * gs2d.h -- C ABI of libgs2d.so: the gsplat 2D-Gaussian hot path of ac-freeman/GSVC,
+ * written from scratch for NVIDIA B200 (sm_100a).
+ *
+ * Conventions (all entry points):
+ *   - every pointer is a DEVICE pointer unless its name ends in _host;
+ *   - `stream` is a cudaStream_t (NULL = legacy default stream); nothing synchronises
+ *     the host and nothing allocates: outputs and workspaces are caller-owned;
+ *   - the return value is GS2D_OK or an error code; gs2d_last_error() gives the text of
+ *     the calling thread's last failure.  Launch errors are checked after every launch
+ *     (the reference checks none);
+ *   - layouts are the reference's: row-major contiguous fp32 / int32 AoS exactly as its
+ *     torch tensors ([N,2] xys, [N,3] conics, ...).
+ * Each function cites the reference interface it replaces (paths relative to
+ * gsplat/gsplat/cuda/csrc/ of the reference tree unless noted).
+ */
+#ifndef GS2D_H
+#define GS2D_H
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define GS2D_OK 0
+#define GS2D_ERR_ARG 1
+#define GS2D_ERR_CUDA 2
+
+typedef void* gs2d_stream_t; /* cudaStream_t */
+typedef void* gs2d_event_t;  /* cudaEvent_t  */
+
+int gs2d_version(void);
+const char* gs2d_last_error(void);
+/* compute capability major*10+minor of `device`; the library only runs on 100 (sm_100a) */
+int gs2d_device_arch(int device);
+
+/* ---- projection ------------------------------------------------------------------- */
+/* replaces project_gaussians_2d_forward_tensor, bindings.cu:787-839 (kernel foward2d.cu:12-69).
+ * Writes every element of all five outputs (no pre-zeroing needed). clip_thresh is accepted
+ * and unused, as in the reference. */
+int gs2d_project_chol_fwd(int n, const float* means2d, const float* L_elements, int img_h, int img_w,
+                          int tiles_x, int tiles_y, float clip_thresh, float* xys, float* depths, int32_t* radii,
+                          float* conics, int32_t* num_tiles_hit, gs2d_stream_t stream);
+/* replaces project_gaussians_2d_scale_rot_forward_tensor, bindings.cu:841-899 (foward2d.cu:71-124) */
+int gs2d_project_scalerot_fwd(int n, const float* means2d, const float* scales2d, const float* rotation, int img_h,
+                              int img_w, int tiles_x, int tiles_y, float clip_thresh, float* xys, float* depths,
+                              int32_t* radii, float* conics, int32_t* num_tiles_hit, gs2d_stream_t stream);
+/* replaces project_gaussians_2d_backward_tensor, bindings.cu:902-949 (backward2d.cu:8-51).
+ * v_xy / v_conic rows may be strided: ld_* = floats between consecutive rows (2 / 3 when
+ * contiguous).  Reference formula incl. the doubled off-diagonal term. */
+int gs2d_project_chol_bwd(int n, const float* L_elements, int img_h, int img_w, const int32_t* radii,
+                          const float* conics, const float* v_xy, int ld_v_xy, const float* v_conic, int ld_v_conic,
+                          float* v_cov2d, float* v_mean2d, float* v_L_elements, gs2d_stream_t stream);
+/* replaces project_gaussians_2d_scale_rot_backward_tensor, bindings.cu:951-1004 (backward2d.cu:53-110) */
+int gs2d_project_scalerot_bwd(int n, const float* scales2d, const float* rotation, int img_h, int img_w,
+                              const int32_t* radii, const float* conics, const float* v_xy, int ld_v_xy,
+                              const float* v_conic, int ld_v_conic, float* v_cov2d, float* v_mean2d, float* v_scale,
+                              float* v_rot, gs2d_stream_t stream);
+/* replaces compute_cov2d_bounds_tensor, bindings.cu:41-61 (helpers.cuh:45-68); radii is fp32 [n] */
+int gs2d_cov2d_bounds(int n, const float* cov2d, float* conics, float* radii, gs2d_stream_t stream);
+
+/* ---- binning, step by step (the reference's public utilities) ----------------------- */
+/* replaces torch.cumsum(num_tiles_hit, dtype=int32), gsplat/gsplat/utils.py:116.  Inclusive scan.
+ * scratch: gs2d_scan_scratch_bytes(n) bytes.  The total (= cum[n-1]) is also written to
+ * total_out (device, may be NULL) and total_host (pinned host memory, may be NULL). */
+size_t gs2d_scan_scratch_bytes(int n);
+int gs2d_cumsum_tiles_hit(int n, const int32_t* num_tiles_hit, int32_t* cum_tiles_hit, int32_t* total_out,
+                          int32_t* total_host, void* scratch, size_t scratch_bytes, gs2d_stream_t stream);
+/* replaces map_gaussian_to_intersects_tensor, bindings.cu:274-313 (forward.cu:100-136).
+ * Key = (tile_id << 32) | sign-extended depth bits.  Slots of Gaussians with radii <= 0 are
+ * written as zero, matching the reference's zero-initialised outputs. */
+int gs2d_map_intersects(int n, int num_intersects, const float* xys, const float* depths, const int32_t* radii,
+                        const int32_t* cum_tiles_hit, int tiles_x, int tiles_y, int64_t* isect_ids,
+                        int32_t* gaussian_ids, gs2d_stream_t stream);
+/* replaces torch.sort(int64) + torch.gather, gsplat/gsplat/utils.py:164-165: stable ascending
+ * onesweep LSD radix sort of (int64 key, int32 value) pairs over key bits [begin_bit, end_bit)
+ * (signed order when end_bit == 64).  scratch: gs2d_sort_scratch_bytes(n). */
+size_t gs2d_sort_scratch_bytes(int n);
+int gs2d_sort_pairs(int n, const int64_t* keys_in, const int32_t* vals_in, int64_t* keys_out, int32_t* vals_out,
+                    int begin_bit, int end_bit, void* scratch, size_t scratch_bytes, gs2d_stream_t stream);
+/* replaces get_tile_bin_edges_tensor, bindings.cu:315-330 (forward.cu:141-163).  tile_bins has
+ * `rows` rows of (lo, hi) and is zero-filled here; rows must exceed every tile id. */
+int gs2d_tile_bin_edges(int num_intersects, const int64_t* isect_ids_sorted, int32_t* tile_bins, int rows,
+                        gs2d_stream_t stream);
+
+/* ---- rasteriser ---------------------------------------------------------------------- */
+/* Layout of the caller-owned state buffer of one forward (kept until its backward). */
+typedef struct {
+    size_t total_bytes;
+    size_t off_status;      /* int32[8]: [0] num_intersects, [1] overflow (num_intersects > cap),
+                               [2] OR of all depth bits, [3] min(num_intersects, cap) */
+    size_t off_tile_bins;   /* int32[tiles][2] */
+    size_t off_ids_sorted;  /* int32[cap]  gaussian_ids_sorted */
+    size_t off_keys_sorted; /* uint32[cap] tile id of each sorted intersection */
+    size_t off_packed;      /* float4[cap][3] sorted packed copy of the Gaussian parameters */
+    size_t off_scratch;     /* sort ping-pong, histograms, look-back state (dead after forward) */
+    size_t zero_begin;      /* [zero_begin, zero_begin + zero_bytes) is memset by the library */
+    size_t zero_bytes;
+    int key_bits;           /* ceil(log2(tiles)) : width of the radix sort */
+    int sort_passes;
+} gs2d_state_layout;
+int gs2d_state_layout_for(int n, int cap, int tiles_x, int tiles_y, gs2d_state_layout* out);
+
+/* Fused, sync-free replacement of the whole body of _RasterizeGaussiansSum.forward
+ * (gsplat/gsplat/rasterize_sum.py:93-186): compute_cumulative_intersects (utils.py:99-118),
+ * bin_and_sort_gaussians (utils.py:121-167: map forward.cu:100-136, torch.sort, gather, bin
+ * edges forward.cu:141-163) and rasterize_forward_sum (forward.cu:512-627, host bindings.cu:400-469).
+ * depths may be NULL (= all zero, which is what both projections produce); otherwise the OR of
+ * the depth bits is reported in status[2] and a non-zero value means the caller must use the
+ * step-by-step path (64-bit keys).  cap = capacity in intersections of the state buffer; when
+ * num_intersects > cap nothing past cap is written, status[1] is set and the caller retries with
+ * a larger buffer.  status_host (pinned, int32[4], may be NULL) receives status[0..3] as soon as
+ * the scan stage is done; scan_done (may be NULL) is recorded right after that stage so the host
+ * can wait for exactly that and no more.  out_img [H,W,3] fp32; final_idx [H,W] int32 or NULL
+ * (render-only).  final_Ts is the constant 1 in the sum variant and is not
+ * materialised. */
+int gs2d_rasterize_sum_fwd(int n, const float* xys, const float* depths, const int32_t* radii, const float* conics,
+                           const int32_t* num_tiles_hit, const float* colors, const float* opacities, int img_h,
+                           int img_w, int cap, void* state, size_t state_bytes, float* out_img, int32_t* final_idx,
+                           int32_t* status_host, gs2d_event_t scan_done, gs2d_stream_t stream);
+
+/* The rasteriser kernel alone on caller-provided binning (replaces rasterize_forward_sum_tensor,
+ * bindings.cu:400-469).  tile_bins must have a row for every tile.  final_Ts [H,W] may be NULL. */
+int gs2d_rasterize_sum_fwd_binned(int n, int num_intersects, const int32_t* gaussian_ids_sorted,
+                                  const int32_t* tile_bins, const float* xys, const float* conics,
+                                  const float* colors, const float* opacities, int img_h, int img_w, float* out_img,
+                                  float* final_Ts, int32_t* final_idx, void* scratch, size_t scratch_bytes,
+                                  gs2d_stream_t stream);
+size_t gs2d_raster_binned_scratch_bytes(int num_intersects);
+
+/* Replaces rasterize_backward_sum_tensor, bindings.cu:706-779 (kernel backward.cu:696-862), on
+ * the state of the matching forward.  v_out [H,W,3] fp32 (contiguous).  grads: fp32 [n][12] rows
+ * = v_xy(2) v_conic(3) v_colors(3) v_opacity(1) pad(3); zero-filled here, then one 3 x 16-byte
+ * reduction per (Gaussian, tile) pair. */
+int gs2d_rasterize_sum_bwd(int n, int img_h, int img_w, int cap, const void* state, size_t state_bytes,
+                           const int32_t* final_idx, const float* v_out, float* grads, gs2d_stream_t stream);
+/* Same on caller-provided binning (ids sorted + tile_bins), for parity tests of the kernel alone. */
+int gs2d_rasterize_sum_bwd_binned(int n, int num_intersects, const int32_t* gaussian_ids_sorted,
+                                  const int32_t* tile_bins, const float* xys, const float* conics,
+                                  const float* colors, const float* opacities, int img_h, int img_w,
+                                  const int32_t* final_idx, const float* v_out, float* grads, void* scratch,
+                                  size_t scratch_bytes, gs2d_stream_t stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GS2D_H */
