@@ -91,7 +91,10 @@ def test_cov2d_bounds(C, golden_dir):
     from gsvc_b200 import compute_cov2d_bounds
     conic, radii = compute_cov2d_bounds(cov)
     m = torch.from_numpy(g["mask"]).to(cuda)
-    torch.testing.assert_close(conic[m], torch.from_numpy(g["conic"]).to(cuda)[m])
+    # the golden is torch's exact-division restatement; the reference's shipped build
+    # (--use_fast_math: MUFU.RCP, FFMA-contracted det) differs from it by a few 1e-6 relative
+    # where a*c - b*b cancels, and so do we -- bit-equality with that build is asserted below
+    torch.testing.assert_close(conic[m], torch.from_numpy(g["conic"]).to(cuda)[m], rtol=2e-5, atol=1e-5)
     torch.testing.assert_close(radii.squeeze(-1)[m], torch.from_numpy(g["radii"]).to(cuda)[m])
     rc, rr = ref_gpu.compute_cov2d_bounds(cov)
     assert torch.equal(conic[m], rc[m]) and torch.equal(radii[m], rr[m])
