@@ -1,0 +1,374 @@
+#!/usr/bin/env python
+"""bench.py -- BASELINE.json's headline metric on synthetic data.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference|reference-gpu]
+
+A step is one fit iteration of BASELINE.json configs[1]: 1920x1080 frame, 50 000 Cholesky
+Gaussians, project -> bin/sort -> sum-rasterise -> L2 loss -> backward -> Adan.  One JSON line
+on stdout (rank 0).  `value` = iterations/s with everything resident in HBM (L2 flushed between
+timed steps, each step timed with CUDA events on the launching stream); `e2e` = the same through
+the public API with the target frame in pinned HOST memory, copied every step, and the loss read
+back every step.  N > 1 (torchrun): every rank fits its own GOP's frame, no data-path collective,
+weak scaling, value = all ranks' iterations / max-over-ranks time.
+
+--impl reference: the CPU restatement of the reference's kernels (oracle/, C + OpenMP, all host
+threads) + numpy Adan on the same workload; rank 0 only.
+--impl reference-gpu (not used by the driver): the reference's own CUDA kernels (oracle/_ref,
+compiled from /root/reference for sm_100a) strung together with torch.cumsum/.item()/torch.sort/
+gather exactly as the reference's Python does, same loop, same GPU.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import math
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+METRIC = "fit_iters_per_s_1080p_50k"
+UNIT = "iters/s"
+H, W, NPTS = 1080, 1920, 50_000
+WORKLOAD = "C2: 1920x1080 synthetic frame, 50k Cholesky Gaussians, rasterize_gaussians_sum fwd+bwd fit loop (L2, Adan)"
+L2_FLUSH_BYTES = 256 << 20
+
+
+def _env_int(name, default):
+    try:
+        return int(os.environ.get(name, default))
+    except ValueError:
+        return default
+
+
+# ------------------------------------------------------------------------------------------
+# clocks during the timed region (B200_PROFILING.md recipe)
+# ------------------------------------------------------------------------------------------
+class ClockSampler:
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
+         "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        self.index = index
+        self.proc = None
+        self.lines = []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100", "-i",
+                 str(self.index)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self) -> dict:
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except subprocess.TimeoutExpired:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 9:
+                continue
+            try:
+                sm.append(float(f[1])); mx.append(float(f[2]))
+            except ValueError:
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), f[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+# ------------------------------------------------------------------------------------------
+# algorithmic bytes per launch of each stage (DESIGN.md "Kernels and rooflines")
+# ------------------------------------------------------------------------------------------
+def algorithmic_bytes(stage: str, n: int, I: int, hw: int, tiles: int) -> float:
+    return {
+        "project_fwd": 20 * n + 32 * n,
+        "scan_map": 4 * n + 12 * n + 8 * I,
+        "sort": 2 * 8 * I,                                   # one digit pass: read + write (key, id)
+        "edges_pack": 8 * I + 36 * I + 48 * I + 8 * tiles,   # sorted pairs + gathered params -> packed + bins
+        "raster_fwd": 48 * I + 8 * tiles + 12 * hw + 4 * hw,
+        "raster_bwd": 48 * I + 16 * hw + 36 * I,
+        "project_bwd": 12 * n + 4 * n + 12 * n + 20 * n + 32 * n,
+        "fit_tiles": 48 * I + 8 * tiles + 3 * hw + 36 * I,
+        "adan": 9 * n * 4 * 9,
+        "memset": 0, "other": 0,
+    }[stage]
+
+
+# ------------------------------------------------------------------------------------------
+# CPU arm: the oracle port on the host cores
+# ------------------------------------------------------------------------------------------
+class CpuFit:
+    """the same fit iteration on the CPU: oracle C kernels (OpenMP) + numpy glue + numpy Adan"""
+
+    def __init__(self, seed=1):
+        import numpy as np
+        from gsvc_b200 import synth
+        from oracle import oracle as O
+        self.np, self.O = np, O
+        g = synth.gaussians(NPTS, seed=seed)
+        self.p = [g["_xyz"].numpy().copy(), g["_cholesky"].numpy().copy(), g["_features_dc"].numpy().copy()]
+        self.m = [np.zeros_like(a) for a in self.p]
+        self.n = [np.zeros_like(a) for a in self.p]
+        self.d = [np.zeros_like(a) for a in self.p]
+        self.prev = None
+        self.t = 0
+        self.opacity = np.ones((NPTS, 1), np.float32)
+        self.gt = synth.target_frame(H, W)[0].permute(1, 2, 0).contiguous().numpy()
+        self.bound = np.array([[0.5, 0.0, 0.5]], np.float32)
+        self.cores = O.num_threads()
+
+    def step(self):
+        np, O = self.np, self.O
+        xyz, chol, feat = self.p
+        means = np.tanh(xyz)
+        gt = self.gt
+        scale = np.float32(2.0 / gt.size)
+        r = O.fit_grads(means, chol + self.bound, feat, self.opacity, H, W,
+                        lambda img: scale * (np.clip(img, 0, 1) - gt) * ((img > 0) & (img < 1)))
+        loss = float(np.mean((np.clip(r["out_img"], 0, 1) - gt) ** 2))
+        grads = [r["v_mean2d"] * (1 - means * means), r["v_L"], r["v_colors"]]
+        self.t += 1
+        t, (b1, b2, b3), lr, eps = self.t, (0.98, 0.92, 0.99), 1e-3, 1e-8
+        if self.prev is None:
+            self.prev = [g.copy() for g in grads]
+        bc1, bc2, bc3s = 1 - b1 ** t, 1 - b2 ** t, math.sqrt(1 - b3 ** t)
+        for i, g in enumerate(grads):
+            diff = g - self.prev[i]
+            self.m[i] = b1 * self.m[i] + (1 - b1) * g
+            self.d[i] = b2 * self.d[i] + (1 - b2) * diff
+            u = g + b2 * diff
+            self.n[i] = b3 * self.n[i] + (1 - b3) * u * u
+            denom = np.sqrt(self.n[i]) / bc3s + eps
+            self.p[i] = (self.p[i] - (lr / bc1) * self.m[i] / denom - (lr * b2 / bc2) * self.d[i] / denom).astype(np.float32)
+            self.prev[i] = g
+        return loss
+
+
+def run_cpu(steps: int, warmup: int) -> dict:
+    fit = CpuFit()
+    for _ in range(warmup):
+        fit.step()
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        fit.step()
+    dt = time.perf_counter() - t0
+    return {"value": steps / dt, "unit": UNIT, "cores": fit.cores, "kind": "port",
+            "sample": f"{steps} full-size fit iterations ({WORKLOAD.split(':')[0]}) after {warmup} warm-up, "
+                      f"oracle C kernels with OpenMP on {fit.cores} threads + numpy Adan",
+            "seconds": dt}
+
+
+def main_reference(args, rank: int):
+    if rank != 0:
+        return
+    steps, warmup = min(args.steps, 40), min(args.warmup, 3)
+    r = run_cpu(steps, warmup)
+    line = {
+        "impl": "reference", "metric": METRIC, "value": r["value"], "unit": UNIT, "n_gpus": args.gpus,
+        "steps": steps, "warmup": warmup, "ms_per_step": 1e3 / r["value"], "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": WORKLOAD, "H": H, "W": W, "gaussians": NPTS, "device": "host cpu"},
+        "cpu_baseline": {k: r[k] for k in ("value", "unit", "cores", "kind", "sample")},
+        "e2e": {"value": r["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+# ------------------------------------------------------------------------------------------
+# GPU arms
+# ------------------------------------------------------------------------------------------
+def make_fitter(impl: str, dev, seed: int):
+    import torch
+    if impl == "reference-gpu":
+        sys.path.insert(0, os.path.join(ROOT, "tests"))
+        import ref_fit
+        return ref_fit.RefFrameFit(H, W, NPTS, dev, seed=seed)
+    from gsvc_b200.fit import FrameFit
+    return FrameFit(H, W, NPTS, dev, seed=seed)
+
+
+def main_gpu(args, rank: int, world: int, local_rank: int):
+    import torch
+    import torch.distributed as dist
+    from gsvc_b200 import _lib, synth
+
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+
+    mine = args.impl == "b200"
+    fit = make_fitter(args.impl, dev, seed=1 + rank)
+    gt_host = synth.target_frame(H, W, seed=1 + rank).pin_memory()       # [1,3,H,W] fp32, what the loader yields
+    gt = gt_host.to(dev)
+    flush = torch.empty(L2_FLUSH_BYTES, dtype=torch.uint8, device=dev)
+    K, Wm = args.steps, max(args.warmup, 3)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize(dev)
+
+    # ---- warm-up ---------------------------------------------------------------------------
+    for _ in range(Wm):
+        fit.train_iter(gt)
+    barrier()
+
+    # ---- value: HBM-resident inputs, L2 flushed between steps, per-step CUDA events ------------
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(K)]
+    launches0 = _lib.launch_count() if mine else 0
+    barrier()
+    wall0 = time.perf_counter()
+    for a, b in ev:
+        flush.zero_()
+        a.record()
+        fit.train_iter(gt)
+        b.record()
+    barrier()
+    wall = time.perf_counter() - wall0
+    launches = (_lib.launch_count() - launches0) if mine else 0
+    step_ms = sum(a.elapsed_time(b) for a, b in ev) / K
+
+    # ---- same loop back to back (L2 warm: what a real fit loop sees), one event pair -----------
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    a.record()
+    for _ in range(K):
+        fit.train_iter(gt)
+    b.record()
+    barrier()
+    warm_ms = a.elapsed_time(b) / K
+
+    # ---- e2e: target frame in pinned host memory every step, loss read back every step -------
+    barrier()
+    a.record()
+    psnr = 0.0
+    for _ in range(K):
+        g = gt_host.to(dev, non_blocking=True)
+        _loss, psnr = fit.train_iter(g)        # reads the loss back (psnr), like the reference loop
+    b.record()
+    barrier()
+    e2e_ms = a.elapsed_time(b) / K
+    clocks = sampler.stop() if rank == 0 else None
+
+    # ---- render-only fps (config 3), device-resident -----------------------------------------
+    with torch.no_grad():
+        for _ in range(3):
+            fit.forward()
+        barrier()
+        a.record()
+        for _ in range(K):
+            fit.forward()
+        b.record()
+        barrier()
+    render_ms = a.elapsed_time(b) / K
+
+    # ---- per-stage timing pass (CUDA events inside the library, on the launching stream) ------
+    stages = {}
+    if mine:
+        _lib.prof_enable(True)
+        for _ in range(K):
+            flush.zero_()
+            fit.train_iter(gt)
+        torch.cuda.synchronize(dev)
+        _lib.prof_enable(False)
+        prof = _lib.prof_read()
+        stages = {k: {"ms_per_step": v[0] / K, "launches_per_step": v[1] / K} for k, v in prof.items() if v[1]}
+
+    # ---- max over ranks ----------------------------------------------------------------------
+    t = torch.tensor([step_ms, warm_ms, e2e_ms, render_ms], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    step_ms, warm_ms, e2e_ms, render_ms = (float(x) for x in t.tolist())
+
+    if rank == 0:
+        I = int(getattr(fit, "last_num_intersects", 0)) or None
+        line = {
+            "metric": METRIC, "value": world * 1e3 / step_ms, "unit": UNIT, "n_gpus": world, "steps": K,
+            "warmup": Wm, "ms_per_step": step_ms, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": WORKLOAD, "H": H, "W": W, "gaussians": NPTS, "intersections": I,
+                       "l2": f"flushed between timed steps ({L2_FLUSH_BYTES >> 20} MiB memset outside the event pair)",
+                       "path": getattr(fit, "path_name", "autograd drop-in ops + torch glue"),
+                       "parallelism": f"{world} independent GOP chains, one per GPU, no collective"},
+            "clocks": clocks,
+            "e2e": {"value": world * 1e3 / e2e_ms, "unit": UNIT, "h2d_bytes_per_step": gt_host.numel() * 4,
+                    "d2h_bytes_per_step": 4, "ms_per_step": e2e_ms},
+            "gpu_launches": launches,
+            "l2_warm": {"value": world * 1e3 / warm_ms, "unit": UNIT, "ms_per_step": warm_ms},
+            "render": {"value": world * 1e3 / render_ms, "unit": "frames/s", "ms_per_frame": render_ms},
+            "wall_s_timed_region": wall, "final_psnr": psnr,
+        }
+        if args.impl != "b200":
+            line["impl"] = args.impl
+        if stages:
+            line["stages"] = stages
+            kern = {k: v for k, v in stages.items() if k != "memset"}
+            top = max(kern, key=lambda k: kern[k]["ms_per_step"])
+            peaks = {}
+            try:
+                peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+            except (OSError, ValueError):
+                pass
+            peak = float(peaks.get("hbm_gbs", 6650.0))
+            n_l = max(kern[top]["launches_per_step"], 1e-9)
+            tiles = ((W + 15) // 16) * ((H + 15) // 16)
+            alg = algorithmic_bytes(top, NPTS, I or 124_000, H * W, tiles)
+            dur_s = kern[top]["ms_per_step"] / n_l * 1e-3
+            line["roofline"] = {"kernel": top, "bound": "hbm", "achieved": alg / dur_s / 1e9, "peak": peak,
+                                "unit": "GB/s", "frac": alg / dur_s / 1e9 / peak, "traffic": None,
+                                "algorithmic_bytes": alg, "avg_launch_us": dur_s * 1e6,
+                                "peak_source": "MEASURED_PEAKS.json hbm_gbs (measured)" if peaks else "fallback 6650"}
+        if world == 1 and mine and not args.no_cpu:
+            r = run_cpu(args.cpu_steps, 1)
+            line["cpu_baseline"] = {k: r[k] for k in ("value", "unit", "cores", "kind", "sample")}
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=200)
+    ap.add_argument("--warmup", type=int, default=20)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference", "reference-gpu"])
+    ap.add_argument("--cpu-steps", type=int, default=20, help="fit iterations of the cpu_baseline leg")
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    args = ap.parse_args()
+    rank, world, local_rank = _env_int("RANK", 0), _env_int("WORLD_SIZE", 1), _env_int("LOCAL_RANK", 0)
+    if args.impl == "reference":
+        main_reference(args, rank)
+    else:
+        main_gpu(args, rank, world, local_rank)
+
+
+if __name__ == "__main__":
+    main()

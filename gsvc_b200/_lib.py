@@ -35,6 +35,9 @@ _SIGNATURES = {
     "gs2d_version": (c_int, []),
     "gs2d_last_error": (c_char_p, []),
     "gs2d_device_arch": (c_int, [c_int]),
+    "gs2d_launch_count": (ctypes.c_longlong, []),
+    "gs2d_prof_enable": (c_int, [c_int]),
+    "gs2d_prof_read": (c_int, [POINTER(ctypes.c_double), POINTER(c_int), c_int]),
     "gs2d_project_chol_fwd": (c_int, [c_int, _P, _P, c_int, c_int, c_int, c_int, c_float, _P, _P, _P, _P, _P, _P]),
     "gs2d_project_scalerot_fwd": (c_int, [c_int, _P, _P, _P, c_int, c_int, c_int, c_int, c_float, _P, _P, _P, _P, _P, _P]),
     "gs2d_project_chol_bwd": (c_int, [c_int, _P, c_int, c_int, _P, _P, _P, c_int, _P, c_int, _P, _P, _P, _P]),
@@ -97,3 +100,24 @@ def require_device(index: int) -> None:
             raise RuntimeError(f"gsvc_b200 needs an sm_100 (B200) device, cuda:{index} reports sm_{arch}")
     elif not ok:
         raise RuntimeError(f"gsvc_b200 needs an sm_100 (B200) device, cuda:{index} is not")
+
+
+STAGES = ("project_fwd", "memset", "scan_map", "sort", "edges_pack", "raster_fwd", "raster_bwd", "project_bwd",
+          "fit_tiles", "adan", "other")   # GS2D_STAGE_* of include/gs2d.h
+
+
+def prof_enable(on: bool) -> None:
+    check(load().gs2d_prof_enable(1 if on else 0), "prof_enable")
+
+
+def prof_read() -> dict:
+    """{stage: (total_ms, spans)} of everything recorded since the last read (synchronises)"""
+    n = len(STAGES)
+    ms = (ctypes.c_double * n)()
+    cnt = (c_int * n)()
+    check(load().gs2d_prof_read(ms, cnt, n), "prof_read")
+    return {STAGES[i]: (float(ms[i]), int(cnt[i])) for i in range(n)}
+
+
+def launch_count() -> int:
+    return int(load().gs2d_launch_count())

@@ -499,15 +499,21 @@ int launch_bin_and_pack(int n, const float* xys, const float* depths, const int3
     float4* packed = (float4*)(state + L.off_packed);
     const int passes = L.sort_passes;
 
-    GS2D_CHECK_CUDA(cudaMemsetAsync(state + L.zero_begin, 0, L.zero_bytes, s));
+    {
+        ProfScope ps_(GS2D_STAGE_MEMSET, s);
+        GS2D_CHECK_CUDA(cudaMemsetAsync(state + L.zero_begin, 0, L.zero_bytes, s));
+    }
     // the map writes into the buffer from which `passes` ping-pong steps end in the final one
     uint32_t* kin = (passes % 2 == 0) ? keys_fin : keys_tmp;
     int32_t* vin = (passes % 2 == 0) ? ids_fin : ids_tmp;
     uint32_t* kout = (passes % 2 == 0) ? keys_tmp : keys_fin;
     int32_t* vout = (passes % 2 == 0) ? ids_tmp : ids_fin;
     if (n > 0) {
-        k_scan_map<<<so.scan_blocks, kScanThreads, 0, s>>>(n, nth, xys, radii, depths, tx, ty, cap, passes,
+        {
+            ProfScope ps_(GS2D_STAGE_SCAN_MAP, s);
+            k_scan_map<<<so.scan_blocks, kScanThreads, 0, s>>>(n, nth, xys, radii, depths, tx, ty, cap, passes,
                                                              scan_state, status, status_host, kin, vin, ghist);
+        }
         GS2D_CHECK_LAUNCH("scan_map");
     } else if (status_host) {
         GS2D_CHECK_CUDA(cudaMemcpyAsync(status_host, status, 4 * sizeof(int32_t), cudaMemcpyDeviceToHost, s));
@@ -516,16 +522,22 @@ int launch_bin_and_pack(int n, const float* xys, const float* depths, const int3
     if (n == 0) return GS2D_OK;
     for (int p = 0; p < passes; ++p) {
         const int shift = 8 * p, bits = min(8, L.key_bits - shift);
-        k_sort_pass<uint32_t><<<so.sort_blocks, kSortThreads, 0, s>>>(
+        {
+            ProfScope ps_(GS2D_STAGE_SORT, s);
+            k_sort_pass<uint32_t><<<so.sort_blocks, kSortThreads, 0, s>>>(
             kin, vin, kout, vout, status + 3, 0, shift, bits, 0u, ghist + p * 256,
             lookback + (size_t)p * so.sort_blocks * 256);
+        }
         GS2D_CHECK_LAUNCH("sort_pass");
         uint32_t* tk = kin; kin = kout; kout = tk;
         int32_t* tv = vin; vin = vout; vout = tv;
     }
     // kin/vin now alias keys_fin/ids_fin
-    k_edges_pack<<<div_up(cap, 256), 256, 0, s>>>(status + 3, 0, keys_fin, ids_fin, xys, conics, colors, opac, tx,
+    {
+        ProfScope ps_(GS2D_STAGE_EDGES_PACK, s);
+        k_edges_pack<<<div_up(cap, 256), 256, 0, s>>>(status + 3, 0, keys_fin, ids_fin, xys, conics, colors, opac, tx,
                                                   img_w, img_h, tile_bins, packed);
+    }
     GS2D_CHECK_LAUNCH("edges_pack");
     return GS2D_OK;
 }
@@ -535,8 +547,11 @@ int launch_pack_binned(int num_intersects, const int32_t* ids_sorted, const int3
                        int img_w, float4* packed, cudaStream_t s) {
     const int tx = div_up(img_w, GS2D_TILE);
     (void)img_h;
-    k_pack_binned<<<div_up(tiles, 8), 256, 0, s>>>(num_intersects, ids_sorted, tile_bins, tiles, xys, conics, colors,
+    {
+        ProfScope ps_(GS2D_STAGE_EDGES_PACK, s);
+        k_pack_binned<<<div_up(tiles, 8), 256, 0, s>>>(num_intersects, ids_sorted, tile_bins, tiles, xys, conics, colors,
                                                    opac, tx, img_w, img_h, packed);
+    }
     GS2D_CHECK_LAUNCH("pack_binned");
     return GS2D_OK;
 }
@@ -570,8 +585,11 @@ int gs2d_cumsum_tiles_hit(int n, const int32_t* nth, int32_t* cum, int32_t* tota
         return GS2D_OK;
     }
     GS2D_CHECK_CUDA(cudaMemsetAsync(scratch, 0, gs2d_scan_scratch_bytes(n), s));
-    k_cumsum<<<div_up(n, kScanThreads), kScanThreads, 0, s>>>(n, nth, cum, (unsigned long long*)scratch, total_out,
+    {
+        ProfScope ps_(GS2D_STAGE_SCAN_MAP, s);
+        k_cumsum<<<div_up(n, kScanThreads), kScanThreads, 0, s>>>(n, nth, cum, (unsigned long long*)scratch, total_out,
                                                                total_host);
+    }
     GS2D_CHECK_LAUNCH("cumsum");
     return GS2D_OK;
 }
@@ -581,8 +599,11 @@ int gs2d_map_intersects(int n, int num_intersects, const float* xys, const float
                         gs2d_stream_t stream) {
     GS2D_REQUIRE(n >= 0 && num_intersects >= 0 && tx > 0 && ty > 0, "map_intersects: bad sizes");
     if (n == 0 || num_intersects == 0) return GS2D_OK;
-    k_map_intersects64<<<div_up(n, kScanThreads), kScanThreads, 0, (cudaStream_t)stream>>>(
+    {
+        ProfScope ps_(GS2D_STAGE_SCAN_MAP, (cudaStream_t)stream);
+        k_map_intersects64<<<div_up(n, kScanThreads), kScanThreads, 0, (cudaStream_t)stream>>>(
         n, num_intersects, xys, depths, radii, cum, tx, ty, isect_ids, gaussian_ids);
+    }
     GS2D_CHECK_LAUNCH("map_intersects");
     return GS2D_OK;
 }
@@ -615,8 +636,11 @@ int gs2d_sort_pairs(int n, const int64_t* keys_in, const int32_t* vals_in, int64
     GS2D_CHECK_CUDA(cudaMemsetAsync(base, 0, zero_bytes, s));
     const int top_bits = (end_bit - begin_bit) - 8 * (passes - 1);
     const uint32_t top_flip = end_bit == 64 ? (1u << (top_bits - 1)) : 0u;   // signed int64 order
-    k_sort_hist<uint64_t><<<blocks, kSortThreads, 0, s>>>((const uint64_t*)keys_in, n, begin_bit, end_bit, passes,
+    {
+        ProfScope ps_(GS2D_STAGE_SORT, s);
+        k_sort_hist<uint64_t><<<blocks, kSortThreads, 0, s>>>((const uint64_t*)keys_in, n, begin_bit, end_bit, passes,
                                                           top_flip, ghist);
+    }
     GS2D_CHECK_LAUNCH("sort_hist");
     // ping-pong so that the last pass lands in keys_out / vals_out
     const uint64_t* kin = (const uint64_t*)keys_in;
@@ -626,9 +650,12 @@ int gs2d_sort_pairs(int n, const int64_t* keys_in, const int32_t* vals_in, int64
         uint64_t* kout = to_out ? (uint64_t*)keys_out : keys_tmp;
         int32_t* vout = to_out ? vals_out : vals_tmp;
         const int shift = begin_bit + 8 * p, bits = min(8, end_bit - shift);
-        k_sort_pass<uint64_t><<<blocks, kSortThreads, 0, s>>>(kin, vin, kout, vout, nullptr, n, shift, bits,
+        {
+            ProfScope ps_(GS2D_STAGE_SORT, s);
+            k_sort_pass<uint64_t><<<blocks, kSortThreads, 0, s>>>(kin, vin, kout, vout, nullptr, n, shift, bits,
                                                               p == passes - 1 ? top_flip : 0u, ghist + p * 256,
                                                               lookback + (size_t)p * blocks * 256);
+        }
         GS2D_CHECK_LAUNCH("sort_pass64");
         kin = kout;
         vin = vout;
@@ -642,7 +669,10 @@ int gs2d_tile_bin_edges(int num_intersects, const int64_t* keys_sorted, int32_t*
     cudaStream_t s = (cudaStream_t)stream;
     if (rows > 0) GS2D_CHECK_CUDA(cudaMemsetAsync(tile_bins, 0, (size_t)rows * 2 * sizeof(int32_t), s));
     if (num_intersects == 0) return GS2D_OK;
-    k_tile_bin_edges64<<<div_up(num_intersects, 256), 256, 0, s>>>(num_intersects, keys_sorted, tile_bins);
+    {
+        ProfScope ps_(GS2D_STAGE_EDGES_PACK, s);
+        k_tile_bin_edges64<<<div_up(num_intersects, 256), 256, 0, s>>>(num_intersects, keys_sorted, tile_bins);
+    }
     GS2D_CHECK_LAUNCH("tile_bin_edges");
     return GS2D_OK;
 }

@@ -13,6 +13,27 @@ void set_error(const char* fmt, ...);
 
 inline int div_up(long long a, long long b) { return (int)((a + b - 1) / b); }
 
+// kernel-launch counter and optional per-stage CUDA-event timing (capi.cu); stage ids are
+// the GS2D_STAGE_* constants of gs2d.h
+void count_launch();
+bool prof_enabled();
+void prof_begin(int stage, cudaStream_t s);
+void prof_end(int stage, cudaStream_t s);
+
+// Brackets the launches of one stage with an event pair on the launching stream when
+// profiling is on (gs2d_prof_enable); a single predictable branch when it is off.
+struct ProfScope {
+    int stage;
+    cudaStream_t s;
+    bool on;
+    ProfScope(int stage_, cudaStream_t s_) : stage(stage_), s(s_), on(prof_enabled()) {
+        if (on) prof_begin(stage, s);
+    }
+    ~ProfScope() {
+        if (on) prof_end(stage, s);
+    }
+};
+
 }  // namespace gs2d
 
 // Every kernel launch is followed by this (the reference checks nothing).
@@ -23,6 +44,7 @@ inline int div_up(long long a, long long b) { return (int)((a + b - 1) / b); }
             gs2d::set_error("%s: %s", what, cudaGetErrorString(e_));                   \
             return GS2D_ERR_CUDA;                                                      \
         }                                                                              \
+        gs2d::count_launch();                                                          \
     } while (0)
 
 #define GS2D_CHECK_CUDA(expr)                                                          \

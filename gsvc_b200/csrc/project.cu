@@ -181,9 +181,12 @@ int gs2d_project_chol_fwd(int n, const float* means2d, const float* L, int img_h
                           int32_t* num_tiles_hit, gs2d_stream_t stream) {
     GS2D_REQUIRE(n >= 0 && img_h > 0 && img_w > 0 && tx > 0 && ty > 0, "project_chol_fwd: bad sizes");
     if (n == 0) return GS2D_OK;
-    k_project_chol_fwd<<<div_up(n, kProjThreads), kProjThreads, 0, (cudaStream_t)stream>>>(
+    {
+        ProfScope ps_(GS2D_STAGE_PROJECT_FWD, (cudaStream_t)stream);
+        k_project_chol_fwd<<<div_up(n, kProjThreads), kProjThreads, 0, (cudaStream_t)stream>>>(
         n, means2d, L, 0.5f * (float)(unsigned)img_w, 0.5f * (float)(unsigned)img_h, tx, ty, xys, depths, radii,
         conics, num_tiles_hit);
+    }
     GS2D_CHECK_LAUNCH("project_chol_fwd");
     return GS2D_OK;
 }
@@ -193,9 +196,12 @@ int gs2d_project_scalerot_fwd(int n, const float* means2d, const float* scales, 
                               int32_t* radii, float* conics, int32_t* num_tiles_hit, gs2d_stream_t stream) {
     GS2D_REQUIRE(n >= 0 && img_h > 0 && img_w > 0 && tx > 0 && ty > 0, "project_scalerot_fwd: bad sizes");
     if (n == 0) return GS2D_OK;
-    k_project_scalerot_fwd<<<div_up(n, kProjThreads), kProjThreads, 0, (cudaStream_t)stream>>>(
+    {
+        ProfScope ps_(GS2D_STAGE_PROJECT_FWD, (cudaStream_t)stream);
+        k_project_scalerot_fwd<<<div_up(n, kProjThreads), kProjThreads, 0, (cudaStream_t)stream>>>(
         n, means2d, scales, rot, 0.5f * (float)(unsigned)img_w, 0.5f * (float)(unsigned)img_h, tx, ty, xys, depths,
         radii, conics, num_tiles_hit);
+    }
     GS2D_CHECK_LAUNCH("project_scalerot_fwd");
     return GS2D_OK;
 }
@@ -205,9 +211,12 @@ int gs2d_project_chol_bwd(int n, const float* L, int img_h, int img_w, const int
                           float* v_mean2d, float* v_L, gs2d_stream_t stream) {
     GS2D_REQUIRE(n >= 0 && ld_v_xy >= 2 && ld_v_conic >= 3, "project_chol_bwd: bad sizes");
     if (n == 0) return GS2D_OK;
-    k_project_chol_bwd<<<div_up(n, kProjThreads), kProjThreads, 0, (cudaStream_t)stream>>>(
+    {
+        ProfScope ps_(GS2D_STAGE_PROJECT_BWD, (cudaStream_t)stream);
+        k_project_chol_bwd<<<div_up(n, kProjThreads), kProjThreads, 0, (cudaStream_t)stream>>>(
         n, L, 0.5f * (float)(unsigned)img_w, 0.5f * (float)(unsigned)img_h, radii, conics, v_xy, ld_v_xy, v_conic,
         ld_v_conic, v_cov2d, v_mean2d, v_L);
+    }
     GS2D_CHECK_LAUNCH("project_chol_bwd");
     return GS2D_OK;
 }
@@ -218,9 +227,12 @@ int gs2d_project_scalerot_bwd(int n, const float* scales, const float* rot, int 
                               float* v_rot, gs2d_stream_t stream) {
     GS2D_REQUIRE(n >= 0 && ld_v_xy >= 2 && ld_v_conic >= 3, "project_scalerot_bwd: bad sizes");
     if (n == 0) return GS2D_OK;
-    k_project_scalerot_bwd<<<div_up(n, kProjThreads), kProjThreads, 0, (cudaStream_t)stream>>>(
+    {
+        ProfScope ps_(GS2D_STAGE_PROJECT_BWD, (cudaStream_t)stream);
+        k_project_scalerot_bwd<<<div_up(n, kProjThreads), kProjThreads, 0, (cudaStream_t)stream>>>(
         n, scales, rot, 0.5f * (float)(unsigned)img_w, 0.5f * (float)(unsigned)img_h, radii, conics, v_xy, ld_v_xy,
         v_conic, ld_v_conic, v_cov2d, v_mean2d, v_scale, v_rot);
+    }
     GS2D_CHECK_LAUNCH("project_scalerot_bwd");
     return GS2D_OK;
 }
@@ -228,7 +240,10 @@ int gs2d_project_scalerot_bwd(int n, const float* scales, const float* rot, int 
 int gs2d_cov2d_bounds(int n, const float* cov2d, float* conics, float* radii, gs2d_stream_t stream) {
     GS2D_REQUIRE(n >= 0, "cov2d_bounds: bad size");
     if (n == 0) return GS2D_OK;
-    k_cov2d_bounds<<<div_up(n, kProjThreads), kProjThreads, 0, (cudaStream_t)stream>>>(n, cov2d, conics, radii);
+    {
+        ProfScope ps_(GS2D_STAGE_OTHER, (cudaStream_t)stream);
+        k_cov2d_bounds<<<div_up(n, kProjThreads), kProjThreads, 0, (cudaStream_t)stream>>>(n, cov2d, conics, radii);
+    }
     GS2D_CHECK_LAUNCH("cov2d_bounds");
     return GS2D_OK;
 }

@@ -202,9 +202,12 @@ int gs2d_rasterize_sum_fwd(int n, const float* xys, const float* depths, const i
     rc = launch_bin_and_pack(n, xys, depths, radii, num_tiles_hit, conics, colors, opacities, img_h, img_w, cap, so,
                              st, status_host, (cudaEvent_t)scan_done, s);
     if (rc != GS2D_OK) return rc;
-    k_raster_fwd<<<dim3(tx, ty), GS2D_TILE_PIX, 0, s>>>(img_w, img_h, tx, (const int32_t*)(st + so.pub.off_tile_bins),
+    {
+        ProfScope ps_(GS2D_STAGE_RASTER_FWD, s);
+        k_raster_fwd<<<dim3(tx, ty), GS2D_TILE_PIX, 0, s>>>(img_w, img_h, tx, (const int32_t*)(st + so.pub.off_tile_bins),
                                                         (const float4*)(st + so.pub.off_packed), out_img, nullptr,
                                                         final_idx);
+    }
     GS2D_CHECK_LAUNCH("raster_fwd");
     return GS2D_OK;
 }
@@ -225,8 +228,11 @@ int gs2d_rasterize_sum_fwd_binned(int n, int num_intersects, const int32_t* ids_
     int rc = launch_pack_binned(num_intersects, ids_sorted, tile_bins, tx * ty, xys, conics, colors, opacities, img_h,
                                 img_w, (float4*)scratch, s);
     if (rc != GS2D_OK) return rc;
-    k_raster_fwd<<<dim3(tx, ty), GS2D_TILE_PIX, 0, s>>>(img_w, img_h, tx, tile_bins, (const float4*)scratch, out_img,
+    {
+        ProfScope ps_(GS2D_STAGE_RASTER_FWD, s);
+        k_raster_fwd<<<dim3(tx, ty), GS2D_TILE_PIX, 0, s>>>(img_w, img_h, tx, tile_bins, (const float4*)scratch, out_img,
                                                         final_Ts, final_idx);
+    }
     GS2D_CHECK_LAUNCH("raster_fwd_binned");
     return GS2D_OK;
 }
@@ -242,10 +248,16 @@ int gs2d_rasterize_sum_bwd(int n, int img_h, int img_w, int cap, const void* sta
     cudaStream_t s = (cudaStream_t)stream;
     const char* st = (const char*)state;
     if (n == 0) return GS2D_OK;
-    GS2D_CHECK_CUDA(cudaMemsetAsync(grads, 0, (size_t)n * 12 * sizeof(float), s));
-    k_raster_bwd<<<div_up(cap, kBwdThreads / 32), kBwdThreads, 0, s>>>(
+    {
+        ProfScope ps_(GS2D_STAGE_MEMSET, s);
+        GS2D_CHECK_CUDA(cudaMemsetAsync(grads, 0, (size_t)n * 12 * sizeof(float), s));
+    }
+    {
+        ProfScope ps_(GS2D_STAGE_RASTER_BWD, s);
+        k_raster_bwd<<<div_up(cap, kBwdThreads / 32), kBwdThreads, 0, s>>>(
         (const int32_t*)(st + so.pub.off_status) + 3, 0, img_w, tx, (const int32_t*)(st + so.pub.off_tile_bins),
         (const float4*)(st + so.pub.off_packed), final_idx, v_out, grads);
+    }
     GS2D_CHECK_LAUNCH("raster_bwd");
     return GS2D_OK;
 }
@@ -267,8 +279,11 @@ int gs2d_rasterize_sum_bwd_binned(int n, int num_intersects, const int32_t* ids_
     int rc = launch_pack_binned(num_intersects, ids_sorted, tile_bins, tx * ty, xys, conics, colors, opacities, img_h,
                                 img_w, (float4*)scratch, s);
     if (rc != GS2D_OK) return rc;
-    k_raster_bwd<<<div_up(num_intersects, kBwdThreads / 32), kBwdThreads, 0, s>>>(
+    {
+        ProfScope ps_(GS2D_STAGE_RASTER_BWD, s);
+        k_raster_bwd<<<div_up(num_intersects, kBwdThreads / 32), kBwdThreads, 0, s>>>(
         nullptr, num_intersects, img_w, tx, tile_bins, (const float4*)scratch, final_idx, v_out, grads);
+    }
     GS2D_CHECK_LAUNCH("raster_bwd_binned");
     return GS2D_OK;
 }

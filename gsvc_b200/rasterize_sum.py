@@ -36,6 +36,7 @@ class _DeviceCtx:
                 e.record()   # creates the underlying cudaEvent_t
                 self.events.append(e)
         self.slot = 0
+        self.last_num_intersects = 0
         self.cap = {}       # (H, W) -> capacity in intersections
         self.layouts = {}   # (n, cap, tx, ty) -> StateLayout
 
@@ -158,6 +159,7 @@ class _RasterizeGaussiansSum(Function):
                 ev.synchronize()   # waits for the scan stage only; the rest is already queued
                 m = dctx.mail_np[slot]
                 num_intersects, overflow, depth_or = int(m[0]), int(m[1]), int(m[2])
+                dctx.last_num_intersects = num_intersects
                 if overflow:
                     cap = _round_cap(num_intersects + num_intersects // 4)
                     continue

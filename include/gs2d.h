@@ -35,6 +35,28 @@ const char* gs2d_last_error(void);
 /* compute capability major*10+minor of `device`; the library only runs on 100 (sm_100a) */
 int gs2d_device_arch(int device);
 
+/* ---- instrumentation (no reference counterpart) ------------------------------------------
+ * gs2d_launch_count: kernels this library has launched since it was loaded (all threads).
+ * gs2d_prof_enable(1) makes every entry point bracket each of its stages with a CUDA event pair
+ * on the launching stream; gs2d_prof_read synchronises those events, adds the elapsed time and
+ * the number of spans per GS2D_STAGE_* into total_ms[] / spans[] (num_stages entries) and
+ * forgets them.  Off by default; the timed `value` runs of bench.py keep it off. */
+#define GS2D_STAGE_PROJECT_FWD 0
+#define GS2D_STAGE_MEMSET 1
+#define GS2D_STAGE_SCAN_MAP 2
+#define GS2D_STAGE_SORT 3
+#define GS2D_STAGE_EDGES_PACK 4
+#define GS2D_STAGE_RASTER_FWD 5
+#define GS2D_STAGE_RASTER_BWD 6
+#define GS2D_STAGE_PROJECT_BWD 7
+#define GS2D_STAGE_FIT_TILES 8
+#define GS2D_STAGE_ADAN 9
+#define GS2D_STAGE_OTHER 10
+#define GS2D_NUM_STAGES 11
+long long gs2d_launch_count(void);
+int gs2d_prof_enable(int on);
+int gs2d_prof_read(double* total_ms, int* spans, int num_stages);
+
 /* ---- projection ------------------------------------------------------------------- */
 /* replaces project_gaussians_2d_forward_tensor, bindings.cu:787-839 (kernel foward2d.cu:12-69).
  * Writes every element of all five outputs (no pre-zeroing needed). clip_thresh is accepted
