@@ -120,55 +120,16 @@ def algorithmic_bytes(stage: str, n: int, I: int, hw: int, tiles: int) -> float:
 # ------------------------------------------------------------------------------------------
 # CPU arm: the oracle port on the host cores
 # ------------------------------------------------------------------------------------------
-class CpuFit:
-    """the same fit iteration on the CPU: oracle C kernels (OpenMP) + numpy glue + numpy Adan"""
-
-    def __init__(self, seed=1):
-        import numpy as np
-        from gsvc_b200 import synth
-        from oracle import oracle as O
-        self.np, self.O = np, O
-        g = synth.gaussians(NPTS, seed=seed)
-        self.p = [g["_xyz"].numpy().copy(), g["_cholesky"].numpy().copy(), g["_features_dc"].numpy().copy()]
-        self.m = [np.zeros_like(a) for a in self.p]
-        self.n = [np.zeros_like(a) for a in self.p]
-        self.d = [np.zeros_like(a) for a in self.p]
-        self.prev = None
-        self.t = 0
-        self.opacity = np.ones((NPTS, 1), np.float32)
-        self.gt = synth.target_frame(H, W)[0].permute(1, 2, 0).contiguous().numpy()
-        self.bound = np.array([[0.5, 0.0, 0.5]], np.float32)
-        self.cores = O.num_threads()
-
-    def step(self):
-        np, O = self.np, self.O
-        xyz, chol, feat = self.p
-        means = np.tanh(xyz)
-        gt = self.gt
-        scale = np.float32(2.0 / gt.size)
-        r = O.fit_grads(means, chol + self.bound, feat, self.opacity, H, W,
-                        lambda img: scale * (np.clip(img, 0, 1) - gt) * ((img > 0) & (img < 1)))
-        loss = float(np.mean((np.clip(r["out_img"], 0, 1) - gt) ** 2))
-        grads = [r["v_mean2d"] * (1 - means * means), r["v_L"], r["v_colors"]]
-        self.t += 1
-        t, (b1, b2, b3), lr, eps = self.t, (0.98, 0.92, 0.99), 1e-3, 1e-8
-        if self.prev is None:
-            self.prev = [g.copy() for g in grads]
-        bc1, bc2, bc3s = 1 - b1 ** t, 1 - b2 ** t, math.sqrt(1 - b3 ** t)
-        for i, g in enumerate(grads):
-            diff = g - self.prev[i]
-            self.m[i] = b1 * self.m[i] + (1 - b1) * g
-            self.d[i] = b2 * self.d[i] + (1 - b2) * diff
-            u = g + b2 * diff
-            self.n[i] = b3 * self.n[i] + (1 - b3) * u * u
-            denom = np.sqrt(self.n[i]) / bc3s + eps
-            self.p[i] = (self.p[i] - (lr / bc1) * self.m[i] / denom - (lr * b2 / bc2) * self.d[i] / denom).astype(np.float32)
-            self.prev[i] = g
-        return loss
+def make_cpu_fit(seed=1):
+    from gsvc_b200 import synth
+    from oracle.fit_cpu import CpuFit
+    g = synth.gaussians(NPTS, seed=seed)
+    gt = synth.target_frame(H, W, seed=seed)[0].permute(1, 2, 0).contiguous().numpy()
+    return CpuFit(H, W, {k: g[k].numpy() for k in ("_xyz", "_cholesky", "_features_dc")}, gt)
 
 
 def run_cpu(steps: int, warmup: int) -> dict:
-    fit = CpuFit()
+    fit = make_cpu_fit()
     for _ in range(warmup):
         fit.step()
     t0 = time.perf_counter()
@@ -207,8 +168,10 @@ def make_fitter(impl: str, dev, seed: int):
         sys.path.insert(0, os.path.join(ROOT, "tests"))
         import ref_fit
         return ref_fit.RefFrameFit(H, W, NPTS, dev, seed=seed)
-    from gsvc_b200.fit import FrameFit
-    return FrameFit(H, W, NPTS, dev, seed=seed)
+    from gsvc_b200.fit import FrameFit, FusedFrameFit
+    if impl == "b200-dropin":
+        return FrameFit(H, W, NPTS, dev, seed=seed)
+    return FusedFrameFit(H, W, NPTS, dev, seed=seed)
 
 
 def main_gpu(args, rank: int, world: int, local_rank: int):
@@ -221,9 +184,17 @@ def main_gpu(args, rank: int, world: int, local_rank: int):
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
 
-    mine = args.impl == "b200"
+    mine = args.impl in ("b200", "b200-dropin")
+    fused = args.impl == "b200"
     fit = make_fitter(args.impl, dev, seed=1 + rank)
-    gt_host = synth.target_frame(H, W, seed=1 + rank).pin_memory()       # [1,3,H,W] fp32, what the loader yields
+    frame = synth.target_frame(H, W, seed=1 + rank)                      # [1,3,H,W] fp32 in [0,1]
+    if fused:
+        # the fused path takes the raw RGB frame (uint8 [H,W,3], what the YUV loader decodes to)
+        gt_host = (frame[0] * 255).round().to(torch.uint8).permute(1, 2, 0).contiguous().pin_memory()
+        step_resident = lambda g: fit.train_iters(g, 1)                  # nothing read back
+    else:
+        gt_host = frame.pin_memory()                                     # fp32 NCHW, what the reference's loader yields
+        step_resident = fit.train_iter                                   # reads the loss back every step, as the reference
     gt = gt_host.to(dev)
     flush = torch.empty(L2_FLUSH_BYTES, dtype=torch.uint8, device=dev)
     K, Wm = args.steps, max(args.warmup, 3)
@@ -235,7 +206,7 @@ def main_gpu(args, rank: int, world: int, local_rank: int):
 
     # ---- warm-up ---------------------------------------------------------------------------
     for _ in range(Wm):
-        fit.train_iter(gt)
+        step_resident(gt)
     barrier()
 
     # ---- value: HBM-resident inputs, L2 flushed between steps, per-step CUDA events ------------
@@ -249,7 +220,7 @@ def main_gpu(args, rank: int, world: int, local_rank: int):
     for a, b in ev:
         flush.zero_()
         a.record()
-        fit.train_iter(gt)
+        step_resident(gt)
         b.record()
     barrier()
     wall = time.perf_counter() - wall0
@@ -261,7 +232,7 @@ def main_gpu(args, rank: int, world: int, local_rank: int):
     barrier()
     a.record()
     for _ in range(K):
-        fit.train_iter(gt)
+        step_resident(gt)
     b.record()
     barrier()
     warm_ms = a.elapsed_time(b) / K
@@ -296,7 +267,7 @@ def main_gpu(args, rank: int, world: int, local_rank: int):
         _lib.prof_enable(True)
         for _ in range(K):
             flush.zero_()
-            fit.train_iter(gt)
+            step_resident(gt)
         torch.cuda.synchronize(dev)
         _lib.prof_enable(False)
         prof = _lib.prof_read()
@@ -319,8 +290,8 @@ def main_gpu(args, rank: int, world: int, local_rank: int):
                        "path": getattr(fit, "path_name", "autograd drop-in ops + torch glue"),
                        "parallelism": f"{world} independent GOP chains, one per GPU, no collective"},
             "clocks": clocks,
-            "e2e": {"value": world * 1e3 / e2e_ms, "unit": UNIT, "h2d_bytes_per_step": gt_host.numel() * 4,
-                    "d2h_bytes_per_step": 4, "ms_per_step": e2e_ms},
+            "e2e": {"value": world * 1e3 / e2e_ms, "unit": UNIT, "h2d_bytes_per_step": gt_host.numel() * gt_host.element_size(),
+                    "d2h_bytes_per_step": 16 if fused else 4, "ms_per_step": e2e_ms},
             "gpu_launches": launches,
             "l2_warm": {"value": world * 1e3 / warm_ms, "unit": UNIT, "ms_per_step": warm_ms},
             "render": {"value": world * 1e3 / render_ms, "unit": "frames/s", "ms_per_frame": render_ms},
@@ -328,6 +299,8 @@ def main_gpu(args, rank: int, world: int, local_rank: int):
         }
         if args.impl != "b200":
             line["impl"] = args.impl
+        if hasattr(fit, "status"):
+            line["config"]["max_per_tile"] = fit.status()[2]
         if stages:
             line["stages"] = stages
             kern = {k: v for k, v in stages.items() if k != "memset"}
@@ -359,7 +332,7 @@ def main():
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=200)
     ap.add_argument("--warmup", type=int, default=20)
-    ap.add_argument("--impl", default="b200", choices=["b200", "reference", "reference-gpu"])
+    ap.add_argument("--impl", default="b200", choices=["b200", "b200-dropin", "reference", "reference-gpu"])
     ap.add_argument("--cpu-steps", type=int, default=20, help="fit iterations of the cpu_baseline leg")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     args = ap.parse_args()

@@ -30,6 +30,25 @@ class StateLayout(Structure):
     ]
 
 
+class FitLayout(Structure):
+    """mirror of gs2d_fit_layout (include/gs2d.h)"""
+
+    _fields_ = [
+        ("total_bytes", c_size_t),
+        ("off_status", c_size_t),
+        ("off_loss", c_size_t),
+        ("off_tile_count", c_size_t),
+        ("off_tile_off", c_size_t),
+        ("off_grads", c_size_t),
+        ("off_packed", c_size_t),
+        ("zero_bytes", c_size_t),
+        ("tiles", c_int),
+    ]
+
+
+FIT_LOSS_SLOTS = 64
+TARGET_F32_CHW, TARGET_U8_HWC = 0, 1
+
 _P = c_void_p
 _SIGNATURES = {
     "gs2d_version": (c_int, []),
@@ -55,6 +74,12 @@ _SIGNATURES = {
     "gs2d_rasterize_sum_fwd_binned": (c_int, [c_int, c_int, _P, _P, _P, _P, _P, _P, c_int, c_int, _P, _P, _P, _P, c_size_t, _P]),
     "gs2d_rasterize_sum_bwd": (c_int, [c_int, c_int, c_int, c_int, _P, c_size_t, _P, _P, _P, _P]),
     "gs2d_rasterize_sum_bwd_binned": (c_int, [c_int, c_int, _P, _P, _P, _P, _P, _P, c_int, c_int, _P, _P, _P, _P, c_size_t, _P]),
+    "gs2d_fit_layout_for": (c_int, [c_int, c_int, c_int, c_int, POINTER(FitLayout)]),
+    "gs2d_fit_init": (c_int, [c_int, c_int, c_int, c_int, _P, c_size_t, _P, _P]),
+    "gs2d_fit_step": (c_int, [c_int, c_int, c_int, c_int, _P, _P, _P, _P, _P, c_int, _P, c_size_t, c_int,
+                              c_float, c_float, c_float, c_float, c_float, c_float, _P, _P, _P, _P]),
+    "gs2d_render_chol": (c_int, [c_int, c_int, c_int, c_int, _P, _P, _P, _P, c_int, _P, c_size_t, _P, c_int, c_int,
+                                 _P, _P, _P]),
 }
 
 _lib = None

@@ -1,0 +1,615 @@
+// fit.cu -- the fit iteration of one frame as four kernels, no host synchronisation, no
+// allocation, no memset:
+//
+//   k_fit_count    per Gaussian: tanh / Cholesky-bound activations, projection, one atomic per
+//                  touched tile into tile_count; the last block to finish scans tile_count into
+//                  tile_off (= the reference's tile_bins) and publishes num_intersects.
+//   k_fit_scatter  per Gaussian: same projection, claims a slot in each touched tile's range and
+//                  writes the 48-byte packed record there.  Order inside a tile is restored in
+//                  the tile kernel by ranking the records on Gaussian id, which is exactly the
+//                  order the reference's stable sort on tile id produces.
+//   k_fit_tiles    one CTA per 16x16 tile: sum-rasterise forward (forward.cu:512-627, first 256
+//                  entries only), clamp + L2 loss against the target and its
+//                  gradient (GaussianSplats_Represent.py:88-89,194 + utils.py:21-26 of the
+//                  reference) kept in shared memory, then the rasteriser backward
+//                  (backward.cu:696-862) warp-per-Gaussian from shared memory: one 9-float
+//                  reduction per (Gaussian, tile) pair.
+//   k_fit_update   per Gaussian: projection backward (backward2d.cu:8-51, reference formula,
+//                  SURVEY Q12), tanh backward, Adan update of the 8 parameters, and re-zeroing
+//                  of the gradient row for the next iteration.
+//
+// The same count/scatter/tile kernels without the loss and backward are the render-only path.
+#include "gs2d_internal.h"
+#include "gs2d_math.cuh"
+
+namespace gs2d {
+
+constexpr int kFitThreads = 256;
+constexpr int kStNumIntersects = 0;   // status words (int32[16])
+constexpr int kStOverflow = 1;        // first step index whose intersections exceeded cap (0 = none)
+constexpr int kStTicket = 2;
+constexpr int kStMaxPerTile = 3;      // max entries of any tile in the last step
+
+__device__ __forceinline__ void cp_async16(void* smem, const void* gmem) {
+    const unsigned sa = (unsigned)__cvta_generic_to_shared(smem);
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(sa), "l"(gmem) : "memory");
+}
+__device__ __forceinline__ void cp_async_wait_all() {
+    asm volatile("cp.async.commit_group;\ncp.async.wait_group 0;" ::: "memory");
+}
+
+// activations of the reference's frame model (GaussianSplats_Represent.py:56-70) + projection
+__device__ __forceinline__ void fit_project(int i, const float* __restrict__ xyz_raw, const float* __restrict__ chol_raw,
+                                            int activate, float half_w, float half_h, int tx, int ty, Proj2d& p,
+                                            float2& means, float3& L) {
+    const float2 r = reinterpret_cast<const float2*>(xyz_raw)[i];
+    L = make_float3(chol_raw[3 * i], chol_raw[3 * i + 1], chol_raw[3 * i + 2]);
+    if (activate) {
+        means = make_float2(tanhf(r.x), tanhf(r.y));
+        L.x = addf(L.x, 0.5f); L.y = addf(L.y, 0.f); L.z = addf(L.z, 0.5f);
+    } else {
+        means = r;
+    }
+    project_chol(means.x, means.y, L.x, L.y, L.z, half_w, half_h, tx, ty, p);
+}
+
+// ------------------------------------------------------------------------------------------
+// K1: count + (last block) scan of the per-tile counts
+// ------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kFitThreads)
+k_fit_count(int n, const float* __restrict__ xyz_raw, const float* __restrict__ chol_raw, int activate, float half_w,
+            float half_h, int tx, int ty, int cap, int step, int32_t* tile_count, int32_t* __restrict__ tile_off,
+            int32_t* status) {
+    __shared__ int sh[8];
+    __shared__ int s_last;
+    const int i = blockIdx.x * kFitThreads + threadIdx.x;
+    if (i < n) {
+        Proj2d p; float2 m; float3 L;
+        fit_project(i, xyz_raw, chol_raw, activate, half_w, half_h, tx, ty, p, m, L);
+        if (p.nth > 0)
+            for (int y = p.y0; y < p.y1; ++y)
+                for (int x = p.x0; x < p.x1; ++x) atomicAdd(&tile_count[y * tx + x], 1);
+    }
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0) s_last = (atomicAdd(&status[kStTicket], 1) == (int)gridDim.x - 1);
+    __syncthreads();
+    if (!s_last) return;
+    __threadfence();
+    // exclusive scan of tile_count over all tiles by this one block; counts are re-zeroed so the
+    // scatter kernel can use the same array as its per-tile fill counters
+    const int tiles = tx * ty;
+    const int per = (tiles + kFitThreads - 1) / kFitThreads;
+    const int beg = min(threadIdx.x * per, tiles), end = min(beg + per, tiles);
+    int sum = 0, mx = 0;
+    for (int t = beg; t < end; ++t) {
+        const int c = __ldcg(&tile_count[t]);
+        sum += c;
+        mx = max(mx, c);
+    }
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    int incl = sum;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const int v = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o) incl += v;
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) mx = max(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+    if (lane == 31) sh[warp] = incl;
+    __syncthreads();
+    int wexcl = 0, total = 0;
+    for (int w = 0; w < kFitThreads / 32; ++w) {
+        if (w < warp) wexcl += sh[w];
+        total += sh[w];
+    }
+    int run = wexcl + incl - sum;
+    for (int t = beg; t < end; ++t) {
+        const int c = __ldcg(&tile_count[t]);
+        tile_off[t] = run;
+        run += c;
+        tile_count[t] = 0;
+    }
+    __syncthreads();
+    if (lane == 0) sh[warp] = mx;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        for (int w = 1; w < kFitThreads / 32; ++w) mx = max(mx, sh[w]);
+        tile_off[tiles] = total;
+        status[kStNumIntersects] = total;
+        status[kStMaxPerTile] = mx;
+        status[kStTicket] = 0;
+        if (total > cap && status[kStOverflow] == 0) status[kStOverflow] = step > 0 ? step : 1;
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// K2: scatter the packed records into their tiles' ranges
+// packed[pos] = { x, y, conic.x, conic.y | conic.z, opacity, rect, gaussian id | r, g, b, tile }
+// ------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kFitThreads)
+k_fit_scatter(int n, const float* __restrict__ xyz_raw, const float* __restrict__ chol_raw,
+              const float* __restrict__ feat, const float* __restrict__ opac, int activate, float half_w, float half_h,
+              int tx, int ty, int W, int H, const int32_t* __restrict__ tile_off, int32_t* tile_fill,
+              const int32_t* __restrict__ status, float4* __restrict__ packed) {
+    if (status[kStOverflow] != 0) return;
+    const int i = blockIdx.x * kFitThreads + threadIdx.x;
+    if (i >= n) return;
+    Proj2d p; float2 m; float3 L;
+    fit_project(i, xyz_raw, chol_raw, activate, half_w, half_h, tx, ty, p, m, L);
+    if (p.nth <= 0) return;
+    const float o = opac ? opac[i] : 1.f;
+    const float r = feat[3 * i], g = feat[3 * i + 1], b = feat[3 * i + 2];
+    for (int y = p.y0; y < p.y1; ++y)
+        for (int x = p.x0; x < p.x1; ++x) {
+            const int t = y * tx + x;
+            const int pos = tile_off[t] + atomicAdd(&tile_fill[t], 1);
+            const uint32_t rect = pair_rect(p.cx, p.cy, o, p.conic.x, p.conic.y, p.conic.z, x * GS2D_TILE,
+                                            y * GS2D_TILE, W, H);
+            packed[3 * (size_t)pos + 0] = make_float4(p.cx, p.cy, p.conic.x, p.conic.y);
+            packed[3 * (size_t)pos + 1] = make_float4(p.conic.z, o, __uint_as_float(rect), __int_as_float(i));
+            packed[3 * (size_t)pos + 2] = make_float4(r, g, b, __uint_as_float((uint32_t)t));
+        }
+}
+
+// ------------------------------------------------------------------------------------------
+// K3: the tile kernel
+// ------------------------------------------------------------------------------------------
+// Sum 8 per-lane values over the warp with 9 shuffles: the total of v[j] ends up in the lanes
+// with (lane >> 2) == j.
+__device__ __forceinline__ float warp_reduce8_t(float (&v)[8], int lane) {
+    const bool b4 = lane & 16, b3 = lane & 8, b2 = lane & 4;
+    float w[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        const float send = b4 ? v[k] : v[4 + k];
+        const float keep = b4 ? v[4 + k] : v[k];
+        w[k] = keep + __shfl_xor_sync(0xffffffffu, send, 16);
+    }
+    float u[2];
+#pragma unroll
+    for (int k = 0; k < 2; ++k) {
+        const float send = b3 ? w[k] : w[2 + k];
+        const float keep = b3 ? w[2 + k] : w[k];
+        u[k] = keep + __shfl_xor_sync(0xffffffffu, send, 8);
+    }
+    const float send = b2 ? u[0] : u[1];
+    const float keep = b2 ? u[1] : u[0];
+    float r = keep + __shfl_xor_sync(0xffffffffu, send, 4);
+    r += __shfl_xor_sync(0xffffffffu, r, 2);
+    r += __shfl_xor_sync(0xffffffffu, r, 1);
+    return r;
+}
+
+constexpr int kIdChunk = 1024;
+
+// Stage the tile's batch in ascending Gaussian-id order.  cnt <= 256: the whole range is copied
+// with cp.async and a rank permutation is built (perm[rank] = slot).  cnt > 256 (rare; the
+// reference then renders only the 256 lowest ids): ranks are computed against all cnt
+// ids in chunks and the 256 lowest-ranked records are copied straight into sorted position.
+__device__ __forceinline__ int stage_tile_sorted(const float4* __restrict__ src, int cnt, float4* sq, uint8_t* perm,
+                                                 int* sid, int tid) {
+    const int nb = min(cnt, GS2D_MAX_PER_TILE);
+    if (cnt <= GS2D_MAX_PER_TILE) {
+        for (int i = tid; i < cnt * 3; i += GS2D_TILE_PIX) cp_async16(&sq[i], src + i);
+        cp_async_wait_all();
+        __syncthreads();
+        if (tid < cnt) {
+            const int my = __float_as_int(sq[3 * tid + 1].w);
+            int rank = 0;
+            for (int j = 0; j < cnt; ++j) rank += (__float_as_int(sq[3 * j + 1].w) < my) ? 1 : 0;
+            perm[rank] = (uint8_t)tid;
+        }
+        __syncthreads();
+    } else {
+        for (int r0 = 0; r0 < cnt; r0 += GS2D_TILE_PIX) {
+            const int j = r0 + tid;
+            const int my = j < cnt ? __float_as_int(__ldg(&src[3 * (size_t)j + 1]).w) : 0x7fffffff;
+            int rank = 0;
+            for (int c0 = 0; c0 < cnt; c0 += kIdChunk) {
+                const int m = min(kIdChunk, cnt - c0);
+                __syncthreads();
+                for (int k = tid; k < m; k += GS2D_TILE_PIX) sid[k] = __float_as_int(__ldg(&src[3 * (size_t)(c0 + k) + 1]).w);
+                __syncthreads();
+                for (int k = 0; k < m; ++k) rank += (sid[k] < my) ? 1 : 0;
+            }
+            if (j < cnt && rank < GS2D_MAX_PER_TILE) {
+                sq[3 * rank + 0] = __ldg(&src[3 * (size_t)j + 0]);
+                sq[3 * rank + 1] = __ldg(&src[3 * (size_t)j + 1]);
+                sq[3 * rank + 2] = __ldg(&src[3 * (size_t)j + 2]);
+            }
+        }
+        perm[tid] = (uint8_t)tid;
+        __syncthreads();
+    }
+    return nb;
+}
+
+// MODE 0: fit (loss + backward, no image written unless out_img != NULL)
+// MODE 1: render only (image [+ final_idx] written, no target, no backward)
+// GT: 0 = target is fp32 planar [3][H][W] (what torchvision's ToTensor / the reference's loader
+//         yields), 1 = uint8 interleaved [H][W][3] (raw frame; compared as value / 255)
+template <int MODE, int GT>
+__global__ void __launch_bounds__(GS2D_TILE_PIX)
+k_fit_tiles(int W, int H, int tx, const int32_t* __restrict__ tile_off, int32_t* tile_fill,
+            const float4* __restrict__ packed, const void* __restrict__ gt, float grad_scale,
+            float* __restrict__ grads, double* loss_acc, const int32_t* __restrict__ status,
+            float* __restrict__ out_img, int out_chw, int out_clamp, int32_t* __restrict__ final_idx,
+            int32_t* __restrict__ ids_sorted_dbg) {
+    __shared__ float4 sq[GS2D_MAX_PER_TILE * 3];
+    __shared__ float4 sv[GS2D_TILE_PIX];
+    __shared__ int sid[kIdChunk];
+    __shared__ uint8_t perm[GS2D_MAX_PER_TILE];
+    __shared__ float sred[GS2D_TILE_PIX / 32];
+    if (status[kStOverflow] != 0) return;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int t = blockIdx.y * tx + blockIdx.x;
+    const int lo = tile_off[t], cnt = tile_off[t + 1] - lo;
+    if (tid == 0) tile_fill[t] = 0;   // ready for the next iteration's scatter
+
+    const int lx = tid & 15, ly = tid >> 4;   // warp w owns rows 2w, 2w+1 of the tile
+    const int px_i = blockIdx.x * GS2D_TILE + lx, py_i = blockIdx.y * GS2D_TILE + ly;
+    const bool inside = px_i < W && py_i < H;
+    const size_t pid = (size_t)py_i * W + px_i;
+    float3 tgt = make_float3(0.f, 0.f, 0.f);
+    if (MODE == 0 && inside) {   // issued before the batch arrives: independent loads
+        if (GT == 0) {
+            const float* g = (const float*)gt;
+            const size_t plane = (size_t)H * W;
+            tgt = make_float3(__ldg(g + pid), __ldg(g + plane + pid), __ldg(g + 2 * plane + pid));
+        } else {
+            const uint8_t* g = (const uint8_t*)gt + 3 * pid;
+            tgt = make_float3((float)g[0] / 255.f, (float)g[1] / 255.f, (float)g[2] / 255.f);
+        }
+    }
+
+    const int nb = stage_tile_sorted(packed + 3 * (size_t)lo, cnt, sq, perm, sid, tid);
+    if (ids_sorted_dbg) {   // parity tests: the order the batch is rendered in
+        for (int r = tid; r < nb; r += GS2D_TILE_PIX) ids_sorted_dbg[lo + r] = __float_as_int(sq[3 * perm[r] + 1].w);
+        for (int r = nb + tid; r < cnt; r += GS2D_TILE_PIX) ids_sorted_dbg[lo + r] = -1;
+    }
+
+    // ---- forward (forward.cu:590-612) --------------------------------------------------------
+    const float px = (float)px_i, py = (float)py_i;
+    const int row_lo = 2 * warp, row_hi = 2 * warp + 1;
+    float3 pix = make_float3(0.f, 0.f, 0.f);
+    int cur_idx = 0;
+    for (int c = 0; c < nb; c += 32) {
+        const int r_lane = c + lane;
+        bool touch = false;
+        if (r_lane < nb) {
+            const uint32_t rect = __float_as_uint(sq[3 * perm[r_lane] + 1].z);
+            const int y0 = (rect >> 16) & 255, y1 = rect >> 24;
+            touch = (y1 >= row_lo) && (y0 <= row_hi);
+        }
+        unsigned m = __ballot_sync(0xffffffffu, touch);
+        while (m) {
+            const int r = c + __ffs(m) - 1;
+            m &= m - 1;
+            const int k = perm[r];
+            const float4 q0 = sq[3 * k];       // x, y, conic.x, conic.y
+            const float4 q1 = sq[3 * k + 1];   // conic.z, opacity, rect, id
+            const float dx = subf(q0.x, px), dy = subf(q0.y, py);
+            const float sigma = gauss_sigma(dx, dy, q0.z, q0.w, q1.x);
+            const float alpha = minf(mulf(q1.y, gauss_vis(sigma)), 1.f);
+            if (inside && gauss_pass(sigma, alpha)) {
+                const float4 q2 = sq[3 * k + 2];   // r, g, b, tile
+                pix.x = fmaf_(alpha, q2.x, pix.x);
+                pix.y = fmaf_(alpha, q2.y, pix.y);
+                pix.z = fmaf_(alpha, q2.z, pix.z);
+                cur_idx = lo + r;
+            }
+        }
+    }
+    if (inside && out_img) {
+        float3 o = pix;
+        if (out_clamp) o = make_float3(fminf(fmaxf(o.x, 0.f), 1.f), fminf(fmaxf(o.y, 0.f), 1.f), fminf(fmaxf(o.z, 0.f), 1.f));
+        if (out_chw) {
+            const size_t plane = (size_t)H * W;
+            out_img[pid] = o.x; out_img[plane + pid] = o.y; out_img[2 * plane + pid] = o.z;
+        } else {
+            out_img[3 * pid] = o.x; out_img[3 * pid + 1] = o.y; out_img[3 * pid + 2] = o.z;
+        }
+    }
+    if (inside && final_idx) final_idx[pid] = cur_idx;
+    if (MODE == 1) return;
+
+    // ---- clamp + L2 loss and its gradient w.r.t. the unclamped sum --------------------------
+    float l = 0.f;
+    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (inside) {
+        const float dxr = fminf(fmaxf(pix.x, 0.f), 1.f) - tgt.x;
+        const float dyg = fminf(fmaxf(pix.y, 0.f), 1.f) - tgt.y;
+        const float dzb = fminf(fmaxf(pix.z, 0.f), 1.f) - tgt.z;
+        l = dxr * dxr + dyg * dyg + dzb * dzb;
+        // clamp passes the gradient where 0 <= x <= 1 (torch's clamp backward, bounds inclusive)
+        v.x = (pix.x >= 0.f && pix.x <= 1.f) ? grad_scale * dxr : 0.f;
+        v.y = (pix.y >= 0.f && pix.y <= 1.f) ? grad_scale * dyg : 0.f;
+        v.z = (pix.z >= 0.f && pix.z <= 1.f) ? grad_scale * dzb : 0.f;
+    }
+    sv[tid] = v;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) l += __shfl_xor_sync(0xffffffffu, l, o);
+    if (lane == 0) sred[warp] = l;
+    __syncthreads();
+    if (tid == 0) {
+        float s = 0.f;
+#pragma unroll
+        for (int w = 0; w < GS2D_TILE_PIX / 32; ++w) s += sred[w];
+        if (s != 0.f) atomicAdd(loss_acc, (double)s);
+    }
+
+    // ---- backward (backward.cu:783-859): one warp per (tile, Gaussian) pair -----------------
+    for (int r = warp; r < nb; r += GS2D_TILE_PIX / 32) {
+        const int k = perm[r];
+        const float4 q1 = sq[3 * k + 1];
+        const uint32_t rect = __float_as_uint(q1.z);
+        const int rx0 = rect & 255, rx1 = (rect >> 8) & 255, ry0 = (rect >> 16) & 255, ry1 = rect >> 24;
+        if (ry1 < ry0) continue;   // no pixel of this tile can pass
+        const float4 q0 = sq[3 * k], q2 = sq[3 * k + 2];
+        const float gx = q0.x, gy = q0.y, cx = q0.z, cy = q0.w, cz = q1.x, opac = q1.y;
+        const int ox = blockIdx.x * GS2D_TILE, oy = blockIdx.y * GS2D_TILE;
+        const int w = rx1 - rx0 + 1, area = w * (ry1 - ry0 + 1);
+        const float inv_w = 1.f / (float)w;
+        float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+        float acc_op = 0.f;
+        for (int p = lane; p < area; p += 32) {
+            const int ry = (int)(((float)p + 0.5f) * inv_w);
+            const int lxp = rx0 + (p - ry * w), lyp = ry0 + ry;
+            const float dx = subf(gx, (float)(ox + lxp)), dy = subf(gy, (float)(oy + lyp));
+            const float sigma = gauss_sigma(dx, dy, cx, cy, cz);
+            const float vis = gauss_vis(sigma);
+            const float alpha = minf(mulf(opac, vis), 1.f);
+            if (!gauss_pass(sigma, alpha)) continue;
+            const float4 vo = sv[lyp * GS2D_TILE + lxp];
+            const float v_alpha = q2.x * vo.x + q2.y * vo.y + q2.z * vo.z;   // backward.cu:821-825
+            const float v_sigma = -opac * vis * v_alpha;                      // :827
+            acc[0] += v_sigma * (cx * dx + cy * dy);                          // v_xy     :831-832
+            acc[1] += v_sigma * (cy * dx + cz * dy);
+            const float hs = 0.5f * v_sigma;
+            acc[2] += hs * dx * dx;                                           // v_conic  :828-830
+            acc[3] += hs * dx * dy;
+            acc[4] += hs * dy * dy;
+            acc[5] += alpha * vo.x;                                           // v_rgb    :817
+            acc[6] += alpha * vo.y;
+            acc[7] += alpha * vo.z;
+            acc_op += vis * v_alpha;                                          // v_opacity :833
+        }
+        const float tot = warp_reduce8_t(acc, lane);
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) acc_op += __shfl_xor_sync(0xffffffffu, acc_op, o);
+        float* row = grads + (size_t)__float_as_int(q1.w) * 12;
+        if ((lane & 3) == 0) {
+            if (tot != 0.f) atomicAdd(row + (lane >> 2), tot);   // 8 lanes, 8 consecutive floats
+        } else if (lane == 1) {
+            if (acc_op != 0.f) atomicAdd(row + 8, acc_op);
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// K4: projection backward + tanh backward + Adan + gradient re-zeroing
+// ------------------------------------------------------------------------------------------
+struct AdanHyper {
+    float b1, b2, b3;
+    float step_size;        // lr / (1 - b1^t)
+    float step_size_diff;   // lr * b2 / (1 - b2^t)
+    float inv_bc3_sqrt;     // 1 / sqrt(1 - b3^t)
+    float eps;
+    float decay_div;        // 1 + lr * weight_decay
+    int first;              // t == 1: previous gradient := gradient
+};
+
+__device__ __forceinline__ float adan_one(float p, float g, float& m, float& nn, float& d, float& prev,
+                                          const AdanHyper& h) {
+    const float diff = h.first ? 0.f : g - prev;
+    m = m * h.b1 + (1.f - h.b1) * g;
+    d = d * h.b2 + (1.f - h.b2) * diff;
+    const float u = g + h.b2 * diff;
+    nn = nn * h.b3 + (1.f - h.b3) * u * u;
+    const float denom = sqrtf(nn) * h.inv_bc3_sqrt + h.eps;
+    prev = g;
+    return (p - h.step_size * (m / denom) - h.step_size_diff * (d / denom)) / h.decay_div;
+}
+
+__global__ void __launch_bounds__(kFitThreads)
+k_fit_update(int n, float* __restrict__ xyz_raw, float* __restrict__ chol_raw, float* __restrict__ feat,
+             float* __restrict__ adan, float* __restrict__ grads, float half_w, float half_h, int tx, int ty,
+             AdanHyper h, const int32_t* __restrict__ status, double* loss_next, float* __restrict__ grads_out) {
+    if (status[kStOverflow] != 0) return;
+    const int i = blockIdx.x * kFitThreads + threadIdx.x;
+    if (i == 0 && loss_next) *loss_next = 0.0;
+    if (i >= n) return;
+    Proj2d p; float2 m; float3 L;
+    fit_project(i, xyz_raw, chol_raw, 1, half_w, half_h, tx, ty, p, m, L);
+    float4* grow = reinterpret_cast<float4*>(grads + (size_t)i * 12);
+    const float4 g0 = grow[0], g1 = grow[1], g2 = grow[2];   // v_xy(2) v_conic(3) v_rgb(3) v_opacity(1) pad(3)
+    const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
+    grow[0] = z; grow[1] = z; grow[2] = z;
+    float g[8] = {0.f, 0.f, 0.f, 0.f, 0.f, g1.y, g1.z, g1.w};   // xyz(2) chol(3) feat(3)
+    if (p.ok && (int)p.radius > 0) {   // backward2d.cu:23-25
+        const float3 vc = conic_vjp(p.conic, make_float3(g0.z, g0.w, g1.x));
+        const float3 vl = chol_vjp(L.x, L.y, L.z, vc);
+        const float vmx = g0.x * half_w, vmy = g0.y * half_h;            // backward2d.cu:48-49
+        g[0] = vmx * (1.f - m.x * m.x);                                   // d tanh
+        g[1] = vmy * (1.f - m.y * m.y);
+        g[2] = vl.x; g[3] = vl.y; g[4] = vl.z;
+    }
+    if (grads_out) {   // parity tests: the parameter gradients autograd would hand to the optimizer
+#pragma unroll
+        for (int k = 0; k < 8; ++k) grads_out[(size_t)i * 8 + k] = g[k];
+    }
+    float par[8] = {xyz_raw[2 * i], xyz_raw[2 * i + 1], chol_raw[3 * i], chol_raw[3 * i + 1], chol_raw[3 * i + 2],
+                    feat[3 * i], feat[3 * i + 1], feat[3 * i + 2]};
+    const size_t plane = (size_t)n * 8;
+    float4* sm = reinterpret_cast<float4*>(adan + (size_t)i * 8);
+    float4* sn = reinterpret_cast<float4*>(adan + plane + (size_t)i * 8);
+    float4* sd = reinterpret_cast<float4*>(adan + 2 * plane + (size_t)i * 8);
+    float4* sp = reinterpret_cast<float4*>(adan + 3 * plane + (size_t)i * 8);
+    float am[8], an[8], ad[8], ap[8];
+    *reinterpret_cast<float4*>(am) = sm[0]; *reinterpret_cast<float4*>(am + 4) = sm[1];
+    *reinterpret_cast<float4*>(an) = sn[0]; *reinterpret_cast<float4*>(an + 4) = sn[1];
+    *reinterpret_cast<float4*>(ad) = sd[0]; *reinterpret_cast<float4*>(ad + 4) = sd[1];
+    *reinterpret_cast<float4*>(ap) = sp[0]; *reinterpret_cast<float4*>(ap + 4) = sp[1];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) par[k] = adan_one(par[k], g[k], am[k], an[k], ad[k], ap[k], h);
+    sm[0] = *reinterpret_cast<float4*>(am); sm[1] = *reinterpret_cast<float4*>(am + 4);
+    sn[0] = *reinterpret_cast<float4*>(an); sn[1] = *reinterpret_cast<float4*>(an + 4);
+    sd[0] = *reinterpret_cast<float4*>(ad); sd[1] = *reinterpret_cast<float4*>(ad + 4);
+    sp[0] = *reinterpret_cast<float4*>(ap); sp[1] = *reinterpret_cast<float4*>(ap + 4);
+    xyz_raw[2 * i] = par[0]; xyz_raw[2 * i + 1] = par[1];
+    chol_raw[3 * i] = par[2]; chol_raw[3 * i + 1] = par[3]; chol_raw[3 * i + 2] = par[4];
+    feat[3 * i] = par[5]; feat[3 * i + 1] = par[6]; feat[3 * i + 2] = par[7];
+}
+
+static inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+static int fit_layout(int n, int cap, int img_h, int img_w, gs2d_fit_layout* L) {
+    if (n < 0 || cap < 1 || img_h < 1 || img_w < 1) {
+        set_error("fit layout: bad sizes (n=%d cap=%d %dx%d)", n, cap, img_w, img_h);
+        return GS2D_ERR_ARG;
+    }
+    const long long tiles = (long long)div_up(img_w, GS2D_TILE) * div_up(img_h, GS2D_TILE);
+    size_t o = 0;
+    L->off_status = o;      o = align_up(o + 16 * sizeof(int32_t), 256);
+    L->off_loss = o;        o = align_up(o + GS2D_FIT_LOSS_SLOTS * sizeof(double), 256);
+    L->off_tile_count = o;  o = align_up(o + (size_t)tiles * sizeof(int32_t), 256);
+    L->off_tile_off = o;    o = align_up(o + (size_t)(tiles + 1) * sizeof(int32_t), 256);
+    L->off_grads = o;       o = align_up(o + (size_t)(n > 0 ? n : 1) * 12 * sizeof(float), 256);
+    L->zero_bytes = o;      // everything up to here must be zero before the first step
+    L->off_packed = o;      o = align_up(o + (size_t)cap * 3 * sizeof(float4), 256);
+    L->total_bytes = o;
+    L->tiles = (int)tiles;
+    return GS2D_OK;
+}
+
+}  // namespace gs2d
+
+using namespace gs2d;
+
+extern "C" {
+
+int gs2d_fit_layout_for(int n, int cap, int img_h, int img_w, gs2d_fit_layout* out) {
+    GS2D_REQUIRE(out != nullptr, "fit_layout_for: null out");
+    return fit_layout(n, cap, img_h, img_w, out);
+}
+
+int gs2d_fit_init(int n, int cap, int img_h, int img_w, void* work, size_t work_bytes, float* adan_state,
+                  gs2d_stream_t stream) {
+    gs2d_fit_layout L;
+    const int rc = fit_layout(n, cap, img_h, img_w, &L);
+    if (rc != GS2D_OK) return rc;
+    GS2D_REQUIRE(work != nullptr && work_bytes >= L.total_bytes, "fit_init: workspace too small");
+    GS2D_REQUIRE(((uintptr_t)work & 255) == 0, "fit_init: workspace must be 256-byte aligned");
+    cudaStream_t s = (cudaStream_t)stream;
+    GS2D_CHECK_CUDA(cudaMemsetAsync(work, 0, L.zero_bytes, s));
+    if (adan_state && n > 0) GS2D_CHECK_CUDA(cudaMemsetAsync(adan_state, 0, (size_t)n * 8 * 4 * sizeof(float), s));
+    return GS2D_OK;
+}
+
+static int launch_bin(int n, const float* xyz, const float* chol, const float* feat, const float* opac, int activate,
+                      int img_h, int img_w, int cap, int step, const gs2d_fit_layout& L, char* w, cudaStream_t s) {
+    const int tx = div_up(img_w, GS2D_TILE), ty = div_up(img_h, GS2D_TILE);
+    const float half_w = 0.5f * (float)(unsigned)img_w, half_h = 0.5f * (float)(unsigned)img_h;
+    int32_t* status = (int32_t*)(w + L.off_status);
+    int32_t* tile_count = (int32_t*)(w + L.off_tile_count);
+    int32_t* tile_off = (int32_t*)(w + L.off_tile_off);
+    const int blocks = div_up(n > 0 ? n : 1, kFitThreads);
+    {
+        ProfScope ps_(GS2D_STAGE_SCAN_MAP, s);
+        k_fit_count<<<blocks, kFitThreads, 0, s>>>(n, xyz, chol, activate, half_w, half_h, tx, ty, cap, step,
+                                                   tile_count, tile_off, status);
+        GS2D_CHECK_LAUNCH("fit_count");
+    }
+    {
+        ProfScope ps_(GS2D_STAGE_EDGES_PACK, s);
+        k_fit_scatter<<<blocks, kFitThreads, 0, s>>>(n, xyz, chol, feat, opac, activate, half_w, half_h, tx, ty, img_w,
+                                                     img_h, tile_off, tile_count, status,
+                                                     (float4*)(w + L.off_packed));
+        GS2D_CHECK_LAUNCH("fit_scatter");
+    }
+    return GS2D_OK;
+}
+
+int gs2d_fit_step(int n, int cap, int img_h, int img_w, float* xyz_raw, float* chol_raw, float* features,
+                  float* adan_state, const void* target, int target_format, void* work, size_t work_bytes, int step,
+                  float lr, float beta1, float beta2, float beta3, float eps, float weight_decay, float* out_img,
+                  float* param_grads_out, int32_t* ids_sorted_out, gs2d_stream_t stream) {
+    gs2d_fit_layout L;
+    int rc = fit_layout(n, cap, img_h, img_w, &L);
+    if (rc != GS2D_OK) return rc;
+    GS2D_REQUIRE(n > 0 && step >= 1, "fit_step: n and step must be positive");
+    GS2D_REQUIRE(work != nullptr && work_bytes >= L.total_bytes, "fit_step: workspace too small");
+    GS2D_REQUIRE(target_format == GS2D_TARGET_F32_CHW || target_format == GS2D_TARGET_U8_HWC,
+                 "fit_step: unknown target format");
+    GS2D_REQUIRE(xyz_raw && chol_raw && features && adan_state && target, "fit_step: null pointer");
+    cudaStream_t s = (cudaStream_t)stream;
+    char* w = (char*)work;
+    const int tx = div_up(img_w, GS2D_TILE), ty = div_up(img_h, GS2D_TILE);
+    const float half_w = 0.5f * (float)(unsigned)img_w, half_h = 0.5f * (float)(unsigned)img_h;
+    rc = launch_bin(n, xyz_raw, chol_raw, features, nullptr, 1, img_h, img_w, cap, step, L, w, s);
+    if (rc != GS2D_OK) return rc;
+    int32_t* status = (int32_t*)(w + L.off_status);
+    double* loss = (double*)(w + L.off_loss);
+    float* grads = (float*)(w + L.off_grads);
+    const float grad_scale = (float)(2.0 / (3.0 * (double)img_h * (double)img_w));
+    {
+        ProfScope ps_(GS2D_STAGE_FIT_TILES, s);
+        const dim3 grid(tx, ty);
+        if (target_format == GS2D_TARGET_F32_CHW)
+            k_fit_tiles<0, 0><<<grid, GS2D_TILE_PIX, 0, s>>>(
+                img_w, img_h, tx, (const int32_t*)(w + L.off_tile_off), (int32_t*)(w + L.off_tile_count),
+                (const float4*)(w + L.off_packed), target, grad_scale, grads, loss + (step % GS2D_FIT_LOSS_SLOTS),
+                status, out_img, 1, 1, nullptr, ids_sorted_out);
+        else
+            k_fit_tiles<0, 1><<<grid, GS2D_TILE_PIX, 0, s>>>(
+                img_w, img_h, tx, (const int32_t*)(w + L.off_tile_off), (int32_t*)(w + L.off_tile_count),
+                (const float4*)(w + L.off_packed), target, grad_scale, grads, loss + (step % GS2D_FIT_LOSS_SLOTS),
+                status, out_img, 1, 1, nullptr, ids_sorted_out);
+        GS2D_CHECK_LAUNCH("fit_tiles");
+    }
+    AdanHyper h;
+    h.b1 = beta1; h.b2 = beta2; h.b3 = beta3;
+    h.step_size = (float)((double)lr / (1.0 - pow((double)beta1, step)));
+    h.step_size_diff = (float)((double)lr * (double)beta2 / (1.0 - pow((double)beta2, step)));
+    h.inv_bc3_sqrt = (float)(1.0 / sqrt(1.0 - pow((double)beta3, step)));
+    h.eps = eps;
+    h.decay_div = 1.f + lr * weight_decay;
+    h.first = step == 1;
+    {
+        ProfScope ps_(GS2D_STAGE_ADAN, s);
+        k_fit_update<<<div_up(n, kFitThreads), kFitThreads, 0, s>>>(
+            n, xyz_raw, chol_raw, features, adan_state, grads, half_w, half_h, tx, ty, h, status,
+            loss + ((step + 1) % GS2D_FIT_LOSS_SLOTS), param_grads_out);
+        GS2D_CHECK_LAUNCH("fit_update");
+    }
+    return GS2D_OK;
+}
+
+int gs2d_render_chol(int n, int cap, int img_h, int img_w, const float* means_or_xyz_raw, const float* chol,
+                     const float* colors, const float* opacities, int activate, void* work, size_t work_bytes,
+                     float* out_img, int out_chw, int out_clamp, int32_t* final_idx, int32_t* ids_sorted_out,
+                     gs2d_stream_t stream) {
+    gs2d_fit_layout L;
+    int rc = fit_layout(n, cap, img_h, img_w, &L);
+    if (rc != GS2D_OK) return rc;
+    GS2D_REQUIRE(n > 0, "render_chol: n must be positive");
+    GS2D_REQUIRE(work != nullptr && work_bytes >= L.total_bytes, "render_chol: workspace too small");
+    GS2D_REQUIRE(means_or_xyz_raw && chol && colors && out_img, "render_chol: null pointer");
+    cudaStream_t s = (cudaStream_t)stream;
+    char* w = (char*)work;
+    const int tx = div_up(img_w, GS2D_TILE), ty = div_up(img_h, GS2D_TILE);
+    rc = launch_bin(n, means_or_xyz_raw, chol, colors, opacities, activate, img_h, img_w, cap, 0, L, w, s);
+    if (rc != GS2D_OK) return rc;
+    {
+        ProfScope ps_(GS2D_STAGE_RASTER_FWD, s);
+        k_fit_tiles<1, 0><<<dim3(tx, ty), GS2D_TILE_PIX, 0, s>>>(
+            img_w, img_h, tx, (const int32_t*)(w + L.off_tile_off), (int32_t*)(w + L.off_tile_count),
+            (const float4*)(w + L.off_packed), nullptr, 0.f, nullptr, nullptr, (const int32_t*)(w + L.off_status),
+            out_img, out_chw, out_clamp, final_idx, ids_sorted_out);
+        GS2D_CHECK_LAUNCH("render_tiles");
+    }
+    return GS2D_OK;
+}
+
+}  // extern "C"

@@ -76,18 +76,6 @@ k_project_scalerot_fwd(int n, const float* __restrict__ means2d, const float* __
     project_tail(i, cx, cy, a, b, c, tx, ty, xys, depths, radii, conics, num_tiles_hit);
 }
 
-// reference helpers.cuh:71-82: v_Sigma = -X G X, v_cov2d = (S00, S10 + S01, S11)
-__device__ __forceinline__ float3 conic_vjp(float3 x, float3 g) {
-    // X = [x.x x.y; x.y x.z], G likewise (both symmetric)
-    const float a00 = x.x * g.x + x.y * g.y, a01 = x.x * g.y + x.y * g.z;   // X G
-    const float a10 = x.y * g.x + x.z * g.y, a11 = x.y * g.y + x.z * g.z;
-    const float s00 = -(a00 * x.x + a01 * x.y);
-    const float s01 = -(a00 * x.y + a01 * x.z);
-    const float s10 = -(a10 * x.x + a11 * x.y);
-    const float s11 = -(a10 * x.y + a11 * x.z);
-    return make_float3(s00, s10 + s01, s11);
-}
-
 __global__ void __launch_bounds__(kProjThreads)
 k_project_chol_bwd(int n, const float* __restrict__ L, float half_w, float half_h, const int32_t* __restrict__ radii,
                    const float* __restrict__ conics, const float* __restrict__ v_xy, int ld_xy,
@@ -103,9 +91,7 @@ k_project_chol_bwd(int n, const float* __restrict__ L, float half_w, float half_
         vc = conic_vjp(x, make_float3(gp[0], gp[1], gp[2]));
         const float l11 = L[3 * i], l21 = L[3 * i + 1], l22 = L[3 * i + 2];
         // reference formula (backward2d.cu:39-41), off-diagonal counted twice
-        vl.x = 2.f * l11 * vc.x + 2.f * vc.y * l21;
-        vl.y = 2.f * l11 * vc.y + 2.f * l21 * vc.z;
-        vl.z = 2.f * l22 * vc.z;
+        vl = chol_vjp(l11, l21, l22, vc);
         const float* xp = v_xy + (size_t)i * ld_xy;
         vm = make_float2(xp[0] * half_w, xp[1] * half_h);   // backward2d.cu:48-49
     }

@@ -164,6 +164,63 @@ int gs2d_rasterize_sum_bwd_binned(int n, int num_intersects, const int32_t* gaus
                                   const int32_t* final_idx, const float* v_out, float* grads, void* scratch,
                                   size_t scratch_bytes, gs2d_stream_t stream);
 
+/* ---- fused fit iteration and render (callers either side of the path) ----
+ * One frame model = raw parameters exactly as the reference's GaussianVideo_frame holds them
+ * (GaussianSplats_Represent.py:28-45): xyz_raw [n,2] (means2d = tanh), chol_raw [n,3]
+ * (L = chol_raw + [0.5, 0, 0.5]), features [n,3] (colours; rgb_W = 1, opacity = 1).
+ * gs2d_fit_step runs ONE iteration of GaussianVideo_frame.train_iter
+ * (GaussianSplats_Represent.py:191-207: forward :83-90, L2 loss utils.py:21-26, backward,
+ * Adan step optimizer.py:125-236 with the reference's defaults) as four kernels on `stream`
+ * with no host synchronisation, no allocation and no memset: project+count+scan,
+ * scatter-pack, tile kernel (rasterise forward + clamp/L2 + rasterise backward) and
+ * projection-backward+Adan.  Everything lives in caller-owned memory:
+ *   work        gs2d_fit_layout_for(...).total_bytes, 256-byte aligned; gs2d_fit_init zeroes its
+ *               control region once (and the Adan state);
+ *   adan_state  fp32 [4][n][8]: m, n, d, previous gradient of (xyz 2, chol 3, features 3);
+ *   target      the frame to fit: GS2D_TARGET_F32_CHW fp32 planar [3][H][W] in [0,1], or
+ *               GS2D_TARGET_U8_HWC uint8 interleaved [H][W][3] (compared as value / 255).
+ * step is 1-based (bias correction).  The step's loss SUM (sum of squared errors over 3*H*W
+ * values, a double) accumulates in work + off_loss + 8 * (step % GS2D_FIT_LOSS_SLOTS); mean =
+ * sum / (3*H*W).  status (int32[16] at off_status): [0] num_intersects of the last step,
+ * [1] != 0: the step index at which num_intersects first exceeded cap -- from then on every step
+ * is a no-op (parameters untouched) until the caller re-initialises a larger workspace,
+ * [3] largest per-tile count of the last step.
+ * Optional outputs (may be NULL): out_img fp32 planar [3][H][W], clamped to [0,1] (the
+ * reference's render); param_grads_out fp32 [n][8] the gradients handed to Adan;
+ * ids_sorted_out int32[cap] the Gaussian ids of every tile range in rendering order (-1 beyond
+ * the first 256 of a tile). */
+#define GS2D_FIT_LOSS_SLOTS 64
+#define GS2D_TARGET_F32_CHW 0
+#define GS2D_TARGET_U8_HWC 1
+typedef struct {
+    size_t total_bytes;
+    size_t off_status;      /* int32[16] */
+    size_t off_loss;        /* double[GS2D_FIT_LOSS_SLOTS] */
+    size_t off_tile_count;  /* int32[tiles]   per-tile fill counters (zero between kernels) */
+    size_t off_tile_off;    /* int32[tiles+1] exclusive scan of the per-tile counts = tile ranges */
+    size_t off_grads;       /* fp32[n][12]    v_xy(2) v_conic(3) v_colors(3) v_opacity(1) pad(3) */
+    size_t off_packed;      /* float4[cap][3] packed records, grouped by tile */
+    size_t zero_bytes;      /* [0, zero_bytes) is what gs2d_fit_init clears */
+    int tiles;
+} gs2d_fit_layout;
+int gs2d_fit_layout_for(int n, int cap, int img_h, int img_w, gs2d_fit_layout* out);
+int gs2d_fit_init(int n, int cap, int img_h, int img_w, void* work, size_t work_bytes, float* adan_state,
+                  gs2d_stream_t stream);
+int gs2d_fit_step(int n, int cap, int img_h, int img_w, float* xyz_raw, float* chol_raw, float* features,
+                  float* adan_state, const void* target, int target_format, void* work, size_t work_bytes, int step,
+                  float lr, float beta1, float beta2, float beta3, float eps, float weight_decay, float* out_img,
+                  float* param_grads_out, int32_t* ids_sorted_out, gs2d_stream_t stream);
+/* Render-only (decode): project_gaussians_2d + rasterize_gaussians_sum forward of the reference
+ * (GaussianSplats_Represent.py:83-90) as three kernels, sync-free.  activate != 0: inputs are
+ * the raw parameters (tanh / bound applied here); else means2d / L_elements as the projection
+ * API takes them.  opacities may be NULL (= 1).  out_img fp32: planar [3][H][W] when out_chw,
+ * else [H][W][3]; clamped to [0,1] when out_clamp.  final_idx [H][W] and ids_sorted_out may be
+ * NULL.  work as above (gs2d_fit_init first; the Adan pointer may be NULL there). */
+int gs2d_render_chol(int n, int cap, int img_h, int img_w, const float* means_or_xyz_raw, const float* chol,
+                     const float* colors, const float* opacities, int activate, void* work, size_t work_bytes,
+                     float* out_img, int out_chw, int out_clamp, int32_t* final_idx, int32_t* ids_sorted_out,
+                     gs2d_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif
