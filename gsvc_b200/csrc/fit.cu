@@ -77,49 +77,79 @@ k_fit_count(int n, const float* __restrict__ xyz_raw, const float* __restrict__ 
     if (!s_last) return;
     __threadfence();
     // exclusive scan of tile_count over all tiles by this one block; counts are re-zeroed so the
-    // scatter kernel can use the same array as its per-tile fill counters
+    // scatter kernel can use the same array as its per-tile fill counters.  Each thread owns 32
+    // consecutive tiles per pass and keeps them in registers: eight 16-byte loads in flight at
+    // once (one L2 round trip per 8192 tiles instead of one per tile).
     const int tiles = tx * ty;
-    const int per = (tiles + kFitThreads - 1) / kFitThreads;
-    const int beg = min(threadIdx.x * per, tiles), end = min(beg + per, tiles);
-    int sum = 0, mx = 0;
-    for (int t = beg; t < end; ++t) {
-        const int c = __ldcg(&tile_count[t]);
-        sum += c;
-        mx = max(mx, c);
-    }
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    int incl = sum;
+    int carry = 0, mx = 0;
+    for (int base = 0; base < tiles; base += kFitThreads * 32) {
+        const int t0 = base + threadIdx.x * 32;
+        int v[32];
 #pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-        const int v = __shfl_up_sync(0xffffffffu, incl, o);
-        if (lane >= o) incl += v;
+        for (int k = 0; k < 8; ++k) {
+            const int t = t0 + 4 * k;
+            if (t + 3 < tiles) {
+                const int4 q = __ldcg(reinterpret_cast<const int4*>(tile_count + t));
+                v[4 * k] = q.x; v[4 * k + 1] = q.y; v[4 * k + 2] = q.z; v[4 * k + 3] = q.w;
+            } else {
+#pragma unroll
+                for (int j = 0; j < 4; ++j) v[4 * k + j] = (t + j < tiles) ? __ldcg(tile_count + t + j) : 0;
+            }
+        }
+        int sum = 0;
+#pragma unroll
+        for (int j = 0; j < 32; ++j) {
+            const int c = v[j];
+            mx = max(mx, c);
+            v[j] = sum;      // exclusive within the thread
+            sum += c;
+        }
+        int incl = sum;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int u = __shfl_up_sync(0xffffffffu, incl, o);
+            if (lane >= o) incl += u;
+        }
+        __syncthreads();   // sh is reused across passes
+        if (lane == 31) sh[warp] = incl;
+        __syncthreads();
+        int wexcl = 0, total = 0;
+#pragma unroll
+        for (int w = 0; w < kFitThreads / 32; ++w) {
+            const int x = sh[w];
+            if (w < warp) wexcl += x;
+            total += x;
+        }
+        const int excl = carry + wexcl + incl - sum;
+        const int4 z = make_int4(0, 0, 0, 0);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+            const int t = t0 + 4 * k;
+            if (t + 3 < tiles) {
+                *reinterpret_cast<int4*>(tile_off + t) =
+                    make_int4(excl + v[4 * k], excl + v[4 * k + 1], excl + v[4 * k + 2], excl + v[4 * k + 3]);
+                *reinterpret_cast<int4*>(tile_count + t) = z;
+            } else {
+#pragma unroll
+                for (int j = 0; j < 4; ++j)
+                    if (t + j < tiles) { tile_off[t + j] = excl + v[4 * k + j]; tile_count[t + j] = 0; }
+            }
+        }
+        carry += total;
     }
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) mx = max(mx, __shfl_xor_sync(0xffffffffu, mx, o));
-    if (lane == 31) sh[warp] = incl;
-    __syncthreads();
-    int wexcl = 0, total = 0;
-    for (int w = 0; w < kFitThreads / 32; ++w) {
-        if (w < warp) wexcl += sh[w];
-        total += sh[w];
-    }
-    int run = wexcl + incl - sum;
-    for (int t = beg; t < end; ++t) {
-        const int c = __ldcg(&tile_count[t]);
-        tile_off[t] = run;
-        run += c;
-        tile_count[t] = 0;
-    }
     __syncthreads();
     if (lane == 0) sh[warp] = mx;
     __syncthreads();
     if (threadIdx.x == 0) {
         for (int w = 1; w < kFitThreads / 32; ++w) mx = max(mx, sh[w]);
-        tile_off[tiles] = total;
-        status[kStNumIntersects] = total;
+        tile_off[tiles] = carry;
+        status[kStNumIntersects] = carry;
         status[kStMaxPerTile] = mx;
         status[kStTicket] = 0;
-        if (total > cap && status[kStOverflow] == 0) status[kStOverflow] = step > 0 ? step : 1;
+        if (carry > cap && status[kStOverflow] == 0) status[kStOverflow] = step > 0 ? step : 1;
     }
 }
 
@@ -230,17 +260,19 @@ __device__ __forceinline__ int stage_tile_sorted(const float4* __restrict__ src,
 // GT: 0 = target is fp32 planar [3][H][W] (what torchvision's ToTensor / the reference's loader
 //         yields), 1 = uint8 interleaved [H][W][3] (raw frame; compared as value / 255)
 template <int MODE, int GT>
-__global__ void __launch_bounds__(GS2D_TILE_PIX)
+__global__ void __launch_bounds__(GS2D_TILE_PIX, 6)
 k_fit_tiles(int W, int H, int tx, const int32_t* __restrict__ tile_off, int32_t* tile_fill,
             const float4* __restrict__ packed, const void* __restrict__ gt, float grad_scale,
             float* __restrict__ grads, double* loss_acc, const int32_t* __restrict__ status,
             float* __restrict__ out_img, int out_chw, int out_clamp, int32_t* __restrict__ final_idx,
-            int32_t* __restrict__ ids_sorted_dbg) {
+            int32_t* __restrict__ ids_sorted_dbg, int want_opacity_grad) {
     __shared__ float4 sq[GS2D_MAX_PER_TILE * 3];
-    __shared__ float4 sv[GS2D_TILE_PIX];
-    __shared__ int sid[kIdChunk];
+    __shared__ float4 sv[GS2D_TILE_PIX];          // v_out of the tile; before that, the id chunk of the slow path
     __shared__ uint8_t perm[GS2D_MAX_PER_TILE];
     __shared__ float sred[GS2D_TILE_PIX / 32];
+    __shared__ float s_u8[(MODE == 0 && GT == 1) ? 256 : 1];
+    int* sid = reinterpret_cast<int*>(sv);
+    static_assert(sizeof(float4) * GS2D_TILE_PIX >= sizeof(int) * kIdChunk, "id chunk must fit in sv");
     if (status[kStOverflow] != 0) return;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int t = blockIdx.y * tx + blockIdx.x;
@@ -252,6 +284,8 @@ k_fit_tiles(int W, int H, int tx, const int32_t* __restrict__ tile_off, int32_t*
     const bool inside = px_i < W && py_i < H;
     const size_t pid = (size_t)py_i * W + px_i;
     float3 tgt = make_float3(0.f, 0.f, 0.f);
+    uint32_t tgt_u8 = 0;
+    if (MODE == 0 && GT == 1) s_u8[tid] = (float)tid / 255.f;   // exact value / 255 (IEEE division), once per tile
     if (MODE == 0 && inside) {   // issued before the batch arrives: independent loads
         if (GT == 0) {
             const float* g = (const float*)gt;
@@ -259,7 +293,7 @@ k_fit_tiles(int W, int H, int tx, const int32_t* __restrict__ tile_off, int32_t*
             tgt = make_float3(__ldg(g + pid), __ldg(g + plane + pid), __ldg(g + 2 * plane + pid));
         } else {
             const uint8_t* g = (const uint8_t*)gt + 3 * pid;
-            tgt = make_float3((float)g[0] / 255.f, (float)g[1] / 255.f, (float)g[2] / 255.f);
+            tgt_u8 = (uint32_t)__ldg(g) | ((uint32_t)__ldg(g + 1) << 8) | ((uint32_t)__ldg(g + 2) << 16);
         }
     }
 
@@ -317,6 +351,7 @@ k_fit_tiles(int W, int H, int tx, const int32_t* __restrict__ tile_off, int32_t*
     // ---- clamp + L2 loss and its gradient w.r.t. the unclamped sum --------------------------
     float l = 0.f;
     float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (GT == 1) tgt = make_float3(s_u8[tgt_u8 & 255u], s_u8[(tgt_u8 >> 8) & 255u], s_u8[(tgt_u8 >> 16) & 255u]);
     if (inside) {
         const float dxr = fminf(fmaxf(pix.x, 0.f), 1.f) - tgt.x;
         const float dyg = fminf(fmaxf(pix.y, 0.f), 1.f) - tgt.y;
@@ -327,9 +362,9 @@ k_fit_tiles(int W, int H, int tx, const int32_t* __restrict__ tile_off, int32_t*
         v.y = (pix.y >= 0.f && pix.y <= 1.f) ? grad_scale * dyg : 0.f;
         v.z = (pix.z >= 0.f && pix.z <= 1.f) ? grad_scale * dzb : 0.f;
     }
-    sv[tid] = v;
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) l += __shfl_xor_sync(0xffffffffu, l, o);
+    sv[tid] = v;   // (the id chunk of the slow path that aliases sv is dead since stage_tile_sorted's last barrier)
     if (lane == 0) sred[warp] = l;
     __syncthreads();
     if (tid == 0) {
@@ -376,14 +411,13 @@ k_fit_tiles(int W, int H, int tx, const int32_t* __restrict__ tile_off, int32_t*
             acc_op += vis * v_alpha;                                          // v_opacity :833
         }
         const float tot = warp_reduce8_t(acc, lane);
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) acc_op += __shfl_xor_sync(0xffffffffu, acc_op, o);
         float* row = grads + (size_t)__float_as_int(q1.w) * 12;
-        if ((lane & 3) == 0) {
-            if (tot != 0.f) atomicAdd(row + (lane >> 2), tot);   // 8 lanes, 8 consecutive floats
-        } else if (lane == 1) {
-            if (acc_op != 0.f) atomicAdd(row + 8, acc_op);
+        if (want_opacity_grad) {   // the frame model keeps opacity fixed at 1: not needed by the fit step
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) acc_op += __shfl_xor_sync(0xffffffffu, acc_op, o);
+            if (lane == 1 && acc_op != 0.f) atomicAdd(row + 8, acc_op);
         }
+        if ((lane & 3) == 0 && tot != 0.f) atomicAdd(row + (lane >> 2), tot);   // 8 lanes, 8 consecutive floats
     }
 }
 
@@ -560,12 +594,12 @@ int gs2d_fit_step(int n, int cap, int img_h, int img_w, float* xyz_raw, float* c
             k_fit_tiles<0, 0><<<grid, GS2D_TILE_PIX, 0, s>>>(
                 img_w, img_h, tx, (const int32_t*)(w + L.off_tile_off), (int32_t*)(w + L.off_tile_count),
                 (const float4*)(w + L.off_packed), target, grad_scale, grads, loss + (step % GS2D_FIT_LOSS_SLOTS),
-                status, out_img, 1, 1, nullptr, ids_sorted_out);
+                status, out_img, 1, 1, nullptr, ids_sorted_out, 0);
         else
             k_fit_tiles<0, 1><<<grid, GS2D_TILE_PIX, 0, s>>>(
                 img_w, img_h, tx, (const int32_t*)(w + L.off_tile_off), (int32_t*)(w + L.off_tile_count),
                 (const float4*)(w + L.off_packed), target, grad_scale, grads, loss + (step % GS2D_FIT_LOSS_SLOTS),
-                status, out_img, 1, 1, nullptr, ids_sorted_out);
+                status, out_img, 1, 1, nullptr, ids_sorted_out, 0);
         GS2D_CHECK_LAUNCH("fit_tiles");
     }
     AdanHyper h;
@@ -606,7 +640,7 @@ int gs2d_render_chol(int n, int cap, int img_h, int img_w, const float* means_or
         k_fit_tiles<1, 0><<<dim3(tx, ty), GS2D_TILE_PIX, 0, s>>>(
             img_w, img_h, tx, (const int32_t*)(w + L.off_tile_off), (int32_t*)(w + L.off_tile_count),
             (const float4*)(w + L.off_packed), nullptr, 0.f, nullptr, nullptr, (const int32_t*)(w + L.off_status),
-            out_img, out_chw, out_clamp, final_idx, ids_sorted_out);
+            out_img, out_chw, out_clamp, final_idx, ids_sorted_out, 0);
         GS2D_CHECK_LAUNCH("render_tiles");
     }
     return GS2D_OK;
