@@ -1,4 +1,4 @@
-// fit.cu -- the fit iteration of one frame as four kernels, no host synchronisation, no
+// fit.cu -- the fit iteration of one frame as three (first: four) kernels, no host synchronisation, no
 // allocation, no memset:
 //
 //   k_fit_count    per Gaussian: tanh / Cholesky-bound activations, projection, one atomic per
@@ -15,8 +15,10 @@
 //                  (backward.cu:696-862) warp-per-Gaussian from shared memory: one 9-float
 //                  reduction per (Gaussian, tile) pair.
 //   k_fit_update   per Gaussian: projection backward (backward2d.cu:8-51, reference formula,
-//                  SURVEY Q12), tanh backward, Adan update of the 8 parameters, and re-zeroing
-//                  of the gradient row for the next iteration.
+//                  SURVEY Q12), tanh backward, Adan update of the 8 parameters, re-zeroing of the
+//                  gradient row, and -- with the updated parameters still in registers -- the
+//                  NEXT iteration's projection + tile count + scan, so a steady-state iteration
+//                  is three kernels (scatter, tiles, update) and k_fit_count runs only first.
 //
 // The same count/scatter/tile kernels without the loss and backward are the render-only path.
 #include "gs2d_internal.h"
@@ -38,6 +40,15 @@ __device__ __forceinline__ void cp_async_wait_all() {
     asm volatile("cp.async.commit_group;\ncp.async.wait_group 0;" ::: "memory");
 }
 
+// (float)v / 255.f for v in 0..255, correctly rounded, without the division: q = v * fl(1/255),
+// one FMA residual step (the recurrence is checked exhaustively against IEEE division in
+// tests/test_capi_cpu.py; the device result in tests/test_gpu_fit.py)
+__device__ __forceinline__ float u8_over_255(uint32_t v) {
+    const float x = (float)v, r = 0.0039215688593685626984f;
+    const float q = mulf(x, r);
+    return fmaf_(fmaf_(-q, 255.f, x), r, q);
+}
+
 // activations of the reference's frame model (GaussianSplats_Represent.py:56-70) + projection
 __device__ __forceinline__ void fit_project(int i, const float* __restrict__ xyz_raw, const float* __restrict__ chol_raw,
                                             int activate, float half_w, float half_h, int tx, int ty, Proj2d& p,
@@ -56,25 +67,22 @@ __device__ __forceinline__ void fit_project(int i, const float* __restrict__ xyz
 // ------------------------------------------------------------------------------------------
 // K1: count + (last block) scan of the per-tile counts
 // ------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(kFitThreads)
-k_fit_count(int n, const float* __restrict__ xyz_raw, const float* __restrict__ chol_raw, int activate, float half_w,
-            float half_h, int tx, int ty, int cap, int step, int32_t* tile_count, int32_t* __restrict__ tile_off,
-            int32_t* status) {
-    __shared__ int sh[8];
-    __shared__ int s_last;
-    const int i = blockIdx.x * kFitThreads + threadIdx.x;
-    if (i < n) {
-        Proj2d p; float2 m; float3 L;
-        fit_project(i, xyz_raw, chol_raw, activate, half_w, half_h, tx, ty, p, m, L);
-        if (p.nth > 0)
-            for (int y = p.y0; y < p.y1; ++y)
-                for (int x = p.x0; x < p.x1; ++x) atomicAdd(&tile_count[y * tx + x], 1);
-    }
+__device__ __forceinline__ void count_tiles(const Proj2d& p, int tx, int32_t* tile_count) {
+    if (p.nth > 0)
+        for (int y = p.y0; y < p.y1; ++y)
+            for (int x = p.x0; x < p.x1; ++x) atomicAdd(&tile_count[y * tx + x], 1);
+}
+
+// Called by every thread of every block after its count_tiles(): the last block to arrive turns
+// the per-tile counts into tile ranges.  sh: 8 ints, s_last: 1 int of shared memory.
+__device__ __forceinline__ void scan_tiles_by_last_block(int tx, int ty, int cap, int step, int32_t* tile_count,
+                                                         int32_t* __restrict__ tile_off, int32_t* status, int* sh,
+                                                         int* s_last) {
     __threadfence();
     __syncthreads();
-    if (threadIdx.x == 0) s_last = (atomicAdd(&status[kStTicket], 1) == (int)gridDim.x - 1);
+    if (threadIdx.x == 0) *s_last = (atomicAdd(&status[kStTicket], 1) == (int)gridDim.x - 1);
     __syncthreads();
-    if (!s_last) return;
+    if (!*s_last) return;
     __threadfence();
     // exclusive scan of tile_count over all tiles by this one block; counts are re-zeroed so the
     // scatter kernel can use the same array as its per-tile fill counters.  Each thread owns 32
@@ -153,6 +161,21 @@ k_fit_count(int n, const float* __restrict__ xyz_raw, const float* __restrict__ 
     }
 }
 
+__global__ void __launch_bounds__(kFitThreads)
+k_fit_count(int n, const float* __restrict__ xyz_raw, const float* __restrict__ chol_raw, int activate, float half_w,
+            float half_h, int tx, int ty, int cap, int step, int32_t* tile_count, int32_t* __restrict__ tile_off,
+            int32_t* status) {
+    __shared__ int sh[8];
+    __shared__ int s_last;
+    const int i = blockIdx.x * kFitThreads + threadIdx.x;
+    if (i < n) {
+        Proj2d p; float2 m; float3 L;
+        fit_project(i, xyz_raw, chol_raw, activate, half_w, half_h, tx, ty, p, m, L);
+        count_tiles(p, tx, tile_count);
+    }
+    scan_tiles_by_last_block(tx, ty, cap, step, tile_count, tile_off, status, sh, &s_last);
+}
+
 // ------------------------------------------------------------------------------------------
 // K2: scatter the packed records into their tiles' ranges
 // packed[pos] = { x, y, conic.x, conic.y | conic.z, opacity, rect, gaussian id | r, g, b, tile }
@@ -185,50 +208,34 @@ k_fit_scatter(int n, const float* __restrict__ xyz_raw, const float* __restrict_
 // ------------------------------------------------------------------------------------------
 // K3: the tile kernel
 // ------------------------------------------------------------------------------------------
-// Sum 8 per-lane values over the warp with 9 shuffles: the total of v[j] ends up in the lanes
-// with (lane >> 2) == j.
-__device__ __forceinline__ float warp_reduce8_t(float (&v)[8], int lane) {
-    const bool b4 = lane & 16, b3 = lane & 8, b2 = lane & 4;
-    float w[4];
-#pragma unroll
-    for (int k = 0; k < 4; ++k) {
-        const float send = b4 ? v[k] : v[4 + k];
-        const float keep = b4 ? v[4 + k] : v[k];
-        w[k] = keep + __shfl_xor_sync(0xffffffffu, send, 16);
-    }
-    float u[2];
-#pragma unroll
-    for (int k = 0; k < 2; ++k) {
-        const float send = b3 ? w[k] : w[2 + k];
-        const float keep = b3 ? w[2 + k] : w[k];
-        u[k] = keep + __shfl_xor_sync(0xffffffffu, send, 8);
-    }
-    const float send = b2 ? u[0] : u[1];
-    const float keep = b2 ? u[1] : u[0];
-    float r = keep + __shfl_xor_sync(0xffffffffu, send, 4);
-    r += __shfl_xor_sync(0xffffffffu, r, 2);
-    r += __shfl_xor_sync(0xffffffffu, r, 1);
-    return r;
-}
-
 constexpr int kIdChunk = 1024;
 
-// Stage the tile's batch in ascending Gaussian-id order.  cnt <= 256: the whole range is copied
-// with cp.async and a rank permutation is built (perm[rank] = slot).  cnt > 256 (rare; the
-// reference then renders only the 256 lowest ids): ranks are computed against all cnt
-// ids in chunks and the 256 lowest-ranked records are copied straight into sorted position.
-__device__ __forceinline__ int stage_tile_sorted(const float4* __restrict__ src, int cnt, float4* sq, uint8_t* perm,
-                                                 int* sid, int tid) {
+// Stage the tile's batch into shared memory in ascending Gaussian-id order (the scatter wrote
+// the range in arbitrary order; ascending id is the order of the reference's stable sort on
+// tile id).  cnt <= 256: thread j keeps record j in registers, ranks its id
+// against the ids of the range (shared memory) and stores the record at its rank.
+// cnt > 256 (rare; the reference then renders only the 256 lowest ids): ranks are
+// computed against all cnt ids in chunks and the 256 lowest-ranked records are kept.
+__device__ __forceinline__ int stage_tile_sorted(const float4* __restrict__ src, int cnt, float4* sq, int* sid,
+                                                 int tid) {
     const int nb = min(cnt, GS2D_MAX_PER_TILE);
     if (cnt <= GS2D_MAX_PER_TILE) {
-        for (int i = tid; i < cnt * 3; i += GS2D_TILE_PIX) cp_async16(&sq[i], src + i);
-        cp_async_wait_all();
+        float4 r0, r1, r2;
+        int my = 0;
+        if (tid < cnt) {
+            r0 = __ldg(&src[3 * (size_t)tid + 0]);
+            r1 = __ldg(&src[3 * (size_t)tid + 1]);
+            r2 = __ldg(&src[3 * (size_t)tid + 2]);
+            my = __float_as_int(r1.w);
+            sid[tid] = my;
+        }
         __syncthreads();
         if (tid < cnt) {
-            const int my = __float_as_int(sq[3 * tid + 1].w);
             int rank = 0;
-            for (int j = 0; j < cnt; ++j) rank += (__float_as_int(sq[3 * j + 1].w) < my) ? 1 : 0;
-            perm[rank] = (uint8_t)tid;
+            for (int j = 0; j < cnt; ++j) rank += (sid[j] < my) ? 1 : 0;
+            sq[3 * rank + 0] = r0;
+            sq[3 * rank + 1] = r1;
+            sq[3 * rank + 2] = r2;
         }
         __syncthreads();
     } else {
@@ -249,10 +256,32 @@ __device__ __forceinline__ int stage_tile_sorted(const float4* __restrict__ src,
                 sq[3 * rank + 2] = __ldg(&src[3 * (size_t)j + 2]);
             }
         }
-        perm[tid] = (uint8_t)tid;
         __syncthreads();
     }
     return nb;
+}
+
+// Sum 8 per-lane values over each group of 8 consecutive lanes with 7 shuffles: lane l of a
+// group ends up with the group's total of v[l].
+__device__ __forceinline__ float group8_reduce8_t(float (&v)[8], int lane) {
+    const bool b2 = lane & 4, b1 = lane & 2, b0 = lane & 1;
+    float w[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        const float send = b2 ? v[k] : v[4 + k];
+        const float keep = b2 ? v[4 + k] : v[k];
+        w[k] = keep + __shfl_xor_sync(0xffffffffu, send, 4);
+    }
+    float u[2];
+#pragma unroll
+    for (int k = 0; k < 2; ++k) {
+        const float send = b1 ? w[k] : w[2 + k];
+        const float keep = b1 ? w[2 + k] : w[k];
+        u[k] = keep + __shfl_xor_sync(0xffffffffu, send, 2);
+    }
+    const float send = b0 ? u[0] : u[1];
+    const float keep = b0 ? u[1] : u[0];
+    return keep + __shfl_xor_sync(0xffffffffu, send, 1);
 }
 
 // MODE 0: fit (loss + backward, no image written unless out_img != NULL)
@@ -268,9 +297,7 @@ k_fit_tiles(int W, int H, int tx, const int32_t* __restrict__ tile_off, int32_t*
             int32_t* __restrict__ ids_sorted_dbg, int want_opacity_grad) {
     __shared__ float4 sq[GS2D_MAX_PER_TILE * 3];
     __shared__ float4 sv[GS2D_TILE_PIX];          // v_out of the tile; before that, the id chunk of the slow path
-    __shared__ uint8_t perm[GS2D_MAX_PER_TILE];
     __shared__ float sred[GS2D_TILE_PIX / 32];
-    __shared__ float s_u8[(MODE == 0 && GT == 1) ? 256 : 1];
     int* sid = reinterpret_cast<int*>(sv);
     static_assert(sizeof(float4) * GS2D_TILE_PIX >= sizeof(int) * kIdChunk, "id chunk must fit in sv");
     if (status[kStOverflow] != 0) return;
@@ -285,7 +312,6 @@ k_fit_tiles(int W, int H, int tx, const int32_t* __restrict__ tile_off, int32_t*
     const size_t pid = (size_t)py_i * W + px_i;
     float3 tgt = make_float3(0.f, 0.f, 0.f);
     uint32_t tgt_u8 = 0;
-    if (MODE == 0 && GT == 1) s_u8[tid] = (float)tid / 255.f;   // exact value / 255 (IEEE division), once per tile
     if (MODE == 0 && inside) {   // issued before the batch arrives: independent loads
         if (GT == 0) {
             const float* g = (const float*)gt;
@@ -297,9 +323,9 @@ k_fit_tiles(int W, int H, int tx, const int32_t* __restrict__ tile_off, int32_t*
         }
     }
 
-    const int nb = stage_tile_sorted(packed + 3 * (size_t)lo, cnt, sq, perm, sid, tid);
+    const int nb = stage_tile_sorted(packed + 3 * (size_t)lo, cnt, sq, sid, tid);
     if (ids_sorted_dbg) {   // parity tests: the order the batch is rendered in
-        for (int r = tid; r < nb; r += GS2D_TILE_PIX) ids_sorted_dbg[lo + r] = __float_as_int(sq[3 * perm[r] + 1].w);
+        for (int r = tid; r < nb; r += GS2D_TILE_PIX) ids_sorted_dbg[lo + r] = __float_as_int(sq[3 * r + 1].w);
         for (int r = nb + tid; r < cnt; r += GS2D_TILE_PIX) ids_sorted_dbg[lo + r] = -1;
     }
 
@@ -312,15 +338,14 @@ k_fit_tiles(int W, int H, int tx, const int32_t* __restrict__ tile_off, int32_t*
         const int r_lane = c + lane;
         bool touch = false;
         if (r_lane < nb) {
-            const uint32_t rect = __float_as_uint(sq[3 * perm[r_lane] + 1].z);
+            const uint32_t rect = __float_as_uint(sq[3 * r_lane + 1].z);
             const int y0 = (rect >> 16) & 255, y1 = rect >> 24;
             touch = (y1 >= row_lo) && (y0 <= row_hi);
         }
         unsigned m = __ballot_sync(0xffffffffu, touch);
         while (m) {
-            const int r = c + __ffs(m) - 1;
+            const int k = c + __ffs(m) - 1;
             m &= m - 1;
-            const int k = perm[r];
             const float4 q0 = sq[3 * k];       // x, y, conic.x, conic.y
             const float4 q1 = sq[3 * k + 1];   // conic.z, opacity, rect, id
             const float dx = subf(q0.x, px), dy = subf(q0.y, py);
@@ -331,7 +356,7 @@ k_fit_tiles(int W, int H, int tx, const int32_t* __restrict__ tile_off, int32_t*
                 pix.x = fmaf_(alpha, q2.x, pix.x);
                 pix.y = fmaf_(alpha, q2.y, pix.y);
                 pix.z = fmaf_(alpha, q2.z, pix.z);
-                cur_idx = lo + r;
+                if (MODE == 1) cur_idx = lo + k;
             }
         }
     }
@@ -351,7 +376,7 @@ k_fit_tiles(int W, int H, int tx, const int32_t* __restrict__ tile_off, int32_t*
     // ---- clamp + L2 loss and its gradient w.r.t. the unclamped sum --------------------------
     float l = 0.f;
     float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-    if (GT == 1) tgt = make_float3(s_u8[tgt_u8 & 255u], s_u8[(tgt_u8 >> 8) & 255u], s_u8[(tgt_u8 >> 16) & 255u]);
+    if (GT == 1) tgt = make_float3(u8_over_255(tgt_u8 & 255u), u8_over_255((tgt_u8 >> 8) & 255u), u8_over_255((tgt_u8 >> 16) & 255u));
     if (inside) {
         const float dxr = fminf(fmaxf(pix.x, 0.f), 1.f) - tgt.x;
         const float dyg = fminf(fmaxf(pix.y, 0.f), 1.f) - tgt.y;
@@ -374,21 +399,29 @@ k_fit_tiles(int W, int H, int tx, const int32_t* __restrict__ tile_off, int32_t*
         if (s != 0.f) atomicAdd(loss_acc, (double)s);
     }
 
-    // ---- backward (backward.cu:783-859): one warp per (tile, Gaussian) pair -----------------
-    for (int r = warp; r < nb; r += GS2D_TILE_PIX / 32) {
-        const int k = perm[r];
+    // ---- backward (backward.cu:783-859): eight lanes per (tile, Gaussian) pair, four pairs per
+    // warp pass; lanes sweep the pair's rectangle, one 7-shuffle transposed reduction leaves the
+    // total of value l in lane l of the group, and one reduction instruction per pass adds the
+    // four pairs' 8 consecutive floats to their gradient rows.
+    const int sub = lane >> 3, l8 = lane & 7;
+    const int ox = blockIdx.x * GS2D_TILE, oy = blockIdx.y * GS2D_TILE;
+    for (int r0 = warp * 4; r0 < nb; r0 += (GS2D_TILE_PIX / 32) * 4) {
+        const int k = min(r0 + sub, nb - 1);
         const float4 q1 = sq[3 * k + 1];
         const uint32_t rect = __float_as_uint(q1.z);
         const int rx0 = rect & 255, rx1 = (rect >> 8) & 255, ry0 = (rect >> 16) & 255, ry1 = rect >> 24;
-        if (ry1 < ry0) continue;   // no pixel of this tile can pass
+        const int w = rx1 - rx0 + 1;
+        const int area = (r0 + sub < nb && ry1 >= ry0) ? w * (ry1 - ry0 + 1) : 0;
+        int max_area = max(area, __shfl_xor_sync(0xffffffffu, area, 8));
+        max_area = max(max_area, __shfl_xor_sync(0xffffffffu, max_area, 16));
+        if (max_area == 0) continue;   // no pixel of this tile can pass for any of the four
         const float4 q0 = sq[3 * k], q2 = sq[3 * k + 2];
         const float gx = q0.x, gy = q0.y, cx = q0.z, cy = q0.w, cz = q1.x, opac = q1.y;
-        const int ox = blockIdx.x * GS2D_TILE, oy = blockIdx.y * GS2D_TILE;
-        const int w = rx1 - rx0 + 1, area = w * (ry1 - ry0 + 1);
         const float inv_w = 1.f / (float)w;
         float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
         float acc_op = 0.f;
-        for (int p = lane; p < area; p += 32) {
+        for (int p = l8; p < max_area; p += 8) {
+            if (p >= area) continue;
             const int ry = (int)(((float)p + 0.5f) * inv_w);
             const int lxp = rx0 + (p - ry * w), lyp = ry0 + ry;
             const float dx = subf(gx, (float)(ox + lxp)), dy = subf(gy, (float)(oy + lyp));
@@ -410,14 +443,15 @@ k_fit_tiles(int W, int H, int tx, const int32_t* __restrict__ tile_off, int32_t*
             acc[7] += alpha * vo.z;
             acc_op += vis * v_alpha;                                          // v_opacity :833
         }
-        const float tot = warp_reduce8_t(acc, lane);
+        const float tot = group8_reduce8_t(acc, lane);
         float* row = grads + (size_t)__float_as_int(q1.w) * 12;
         if (want_opacity_grad) {   // the frame model keeps opacity fixed at 1: not needed by the fit step
-#pragma unroll
-            for (int o = 16; o > 0; o >>= 1) acc_op += __shfl_xor_sync(0xffffffffu, acc_op, o);
-            if (lane == 1 && acc_op != 0.f) atomicAdd(row + 8, acc_op);
+            acc_op += __shfl_xor_sync(0xffffffffu, acc_op, 4);
+            acc_op += __shfl_xor_sync(0xffffffffu, acc_op, 2);
+            acc_op += __shfl_xor_sync(0xffffffffu, acc_op, 1);
+            if (l8 == 0 && area > 0 && acc_op != 0.f) atomicAdd(row + 8, acc_op);
         }
-        if ((lane & 3) == 0 && tot != 0.f) atomicAdd(row + (lane >> 2), tot);   // 8 lanes, 8 consecutive floats
+        if (area > 0 && tot != 0.f) atomicAdd(row + l8, tot);   // 4 pairs x 8 consecutive floats
     }
 }
 
@@ -449,51 +483,62 @@ __device__ __forceinline__ float adan_one(float p, float g, float& m, float& nn,
 __global__ void __launch_bounds__(kFitThreads)
 k_fit_update(int n, float* __restrict__ xyz_raw, float* __restrict__ chol_raw, float* __restrict__ feat,
              float* __restrict__ adan, float* __restrict__ grads, float half_w, float half_h, int tx, int ty,
-             AdanHyper h, const int32_t* __restrict__ status, double* loss_next, float* __restrict__ grads_out) {
+             AdanHyper h, int32_t* status, double* loss_next, float* __restrict__ grads_out, int cap, int next_step,
+             int32_t* tile_count, int32_t* __restrict__ tile_off) {
+    __shared__ int sh[8];
+    __shared__ int s_last;
     if (status[kStOverflow] != 0) return;
     const int i = blockIdx.x * kFitThreads + threadIdx.x;
     if (i == 0 && loss_next) *loss_next = 0.0;
-    if (i >= n) return;
-    Proj2d p; float2 m; float3 L;
-    fit_project(i, xyz_raw, chol_raw, 1, half_w, half_h, tx, ty, p, m, L);
-    float4* grow = reinterpret_cast<float4*>(grads + (size_t)i * 12);
-    const float4 g0 = grow[0], g1 = grow[1], g2 = grow[2];   // v_xy(2) v_conic(3) v_rgb(3) v_opacity(1) pad(3)
-    const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
-    grow[0] = z; grow[1] = z; grow[2] = z;
-    float g[8] = {0.f, 0.f, 0.f, 0.f, 0.f, g1.y, g1.z, g1.w};   // xyz(2) chol(3) feat(3)
-    if (p.ok && (int)p.radius > 0) {   // backward2d.cu:23-25
-        const float3 vc = conic_vjp(p.conic, make_float3(g0.z, g0.w, g1.x));
-        const float3 vl = chol_vjp(L.x, L.y, L.z, vc);
-        const float vmx = g0.x * half_w, vmy = g0.y * half_h;            // backward2d.cu:48-49
-        g[0] = vmx * (1.f - m.x * m.x);                                   // d tanh
-        g[1] = vmy * (1.f - m.y * m.y);
-        g[2] = vl.x; g[3] = vl.y; g[4] = vl.z;
-    }
-    if (grads_out) {   // parity tests: the parameter gradients autograd would hand to the optimizer
+    if (i < n) {
+        Proj2d p; float2 m; float3 L;
+        fit_project(i, xyz_raw, chol_raw, 1, half_w, half_h, tx, ty, p, m, L);
+        float4* grow = reinterpret_cast<float4*>(grads + (size_t)i * 12);
+        const float4 g0 = grow[0], g1 = grow[1];   // v_xy(2) v_conic(3) v_rgb(3) | v_opacity(1) pad(3) unused here
+        const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
+        grow[0] = z; grow[1] = z; grow[2] = z;
+        float g[8] = {0.f, 0.f, 0.f, 0.f, 0.f, g1.y, g1.z, g1.w};   // xyz(2) chol(3) feat(3)
+        if (p.ok && (int)p.radius > 0) {   // backward2d.cu:23-25
+            const float3 vc = conic_vjp(p.conic, make_float3(g0.z, g0.w, g1.x));
+            const float3 vl = chol_vjp(L.x, L.y, L.z, vc);
+            const float vmx = g0.x * half_w, vmy = g0.y * half_h;            // backward2d.cu:48-49
+            g[0] = vmx * (1.f - m.x * m.x);                                   // d tanh
+            g[1] = vmy * (1.f - m.y * m.y);
+            g[2] = vl.x; g[3] = vl.y; g[4] = vl.z;
+        }
+        if (grads_out) {   // parity tests: the parameter gradients autograd would hand to the optimizer
 #pragma unroll
-        for (int k = 0; k < 8; ++k) grads_out[(size_t)i * 8 + k] = g[k];
-    }
-    float par[8] = {xyz_raw[2 * i], xyz_raw[2 * i + 1], chol_raw[3 * i], chol_raw[3 * i + 1], chol_raw[3 * i + 2],
-                    feat[3 * i], feat[3 * i + 1], feat[3 * i + 2]};
-    const size_t plane = (size_t)n * 8;
-    float4* sm = reinterpret_cast<float4*>(adan + (size_t)i * 8);
-    float4* sn = reinterpret_cast<float4*>(adan + plane + (size_t)i * 8);
-    float4* sd = reinterpret_cast<float4*>(adan + 2 * plane + (size_t)i * 8);
-    float4* sp = reinterpret_cast<float4*>(adan + 3 * plane + (size_t)i * 8);
-    float am[8], an[8], ad[8], ap[8];
-    *reinterpret_cast<float4*>(am) = sm[0]; *reinterpret_cast<float4*>(am + 4) = sm[1];
-    *reinterpret_cast<float4*>(an) = sn[0]; *reinterpret_cast<float4*>(an + 4) = sn[1];
-    *reinterpret_cast<float4*>(ad) = sd[0]; *reinterpret_cast<float4*>(ad + 4) = sd[1];
-    *reinterpret_cast<float4*>(ap) = sp[0]; *reinterpret_cast<float4*>(ap + 4) = sp[1];
+            for (int k = 0; k < 8; ++k) grads_out[(size_t)i * 8 + k] = g[k];
+        }
+        float par[8] = {xyz_raw[2 * i], xyz_raw[2 * i + 1], chol_raw[3 * i], chol_raw[3 * i + 1], chol_raw[3 * i + 2],
+                        feat[3 * i], feat[3 * i + 1], feat[3 * i + 2]};
+        const size_t plane = (size_t)n * 8;
+        float4* sm = reinterpret_cast<float4*>(adan + (size_t)i * 8);
+        float4* sn = reinterpret_cast<float4*>(adan + plane + (size_t)i * 8);
+        float4* sd = reinterpret_cast<float4*>(adan + 2 * plane + (size_t)i * 8);
+        float4* sp = reinterpret_cast<float4*>(adan + 3 * plane + (size_t)i * 8);
+        float am[8], an[8], ad[8], ap[8];
+        *reinterpret_cast<float4*>(am) = sm[0]; *reinterpret_cast<float4*>(am + 4) = sm[1];
+        *reinterpret_cast<float4*>(an) = sn[0]; *reinterpret_cast<float4*>(an + 4) = sn[1];
+        *reinterpret_cast<float4*>(ad) = sd[0]; *reinterpret_cast<float4*>(ad + 4) = sd[1];
+        *reinterpret_cast<float4*>(ap) = sp[0]; *reinterpret_cast<float4*>(ap + 4) = sp[1];
 #pragma unroll
-    for (int k = 0; k < 8; ++k) par[k] = adan_one(par[k], g[k], am[k], an[k], ad[k], ap[k], h);
-    sm[0] = *reinterpret_cast<float4*>(am); sm[1] = *reinterpret_cast<float4*>(am + 4);
-    sn[0] = *reinterpret_cast<float4*>(an); sn[1] = *reinterpret_cast<float4*>(an + 4);
-    sd[0] = *reinterpret_cast<float4*>(ad); sd[1] = *reinterpret_cast<float4*>(ad + 4);
-    sp[0] = *reinterpret_cast<float4*>(ap); sp[1] = *reinterpret_cast<float4*>(ap + 4);
-    xyz_raw[2 * i] = par[0]; xyz_raw[2 * i + 1] = par[1];
-    chol_raw[3 * i] = par[2]; chol_raw[3 * i + 1] = par[3]; chol_raw[3 * i + 2] = par[4];
-    feat[3 * i] = par[5]; feat[3 * i + 1] = par[6]; feat[3 * i + 2] = par[7];
+        for (int k = 0; k < 8; ++k) par[k] = adan_one(par[k], g[k], am[k], an[k], ad[k], ap[k], h);
+        sm[0] = *reinterpret_cast<float4*>(am); sm[1] = *reinterpret_cast<float4*>(am + 4);
+        sn[0] = *reinterpret_cast<float4*>(an); sn[1] = *reinterpret_cast<float4*>(an + 4);
+        sd[0] = *reinterpret_cast<float4*>(ad); sd[1] = *reinterpret_cast<float4*>(ad + 4);
+        sp[0] = *reinterpret_cast<float4*>(ap); sp[1] = *reinterpret_cast<float4*>(ap + 4);
+        xyz_raw[2 * i] = par[0]; xyz_raw[2 * i + 1] = par[1];
+        chol_raw[3 * i] = par[2]; chol_raw[3 * i + 1] = par[3]; chol_raw[3 * i + 2] = par[4];
+        feat[3 * i] = par[5]; feat[3 * i + 1] = par[6]; feat[3 * i + 2] = par[7];
+        // the next iteration's binning starts here: project the updated parameters and count tiles
+        // (same arithmetic as k_fit_count / k_fit_scatter, so the ranges match what scatter fills)
+        Proj2d pn;
+        project_chol(tanhf(par[0]), tanhf(par[1]), addf(par[2], 0.5f), addf(par[3], 0.f), addf(par[4], 0.5f), half_w,
+                     half_h, tx, ty, pn);
+        count_tiles(pn, tx, tile_count);
+    }
+    scan_tiles_by_last_block(tx, ty, cap, next_step, tile_count, tile_off, status, sh, &s_last);
 }
 
 static inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
@@ -542,14 +587,15 @@ int gs2d_fit_init(int n, int cap, int img_h, int img_w, void* work, size_t work_
 }
 
 static int launch_bin(int n, const float* xyz, const float* chol, const float* feat, const float* opac, int activate,
-                      int img_h, int img_w, int cap, int step, const gs2d_fit_layout& L, char* w, cudaStream_t s) {
+                      int img_h, int img_w, int cap, int step, const gs2d_fit_layout& L, char* w, cudaStream_t s,
+                      bool precounted = false) {
     const int tx = div_up(img_w, GS2D_TILE), ty = div_up(img_h, GS2D_TILE);
     const float half_w = 0.5f * (float)(unsigned)img_w, half_h = 0.5f * (float)(unsigned)img_h;
     int32_t* status = (int32_t*)(w + L.off_status);
     int32_t* tile_count = (int32_t*)(w + L.off_tile_count);
     int32_t* tile_off = (int32_t*)(w + L.off_tile_off);
     const int blocks = div_up(n > 0 ? n : 1, kFitThreads);
-    {
+    if (!precounted) {
         ProfScope ps_(GS2D_STAGE_SCAN_MAP, s);
         k_fit_count<<<blocks, kFitThreads, 0, s>>>(n, xyz, chol, activate, half_w, half_h, tx, ty, cap, step,
                                                    tile_count, tile_off, status);
@@ -567,8 +613,8 @@ static int launch_bin(int n, const float* xyz, const float* chol, const float* f
 
 int gs2d_fit_step(int n, int cap, int img_h, int img_w, float* xyz_raw, float* chol_raw, float* features,
                   float* adan_state, const void* target, int target_format, void* work, size_t work_bytes, int step,
-                  float lr, float beta1, float beta2, float beta3, float eps, float weight_decay, float* out_img,
-                  float* param_grads_out, int32_t* ids_sorted_out, gs2d_stream_t stream) {
+                  float lr, float beta1, float beta2, float beta3, float eps, float weight_decay, int precounted,
+                  float* out_img, float* param_grads_out, int32_t* ids_sorted_out, gs2d_stream_t stream) {
     gs2d_fit_layout L;
     int rc = fit_layout(n, cap, img_h, img_w, &L);
     if (rc != GS2D_OK) return rc;
@@ -581,7 +627,7 @@ int gs2d_fit_step(int n, int cap, int img_h, int img_w, float* xyz_raw, float* c
     char* w = (char*)work;
     const int tx = div_up(img_w, GS2D_TILE), ty = div_up(img_h, GS2D_TILE);
     const float half_w = 0.5f * (float)(unsigned)img_w, half_h = 0.5f * (float)(unsigned)img_h;
-    rc = launch_bin(n, xyz_raw, chol_raw, features, nullptr, 1, img_h, img_w, cap, step, L, w, s);
+    rc = launch_bin(n, xyz_raw, chol_raw, features, nullptr, 1, img_h, img_w, cap, step, L, w, s, precounted != 0);
     if (rc != GS2D_OK) return rc;
     int32_t* status = (int32_t*)(w + L.off_status);
     double* loss = (double*)(w + L.off_loss);
@@ -614,7 +660,8 @@ int gs2d_fit_step(int n, int cap, int img_h, int img_w, float* xyz_raw, float* c
         ProfScope ps_(GS2D_STAGE_ADAN, s);
         k_fit_update<<<div_up(n, kFitThreads), kFitThreads, 0, s>>>(
             n, xyz_raw, chol_raw, features, adan_state, grads, half_w, half_h, tx, ty, h, status,
-            loss + ((step + 1) % GS2D_FIT_LOSS_SLOTS), param_grads_out);
+            loss + ((step + 1) % GS2D_FIT_LOSS_SLOTS), param_grads_out, cap, step + 1,
+            (int32_t*)(w + L.off_tile_count), (int32_t*)(w + L.off_tile_off));
         GS2D_CHECK_LAUNCH("fit_update");
     }
     return GS2D_OK;

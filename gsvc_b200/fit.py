@@ -124,6 +124,7 @@ class FusedFrameFit(torch.nn.Module):
         self._status = self.work[lay.off_status:lay.off_status + 64].view(torch.int32)
         self._loss = self.work[lay.off_loss:lay.off_loss + 8 * self._lib.FIT_LOSS_SLOTS].view(torch.float64)
         self._render_img = None
+        self._counted_for = None   # nothing pre-counted in a fresh workspace
 
     def _target(self, gt: torch.Tensor):
         if gt.dtype == torch.uint8:
@@ -146,9 +147,19 @@ class FusedFrameFit(torch.nn.Module):
             self.n, self.cap, self.H, self.W, self._xyz.data_ptr(), self._cholesky.data_ptr(),
             self._features_dc.data_ptr(), self.adan_state.data_ptr(), gt.data_ptr(), fmt, self.work.data_ptr(),
             self.layout.total_bytes, self.step_index, self.current_lr(), b1, b2, b3, self.eps, self.weight_decay,
-            None if out_img is None else out_img.data_ptr(), None if grads_out is None else grads_out.data_ptr(),
+            1 if self._precount_valid() else 0, None if out_img is None else out_img.data_ptr(), None if grads_out is None else grads_out.data_ptr(),
             None if ids_out is None else ids_out.data_ptr(), torch.cuda.current_stream(self.device).cuda_stream),
             "fit_step")
+
+    def _versions(self):
+        return (self._xyz._version, self._cholesky._version, self._features_dc._version,
+                self._xyz.data_ptr(), self._cholesky.data_ptr(), self._features_dc.data_ptr())
+
+    def _precount_valid(self) -> bool:
+        """the previous step pre-counted the tiles of the parameters it wrote; that is still valid
+        unless someone modified the parameter tensors since (torch bumps ._version on in-place ops)"""
+        ok = self._counted_for == self._versions()
+        return ok
 
     def train_iters(self, gt_image: torch.Tensor, iters: int = 1, **dbg):
         gt, fmt = self._target(gt_image)
@@ -157,6 +168,7 @@ class FusedFrameFit(torch.nn.Module):
         with self._C._guard(self.device):
             for _ in range(int(iters)):
                 self._issue(gt, fmt, **dbg)
+                self._counted_for = self._versions()
 
     def status(self):
         """(num_intersects, overflow_step, max_per_tile) of the last issued step; synchronises"""

@@ -170,7 +170,7 @@ int gs2d_rasterize_sum_bwd_binned(int n, int num_intersects, const int32_t* gaus
  * (L = chol_raw + [0.5, 0, 0.5]), features [n,3] (colours; rgb_W = 1, opacity = 1).
  * gs2d_fit_step runs ONE iteration of GaussianVideo_frame.train_iter
  * (GaussianSplats_Represent.py:191-207: forward :83-90, L2 loss utils.py:21-26, backward,
- * Adan step optimizer.py:125-236 with the reference's defaults) as four kernels on `stream`
+ * Adan step optimizer.py:125-236 with the reference's defaults) as three or four kernels on `stream`
  * with no host synchronisation, no allocation and no memset: project+count+scan,
  * scatter-pack, tile kernel (rasterise forward + clamp/L2 + rasterise backward) and
  * projection-backward+Adan.  Everything lives in caller-owned memory:
@@ -179,6 +179,11 @@ int gs2d_rasterize_sum_bwd_binned(int n, int num_intersects, const int32_t* gaus
  *   adan_state  fp32 [4][n][8]: m, n, d, previous gradient of (xyz 2, chol 3, features 3);
  *   target      the frame to fit: GS2D_TARGET_F32_CHW fp32 planar [3][H][W] in [0,1], or
  *               GS2D_TARGET_U8_HWC uint8 interleaved [H][W][3] (compared as value / 255).
+ * precounted: every step ends by projecting the UPDATED parameters and counting/scanning their
+ * tiles, i.e. it pre-computes the next step's binning; pass precounted = 1 when the previous call
+ * on this workspace was gs2d_fit_step and neither the parameters nor the workspace were touched
+ * since (a steady-state iteration is then three kernels), 0 otherwise (first step, after loading
+ * parameters, after gs2d_render_chol on the same workspace): the count kernel then runs first.
  * step is 1-based (bias correction).  The step's loss SUM (sum of squared errors over 3*H*W
  * values, a double) accumulates in work + off_loss + 8 * (step % GS2D_FIT_LOSS_SLOTS); mean =
  * sum / (3*H*W).  status (int32[16] at off_status): [0] num_intersects of the last step,
@@ -208,8 +213,8 @@ int gs2d_fit_init(int n, int cap, int img_h, int img_w, void* work, size_t work_
                   gs2d_stream_t stream);
 int gs2d_fit_step(int n, int cap, int img_h, int img_w, float* xyz_raw, float* chol_raw, float* features,
                   float* adan_state, const void* target, int target_format, void* work, size_t work_bytes, int step,
-                  float lr, float beta1, float beta2, float beta3, float eps, float weight_decay, float* out_img,
-                  float* param_grads_out, int32_t* ids_sorted_out, gs2d_stream_t stream);
+                  float lr, float beta1, float beta2, float beta3, float eps, float weight_decay, int precounted,
+                  float* out_img, float* param_grads_out, int32_t* ids_sorted_out, gs2d_stream_t stream);
 /* Render-only (decode): project_gaussians_2d + rasterize_gaussians_sum forward of the reference
  * (GaussianSplats_Represent.py:83-90) as three kernels, sync-free.  activate != 0: inputs are
  * the raw parameters (tanh / bound applied here); else means2d / L_elements as the projection

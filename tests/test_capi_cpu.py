@@ -126,3 +126,19 @@ def test_synthetic_generator_matches_survey_statistics():
     assert r[2].min() >= 3 and r[2].max() <= 7
     gt = synth.target_frame(64, 96)
     assert gt.shape == (1, 3, 64, 96) and 0 <= gt.min() and gt.max() <= 1
+
+
+def test_u8_over_255_recurrence_is_exact():
+    """fit.cu:u8_over_255 replaces (float)v / 255.f by q = v*r, q + fma(-q, 255, v)*r with
+    r = fl(1/255); emulate the two FMAs in float64 (exact for these magnitudes) and compare with
+    IEEE float32 division for all 256 inputs"""
+    import numpy as np
+    v = np.arange(256, dtype=np.float32)
+    exact = v / np.float32(255)
+    r = np.float32(0.0039215688593685626984)
+    assert r == np.float32(1) / np.float32(255)
+    q = (v * r).astype(np.float32)
+    rem = (v.astype(np.float64) - q.astype(np.float64) * 255.0).astype(np.float32)
+    out = (q.astype(np.float64) + rem.astype(np.float64) * np.float64(r)).astype(np.float32)
+    assert np.array_equal(out, exact)
+    assert (q != exact).sum() > 0     # the plain reciprocal multiply alone is NOT exact

@@ -69,21 +69,12 @@ def test_first_step_grads_binning_loss_and_update(H, W, n):
     grads = torch.full((n, 8), float("nan"), device=cuda)
     ids = torch.full((fit.cap,), -7, dtype=torch.int32, device=cuda)
     fit.train_iters(gt.to(cuda), 1, grads_out=grads, ids_out=ids)
-    I, overflow, max_per_tile = fit.status()
-    assert overflow == 0
-    # binning: count, tile ranges and order inside every tile are bit-exact
-    assert I == r["num_intersects"]
-    lay = fit.layout
-    tiles = lay.tiles
-    off = fit.work[lay.off_tile_off:lay.off_tile_off + 4 * (tiles + 1)].view(torch.int32).cpu().numpy()
-    bins = r["tile_bins"][:tiles]
-    cnt = bins[:, 1] - bins[:, 0]
-    assert np.array_equal(off[1:] - off[:-1], cnt)
-    hit = cnt > 0
-    assert np.array_equal(off[:-1][hit], bins[hit, 0])
-    assert max_per_tile == cnt.max()
-    assert cnt.max() <= 256
+    assert fit.status()[1] == 0       # no overflow (status now describes the NEXT step's binning)
+    # binning of this step: the rendering order of every tile range is bit-exact (the tile ranges
+    # themselves are compared in test_render_matches_reference_kernels_and_oracle)
+    I = r["num_intersects"]
     assert np.array_equal(ids[:I].cpu().numpy(), r["gaussian_ids_sorted"])
+    assert (ids[I:] == -7).all()
     # loss and gradients
     loss = fit.loss()
     assert abs(loss - o_loss) <= 2e-6 * max(o_loss, 1e-12) + 1e-9, (loss, o_loss)
@@ -152,8 +143,8 @@ def test_more_than_256_per_tile_truncates_like_the_reference():
     grads = torch.empty((n, 8), device=cuda)
     ids = torch.full((fit.cap,), -7, dtype=torch.int32, device=cuda)
     fit.train_iters(gt.to(cuda), 1, grads_out=grads, ids_out=ids)
-    I, overflow, mpt = fit.status()
-    assert (I, overflow, mpt) == (r["num_intersects"], 0, cnt.max())
+    assert fit.status()[1] == 0
+    I = r["num_intersects"]
     got = ids[:I].cpu().numpy()
     exp = r["gaussian_ids_sorted"].copy()
     for t in range(tiles):                                   # entries past the first 256 are never rendered
@@ -198,12 +189,16 @@ def test_render_matches_reference_kernels_and_oracle(H, W, n, trained):
     torch.cuda.synchronize()
     I = rr["num_intersects"]
     st = work[lay.off_status:lay.off_status + 16].view(torch.int32).cpu()
-    assert (int(st[0]), int(st[1])) == (I, 0)
+    tiles = lay.tiles
+    bins = rr["tile_bins"][:tiles].cpu().numpy()
+    cnt = bins[:, 1] - bins[:, 0]
+    assert (int(st[0]), int(st[1]), int(st[3])) == (I, 0, int(cnt.max()))
+    off = work[lay.off_tile_off:lay.off_tile_off + 4 * (tiles + 1)].view(torch.int32).cpu().numpy()
+    assert np.array_equal(off[1:] - off[:-1], cnt)                 # tile ranges == the reference's tile_bins
+    assert np.array_equal(off[:-1][cnt > 0], bins[cnt > 0, 0])
     assert torch.equal(fidx, rr["final_idx"]), f"{(fidx != rr['final_idx']).sum().item()} final_idx pixels differ"
     assert (out - rr["out_img"]).abs().max().item() <= 1e-5
     exp = rr["gaussian_ids_sorted"].clone()
-    tiles = lay.tiles
-    bins = rr["tile_bins"][:tiles].cpu().numpy()
     for t in np.nonzero(bins[:, 1] - bins[:, 0] > 256)[0]:
         exp[bins[t, 0] + 256:bins[t, 1]] = -1
     assert torch.equal(ids[:I], exp)
@@ -246,3 +241,48 @@ def test_state_dict_round_trip_with_reference_names():
     sd = fit.state_dict()
     assert set(sd) == {"_xyz", "_cholesky", "_features_dc"}
     assert sd["_xyz"].shape == (n, 2) and sd["_cholesky"].shape == (n, 3) and sd["_features_dc"].shape == (n, 3)
+
+
+def test_in_place_parameter_edit_invalidates_the_precount():
+    """every step pre-counts the next step's tiles; editing the parameters from Python in between
+    must fall back to a fresh count (FusedFrameFit watches the tensors' version counters)"""
+    H, W, n = 128, 160, 2_000
+    init, gt, a = _setup(H, W, n, seed=21)
+    _, _, b = _setup(H, W, n, seed=21)
+    gtd = gt.to(cuda)
+    a.train_iters(gtd, 2)
+    b.train_iters(gtd, 2)
+    shift = torch.zeros_like(a._xyz)
+    shift[::2, 0] = 0.3                     # moves half of the Gaussians across tiles
+    a._xyz.data.add_(shift)                 # .data edits do not bump the version: tell the module
+    a._counted_for = None
+    with torch.no_grad():
+        b._xyz.add_(shift)                  # in-place edit: detected through ._version
+    ia = torch.full((a.cap,), -7, dtype=torch.int32, device=cuda)
+    ib = torch.full((b.cap,), -7, dtype=torch.int32, device=cuda)
+    a.train_iters(gtd, 1, ids_out=ia)
+    b.train_iters(gtd, 1, ids_out=ib)
+    assert torch.equal(ia, ib)
+    assert a.loss() == pytest.approx(b.loss(), rel=1e-6)
+    # and the order matches a fresh model holding the same parameters
+    c = FusedFrameFitFrom(b, H, W, n)
+    torch.cuda.synchronize()
+
+
+def FusedFrameFitFrom(src, H, W, n):
+    from gsvc_b200.fit import FusedFrameFit
+    return FusedFrameFit(H, W, n, cuda, init={"_xyz": src._xyz.detach().cpu(), "_cholesky": src._cholesky.detach().cpu(),
+                                              "_features_dc": src._features_dc.detach().cpu()})
+
+
+def test_u8_target_all_values_match_ieee_division():
+    """every uint8 value once per channel: the device's division-free value/255 must give the
+    same loss as the float target holding IEEE value/255 (double accumulation, order-free to 1e-12)"""
+    H, W, n = 16, 16, 64
+    init, _, fa = _setup(H, W, n, seed=2)
+    _, _, fb = _setup(H, W, n, seed=2)
+    vals = torch.arange(256, dtype=torch.uint8).view(16, 16, 1).expand(16, 16, 3).contiguous()
+    gt_f = (vals.float() / 255).permute(2, 0, 1).unsqueeze(0).contiguous()
+    fa.train_iters(gt_f.to(cuda), 1)
+    fb.train_iters(vals.to(cuda), 1)
+    assert fa.loss() == pytest.approx(fb.loss(), rel=1e-12)
