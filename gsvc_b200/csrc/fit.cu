@@ -344,19 +344,34 @@ k_fit_tiles(int W, int H, int tx, const int32_t* __restrict__ tile_off, int32_t*
         }
         unsigned m = __ballot_sync(0xffffffffu, touch);
         while (m) {
-            const int k = c + __ffs(m) - 1;
+            // two records per trip: two independent sigma / ex2 chains in flight (the second is
+            // a masked repeat of the first when only one is left); accumulation stays in order
+            const int ka = c + __ffs(m) - 1;
             m &= m - 1;
-            const float4 q0 = sq[3 * k];       // x, y, conic.x, conic.y
-            const float4 q1 = sq[3 * k + 1];   // conic.z, opacity, rect, id
-            const float dx = subf(q0.x, px), dy = subf(q0.y, py);
-            const float sigma = gauss_sigma(dx, dy, q0.z, q0.w, q1.x);
-            const float alpha = minf(mulf(q1.y, gauss_vis(sigma)), 1.f);
-            if (inside && gauss_pass(sigma, alpha)) {
-                const float4 q2 = sq[3 * k + 2];   // r, g, b, tile
-                pix.x = fmaf_(alpha, q2.x, pix.x);
-                pix.y = fmaf_(alpha, q2.y, pix.y);
-                pix.z = fmaf_(alpha, q2.z, pix.z);
-                if (MODE == 1) cur_idx = lo + k;
+            const bool two = m != 0;
+            const int kb = two ? c + __ffs(m) - 1 : ka;
+            m &= m - 1;
+            const float4 a0 = sq[3 * ka], a1 = sq[3 * ka + 1];   // x, y, conic.x, conic.y | conic.z, opacity, rect, id
+            const float4 b0 = sq[3 * kb], b1 = sq[3 * kb + 1];
+            const float dxa = subf(a0.x, px), dya = subf(a0.y, py);
+            const float dxb = subf(b0.x, px), dyb = subf(b0.y, py);
+            const float sa = gauss_sigma(dxa, dya, a0.z, a0.w, a1.x);
+            const float sb = gauss_sigma(dxb, dyb, b0.z, b0.w, b1.x);
+            const float alpha_a = minf(mulf(a1.y, gauss_vis(sa)), 1.f);
+            const float alpha_b = minf(mulf(b1.y, gauss_vis(sb)), 1.f);
+            if (inside && gauss_pass(sa, alpha_a)) {
+                const float4 q2 = sq[3 * ka + 2];   // r, g, b, tile
+                pix.x = fmaf_(alpha_a, q2.x, pix.x);
+                pix.y = fmaf_(alpha_a, q2.y, pix.y);
+                pix.z = fmaf_(alpha_a, q2.z, pix.z);
+                if (MODE == 1) cur_idx = lo + ka;
+            }
+            if (two && inside && gauss_pass(sb, alpha_b)) {
+                const float4 q2 = sq[3 * kb + 2];
+                pix.x = fmaf_(alpha_b, q2.x, pix.x);
+                pix.y = fmaf_(alpha_b, q2.y, pix.y);
+                pix.z = fmaf_(alpha_b, q2.z, pix.z);
+                if (MODE == 1) cur_idx = lo + kb;
             }
         }
     }
