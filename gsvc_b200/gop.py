@@ -1,0 +1,93 @@
+"""GOP-sharded fitting of a frame sequence across GPUs (BASELINE config 4).
+
+In the reference a keyframe resets the chain (`Trained_Model = None`,
+train_video_Represent.py:362-363) and every P-frame starts from the previous frame's Gaussians
+(:359-367), so keyframe-delimited GOPs are independent sequential chains.  One process per GPU
+(torchrun); rank r fits the GOPs `assign_gops` gives it with no data-path collective, and the
+per-frame parameter dicts (`_xyz`, `_cholesky`, `_features_dc` -- the reference's
+gmodels_state_dict entries, train_video_Represent.py:107-114,379) are gathered to rank 0 once at
+the end.  The reference itself is single-GPU (`cuda:0`); this module is new design, not a mirror.
+
+Prune / random-add inside a frame's fit (GaussianSplats_Represent.py:98-172) needs the learnable
+`rgb_W`, which the fused step does not carry yet: P-frames here start from the previous frame's
+Gaussians and keep their count (listed as "next" in DESIGN.md).
+"""
+from __future__ import annotations
+
+import math
+from typing import Callable, Dict, List, Optional, Sequence, Tuple
+
+import torch
+import torch.distributed as dist
+
+Gop = Tuple[int, int]   # [first frame, one past the last frame)
+
+
+def gops_from_keyframes(keyframes: Sequence[int], num_frames: int) -> List[Gop]:
+    """keyframes: sorted 0-based frame indices that start a GOP (frame 0 is always one)"""
+    ks = sorted(set(int(k) for k in keyframes if 0 <= int(k) < num_frames) | {0})
+    return [(a, b) for a, b in zip(ks, ks[1:] + [num_frames]) if b > a]
+
+
+def assign_gops(gops: Sequence[Gop], world: int, cost: Optional[Callable[[Gop], float]] = None) -> List[List[Gop]]:
+    """Longest-processing-time-first: GOPs sorted by cost (default: frame count, the keyframe
+    weighted by `cost`), each to the least-loaded rank; every rank's list is in frame order.
+    Deterministic, so every rank computes the same assignment without communication."""
+    cost = cost or (lambda g: float(g[1] - g[0]))
+    loads = [0.0] * world
+    out: List[List[Gop]] = [[] for _ in range(world)]
+    for g in sorted(gops, key=lambda g: (-cost(g), g[0])):
+        r = min(range(world), key=lambda i: (loads[i], i))
+        out[r].append(g)
+        loads[r] += cost(g)
+    for lst in out:
+        lst.sort()
+    return out
+
+
+def fit_gop(get_frame: Callable[[int], torch.Tensor], gop: Gop, make_fitter: Callable[[Optional[dict]], object],
+            iters_key: int, iters_pred: int, on_frame: Optional[Callable[[int, object], None]] = None) -> Dict[int, dict]:
+    """Fit one GOP: the keyframe from scratch (`make_fitter(None)`), every following frame from
+    the previous frame's parameters (`make_fitter(prev_state)`).  Returns frame -> {"state": the
+    three parameter tensors on the CPU, "psnr": float, "iters": int}."""
+    out: Dict[int, dict] = {}
+    prev = None
+    for f in range(gop[0], gop[1]):
+        fit = make_fitter(prev)
+        iters = iters_key if prev is None else iters_pred
+        gt = get_frame(f)
+        fit.train_iters(gt, iters)
+        loss = fit.loss()
+        prev = {k: v.detach().clone() for k, v in fit.state_dict().items()}
+        out[f] = {"state": {k: v.cpu() for k, v in prev.items()}, "psnr": 10 * math.log10(1.0 / max(loss, 1e-20)),
+                  "iters": iters}
+        if on_frame is not None:
+            on_frame(f, fit)
+    return out
+
+
+def fit_sequence(get_frame: Callable[[int], torch.Tensor], num_frames: int, keyframes: Sequence[int],
+                 make_fitter: Callable[[Optional[dict]], object], iters_key: int, iters_pred: int,
+                 group=None) -> Optional[Dict[int, dict]]:
+    """Every rank fits its share of the GOPs; rank 0 returns {frame: result} for the whole
+    sequence (other ranks return None).  Works without torch.distributed (one process)."""
+    distributed = dist.is_available() and dist.is_initialized()
+    world = dist.get_world_size(group) if distributed else 1
+    rank = dist.get_rank(group) if distributed else 0
+    gops = gops_from_keyframes(keyframes, num_frames)
+    # a keyframe costs iters_key, a predicted frame iters_pred
+    mine = assign_gops(gops, world, cost=lambda g: iters_key + (g[1] - g[0] - 1) * iters_pred)[rank]
+    local: Dict[int, dict] = {}
+    for g in mine:
+        local.update(fit_gop(get_frame, g, make_fitter, iters_key, iters_pred))
+    if not distributed:
+        return local
+    gathered = [None] * world if rank == 0 else None
+    dist.gather_object(local, gathered, dst=0, group=group)
+    if rank != 0:
+        return None
+    merged: Dict[int, dict] = {}
+    for part in gathered:
+        merged.update(part)
+    assert sorted(merged) == list(range(num_frames)), "GOP sharding lost or duplicated frames"
+    return merged

@@ -1,0 +1,115 @@
+"""CPU tests of the multi-GPU host logic (no GPU): GOP partitioning, and the N>1 path of
+gsvc_b200.gop.fit_sequence under a real world_size-2 `gloo` process group with a stand-in fitter
+(the sharding has no data-path collective: only the final gather is communication)."""
+import os
+import socket
+
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+from gsvc_b200 import gop
+
+
+def test_gops_from_keyframes():
+    assert gop.gops_from_keyframes([0, 30, 60, 90], 120) == [(0, 30), (30, 60), (60, 90), (90, 120)]
+    assert gop.gops_from_keyframes([30, 60], 100) == [(0, 30), (30, 60), (60, 100)]      # frame 0 always starts one
+    assert gop.gops_from_keyframes([0, 5, 5, 200], 10) == [(0, 5), (5, 10)]
+    assert gop.gops_from_keyframes([], 1) == [(0, 1)]
+
+
+@pytest.mark.parametrize("world", [1, 2, 4, 8])
+def test_assignment_is_a_balanced_partition(world):
+    gops = gop.gops_from_keyframes([0, 15, 30, 45, 60, 75, 90, 105], 120)
+    parts = gop.assign_gops(gops, world)
+    flat = sorted(g for p in parts for g in p)
+    assert flat == gops                                            # every GOP exactly once
+    loads = [sum(b - a for a, b in p) for p in parts]
+    assert max(loads) - min(loads) <= 15
+    assert gop.assign_gops(gops, world) == parts                   # deterministic: no communication needed
+    # uneven GOPs: longest-first keeps the spread below the longest GOP
+    uneven = gop.gops_from_keyframes([0, 3, 40, 44, 90], 120)
+    loads = [sum(b - a for a, b in p) for p in gop.assign_gops(uneven, min(world, 4))]
+    assert max(loads) - min(loads) <= 46
+
+
+class _FakeFit:
+    """stand-in with FusedFrameFit's surface: parameters drift by a fixed amount per iteration, so
+    the chain structure (key frame from scratch, predicted frames from the previous one) is visible"""
+
+    def __init__(self, prev):
+        base = torch.zeros(4, 2) if prev is None else prev["_xyz"]
+        self.p = {"_xyz": base.clone(), "_cholesky": torch.ones(4, 3), "_features_dc": torch.ones(4, 3)}
+        self.iters = 0
+
+    def train_iters(self, gt, iters):
+        self.p["_xyz"] += float(gt.mean()) * 0 + iters
+        self.iters += iters
+
+    def loss(self):
+        return 1.0 / (1.0 + self.iters)
+
+    def state_dict(self):
+        return self.p
+
+
+def _expected_xyz(frame, keyframes, ik, ip):
+    k = max(x for x in keyframes if x <= frame)
+    return ik + (frame - k) * ip
+
+
+def test_fit_sequence_single_process():
+    kf = [0, 4, 7]
+    out = gop.fit_sequence(lambda f: torch.full((3, 2, 2), float(f)), 10, kf, _FakeFit, 100, 10)
+    assert sorted(out) == list(range(10))
+    for f, r in out.items():
+        assert float(r["state"]["_xyz"][0, 0]) == _expected_xyz(f, kf, 100, 10)
+        assert r["iters"] == (100 if f in kf else 10)
+
+
+def _free_port():
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+def _worker(rank, world, port, q):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        kf = [0, 5, 9, 12]
+        seen = []
+        fitter = lambda prev: _FakeFit(prev)
+        get = lambda f: (seen.append(f), torch.full((3, 2, 2), float(f)))[1]
+        out = gop.fit_sequence(get, 16, kf, fitter, 50, 5)
+        q.put((rank, sorted(seen), None if out is None else {f: (float(r["state"]["_xyz"][0, 0]), r["iters"])
+                                                              for f, r in out.items()}))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_fit_sequence_world_size_2_gloo():
+    world = 2
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_worker, args=(r, world, port, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    res = {}
+    for _ in range(world):
+        rank, seen, out = q.get(timeout=120)
+        res[rank] = (seen, out)
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    # the two ranks touched disjoint frame sets that cover the sequence
+    assert sorted(res[0][0] + res[1][0]) == list(range(16))
+    assert not set(res[0][0]) & set(res[1][0])
+    assert res[1][1] is None                                   # only rank 0 returns the merged result
+    merged = res[0][1]
+    kf = [0, 5, 9, 12]
+    for f in range(16):
+        assert merged[f] == (_expected_xyz(f, kf, 50, 5), 50 if f in kf else 5)
