@@ -77,7 +77,7 @@ _SIGNATURES = {
     "gs2d_fit_layout_for": (c_int, [c_int, c_int, c_int, c_int, POINTER(FitLayout)]),
     "gs2d_fit_init": (c_int, [c_int, c_int, c_int, c_int, _P, c_size_t, _P, _P]),
     "gs2d_fit_step": (c_int, [c_int, c_int, c_int, c_int, _P, _P, _P, _P, _P, c_int, _P, c_size_t, c_int,
-                              c_float, c_float, c_float, c_float, c_float, c_float, c_int, _P, _P, _P, _P]),
+                              c_float, c_float, c_float, c_float, c_float, c_float, c_int, _P, _P, _P, _P, _P]),
     "gs2d_render_chol": (c_int, [c_int, c_int, c_int, c_int, _P, _P, _P, _P, c_int, _P, c_size_t, _P, c_int, c_int,
                                  _P, _P, _P]),
 }

@@ -498,12 +498,24 @@ __device__ __forceinline__ float adan_one(float p, float g, float& m, float& nn,
 __global__ void __launch_bounds__(kFitThreads)
 k_fit_update(int n, float* __restrict__ xyz_raw, float* __restrict__ chol_raw, float* __restrict__ feat,
              float* __restrict__ adan, float* __restrict__ grads, float half_w, float half_h, int tx, int ty,
-             AdanHyper h, int32_t* status, double* loss_next, float* __restrict__ grads_out, int cap, int next_step,
-             int32_t* tile_count, int32_t* __restrict__ tile_off) {
+             AdanHyper h, int32_t* status, const double* loss_this, double* loss_next,
+             float* __restrict__ grads_out, int cap, int next_step, int32_t* tile_count,
+             int32_t* __restrict__ tile_off, gs2d_fit_report* report_host) {
     __shared__ int sh[8];
     __shared__ int s_last;
-    if (status[kStOverflow] != 0) return;
     const int i = blockIdx.x * kFitThreads + threadIdx.x;
+    if (i == 0 && report_host) {
+        // the step's result straight into pinned host memory (no copy to issue, nothing to wait
+        // for but the kernel itself); written before the scan below replaces status[0]
+        report_host->loss_sum = *loss_this;
+        report_host->num_intersects = status[kStNumIntersects];
+        report_host->overflow_step = status[kStOverflow];
+        report_host->max_per_tile = status[kStMaxPerTile];
+        __threadfence_system();
+        report_host->step = next_step - 1;   // written last: the host treats it as the valid flag
+        __threadfence_system();
+    }
+    if (status[kStOverflow] != 0) return;
     if (i == 0 && loss_next) *loss_next = 0.0;
     if (i < n) {
         Proj2d p; float2 m; float3 L;
@@ -629,7 +641,8 @@ static int launch_bin(int n, const float* xyz, const float* chol, const float* f
 int gs2d_fit_step(int n, int cap, int img_h, int img_w, float* xyz_raw, float* chol_raw, float* features,
                   float* adan_state, const void* target, int target_format, void* work, size_t work_bytes, int step,
                   float lr, float beta1, float beta2, float beta3, float eps, float weight_decay, int precounted,
-                  float* out_img, float* param_grads_out, int32_t* ids_sorted_out, gs2d_stream_t stream) {
+                  float* out_img, float* param_grads_out, int32_t* ids_sorted_out, gs2d_fit_report* report_host,
+                  gs2d_stream_t stream) {
     gs2d_fit_layout L;
     int rc = fit_layout(n, cap, img_h, img_w, &L);
     if (rc != GS2D_OK) return rc;
@@ -675,8 +688,8 @@ int gs2d_fit_step(int n, int cap, int img_h, int img_w, float* xyz_raw, float* c
         ProfScope ps_(GS2D_STAGE_ADAN, s);
         k_fit_update<<<div_up(n, kFitThreads), kFitThreads, 0, s>>>(
             n, xyz_raw, chol_raw, features, adan_state, grads, half_w, half_h, tx, ty, h, status,
-            loss + ((step + 1) % GS2D_FIT_LOSS_SLOTS), param_grads_out, cap, step + 1,
-            (int32_t*)(w + L.off_tile_count), (int32_t*)(w + L.off_tile_off));
+            loss + (step % GS2D_FIT_LOSS_SLOTS), loss + ((step + 1) % GS2D_FIT_LOSS_SLOTS), param_grads_out, cap,
+            step + 1, (int32_t*)(w + L.off_tile_count), (int32_t*)(w + L.off_tile_off), report_host);
         GS2D_CHECK_LAUNCH("fit_update");
     }
     return GS2D_OK;

@@ -79,7 +79,7 @@ class FusedFrameFit(torch.nn.Module):
         .forward()               render [1,3,H,W] (clamped), sync-free
     gt: fp32 [1,3,H,W] / [3,H,W] in [0,1] (the reference loader's format) or uint8 [H,W,3]."""
 
-    path_name = "fused C-ABI fit step (count/scatter binning, tile kernel fwd+L2+bwd, projection-bwd+Adan): 4 kernels/iter"
+    path_name = "fused C-ABI fit step (scatter-pack, tile kernel fwd+L2+bwd, projection-bwd+Adan+next count/scan): 3 kernels/iter"
 
     def __init__(self, H: int, W: int, num_points: int, device, lr: float = 1e-3, seed: int = 1,
                  init: dict | None = None, betas=(0.98, 0.92, 0.99), eps: float = 1e-8, weight_decay: float = 0.0,
@@ -123,6 +123,12 @@ class FusedFrameFit(torch.nn.Module):
                                               adan_ptr, torch.cuda.current_stream(dev).cuda_stream), "fit_init")
         self._status = self.work[lay.off_status:lay.off_status + 64].view(torch.int32)
         self._loss = self.work[lay.off_loss:lay.off_loss + 8 * self._lib.FIT_LOSS_SLOTS].view(torch.float64)
+        # ring of gs2d_fit_report records (24 B each) in pinned host memory, written by the device
+        self._report = torch.zeros((self._lib.FIT_LOSS_SLOTS, 6), dtype=torch.int32).pin_memory()
+        self._report[:, 5] = -1
+        self._report_np = self._report.numpy()
+        self._report_f64 = self._report_np.view("float64")     # [slots, 3]; column 0 = loss_sum
+        self._report_ptr = self._report.data_ptr()
         self._render_img = None
         self._counted_for = None   # nothing pre-counted in a fresh workspace
 
@@ -143,13 +149,15 @@ class FusedFrameFit(torch.nn.Module):
         self.step_index += 1
         b1, b2, b3 = self.betas
         lib = self._lib.load()
+        slot = self.step_index % self._lib.FIT_LOSS_SLOTS
         self._lib.check(lib.gs2d_fit_step(
             self.n, self.cap, self.H, self.W, self._xyz.data_ptr(), self._cholesky.data_ptr(),
             self._features_dc.data_ptr(), self.adan_state.data_ptr(), gt.data_ptr(), fmt, self.work.data_ptr(),
             self.layout.total_bytes, self.step_index, self.current_lr(), b1, b2, b3, self.eps, self.weight_decay,
-            1 if self._precount_valid() else 0, None if out_img is None else out_img.data_ptr(), None if grads_out is None else grads_out.data_ptr(),
-            None if ids_out is None else ids_out.data_ptr(), torch.cuda.current_stream(self.device).cuda_stream),
-            "fit_step")
+            1 if self._precount_valid() else 0, None if out_img is None else out_img.data_ptr(),
+            None if grads_out is None else grads_out.data_ptr(), None if ids_out is None else ids_out.data_ptr(),
+            self._report_ptr + 24 * slot, torch.cuda.current_stream(self.device).cuda_stream), "fit_step")
+        self._counted_for = self._versions()
 
     def _versions(self):
         return (self._xyz._version, self._cholesky._version, self._features_dc._version,
@@ -158,8 +166,7 @@ class FusedFrameFit(torch.nn.Module):
     def _precount_valid(self) -> bool:
         """the previous step pre-counted the tiles of the parameters it wrote; that is still valid
         unless someone modified the parameter tensors since (torch bumps ._version on in-place ops)"""
-        ok = self._counted_for == self._versions()
-        return ok
+        return self._counted_for == self._versions()
 
     def train_iters(self, gt_image: torch.Tensor, iters: int = 1, **dbg):
         gt, fmt = self._target(gt_image)
@@ -168,27 +175,38 @@ class FusedFrameFit(torch.nn.Module):
         with self._C._guard(self.device):
             for _ in range(int(iters)):
                 self._issue(gt, fmt, **dbg)
-                self._counted_for = self._versions()
+
+    def _read_report(self, step: int):
+        """(loss_sum, num_intersects, overflow_step, max_per_tile) a step wrote into the pinned ring;
+        the caller has already waited for that step"""
+        slot = step % self._lib.FIT_LOSS_SLOTS
+        rec = self._report_np[slot]
+        if int(rec[5]) != step:
+            raise ValueError(f"step {step}: its report slot has been recycled (or the step has not finished)")
+        return float(self._report_f64[slot, 0]), int(rec[2]), int(rec[3]), int(rec[4])
 
     def status(self):
         """(num_intersects, overflow_step, max_per_tile) of the last issued step; synchronises"""
-        s = self._status.cpu()
-        return int(s[0]), int(s[1]), int(s[3])
+        torch.cuda.current_stream(self.device).synchronize()
+        if self.step_index == 0:
+            return 0, 0, 0
+        _, i, o, m = self._read_report(self.step_index)
+        return i, o, m
 
-    def loss(self, step: int | None = None) -> float:
-        """mean squared error of `step` (default: the last one); synchronises.  A step's slot
-        is recycled FIT_LOSS_SLOTS - 1 steps later."""
+    def loss(self, step: int | None = None, wait: bool = True) -> float:
+        """mean squared error of `step` (default: the last one).  The step's last kernel wrote it
+        into pinned host memory, so this only waits for the stream (wait=False: the caller already
+        did, e.g. on an event).  A step's slot is recycled FIT_LOSS_SLOTS steps later."""
         step = self.step_index if step is None else int(step)
-        if not (self.step_index - (self._lib.FIT_LOSS_SLOTS - 2) <= step <= self.step_index):
-            raise ValueError("that step's loss slot has been recycled")
-        both = torch.cat([self._loss[step % self._lib.FIT_LOSS_SLOTS].view(1),
-                          self._status[1].to(torch.float64).view(1)]).cpu()
-        if both[1] != 0:
-            self._recover(int(both[1]))
+        if wait:
+            torch.cuda.current_stream(self.device).synchronize()
+        loss_sum, _i, overflow, _m = self._read_report(step)
+        if overflow != 0:
+            self._recover(overflow)
             raise RuntimeError(
-                f"intersections exceeded the workspace capacity at step {int(both[1])}; the workspace was regrown "
+                f"intersections exceeded the workspace capacity at step {overflow}; the workspace was regrown "
                 f"to {self.cap} and the model rewound to step {self.step_index}: re-issue the remaining iterations")
-        return float(both[0]) / (3.0 * self.H * self.W)
+        return loss_sum / (3.0 * self.H * self.W)
 
     def _recover(self, overflow_step: int):
         # steps >= overflow_step were no-ops (parameters and optimizer state untouched)
@@ -200,6 +218,60 @@ class FusedFrameFit(torch.nn.Module):
         self.train_iters(gt_image, 1)
         loss = self.loss()
         return loss, 10 * math.log10(1.0 / loss)
+
+    def fit_stream(self, host_frames, prefetch: int = 2):
+        """One iteration per frame of `host_frames` (an iterable of pinned-host targets, uint8
+        [H,W,3] or fp32 [1,3,H,W]); yields (loss, psnr) of every step.  The copy of frame i+1 runs
+        on a side stream while step i computes (double-buffered device targets), and a step's loss
+        arrives in pinned memory with the step itself, so per step the host only waits on one event."""
+        dev = self.device
+        copy_stream = torch.cuda.Stream(device=dev)
+        main = torch.cuda.current_stream(dev)
+        bufs, copied, freed = [None] * prefetch, [None] * prefetch, [None] * prefetch
+        it = iter(host_frames)
+
+        def stage(j, frame):
+            b = j % prefetch
+            if bufs[b] is None or bufs[b].shape != frame.shape or bufs[b].dtype != frame.dtype:
+                bufs[b] = torch.empty(frame.shape, dtype=frame.dtype, device=dev)
+            with torch.cuda.stream(copy_stream):
+                if freed[b] is not None:
+                    copy_stream.wait_event(freed[b])       # the step that read this buffer is done
+                bufs[b].copy_(frame, non_blocking=True)
+                ev = torch.cuda.Event()
+                ev.record(copy_stream)
+            copied[b] = ev
+
+        pending = []
+        j = 0
+        for frame in it:
+            pending.append(frame)
+            stage(j, frame)
+            j += 1
+            if len(pending) >= prefetch:
+                break
+        i = 0
+        done_ev = torch.cuda.Event()
+        while pending:
+            pending.pop(0)
+            b = i % prefetch
+            main.wait_event(copied[b])
+            gt, fmt = self._target(bufs[b])
+            with self._C._guard(dev):
+                self._issue(gt, fmt)
+            step = self.step_index
+            fr = torch.cuda.Event()
+            fr.record(main)
+            freed[b] = fr
+            nxt = next(it, None)
+            if nxt is not None:                             # next frame's copy overlaps this step
+                pending.append(nxt)
+                stage(j, nxt)
+                j += 1
+            fr.synchronize()
+            loss = self.loss(step, wait=False)
+            yield loss, 10 * math.log10(1.0 / max(loss, 1e-20))
+            i += 1
 
     @property
     def last_num_intersects(self) -> int:

@@ -208,13 +208,25 @@ typedef struct {
     size_t zero_bytes;      /* [0, zero_bytes) is what gs2d_fit_init clears */
     int tiles;
 } gs2d_fit_layout;
+/* What a step reports, written by its last kernel straight into PINNED HOST memory when
+ * report_host != NULL (device-visible, e.g. cudaHostAlloc / torch pin_memory): the host learns
+ * the loss without issuing a copy -- it only has to wait for the step (event or stream sync) or
+ * poll `step`, which is written last. */
+typedef struct {
+    double loss_sum;         /* sum of squared errors over 3*H*W values */
+    int32_t num_intersects;  /* of this step */
+    int32_t overflow_step;   /* see status[1] */
+    int32_t max_per_tile;
+    int32_t step;            /* the step index this record belongs to */
+} gs2d_fit_report;
 int gs2d_fit_layout_for(int n, int cap, int img_h, int img_w, gs2d_fit_layout* out);
 int gs2d_fit_init(int n, int cap, int img_h, int img_w, void* work, size_t work_bytes, float* adan_state,
                   gs2d_stream_t stream);
 int gs2d_fit_step(int n, int cap, int img_h, int img_w, float* xyz_raw, float* chol_raw, float* features,
                   float* adan_state, const void* target, int target_format, void* work, size_t work_bytes, int step,
                   float lr, float beta1, float beta2, float beta3, float eps, float weight_decay, int precounted,
-                  float* out_img, float* param_grads_out, int32_t* ids_sorted_out, gs2d_stream_t stream);
+                  float* out_img, float* param_grads_out, int32_t* ids_sorted_out, gs2d_fit_report* report_host,
+                  gs2d_stream_t stream);
 /* Render-only (decode): project_gaussians_2d + rasterize_gaussians_sum forward of the reference
  * (GaussianSplats_Represent.py:83-90) as three kernels, sync-free.  activate != 0: inputs are
  * the raw parameters (tanh / bound applied here); else means2d / L_elements as the projection

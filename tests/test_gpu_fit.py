@@ -286,3 +286,20 @@ def test_u8_target_all_values_match_ieee_division():
     fa.train_iters(gt_f.to(cuda), 1)
     fb.train_iters(vals.to(cuda), 1)
     assert fa.loss() == pytest.approx(fb.loss(), rel=1e-12)
+
+
+def test_fit_stream_equals_resident_loop():
+    """pinned-host frames streamed with overlapped copies give the same losses as the resident loop"""
+    H, W, n, K = 128, 160, 2_000, 12
+    init, gt, a = _setup(H, W, n, seed=4)
+    _, _, b = _setup(H, W, n, seed=4)
+    u8 = (gt[0] * 255).round().to(torch.uint8).permute(1, 2, 0).contiguous()
+    frames = [((u8.int() + 3 * i) % 256).to(torch.uint8).pin_memory() for i in range(3)]   # three different frames
+    seq = [frames[i % 3] for i in range(K)]
+    la = [l for l, _ in a.fit_stream(seq)]
+    lb = []
+    for f in seq:
+        l, _ = b.train_iter(f.to(cuda))
+        lb.append(l)
+    np.testing.assert_allclose(la, lb, rtol=1e-5)
+    assert a.step_index == K
