@@ -48,6 +48,7 @@ class FitLayout(Structure):
 
 FIT_LOSS_SLOTS = 64
 TARGET_F32_CHW, TARGET_U8_HWC = 0, 1
+FIT_PHASE_GRADS, FIT_PHASE_UPDATE = 1, 2
 
 _P = c_void_p
 _SIGNATURES = {
@@ -78,6 +79,9 @@ _SIGNATURES = {
     "gs2d_fit_init": (c_int, [c_int, c_int, c_int, c_int, _P, c_size_t, _P, _P]),
     "gs2d_fit_step": (c_int, [c_int, c_int, c_int, c_int, _P, _P, _P, _P, _P, c_int, _P, c_size_t, c_int,
                               c_float, c_float, c_float, c_float, c_float, c_float, c_int, _P, _P, _P, _P, _P]),
+    "gs2d_fit_step_band": (c_int, [c_int, c_int, c_int, c_int, _P, _P, _P, _P, _P, c_int, _P, c_size_t, c_int,
+                                   c_float, c_float, c_float, c_float, c_float, c_float, c_int, c_int, c_int, c_int,
+                                   _P, _P, _P, _P, _P]),
     "gs2d_render_chol": (c_int, [c_int, c_int, c_int, c_int, _P, _P, _P, _P, c_int, _P, c_size_t, _P, c_int, c_int,
                                  _P, _P, _P]),
 }

@@ -67,9 +67,11 @@ __device__ __forceinline__ void fit_project(int i, const float* __restrict__ xyz
 // ------------------------------------------------------------------------------------------
 // K1: count + (last block) scan of the per-tile counts
 // ------------------------------------------------------------------------------------------
-__device__ __forceinline__ void count_tiles(const Proj2d& p, int tx, int32_t* tile_count) {
+// [row0, row1): the band of tile rows this rank rasterises (the whole frame unless the frame is
+// split across GPUs by tile rows, SURVEY 8e spatial mode)
+__device__ __forceinline__ void count_tiles(const Proj2d& p, int tx, int row0, int row1, int32_t* tile_count) {
     if (p.nth > 0)
-        for (int y = p.y0; y < p.y1; ++y)
+        for (int y = max(p.y0, row0); y < min(p.y1, row1); ++y)
             for (int x = p.x0; x < p.x1; ++x) atomicAdd(&tile_count[y * tx + x], 1);
 }
 
@@ -163,15 +165,15 @@ __device__ __forceinline__ void scan_tiles_by_last_block(int tx, int ty, int cap
 
 __global__ void __launch_bounds__(kFitThreads)
 k_fit_count(int n, const float* __restrict__ xyz_raw, const float* __restrict__ chol_raw, int activate, float half_w,
-            float half_h, int tx, int ty, int cap, int step, int32_t* tile_count, int32_t* __restrict__ tile_off,
-            int32_t* status) {
+            float half_h, int tx, int ty, int row0, int row1, int cap, int step, int32_t* tile_count,
+            int32_t* __restrict__ tile_off, int32_t* status) {
     __shared__ int sh[8];
     __shared__ int s_last;
     const int i = blockIdx.x * kFitThreads + threadIdx.x;
     if (i < n) {
         Proj2d p; float2 m; float3 L;
         fit_project(i, xyz_raw, chol_raw, activate, half_w, half_h, tx, ty, p, m, L);
-        count_tiles(p, tx, tile_count);
+        count_tiles(p, tx, row0, row1, tile_count);
     }
     scan_tiles_by_last_block(tx, ty, cap, step, tile_count, tile_off, status, sh, &s_last);
 }
@@ -183,8 +185,8 @@ k_fit_count(int n, const float* __restrict__ xyz_raw, const float* __restrict__ 
 __global__ void __launch_bounds__(kFitThreads)
 k_fit_scatter(int n, const float* __restrict__ xyz_raw, const float* __restrict__ chol_raw,
               const float* __restrict__ feat, const float* __restrict__ opac, int activate, float half_w, float half_h,
-              int tx, int ty, int W, int H, const int32_t* __restrict__ tile_off, int32_t* tile_fill,
-              const int32_t* __restrict__ status, float4* __restrict__ packed) {
+              int tx, int ty, int row0, int row1, int W, int H, const int32_t* __restrict__ tile_off,
+              int32_t* tile_fill, const int32_t* __restrict__ status, float4* __restrict__ packed) {
     if (status[kStOverflow] != 0) return;
     const int i = blockIdx.x * kFitThreads + threadIdx.x;
     if (i >= n) return;
@@ -193,7 +195,7 @@ k_fit_scatter(int n, const float* __restrict__ xyz_raw, const float* __restrict_
     if (p.nth <= 0) return;
     const float o = opac ? opac[i] : 1.f;
     const float r = feat[3 * i], g = feat[3 * i + 1], b = feat[3 * i + 2];
-    for (int y = p.y0; y < p.y1; ++y)
+    for (int y = max(p.y0, row0); y < min(p.y1, row1); ++y)
         for (int x = p.x0; x < p.x1; ++x) {
             const int t = y * tx + x;
             const int pos = tile_off[t] + atomicAdd(&tile_fill[t], 1);
@@ -290,11 +292,11 @@ __device__ __forceinline__ float group8_reduce8_t(float (&v)[8], int lane) {
 //         yields), 1 = uint8 interleaved [H][W][3] (raw frame; compared as value / 255)
 template <int MODE, int GT>
 __global__ void __launch_bounds__(GS2D_TILE_PIX, 6)
-k_fit_tiles(int W, int H, int tx, const int32_t* __restrict__ tile_off, int32_t* tile_fill,
+k_fit_tiles(int W, int H, int tx, int row0, const int32_t* __restrict__ tile_off, int32_t* tile_fill,
             const float4* __restrict__ packed, const void* __restrict__ gt, float grad_scale,
             float* __restrict__ grads, double* loss_acc, const int32_t* __restrict__ status,
             float* __restrict__ out_img, int out_chw, int out_clamp, int32_t* __restrict__ final_idx,
-            int32_t* __restrict__ ids_sorted_dbg, int want_opacity_grad) {
+            int32_t* __restrict__ ids_sorted_dbg, int want_opacity_grad, int loss_in_grads) {
     __shared__ float4 sq[GS2D_MAX_PER_TILE * 3];
     __shared__ float4 sv[GS2D_TILE_PIX];          // v_out of the tile; before that, the id chunk of the slow path
     __shared__ float sred[GS2D_TILE_PIX / 32];
@@ -302,12 +304,13 @@ k_fit_tiles(int W, int H, int tx, const int32_t* __restrict__ tile_off, int32_t*
     static_assert(sizeof(float4) * GS2D_TILE_PIX >= sizeof(int) * kIdChunk, "id chunk must fit in sv");
     if (status[kStOverflow] != 0) return;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int t = blockIdx.y * tx + blockIdx.x;
+    const int tile_y = (int)blockIdx.y + row0;
+    const int t = tile_y * tx + blockIdx.x;
     const int lo = tile_off[t], cnt = tile_off[t + 1] - lo;
     if (tid == 0) tile_fill[t] = 0;   // ready for the next iteration's scatter
 
     const int lx = tid & 15, ly = tid >> 4;   // warp w owns rows 2w, 2w+1 of the tile
-    const int px_i = blockIdx.x * GS2D_TILE + lx, py_i = blockIdx.y * GS2D_TILE + ly;
+    const int px_i = blockIdx.x * GS2D_TILE + lx, py_i = tile_y * GS2D_TILE + ly;
     const bool inside = px_i < W && py_i < H;
     const size_t pid = (size_t)py_i * W + px_i;
     float3 tgt = make_float3(0.f, 0.f, 0.f);
@@ -411,7 +414,12 @@ k_fit_tiles(int W, int H, int tx, const int32_t* __restrict__ tile_off, int32_t*
         float s = 0.f;
 #pragma unroll
         for (int w = 0; w < GS2D_TILE_PIX / 32; ++w) s += sred[w];
-        if (s != 0.f) atomicAdd(loss_acc, (double)s);
+        if (s != 0.f) {
+            atomicAdd(loss_acc, (double)s);
+            // spatial mode: the loss rides in the pad of gradient row 0 so that one all-reduce of the
+            // gradient buffer also sums the ranks' partial losses
+            if (loss_in_grads) atomicAdd(grads + 9, s);
+        }
     }
 
     // ---- backward (backward.cu:783-859): eight lanes per (tile, Gaussian) pair, four pairs per
@@ -419,7 +427,7 @@ k_fit_tiles(int W, int H, int tx, const int32_t* __restrict__ tile_off, int32_t*
     // total of value l in lane l of the group, and one reduction instruction per pass adds the
     // four pairs' 8 consecutive floats to their gradient rows.
     const int sub = lane >> 3, l8 = lane & 7;
-    const int ox = blockIdx.x * GS2D_TILE, oy = blockIdx.y * GS2D_TILE;
+    const int ox = blockIdx.x * GS2D_TILE, oy = tile_y * GS2D_TILE;
     for (int r0 = warp * 4; r0 < nb; r0 += (GS2D_TILE_PIX / 32) * 4) {
         const int k = min(r0 + sub, nb - 1);
         const float4 q1 = sq[3 * k + 1];
@@ -500,14 +508,14 @@ k_fit_update(int n, float* __restrict__ xyz_raw, float* __restrict__ chol_raw, f
              float* __restrict__ adan, float* __restrict__ grads, float half_w, float half_h, int tx, int ty,
              AdanHyper h, int32_t* status, const double* loss_this, double* loss_next,
              float* __restrict__ grads_out, int cap, int next_step, int32_t* tile_count,
-             int32_t* __restrict__ tile_off, gs2d_fit_report* report_host) {
+             int32_t* __restrict__ tile_off, gs2d_fit_report* report_host, int row0, int row1, int loss_in_grads) {
     __shared__ int sh[8];
     __shared__ int s_last;
     const int i = blockIdx.x * kFitThreads + threadIdx.x;
     if (i == 0 && report_host) {
         // the step's result straight into pinned host memory (no copy to issue, nothing to wait
         // for but the kernel itself); written before the scan below replaces status[0]
-        report_host->loss_sum = *loss_this;
+        report_host->loss_sum = loss_in_grads ? (double)grads[9] : *loss_this;
         report_host->num_intersects = status[kStNumIntersects];
         report_host->overflow_step = status[kStOverflow];
         report_host->max_per_tile = status[kStMaxPerTile];
@@ -563,7 +571,7 @@ k_fit_update(int n, float* __restrict__ xyz_raw, float* __restrict__ chol_raw, f
         Proj2d pn;
         project_chol(tanhf(par[0]), tanhf(par[1]), addf(par[2], 0.5f), addf(par[3], 0.f), addf(par[4], 0.5f), half_w,
                      half_h, tx, ty, pn);
-        count_tiles(pn, tx, tile_count);
+        count_tiles(pn, tx, row0, row1, tile_count);
     }
     scan_tiles_by_last_block(tx, ty, cap, next_step, tile_count, tile_off, status, sh, &s_last);
 }
@@ -614,8 +622,8 @@ int gs2d_fit_init(int n, int cap, int img_h, int img_w, void* work, size_t work_
 }
 
 static int launch_bin(int n, const float* xyz, const float* chol, const float* feat, const float* opac, int activate,
-                      int img_h, int img_w, int cap, int step, const gs2d_fit_layout& L, char* w, cudaStream_t s,
-                      bool precounted = false) {
+                      int img_h, int img_w, int row0, int row1, int cap, int step, const gs2d_fit_layout& L, char* w,
+                      cudaStream_t s, bool precounted = false) {
     const int tx = div_up(img_w, GS2D_TILE), ty = div_up(img_h, GS2D_TILE);
     const float half_w = 0.5f * (float)(unsigned)img_w, half_h = 0.5f * (float)(unsigned)img_h;
     int32_t* status = (int32_t*)(w + L.off_status);
@@ -624,16 +632,83 @@ static int launch_bin(int n, const float* xyz, const float* chol, const float* f
     const int blocks = div_up(n > 0 ? n : 1, kFitThreads);
     if (!precounted) {
         ProfScope ps_(GS2D_STAGE_SCAN_MAP, s);
-        k_fit_count<<<blocks, kFitThreads, 0, s>>>(n, xyz, chol, activate, half_w, half_h, tx, ty, cap, step,
-                                                   tile_count, tile_off, status);
+        k_fit_count<<<blocks, kFitThreads, 0, s>>>(n, xyz, chol, activate, half_w, half_h, tx, ty, row0, row1, cap,
+                                                   step, tile_count, tile_off, status);
         GS2D_CHECK_LAUNCH("fit_count");
     }
     {
         ProfScope ps_(GS2D_STAGE_EDGES_PACK, s);
-        k_fit_scatter<<<blocks, kFitThreads, 0, s>>>(n, xyz, chol, feat, opac, activate, half_w, half_h, tx, ty, img_w,
-                                                     img_h, tile_off, tile_count, status,
+        k_fit_scatter<<<blocks, kFitThreads, 0, s>>>(n, xyz, chol, feat, opac, activate, half_w, half_h, tx, ty, row0,
+                                                     row1, img_w, img_h, tile_off, tile_count, status,
                                                      (float4*)(w + L.off_packed));
         GS2D_CHECK_LAUNCH("fit_scatter");
+    }
+    return GS2D_OK;
+}
+
+int gs2d_fit_step_band(int n, int cap, int img_h, int img_w, float* xyz_raw, float* chol_raw, float* features,
+                       float* adan_state, const void* target, int target_format, void* work, size_t work_bytes,
+                       int step, float lr, float beta1, float beta2, float beta3, float eps, float weight_decay,
+                       int precounted, int tile_row_begin, int tile_row_end, int phases, float* out_img,
+                       float* param_grads_out, int32_t* ids_sorted_out, gs2d_fit_report* report_host,
+                       gs2d_stream_t stream) {
+    gs2d_fit_layout L;
+    int rc = fit_layout(n, cap, img_h, img_w, &L);
+    if (rc != GS2D_OK) return rc;
+    const int tx = div_up(img_w, GS2D_TILE), ty = div_up(img_h, GS2D_TILE);
+    GS2D_REQUIRE(n > 0 && step >= 1, "fit_step: n and step must be positive");
+    GS2D_REQUIRE(work != nullptr && work_bytes >= L.total_bytes, "fit_step: workspace too small");
+    GS2D_REQUIRE(target_format == GS2D_TARGET_F32_CHW || target_format == GS2D_TARGET_U8_HWC,
+                 "fit_step: unknown target format");
+    GS2D_REQUIRE(xyz_raw && chol_raw && features && adan_state, "fit_step: null pointer");
+    GS2D_REQUIRE(0 <= tile_row_begin && tile_row_begin < tile_row_end && tile_row_end <= ty,
+                 "fit_step: tile row band out of range");
+    GS2D_REQUIRE((phases & ~(GS2D_FIT_PHASE_GRADS | GS2D_FIT_PHASE_UPDATE)) == 0 && phases != 0,
+                 "fit_step: bad phase mask");
+    const int row0 = tile_row_begin, row1 = tile_row_end;
+    const bool banded = !(row0 == 0 && row1 == ty) || phases != (GS2D_FIT_PHASE_GRADS | GS2D_FIT_PHASE_UPDATE);
+    cudaStream_t s = (cudaStream_t)stream;
+    char* w = (char*)work;
+    const float half_w = 0.5f * (float)(unsigned)img_w, half_h = 0.5f * (float)(unsigned)img_h;
+    int32_t* status = (int32_t*)(w + L.off_status);
+    double* loss = (double*)(w + L.off_loss);
+    float* grads = (float*)(w + L.off_grads);
+    if (phases & GS2D_FIT_PHASE_GRADS) {
+        GS2D_REQUIRE(target != nullptr, "fit_step: null target");
+        rc = launch_bin(n, xyz_raw, chol_raw, features, nullptr, 1, img_h, img_w, row0, row1, cap, step, L, w, s,
+                        precounted != 0);
+        if (rc != GS2D_OK) return rc;
+        const float grad_scale = (float)(2.0 / (3.0 * (double)img_h * (double)img_w));   // the WHOLE frame's mean
+        ProfScope ps_(GS2D_STAGE_FIT_TILES, s);
+        const dim3 grid(tx, row1 - row0);
+        if (target_format == GS2D_TARGET_F32_CHW)
+            k_fit_tiles<0, 0><<<grid, GS2D_TILE_PIX, 0, s>>>(
+                img_w, img_h, tx, row0, (const int32_t*)(w + L.off_tile_off), (int32_t*)(w + L.off_tile_count),
+                (const float4*)(w + L.off_packed), target, grad_scale, grads, loss + (step % GS2D_FIT_LOSS_SLOTS),
+                status, out_img, 1, 1, nullptr, ids_sorted_out, 0, banded ? 1 : 0);
+        else
+            k_fit_tiles<0, 1><<<grid, GS2D_TILE_PIX, 0, s>>>(
+                img_w, img_h, tx, row0, (const int32_t*)(w + L.off_tile_off), (int32_t*)(w + L.off_tile_count),
+                (const float4*)(w + L.off_packed), target, grad_scale, grads, loss + (step % GS2D_FIT_LOSS_SLOTS),
+                status, out_img, 1, 1, nullptr, ids_sorted_out, 0, banded ? 1 : 0);
+        GS2D_CHECK_LAUNCH("fit_tiles");
+    }
+    if (phases & GS2D_FIT_PHASE_UPDATE) {
+        AdanHyper h;
+        h.b1 = beta1; h.b2 = beta2; h.b3 = beta3;
+        h.step_size = (float)((double)lr / (1.0 - pow((double)beta1, step)));
+        h.step_size_diff = (float)((double)lr * (double)beta2 / (1.0 - pow((double)beta2, step)));
+        h.inv_bc3_sqrt = (float)(1.0 / sqrt(1.0 - pow((double)beta3, step)));
+        h.eps = eps;
+        h.decay_div = 1.f + lr * weight_decay;
+        h.first = step == 1;
+        ProfScope ps_(GS2D_STAGE_ADAN, s);
+        k_fit_update<<<div_up(n, kFitThreads), kFitThreads, 0, s>>>(
+            n, xyz_raw, chol_raw, features, adan_state, grads, half_w, half_h, tx, ty, h, status,
+            loss + (step % GS2D_FIT_LOSS_SLOTS), loss + ((step + 1) % GS2D_FIT_LOSS_SLOTS), param_grads_out, cap,
+            step + 1, (int32_t*)(w + L.off_tile_count), (int32_t*)(w + L.off_tile_off), report_host, row0, row1,
+            banded ? 1 : 0);
+        GS2D_CHECK_LAUNCH("fit_update");
     }
     return GS2D_OK;
 }
@@ -643,56 +718,11 @@ int gs2d_fit_step(int n, int cap, int img_h, int img_w, float* xyz_raw, float* c
                   float lr, float beta1, float beta2, float beta3, float eps, float weight_decay, int precounted,
                   float* out_img, float* param_grads_out, int32_t* ids_sorted_out, gs2d_fit_report* report_host,
                   gs2d_stream_t stream) {
-    gs2d_fit_layout L;
-    int rc = fit_layout(n, cap, img_h, img_w, &L);
-    if (rc != GS2D_OK) return rc;
-    GS2D_REQUIRE(n > 0 && step >= 1, "fit_step: n and step must be positive");
-    GS2D_REQUIRE(work != nullptr && work_bytes >= L.total_bytes, "fit_step: workspace too small");
-    GS2D_REQUIRE(target_format == GS2D_TARGET_F32_CHW || target_format == GS2D_TARGET_U8_HWC,
-                 "fit_step: unknown target format");
-    GS2D_REQUIRE(xyz_raw && chol_raw && features && adan_state && target, "fit_step: null pointer");
-    cudaStream_t s = (cudaStream_t)stream;
-    char* w = (char*)work;
-    const int tx = div_up(img_w, GS2D_TILE), ty = div_up(img_h, GS2D_TILE);
-    const float half_w = 0.5f * (float)(unsigned)img_w, half_h = 0.5f * (float)(unsigned)img_h;
-    rc = launch_bin(n, xyz_raw, chol_raw, features, nullptr, 1, img_h, img_w, cap, step, L, w, s, precounted != 0);
-    if (rc != GS2D_OK) return rc;
-    int32_t* status = (int32_t*)(w + L.off_status);
-    double* loss = (double*)(w + L.off_loss);
-    float* grads = (float*)(w + L.off_grads);
-    const float grad_scale = (float)(2.0 / (3.0 * (double)img_h * (double)img_w));
-    {
-        ProfScope ps_(GS2D_STAGE_FIT_TILES, s);
-        const dim3 grid(tx, ty);
-        if (target_format == GS2D_TARGET_F32_CHW)
-            k_fit_tiles<0, 0><<<grid, GS2D_TILE_PIX, 0, s>>>(
-                img_w, img_h, tx, (const int32_t*)(w + L.off_tile_off), (int32_t*)(w + L.off_tile_count),
-                (const float4*)(w + L.off_packed), target, grad_scale, grads, loss + (step % GS2D_FIT_LOSS_SLOTS),
-                status, out_img, 1, 1, nullptr, ids_sorted_out, 0);
-        else
-            k_fit_tiles<0, 1><<<grid, GS2D_TILE_PIX, 0, s>>>(
-                img_w, img_h, tx, (const int32_t*)(w + L.off_tile_off), (int32_t*)(w + L.off_tile_count),
-                (const float4*)(w + L.off_packed), target, grad_scale, grads, loss + (step % GS2D_FIT_LOSS_SLOTS),
-                status, out_img, 1, 1, nullptr, ids_sorted_out, 0);
-        GS2D_CHECK_LAUNCH("fit_tiles");
-    }
-    AdanHyper h;
-    h.b1 = beta1; h.b2 = beta2; h.b3 = beta3;
-    h.step_size = (float)((double)lr / (1.0 - pow((double)beta1, step)));
-    h.step_size_diff = (float)((double)lr * (double)beta2 / (1.0 - pow((double)beta2, step)));
-    h.inv_bc3_sqrt = (float)(1.0 / sqrt(1.0 - pow((double)beta3, step)));
-    h.eps = eps;
-    h.decay_div = 1.f + lr * weight_decay;
-    h.first = step == 1;
-    {
-        ProfScope ps_(GS2D_STAGE_ADAN, s);
-        k_fit_update<<<div_up(n, kFitThreads), kFitThreads, 0, s>>>(
-            n, xyz_raw, chol_raw, features, adan_state, grads, half_w, half_h, tx, ty, h, status,
-            loss + (step % GS2D_FIT_LOSS_SLOTS), loss + ((step + 1) % GS2D_FIT_LOSS_SLOTS), param_grads_out, cap,
-            step + 1, (int32_t*)(w + L.off_tile_count), (int32_t*)(w + L.off_tile_off), report_host);
-        GS2D_CHECK_LAUNCH("fit_update");
-    }
-    return GS2D_OK;
+    GS2D_REQUIRE(img_h > 0, "fit_step: bad sizes");
+    return gs2d_fit_step_band(n, cap, img_h, img_w, xyz_raw, chol_raw, features, adan_state, target, target_format,
+                              work, work_bytes, step, lr, beta1, beta2, beta3, eps, weight_decay, precounted, 0,
+                              div_up(img_h, GS2D_TILE), GS2D_FIT_PHASE_GRADS | GS2D_FIT_PHASE_UPDATE, out_img,
+                              param_grads_out, ids_sorted_out, report_host, stream);
 }
 
 int gs2d_render_chol(int n, int cap, int img_h, int img_w, const float* means_or_xyz_raw, const float* chol,
@@ -708,14 +738,14 @@ int gs2d_render_chol(int n, int cap, int img_h, int img_w, const float* means_or
     cudaStream_t s = (cudaStream_t)stream;
     char* w = (char*)work;
     const int tx = div_up(img_w, GS2D_TILE), ty = div_up(img_h, GS2D_TILE);
-    rc = launch_bin(n, means_or_xyz_raw, chol, colors, opacities, activate, img_h, img_w, cap, 0, L, w, s);
+    rc = launch_bin(n, means_or_xyz_raw, chol, colors, opacities, activate, img_h, img_w, 0, ty, cap, 0, L, w, s);
     if (rc != GS2D_OK) return rc;
     {
         ProfScope ps_(GS2D_STAGE_RASTER_FWD, s);
         k_fit_tiles<1, 0><<<dim3(tx, ty), GS2D_TILE_PIX, 0, s>>>(
-            img_w, img_h, tx, (const int32_t*)(w + L.off_tile_off), (int32_t*)(w + L.off_tile_count),
+            img_w, img_h, tx, 0, (const int32_t*)(w + L.off_tile_off), (int32_t*)(w + L.off_tile_count),
             (const float4*)(w + L.off_packed), nullptr, 0.f, nullptr, nullptr, (const int32_t*)(w + L.off_status),
-            out_img, out_chw, out_clamp, final_idx, ids_sorted_out, 0);
+            out_img, out_chw, out_clamp, final_idx, ids_sorted_out, 0, 0);
         GS2D_CHECK_LAUNCH("render_tiles");
     }
     return GS2D_OK;

@@ -296,3 +296,104 @@ class FusedFrameFit(torch.nn.Module):
                 self._features_dc.data_ptr(), None, 1, self._render_work.data_ptr(), self._render_work.numel(),
                 out.data_ptr(), 1, 1, None, None, torch.cuda.current_stream(self.device).cuda_stream), "render_chol")
         return out
+
+
+def split_tile_rows(tile_rows: int, world: int, weights=None):
+    """[(row_begin, row_end)] per rank: contiguous bands of tile rows.  weights (one number per
+    tile row, e.g. intersections per row) balances the bands by work instead of by rows: the
+    partition minimises the heaviest band (binary search on the bound + greedy packing)."""
+    if world < 1 or tile_rows < world:
+        raise ValueError("need at least one tile row per rank")
+    if weights is None:
+        edges = [round(r * tile_rows / world) for r in range(world + 1)]
+        return [(edges[r], edges[r + 1]) for r in range(world)]
+    w = [max(float(x), 0.0) for x in weights]
+    if len(w) != tile_rows:
+        raise ValueError("one weight per tile row")
+
+    def pack(bound):
+        bands, start, acc = [], 0, 0.0
+        for row, x in enumerate(w):
+            if row > start and acc + x > bound:
+                bands.append((start, row))
+                start, acc = row, 0.0
+            acc += x
+        bands.append((start, tile_rows))
+        return bands
+
+    lo, hi = max(w), sum(w)
+    for _ in range(60):
+        mid = 0.5 * (lo + hi)
+        if len(pack(mid)) <= world:
+            hi = mid
+        else:
+            lo = mid
+    bands = pack(hi)
+    while len(bands) < world:   # fewer bands than ranks: split the band with the most rows
+        i = max(range(len(bands)), key=lambda k: bands[k][1] - bands[k][0])
+        a, b = bands[i]
+        m = (a + b) // 2
+        bands[i:i + 1] = [(a, m), (m, b)]
+    return bands
+
+
+class SpatialFrameFit(FusedFrameFit):
+    """One frame split across the ranks of a process group by bands of tile rows (SURVEY 8e,
+    BASELINE config 5: 4K+ frames).  Every rank holds all Gaussians and the whole target frame;
+    it bins and rasterises only its band, one all-reduce sums the packed gradient rows (and, in
+    the same buffer, the partial losses), then every rank applies the identical update.  The
+    reference has nothing like it (single `cuda:0`).
+
+    bands: list of (row_begin, row_end) per rank (default: equal split); `emulate_world` runs all
+    bands in this one process on one GPU and sums in place of the all-reduce (tests)."""
+
+    path_name = "tile-row bands per rank; scatter-pack + tile kernel on the band, NCCL all-reduce of the [N,12] gradient rows, replicated update"
+
+    def __init__(self, H, W, num_points, device, group=None, bands=None, emulate_world: int = 0, **kw):
+        super().__init__(H, W, num_points, device, **kw)
+        import torch.distributed as dist
+        self._dist = dist
+        self.group = group
+        self.emulate_world = int(emulate_world)
+        if self.emulate_world:
+            self.world, self.rank = self.emulate_world, 0
+        else:
+            self.world, self.rank = dist.get_world_size(group), dist.get_rank(group)
+        ty = (self.H + 15) // 16
+        self.bands = list(bands) if bands is not None else split_tile_rows(ty, self.world)
+        if len(self.bands) != self.world or self.bands[0][0] != 0 or self.bands[-1][1] != ty or any(
+                a[1] != b[0] for a, b in zip(self.bands, self.bands[1:])):
+            raise ValueError("bands must tile [0, tile_rows) contiguously, one per rank")
+        lay = self.layout
+        self._grads = self.work[lay.off_grads:lay.off_grads + self.n * 48].view(torch.float32)
+
+    def _band_call(self, gt, fmt, band, phases, precounted, dbg):
+        b1, b2, b3 = self.betas
+        slot = self.step_index % self._lib.FIT_LOSS_SLOTS
+        out_img, grads_out, ids_out = dbg.get("out_img"), dbg.get("grads_out"), dbg.get("ids_out")
+        self._lib.check(self._lib.load().gs2d_fit_step_band(
+            self.n, self.cap, self.H, self.W, self._xyz.data_ptr(), self._cholesky.data_ptr(),
+            self._features_dc.data_ptr(), self.adan_state.data_ptr(), gt.data_ptr(), fmt, self.work.data_ptr(),
+            self.layout.total_bytes, self.step_index, self.current_lr(), b1, b2, b3, self.eps, self.weight_decay,
+            1 if precounted else 0, band[0], band[1], phases, None if out_img is None else out_img.data_ptr(),
+            None if grads_out is None else grads_out.data_ptr(), None if ids_out is None else ids_out.data_ptr(),
+            self._report_ptr + 24 * slot, torch.cuda.current_stream(self.device).cuda_stream), "fit_step_band")
+
+    def _issue(self, gt, fmt, **dbg):
+        self.step_index += 1
+        G, U = self._lib.FIT_PHASE_GRADS, self._lib.FIT_PHASE_UPDATE
+        if self.emulate_world:
+            for band in self.bands:                      # every "rank" adds into the one gradient buffer
+                self._band_call(gt, fmt, band, G, False, dbg)
+            self._band_call(gt, fmt, self.bands[0], U, False, dbg)
+            self._counted_for = None                     # the pre-count covered band 0 only
+            return
+        band = self.bands[self.rank]
+        self._band_call(gt, fmt, band, G, self._precount_valid(), dbg)
+        self._dist.all_reduce(self._grads, op=self._dist.ReduceOp.SUM, group=self.group)
+        self._band_call(gt, fmt, band, U, False, dbg)
+        self._counted_for = self._versions()
+
+    @torch.no_grad()
+    def forward(self):
+        raise NotImplementedError("render a banded model through FusedFrameFit.forward on one rank")

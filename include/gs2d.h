@@ -227,6 +227,25 @@ int gs2d_fit_step(int n, int cap, int img_h, int img_w, float* xyz_raw, float* c
                   float lr, float beta1, float beta2, float beta3, float eps, float weight_decay, int precounted,
                   float* out_img, float* param_grads_out, int32_t* ids_sorted_out, gs2d_fit_report* report_host,
                   gs2d_stream_t stream);
+/* The same step for a frame split across GPUs by tile rows (BASELINE config 5): this
+ * rank bins and rasterises only tile rows [tile_row_begin, tile_row_end) -- projection, the
+ * per-Gaussian update and the optimizer stay replicated -- and the step is issued in two phases
+ * so the caller can sum the ranks' gradients in between:
+ *     gs2d_fit_step_band(..., GS2D_FIT_PHASE_GRADS, ...);
+ *     ncclAllReduce(work + off_grads, n * 12 floats, sum)      -- same stream
+ *     gs2d_fit_step_band(..., GS2D_FIT_PHASE_UPDATE, ...);
+ * The loss is normalised by the WHOLE frame (3*H*W) on every rank; in this mode each tile's loss is
+ * also added into float 9 of the gradient buffer (pad of row 0), so the one all-reduce sums the
+ * ranks' partial losses too and the report's loss_sum is the global one.  All ranks then hold
+ * bit-identical parameters.  gs2d_fit_step == full band, both phases. */
+#define GS2D_FIT_PHASE_GRADS 1
+#define GS2D_FIT_PHASE_UPDATE 2
+int gs2d_fit_step_band(int n, int cap, int img_h, int img_w, float* xyz_raw, float* chol_raw, float* features,
+                       float* adan_state, const void* target, int target_format, void* work, size_t work_bytes,
+                       int step, float lr, float beta1, float beta2, float beta3, float eps, float weight_decay,
+                       int precounted, int tile_row_begin, int tile_row_end, int phases, float* out_img,
+                       float* param_grads_out, int32_t* ids_sorted_out, gs2d_fit_report* report_host,
+                       gs2d_stream_t stream);
 /* Render-only (decode): project_gaussians_2d + rasterize_gaussians_sum forward of the reference
  * (GaussianSplats_Represent.py:83-90) as three kernels, sync-free.  activate != 0: inputs are
  * the raw parameters (tanh / bound applied here); else means2d / L_elements as the projection

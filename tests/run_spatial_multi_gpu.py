@@ -1,0 +1,74 @@
+"""Multi-GPU check of the spatial mode (run under torchrun on N GPUs of one box):
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 \
+        --master-port 29533 tests/run_spatial_multi_gpu.py [--h 2160 --w 3840 --n 200000 --iters 20]
+Every rank fits the same frame on its band of tile rows with one NCCL all-reduce of the gradient
+rows per iteration; rank 0 also runs the whole-frame fit alone and compares losses / parameters,
+then prints one JSON line with the timing of both (CUDA events, max over ranks)."""
+import argparse
+import json
+import os
+import sys
+
+import torch
+import torch.distributed as dist
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--h", type=int, default=2160)
+    ap.add_argument("--w", type=int, default=3840)
+    ap.add_argument("--n", type=int, default=200_000)
+    ap.add_argument("--iters", type=int, default=50)
+    ap.add_argument("--warmup", type=int, default=10)
+    a = ap.parse_args()
+    rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    dist.init_process_group("nccl", device_id=dev)
+    from gsvc_b200 import synth
+    from gsvc_b200.fit import FusedFrameFit, SpatialFrameFit
+
+    init = synth.gaussians(a.n, seed=1)
+    gt = (synth.target_frame(a.h, a.w)[0] * 255).round().to(torch.uint8).permute(1, 2, 0).contiguous().to(dev)
+    fit = SpatialFrameFit(a.h, a.w, a.n, dev, init=init)
+    fit.train_iters(gt, a.warmup)
+    dist.barrier(); torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    fit.train_iters(gt, a.iters)
+    e1.record()
+    dist.barrier(); torch.cuda.synchronize()
+    ms = torch.tensor([e0.elapsed_time(e1) / a.iters], dtype=torch.float64, device=dev)
+    dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    loss = fit.loss()
+    # all ranks must hold bit-identical parameters
+    chk = torch.stack([fit._xyz.double().sum(), fit._cholesky.double().sum(), fit._features_dc.double().sum()])
+    lo, hi = chk.clone(), chk.clone()
+    dist.all_reduce(lo, op=dist.ReduceOp.MIN); dist.all_reduce(hi, op=dist.ReduceOp.MAX)
+    identical = bool(torch.equal(lo, hi))
+    out = None
+    if rank == 0:
+        ref = FusedFrameFit(a.h, a.w, a.n, dev, init=init)
+        ref.train_iters(gt, a.warmup)
+        torch.cuda.synchronize()
+        e0.record()
+        ref.train_iters(gt, a.iters)
+        e1.record()
+        torch.cuda.synchronize()
+        ref_ms = e0.elapsed_time(e1) / a.iters
+        ref_loss = ref.loss()
+        d = (ref._features_dc - fit._features_dc).abs()
+        out = {"world": world, "H": a.h, "W": a.w, "gaussians": a.n, "iters": a.iters, "bands": fit.bands,
+               "spatial_ms_per_iter": float(ms), "single_gpu_ms_per_iter": ref_ms, "speedup": ref_ms / float(ms),
+               "loss_spatial": loss, "loss_single": ref_loss, "params_identical_across_ranks": identical,
+               "median_abs_param_diff_vs_single": float(d.median()), "allreduce_bytes": a.n * 48}
+        assert identical, "ranks diverged"
+        assert abs(loss - ref_loss) <= 2e-3 * ref_loss, (loss, ref_loss)
+        print(json.dumps(out), flush=True)
+    dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -113,3 +113,19 @@ def test_fit_sequence_world_size_2_gloo():
     kf = [0, 5, 9, 12]
     for f in range(16):
         assert merged[f] == (_expected_xyz(f, kf, 50, 5), 50 if f in kf else 5)
+
+
+def test_split_tile_rows():
+    from gsvc_b200.fit import split_tile_rows
+    for rows, world in ((135, 8), (68, 2), (68, 4), (9, 8), (4, 4)):
+        bands = split_tile_rows(rows, world)
+        assert len(bands) == world and bands[0][0] == 0 and bands[-1][1] == rows
+        assert all(a[1] == b[0] for a, b in zip(bands, bands[1:])) and all(b > a for a, b in bands)
+        assert max(b - a for a, b in bands) - min(b - a for a, b in bands) <= 1
+    # weighted: the heaviest band is as light as a contiguous partition allows
+    w = [1, 1, 1, 1, 10, 10, 1, 1, 1, 1]
+    bands = split_tile_rows(10, 4, w)
+    assert max(sum(w[a:b]) for a, b in bands) == 10
+    assert split_tile_rows(6, 2, [0] * 6) == [(0, 3), (3, 6)]
+    with pytest.raises(ValueError):
+        split_tile_rows(3, 4)

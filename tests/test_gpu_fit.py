@@ -303,3 +303,28 @@ def test_fit_stream_equals_resident_loop():
         lb.append(l)
     np.testing.assert_allclose(la, lb, rtol=1e-5)
     assert a.step_index == K
+
+
+@pytest.mark.parametrize("H,W,n,world", [(256, 256, 10_000, 2), (200, 328, 3_000, 3), (1080, 1920, 50_000, 4)])
+def test_tile_row_bands_sum_to_the_whole_frame(H, W, n, world):
+    """spatial mode on ONE GPU: every band's gradients (and loss) added into the same buffer in
+    place of the all-reduce must reproduce the whole-frame step"""
+    from gsvc_b200.fit import SpatialFrameFit
+    from gsvc_b200 import synth
+    init, gt, full = _setup(H, W, n, seed=17)
+    banded = SpatialFrameFit(H, W, n, cuda, init=init, emulate_world=world)
+    gtd = gt.to(cuda)
+    ga = torch.empty((n, 8), device=cuda)
+    gb = torch.empty((n, 8), device=cuda)
+    full.train_iters(gtd, 1, grads_out=ga)
+    banded.train_iters(gtd, 1, grads_out=gb)
+    assert banded.loss() == pytest.approx(full.loss(), rel=2e-6)
+    a, b = ga.cpu().numpy(), gb.cpu().numpy()
+    for sl in (slice(0, 2), slice(2, 5), slice(5, 8)):
+        assert _rel(b[:, sl], a[:, sl]) <= GRAD_RTOL
+    for _ in range(4):
+        full.train_iters(gtd, 1)
+        banded.train_iters(gtd, 1)
+    assert banded.loss() == pytest.approx(full.loss(), rel=1e-4)
+    d = (banded._features_dc - full._features_dc).abs()
+    assert float(d.median()) <= 1e-6
