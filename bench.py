@@ -162,8 +162,12 @@ def main_reference(args, rank: int):
 # ------------------------------------------------------------------------------------------
 # GPU arms
 # ------------------------------------------------------------------------------------------
-def make_fitter(impl: str, dev, seed: int):
+def make_fitter(impl: str, dev, seed: int, trained_like: bool = False):
     import torch
+    if trained_like:
+        from gsvc_b200 import synth
+        from gsvc_b200.fit import FusedFrameFit
+        return FusedFrameFit(H, W, NPTS, dev, init=synth.gaussians(NPTS, seed=seed, trained_like=True), cap=1 << 22)
     if impl == "reference-gpu":
         sys.path.insert(0, os.path.join(ROOT, "tests"))
         import ref_fit
@@ -186,7 +190,7 @@ def main_gpu(args, rank: int, world: int, local_rank: int):
 
     mine = args.impl in ("b200", "b200-dropin")
     fused = args.impl == "b200"
-    fit = make_fitter(args.impl, dev, seed=1 + rank)
+    fit = make_fitter(args.impl, dev, seed=1 + rank, trained_like=args.trained_like)
     frame = synth.target_frame(H, W, seed=1 + rank)                      # [1,3,H,W] fp32 in [0,1]
     if fused:
         # the fused path takes the raw RGB frame (uint8 [H,W,3], what the YUV loader decodes to)
@@ -306,6 +310,8 @@ def main_gpu(args, rank: int, world: int, local_rank: int):
         }
         if args.impl != "b200":
             line["impl"] = args.impl
+        if args.trained_like:
+            line["config"]["workload"] += " [trained-like init: informational, not the headline config]"
         if hasattr(fit, "status"):
             line["config"]["max_per_tile"] = fit.status()[2]
         if stages:
@@ -342,6 +348,8 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "b200-dropin", "reference", "reference-gpu"])
     ap.add_argument("--cpu-steps", type=int, default=20, help="fit iterations of the cpu_baseline leg")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--trained-like", action="store_true",
+                    help="informational: wide Gaussians (L = 4*rand + bound, ~10x the intersections, tiles beyond 256)")
     args = ap.parse_args()
     rank, world, local_rank = _env_int("RANK", 0), _env_int("WORLD_SIZE", 1), _env_int("LOCAL_RANK", 0)
     if args.impl == "reference":

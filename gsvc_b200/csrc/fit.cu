@@ -211,44 +211,56 @@ k_fit_scatter(int n, const float* __restrict__ xyz_raw, const float* __restrict_
 // K3: the tile kernel
 // ------------------------------------------------------------------------------------------
 constexpr int kIdChunk = 1024;
+constexpr int kTileThreads = 64;   // two warps per 16x16 tile, four pixels per thread
+#ifndef GS2D_BWD_ROWS
+#define GS2D_BWD_ROWS 2
+#endif
+constexpr int kBwdRows = GS2D_BWD_ROWS;   // rows of a pair's rectangle a lane evaluates per loop trip
 
 // Stage the tile's batch into shared memory in ascending Gaussian-id order (the scatter wrote
 // the range in arbitrary order; ascending id is the order of the reference's stable sort on
-// tile id).  cnt <= 256: thread j keeps record j in registers, ranks its id
-// against the ids of the range (shared memory) and stores the record at its rank.
-// cnt > 256 (rare; the reference then renders only the 256 lowest ids): ranks are
-// computed against all cnt ids in chunks and the 256 lowest-ranked records are kept.
+// tile id).  cnt <= 256: ids go to shared memory, every thread ranks its records'
+// ids against them and stores each record at its rank (the first record per thread is already
+// in flight while the ids land).  cnt > 256 (rare; the reference then renders only the 256
+// lowest ids): ranks are computed against all cnt ids in chunks and the 256
+// lowest-ranked records are kept.
 __device__ __forceinline__ int stage_tile_sorted(const float4* __restrict__ src, int cnt, float4* sq, int* sid,
                                                  int tid) {
     const int nb = min(cnt, GS2D_MAX_PER_TILE);
     if (cnt <= GS2D_MAX_PER_TILE) {
         float4 r0, r1, r2;
-        int my = 0;
         if (tid < cnt) {
             r0 = __ldg(&src[3 * (size_t)tid + 0]);
             r1 = __ldg(&src[3 * (size_t)tid + 1]);
             r2 = __ldg(&src[3 * (size_t)tid + 2]);
-            my = __float_as_int(r1.w);
-            sid[tid] = my;
+            sid[tid] = __float_as_int(r1.w);
         }
+        for (int j = tid + kTileThreads; j < cnt; j += kTileThreads)
+            sid[j] = __float_as_int(__ldg(&src[3 * (size_t)j + 1]).w);
         __syncthreads();
-        if (tid < cnt) {
+        for (int j = tid; j < cnt; j += kTileThreads) {
+            const int my = sid[j];
             int rank = 0;
-            for (int j = 0; j < cnt; ++j) rank += (sid[j] < my) ? 1 : 0;
+            for (int i = 0; i < cnt; ++i) rank += (sid[i] < my) ? 1 : 0;
+            if (j != tid) {
+                r0 = __ldg(&src[3 * (size_t)j + 0]);
+                r1 = __ldg(&src[3 * (size_t)j + 1]);
+                r2 = __ldg(&src[3 * (size_t)j + 2]);
+            }
             sq[3 * rank + 0] = r0;
             sq[3 * rank + 1] = r1;
             sq[3 * rank + 2] = r2;
         }
         __syncthreads();
     } else {
-        for (int r0 = 0; r0 < cnt; r0 += GS2D_TILE_PIX) {
+        for (int r0 = 0; r0 < cnt; r0 += kTileThreads) {
             const int j = r0 + tid;
             const int my = j < cnt ? __float_as_int(__ldg(&src[3 * (size_t)j + 1]).w) : 0x7fffffff;
             int rank = 0;
             for (int c0 = 0; c0 < cnt; c0 += kIdChunk) {
                 const int m = min(kIdChunk, cnt - c0);
                 __syncthreads();
-                for (int k = tid; k < m; k += GS2D_TILE_PIX) sid[k] = __float_as_int(__ldg(&src[3 * (size_t)(c0 + k) + 1]).w);
+                for (int k = tid; k < m; k += kTileThreads) sid[k] = __float_as_int(__ldg(&src[3 * (size_t)(c0 + k) + 1]).w);
                 __syncthreads();
                 for (int k = 0; k < m; ++k) rank += (sid[k] < my) ? 1 : 0;
             }
@@ -290,16 +302,22 @@ __device__ __forceinline__ float group8_reduce8_t(float (&v)[8], int lane) {
 // MODE 1: render only (image [+ final_idx] written, no target, no backward)
 // GT: 0 = target is fp32 planar [3][H][W] (what torchvision's ToTensor / the reference's loader
 //         yields), 1 = uint8 interleaved [H][W][3] (raw frame; compared as value / 255)
+//
+// One CTA of two warps per tile.  Warp w owns tile rows 8w .. 8w+7; a lane owns one column of
+// two interleaved row sets: pixel j (0..3) of lane l is (x = l & 15, y = 8w + 2j + (l >> 4)), so
+// one warp instruction on pixel j covers the row pair {8w+2j, 8w+2j+1} -- the granularity of the
+// rectangle culling -- while dx, conic.x*dx and conic.y*dx are computed once per Gaussian and
+// reused by the four pixels (same operations as the reference's expression, so bit-identical).
 template <int MODE, int GT>
-__global__ void __launch_bounds__(GS2D_TILE_PIX, 6)
+__global__ void __launch_bounds__(kTileThreads)
 k_fit_tiles(int W, int H, int tx, int row0, const int32_t* __restrict__ tile_off, int32_t* tile_fill,
             const float4* __restrict__ packed, const void* __restrict__ gt, float grad_scale,
             float* __restrict__ grads, double* loss_acc, const int32_t* __restrict__ status,
             float* __restrict__ out_img, int out_chw, int out_clamp, int32_t* __restrict__ final_idx,
             int32_t* __restrict__ ids_sorted_dbg, int want_opacity_grad, int loss_in_grads) {
     __shared__ float4 sq[GS2D_MAX_PER_TILE * 3];
-    __shared__ float4 sv[GS2D_TILE_PIX];          // v_out of the tile; before that, the id chunk of the slow path
-    __shared__ float sred[GS2D_TILE_PIX / 32];
+    __shared__ float4 sv[GS2D_TILE_PIX];          // v_out of the tile; before that, the id chunk of the staging
+    __shared__ float sred[kTileThreads / 32];
     int* sid = reinterpret_cast<int*>(sv);
     static_assert(sizeof(float4) * GS2D_TILE_PIX >= sizeof(int) * kIdChunk, "id chunk must fit in sv");
     if (status[kStOverflow] != 0) return;
@@ -309,111 +327,134 @@ k_fit_tiles(int W, int H, int tx, int row0, const int32_t* __restrict__ tile_off
     const int lo = tile_off[t], cnt = tile_off[t + 1] - lo;
     if (tid == 0) tile_fill[t] = 0;   // ready for the next iteration's scatter
 
-    const int lx = tid & 15, ly = tid >> 4;   // warp w owns rows 2w, 2w+1 of the tile
-    const int px_i = blockIdx.x * GS2D_TILE + lx, py_i = tile_y * GS2D_TILE + ly;
-    const bool inside = px_i < W && py_i < H;
-    const size_t pid = (size_t)py_i * W + px_i;
-    float3 tgt = make_float3(0.f, 0.f, 0.f);
-    uint32_t tgt_u8 = 0;
-    if (MODE == 0 && inside) {   // issued before the batch arrives: independent loads
-        if (GT == 0) {
-            const float* g = (const float*)gt;
-            const size_t plane = (size_t)H * W;
-            tgt = make_float3(__ldg(g + pid), __ldg(g + plane + pid), __ldg(g + 2 * plane + pid));
-        } else {
-            const uint8_t* g = (const uint8_t*)gt + 3 * pid;
-            tgt_u8 = (uint32_t)__ldg(g) | ((uint32_t)__ldg(g + 1) << 8) | ((uint32_t)__ldg(g + 2) << 16);
+    const int lx = lane & 15, ly0 = 8 * warp + (lane >> 4);   // pixel j: (lx, ly0 + 2j)
+    const int ox = blockIdx.x * GS2D_TILE, oy = tile_y * GS2D_TILE;
+    const int px_i = ox + lx;
+    const bool in_x = px_i < W;
+    uint32_t tgt_u8[4] = {0u, 0u, 0u, 0u};
+    float3 tgt[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) tgt[j] = make_float3(0.f, 0.f, 0.f);
+    if (MODE == 0 && in_x) {   // issued before the batch arrives: independent loads
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const int py_i = oy + ly0 + 2 * j;
+            if (py_i < H) {
+                const size_t pid = (size_t)py_i * W + px_i;
+                if (GT == 0) {
+                    const float* g = (const float*)gt;
+                    const size_t plane = (size_t)H * W;
+                    tgt[j] = make_float3(__ldg(g + pid), __ldg(g + plane + pid), __ldg(g + 2 * plane + pid));
+                } else {
+                    const uint8_t* g = (const uint8_t*)gt + 3 * pid;
+                    tgt_u8[j] = (uint32_t)__ldg(g) | ((uint32_t)__ldg(g + 1) << 8) | ((uint32_t)__ldg(g + 2) << 16);
+                }
+            }
         }
     }
 
     const int nb = stage_tile_sorted(packed + 3 * (size_t)lo, cnt, sq, sid, tid);
     if (ids_sorted_dbg) {   // parity tests: the order the batch is rendered in
-        for (int r = tid; r < nb; r += GS2D_TILE_PIX) ids_sorted_dbg[lo + r] = __float_as_int(sq[3 * r + 1].w);
-        for (int r = nb + tid; r < cnt; r += GS2D_TILE_PIX) ids_sorted_dbg[lo + r] = -1;
+        for (int r = tid; r < nb; r += kTileThreads) ids_sorted_dbg[lo + r] = __float_as_int(sq[3 * r + 1].w);
+        for (int r = nb + tid; r < cnt; r += kTileThreads) ids_sorted_dbg[lo + r] = -1;
     }
 
     // ---- forward (forward.cu:590-612) --------------------------------------------------------
-    const float px = (float)px_i, py = (float)py_i;
-    const int row_lo = 2 * warp, row_hi = 2 * warp + 1;
-    float3 pix = make_float3(0.f, 0.f, 0.f);
-    int cur_idx = 0;
+    const float px = (float)px_i;
+    float py[4];
+    bool inside[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        py[j] = (float)(oy + ly0 + 2 * j);
+        inside[j] = in_x && (oy + ly0 + 2 * j) < H;
+    }
+    const int wrow_lo = 8 * warp, wrow_hi = 8 * warp + 7;
+    float3 pix[4];
+    int cur_idx[4] = {0, 0, 0, 0};
+#pragma unroll
+    for (int j = 0; j < 4; ++j) pix[j] = make_float3(0.f, 0.f, 0.f);
     for (int c = 0; c < nb; c += 32) {
         const int r_lane = c + lane;
         bool touch = false;
         if (r_lane < nb) {
             const uint32_t rect = __float_as_uint(sq[3 * r_lane + 1].z);
             const int y0 = (rect >> 16) & 255, y1 = rect >> 24;
-            touch = (y1 >= row_lo) && (y0 <= row_hi);
+            touch = (y1 >= wrow_lo) && (y0 <= wrow_hi);
         }
         unsigned m = __ballot_sync(0xffffffffu, touch);
         while (m) {
-            // two records per trip: two independent sigma / ex2 chains in flight (the second is
-            // a masked repeat of the first when only one is left); accumulation stays in order
-            const int ka = c + __ffs(m) - 1;
+            const int k = c + __ffs(m) - 1;
             m &= m - 1;
-            const bool two = m != 0;
-            const int kb = two ? c + __ffs(m) - 1 : ka;
-            m &= m - 1;
-            const float4 a0 = sq[3 * ka], a1 = sq[3 * ka + 1];   // x, y, conic.x, conic.y | conic.z, opacity, rect, id
-            const float4 b0 = sq[3 * kb], b1 = sq[3 * kb + 1];
-            const float dxa = subf(a0.x, px), dya = subf(a0.y, py);
-            const float dxb = subf(b0.x, px), dyb = subf(b0.y, py);
-            const float sa = gauss_sigma(dxa, dya, a0.z, a0.w, a1.x);
-            const float sb = gauss_sigma(dxb, dyb, b0.z, b0.w, b1.x);
-            const float alpha_a = minf(mulf(a1.y, gauss_vis(sa)), 1.f);
-            const float alpha_b = minf(mulf(b1.y, gauss_vis(sb)), 1.f);
-            if (inside && gauss_pass(sa, alpha_a)) {
-                const float4 q2 = sq[3 * ka + 2];   // r, g, b, tile
-                pix.x = fmaf_(alpha_a, q2.x, pix.x);
-                pix.y = fmaf_(alpha_a, q2.y, pix.y);
-                pix.z = fmaf_(alpha_a, q2.z, pix.z);
-                if (MODE == 1) cur_idx = lo + ka;
-            }
-            if (two && inside && gauss_pass(sb, alpha_b)) {
-                const float4 q2 = sq[3 * kb + 2];
-                pix.x = fmaf_(alpha_b, q2.x, pix.x);
-                pix.y = fmaf_(alpha_b, q2.y, pix.y);
-                pix.z = fmaf_(alpha_b, q2.z, pix.z);
-                if (MODE == 1) cur_idx = lo + kb;
+            const float4 q0 = sq[3 * k];       // x, y, conic.x, conic.y
+            const float4 q1 = sq[3 * k + 1];   // conic.z, opacity, rect, id
+            const float4 q2 = sq[3 * k + 2];   // r, g, b, tile
+            const uint32_t rect = __float_as_uint(q1.z);
+            const int y0 = (int)((rect >> 16) & 255) - wrow_lo, y1 = (int)(rect >> 24) - wrow_lo;   // warp-local rows
+            const float dx = subf(q0.x, px);
+            const float t1 = mulf(q0.z, dx), t3 = mulf(q0.w, dx);
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                if (y1 < 2 * j || y0 > 2 * j + 1) continue;   // warp-uniform: row pair j outside the rectangle
+                const float dy = subf(q0.y, py[j]);
+                // reference expression 0.5*(cx*dx*dx + cz*dy*dy) + cy*dx*dy as its build contracts it
+                const float q = fmaf_(dx, t1, mulf(mulf(q1.x, dy), dy));
+                const float sigma = fmaf_(dy, t3, mulf(q, 0.5f));
+                const float alpha = minf(mulf(q1.y, gauss_vis(sigma)), 1.f);
+                if (inside[j] && gauss_pass(sigma, alpha)) {
+                    pix[j].x = fmaf_(alpha, q2.x, pix[j].x);
+                    pix[j].y = fmaf_(alpha, q2.y, pix[j].y);
+                    pix[j].z = fmaf_(alpha, q2.z, pix[j].z);
+                    if (MODE == 1) cur_idx[j] = lo + k;
+                }
             }
         }
     }
-    if (inside && out_img) {
-        float3 o = pix;
-        if (out_clamp) o = make_float3(fminf(fmaxf(o.x, 0.f), 1.f), fminf(fmaxf(o.y, 0.f), 1.f), fminf(fmaxf(o.z, 0.f), 1.f));
-        if (out_chw) {
-            const size_t plane = (size_t)H * W;
-            out_img[pid] = o.x; out_img[plane + pid] = o.y; out_img[2 * plane + pid] = o.z;
-        } else {
-            out_img[3 * pid] = o.x; out_img[3 * pid + 1] = o.y; out_img[3 * pid + 2] = o.z;
+    if (out_img || final_idx) {
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            if (!inside[j]) continue;
+            const size_t pid = (size_t)(oy + ly0 + 2 * j) * W + px_i;
+            if (out_img) {
+                float3 o = pix[j];
+                if (out_clamp) o = make_float3(fminf(fmaxf(o.x, 0.f), 1.f), fminf(fmaxf(o.y, 0.f), 1.f), fminf(fmaxf(o.z, 0.f), 1.f));
+                if (out_chw) {
+                    const size_t plane = (size_t)H * W;
+                    out_img[pid] = o.x; out_img[plane + pid] = o.y; out_img[2 * plane + pid] = o.z;
+                } else {
+                    out_img[3 * pid] = o.x; out_img[3 * pid + 1] = o.y; out_img[3 * pid + 2] = o.z;
+                }
+            }
+            if (final_idx) final_idx[pid] = cur_idx[j];
         }
     }
-    if (inside && final_idx) final_idx[pid] = cur_idx;
     if (MODE == 1) return;
 
     // ---- clamp + L2 loss and its gradient w.r.t. the unclamped sum --------------------------
     float l = 0.f;
-    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-    if (GT == 1) tgt = make_float3(u8_over_255(tgt_u8 & 255u), u8_over_255((tgt_u8 >> 8) & 255u), u8_over_255((tgt_u8 >> 16) & 255u));
-    if (inside) {
-        const float dxr = fminf(fmaxf(pix.x, 0.f), 1.f) - tgt.x;
-        const float dyg = fminf(fmaxf(pix.y, 0.f), 1.f) - tgt.y;
-        const float dzb = fminf(fmaxf(pix.z, 0.f), 1.f) - tgt.z;
-        l = dxr * dxr + dyg * dyg + dzb * dzb;
-        // clamp passes the gradient where 0 <= x <= 1 (torch's clamp backward, bounds inclusive)
-        v.x = (pix.x >= 0.f && pix.x <= 1.f) ? grad_scale * dxr : 0.f;
-        v.y = (pix.y >= 0.f && pix.y <= 1.f) ? grad_scale * dyg : 0.f;
-        v.z = (pix.z >= 0.f && pix.z <= 1.f) ? grad_scale * dzb : 0.f;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (GT == 1) tgt[j] = make_float3(u8_over_255(tgt_u8[j] & 255u), u8_over_255((tgt_u8[j] >> 8) & 255u),
+                                          u8_over_255((tgt_u8[j] >> 16) & 255u));
+        if (inside[j]) {
+            const float cr = fminf(fmaxf(pix[j].x, 0.f), 1.f), cg = fminf(fmaxf(pix[j].y, 0.f), 1.f),
+                        cb = fminf(fmaxf(pix[j].z, 0.f), 1.f);
+            const float dr = cr - tgt[j].x, dg = cg - tgt[j].y, db = cb - tgt[j].z;
+            l += dr * dr + dg * dg + db * db;
+            // clamp passes the gradient where 0 <= x <= 1 (torch's clamp backward, bounds inclusive),
+            // i.e. exactly where clamping left the value unchanged
+            v.x = (cr == pix[j].x) ? grad_scale * dr : 0.f;
+            v.y = (cg == pix[j].y) ? grad_scale * dg : 0.f;
+            v.z = (cb == pix[j].z) ? grad_scale * db : 0.f;
+        }
+        sv[(ly0 + 2 * j) * GS2D_TILE + lx] = v;   // (the staging's id chunk that aliases sv is dead since its last barrier)
     }
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) l += __shfl_xor_sync(0xffffffffu, l, o);
-    sv[tid] = v;   // (the id chunk of the slow path that aliases sv is dead since stage_tile_sorted's last barrier)
     if (lane == 0) sred[warp] = l;
     __syncthreads();
     if (tid == 0) {
-        float s = 0.f;
-#pragma unroll
-        for (int w = 0; w < GS2D_TILE_PIX / 32; ++w) s += sred[w];
+        const float s = sred[0] + sred[1];
         if (s != 0.f) {
             atomicAdd(loss_acc, (double)s);
             // spatial mode: the loss rides in the pad of gradient row 0 so that one all-reduce of the
@@ -423,48 +464,70 @@ k_fit_tiles(int W, int H, int tx, int row0, const int32_t* __restrict__ tile_off
     }
 
     // ---- backward (backward.cu:783-859): eight lanes per (tile, Gaussian) pair, four pairs per
-    // warp pass; lanes sweep the pair's rectangle, one 7-shuffle transposed reduction leaves the
-    // total of value l in lane l of the group, and one reduction instruction per pass adds the
-    // four pairs' 8 consecutive floats to their gradient rows.
+    // warp pass.  A lane owns one column of the pair's rectangle (two when it is wider than 8) and
+    // walks its rows, so dx and the conic products with dx are per-lane constants; one 7-shuffle
+    // transposed reduction leaves the total of value l in lane l of the group, and one reduction
+    // instruction per pass adds the four pairs' 8 consecutive floats to their gradient rows.
     const int sub = lane >> 3, l8 = lane & 7;
-    const int ox = blockIdx.x * GS2D_TILE, oy = tile_y * GS2D_TILE;
-    for (int r0 = warp * 4; r0 < nb; r0 += (GS2D_TILE_PIX / 32) * 4) {
+    for (int r0 = warp * 4; r0 < nb; r0 += (kTileThreads / 32) * 4) {
         const int k = min(r0 + sub, nb - 1);
         const float4 q1 = sq[3 * k + 1];
         const uint32_t rect = __float_as_uint(q1.z);
         const int rx0 = rect & 255, rx1 = (rect >> 8) & 255, ry0 = (rect >> 16) & 255, ry1 = rect >> 24;
-        const int w = rx1 - rx0 + 1;
-        const int area = (r0 + sub < nb && ry1 >= ry0) ? w * (ry1 - ry0 + 1) : 0;
-        int max_area = max(area, __shfl_xor_sync(0xffffffffu, area, 8));
-        max_area = max(max_area, __shfl_xor_sync(0xffffffffu, max_area, 16));
-        if (max_area == 0) continue;   // no pixel of this tile can pass for any of the four
+        const bool live = (r0 + sub < nb) && ry1 >= ry0;
+        const int h = live ? ry1 - ry0 + 1 : 0;
+        const int ncol = live ? ((rx1 - rx0) >> 3) + 1 : 0;          // column blocks of 8: 1 or 2
+        const int iters = h * ncol;
+        int max_iters = max(iters, __shfl_xor_sync(0xffffffffu, iters, 8));
+        max_iters = max(max_iters, __shfl_xor_sync(0xffffffffu, max_iters, 16));
+        if (max_iters == 0) continue;   // no pixel of this tile can pass for any of the four
         const float4 q0 = sq[3 * k], q2 = sq[3 * k + 2];
         const float gx = q0.x, gy = q0.y, cx = q0.z, cy = q0.w, cz = q1.x, opac = q1.y;
-        const float inv_w = 1.f / (float)w;
         float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
         float acc_op = 0.f;
-        for (int p = l8; p < max_area; p += 8) {
-            if (p >= area) continue;
-            const int ry = (int)(((float)p + 0.5f) * inv_w);
-            const int lxp = rx0 + (p - ry * w), lyp = ry0 + ry;
-            const float dx = subf(gx, (float)(ox + lxp)), dy = subf(gy, (float)(oy + lyp));
-            const float sigma = gauss_sigma(dx, dy, cx, cy, cz);
-            const float vis = gauss_vis(sigma);
-            const float alpha = minf(mulf(opac, vis), 1.f);
-            if (!gauss_pass(sigma, alpha)) continue;
-            const float4 vo = sv[lyp * GS2D_TILE + lxp];
-            const float v_alpha = q2.x * vo.x + q2.y * vo.y + q2.z * vo.z;   // backward.cu:821-825
-            const float v_sigma = -opac * vis * v_alpha;                      // :827
-            acc[0] += v_sigma * (cx * dx + cy * dy);                          // v_xy     :831-832
-            acc[1] += v_sigma * (cy * dx + cz * dy);
-            const float hs = 0.5f * v_sigma;
-            acc[2] += hs * dx * dx;                                           // v_conic  :828-830
-            acc[3] += hs * dx * dy;
-            acc[4] += hs * dy * dy;
-            acc[5] += alpha * vo.x;                                           // v_rgb    :817
-            acc[6] += alpha * vo.y;
-            acc[7] += alpha * vo.z;
-            acc_op += vis * v_alpha;                                          // v_opacity :833
+        for (int cb0 = 0; cb0 < 2; ++cb0) {
+            int max_h = (cb0 < ncol) ? h : 0;
+            max_h = max(max_h, __shfl_xor_sync(0xffffffffu, max_h, 8));
+            max_h = max(max_h, __shfl_xor_sync(0xffffffffu, max_h, 16));
+            if (max_h == 0) break;
+            const int lxp = rx0 + l8 + 8 * cb0;
+            const bool col_ok = (cb0 < ncol) && lxp <= rx1;
+            const float dx = subf(gx, (float)(ox + lxp));
+            const float t1 = mulf(cx, dx), t3 = mulf(cy, dx);
+            const float cxdx = cx * dx, cydx = cy * dx, dx2 = dx * dx;
+            // kBwdRows rows per trip: that many independent sigma / ex2 chains in flight per lane
+            // (the loop is latency-bound, not issue-bound: profiles/r1 notes)
+            for (int ry = 0; ry < max_h; ry += kBwdRows) {
+                float dy[kBwdRows], sg[kBwdRows], vis[kBwdRows], al[kBwdRows];
+#pragma unroll
+                for (int u = 0; u < kBwdRows; ++u) {
+                    dy[u] = subf(gy, (float)(oy + ry0 + ry + u));
+                    const float q = fmaf_(dx, t1, mulf(mulf(cz, dy[u]), dy[u]));
+                    sg[u] = fmaf_(dy[u], t3, mulf(q, 0.5f));
+                }
+#pragma unroll
+                for (int u = 0; u < kBwdRows; ++u) {
+                    vis[u] = gauss_vis(sg[u]);
+                    al[u] = minf(mulf(opac, vis[u]), 1.f);
+                }
+#pragma unroll
+                for (int u = 0; u < kBwdRows; ++u) {
+                    if (!(col_ok && ry + u < h && gauss_pass(sg[u], al[u]))) continue;
+                    const float4 vo = sv[(ry0 + ry + u) * GS2D_TILE + lxp];
+                    const float v_alpha = q2.x * vo.x + q2.y * vo.y + q2.z * vo.z;   // backward.cu:821-825
+                    const float v_sigma = -opac * vis[u] * v_alpha;                   // :827
+                    acc[0] += v_sigma * (cxdx + cy * dy[u]);                          // v_xy     :831-832
+                    acc[1] += v_sigma * (cydx + cz * dy[u]);
+                    const float hs = 0.5f * v_sigma;
+                    acc[2] += hs * dx2;                                               // v_conic  :828-830
+                    acc[3] += hs * dx * dy[u];
+                    acc[4] += hs * dy[u] * dy[u];
+                    acc[5] += al[u] * vo.x;                                           // v_rgb    :817
+                    acc[6] += al[u] * vo.y;
+                    acc[7] += al[u] * vo.z;
+                    acc_op += vis[u] * v_alpha;                                       // v_opacity :833
+                }
+            }
         }
         const float tot = group8_reduce8_t(acc, lane);
         float* row = grads + (size_t)__float_as_int(q1.w) * 12;
@@ -472,9 +535,9 @@ k_fit_tiles(int W, int H, int tx, int row0, const int32_t* __restrict__ tile_off
             acc_op += __shfl_xor_sync(0xffffffffu, acc_op, 4);
             acc_op += __shfl_xor_sync(0xffffffffu, acc_op, 2);
             acc_op += __shfl_xor_sync(0xffffffffu, acc_op, 1);
-            if (l8 == 0 && area > 0 && acc_op != 0.f) atomicAdd(row + 8, acc_op);
+            if (l8 == 0 && live && acc_op != 0.f) atomicAdd(row + 8, acc_op);
         }
-        if (area > 0 && tot != 0.f) atomicAdd(row + l8, tot);   // 4 pairs x 8 consecutive floats
+        if (live && tot != 0.f) atomicAdd(row + l8, tot);   // 4 pairs x 8 consecutive floats
     }
 }
 
@@ -682,12 +745,12 @@ int gs2d_fit_step_band(int n, int cap, int img_h, int img_w, float* xyz_raw, flo
         ProfScope ps_(GS2D_STAGE_FIT_TILES, s);
         const dim3 grid(tx, row1 - row0);
         if (target_format == GS2D_TARGET_F32_CHW)
-            k_fit_tiles<0, 0><<<grid, GS2D_TILE_PIX, 0, s>>>(
+            k_fit_tiles<0, 0><<<grid, kTileThreads, 0, s>>>(
                 img_w, img_h, tx, row0, (const int32_t*)(w + L.off_tile_off), (int32_t*)(w + L.off_tile_count),
                 (const float4*)(w + L.off_packed), target, grad_scale, grads, loss + (step % GS2D_FIT_LOSS_SLOTS),
                 status, out_img, 1, 1, nullptr, ids_sorted_out, 0, banded ? 1 : 0);
         else
-            k_fit_tiles<0, 1><<<grid, GS2D_TILE_PIX, 0, s>>>(
+            k_fit_tiles<0, 1><<<grid, kTileThreads, 0, s>>>(
                 img_w, img_h, tx, row0, (const int32_t*)(w + L.off_tile_off), (int32_t*)(w + L.off_tile_count),
                 (const float4*)(w + L.off_packed), target, grad_scale, grads, loss + (step % GS2D_FIT_LOSS_SLOTS),
                 status, out_img, 1, 1, nullptr, ids_sorted_out, 0, banded ? 1 : 0);
@@ -742,7 +805,7 @@ int gs2d_render_chol(int n, int cap, int img_h, int img_w, const float* means_or
     if (rc != GS2D_OK) return rc;
     {
         ProfScope ps_(GS2D_STAGE_RASTER_FWD, s);
-        k_fit_tiles<1, 0><<<dim3(tx, ty), GS2D_TILE_PIX, 0, s>>>(
+        k_fit_tiles<1, 0><<<dim3(tx, ty), kTileThreads, 0, s>>>(
             img_w, img_h, tx, 0, (const int32_t*)(w + L.off_tile_off), (int32_t*)(w + L.off_tile_count),
             (const float4*)(w + L.off_packed), nullptr, 0.f, nullptr, nullptr, (const int32_t*)(w + L.off_status),
             out_img, out_chw, out_clamp, final_idx, ids_sorted_out, 0, 0);
