@@ -117,6 +117,20 @@ def algorithmic_bytes(stage: str, n: int, I: int, hw: int, tiles: int) -> float:
     }[stage]
 
 
+def ncu_traffic(stage: str):
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch of the stage's kernel from the committed
+    `ncu --set full` capture (profiles/r1_fit_kernels_ncu.json; taken at ~124k intersections), or None"""
+    kern = {"fit_tiles": "k_fit_tiles", "adan": "k_fit_update", "edges_pack": "k_fit_scatter"}.get(stage)
+    try:
+        recs = json.load(open(os.path.join(ROOT, "profiles", "r1_fit_kernels_ncu.json")))
+    except (OSError, ValueError):
+        return None
+    for r in recs:
+        if kern and kern in r.get("kernel", ""):
+            return r.get("dram_traffic_bytes")
+    return None
+
+
 # ------------------------------------------------------------------------------------------
 # CPU arm: the oracle port on the host cores
 # ------------------------------------------------------------------------------------------
@@ -329,7 +343,7 @@ def main_gpu(args, rank: int, world: int, local_rank: int):
             alg = algorithmic_bytes(top, NPTS, I or 124_000, H * W, tiles)
             dur_s = kern[top]["ms_per_step"] / n_l * 1e-3
             line["roofline"] = {"kernel": top, "bound": "hbm", "achieved": alg / dur_s / 1e9, "peak": peak,
-                                "unit": "GB/s", "frac": alg / dur_s / 1e9 / peak, "traffic": None,
+                                "unit": "GB/s", "frac": alg / dur_s / 1e9 / peak, "traffic": ncu_traffic(top),
                                 "algorithmic_bytes": alg, "avg_launch_us": dur_s * 1e6,
                                 "peak_source": "MEASURED_PEAKS.json hbm_gbs (measured)" if peaks else "fallback 6650"}
         if world == 1 and mine and not args.no_cpu:
