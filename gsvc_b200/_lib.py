@@ -46,6 +46,12 @@ class FitLayout(Structure):
     ]
 
 
+class GradExchange(Structure):
+    """mirror of gs2d_grad_exchange (include/gs2d.h)"""
+
+    _fields_ = [("accumulate", c_void_p), ("peers", c_void_p), ("num_peers", c_int), ("zero", c_void_p)]
+
+
 FIT_LOSS_SLOTS = 64
 TARGET_F32_CHW, TARGET_U8_HWC = 0, 1
 FIT_PHASE_GRADS, FIT_PHASE_UPDATE = 1, 2
@@ -81,7 +87,7 @@ _SIGNATURES = {
                               c_float, c_float, c_float, c_float, c_float, c_float, c_int, _P, _P, _P, _P, _P]),
     "gs2d_fit_step_band": (c_int, [c_int, c_int, c_int, c_int, _P, _P, _P, _P, _P, c_int, _P, c_size_t, c_int,
                                    c_float, c_float, c_float, c_float, c_float, c_float, c_int, c_int, c_int, c_int,
-                                   _P, _P, _P, _P, _P]),
+                                   _P, _P, _P, _P, _P, _P]),
     "gs2d_render_chol": (c_int, [c_int, c_int, c_int, c_int, _P, _P, _P, _P, c_int, _P, c_size_t, _P, c_int, c_int,
                                  _P, _P, _P]),
 }

@@ -571,14 +571,25 @@ k_fit_update(int n, float* __restrict__ xyz_raw, float* __restrict__ chol_raw, f
              float* __restrict__ adan, float* __restrict__ grads, float half_w, float half_h, int tx, int ty,
              AdanHyper h, int32_t* status, const double* loss_this, double* loss_next,
              float* __restrict__ grads_out, int cap, int next_step, int32_t* tile_count,
-             int32_t* __restrict__ tile_off, gs2d_fit_report* report_host, int row0, int row1, int loss_in_grads) {
+             int32_t* __restrict__ tile_off, gs2d_fit_report* report_host, int row0, int row1, int loss_in_grads,
+             const float* const* __restrict__ peer_grads, int num_peers, float* __restrict__ grads_zero) {
     __shared__ int sh[8];
     __shared__ int s_last;
     const int i = blockIdx.x * kFitThreads + threadIdx.x;
     if (i == 0 && report_host) {
         // the step's result straight into pinned host memory (no copy to issue, nothing to wait
         // for but the kernel itself); written before the scan below replaces status[0]
-        report_host->loss_sum = loss_in_grads ? (double)grads[9] : *loss_this;
+        double ls = *loss_this;
+        if (loss_in_grads) {
+            if (num_peers > 0) {
+                float acc = 0.f;
+                for (int r = 0; r < num_peers; ++r) acc += __ldcg(peer_grads[r] + 9);
+                ls = (double)acc;
+            } else {
+                ls = (double)grads[9];
+            }
+        }
+        report_host->loss_sum = ls;
         report_host->num_intersects = status[kStNumIntersects];
         report_host->overflow_step = status[kStOverflow];
         report_host->max_per_tile = status[kStMaxPerTile];
@@ -591,10 +602,29 @@ k_fit_update(int n, float* __restrict__ xyz_raw, float* __restrict__ chol_raw, f
     if (i < n) {
         Proj2d p; float2 m; float3 L;
         fit_project(i, xyz_raw, chol_raw, 1, half_w, half_h, tx, ty, p, m, L);
-        float4* grow = reinterpret_cast<float4*>(grads + (size_t)i * 12);
-        const float4 g0 = grow[0], g1 = grow[1];   // v_xy(2) v_conic(3) v_rgb(3) | v_opacity(1) pad(3) unused here
-        const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
-        grow[0] = z; grow[1] = z; grow[2] = z;
+        float4 g0, g1;   // v_xy(2) v_conic(3) v_rgb(3) | v_opacity(1) pad(3) unused here
+        if (num_peers > 0) {
+            // spatial mode over peer memory: the all-reduce IS this read -- every rank sums the
+            // ranks' gradient rows (NVLink peer loads) in rank order, so all ranks compute
+            // bit-identical updates with no collective kernel and no extra pass over the rows
+            g0 = make_float4(0.f, 0.f, 0.f, 0.f);
+            g1 = g0;
+            for (int r = 0; r < num_peers; ++r) {
+                const float4* prow = reinterpret_cast<const float4*>(peer_grads[r] + (size_t)i * 12);
+                const float4 a = __ldcg(prow), b = __ldcg(prow + 1);
+                g0.x += a.x; g0.y += a.y; g0.z += a.z; g0.w += a.w;
+                g1.x += b.x; g1.y += b.y; g1.z += b.z; g1.w += b.w;
+            }
+        } else {
+            const float4* grow = reinterpret_cast<const float4*>(grads + (size_t)i * 12);
+            g0 = grow[0]; g1 = grow[1];
+        }
+        {   // re-zero a gradient row for a later step: this step's buffer, or (peer exchange) the
+            // OTHER buffer of the pair, which no peer can still be reading (see SpatialFrameFit)
+            float4* zrow = reinterpret_cast<float4*>((grads_zero ? grads_zero : grads) + (size_t)i * 12);
+            const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
+            zrow[0] = z; zrow[1] = z; zrow[2] = z;
+        }
         float g[8] = {0.f, 0.f, 0.f, 0.f, 0.f, g1.y, g1.z, g1.w};   // xyz(2) chol(3) feat(3)
         if (p.ok && (int)p.radius > 0) {   // backward2d.cu:23-25
             const float3 vc = conic_vjp(p.conic, make_float3(g0.z, g0.w, g1.x));
@@ -712,9 +742,9 @@ static int launch_bin(int n, const float* xyz, const float* chol, const float* f
 int gs2d_fit_step_band(int n, int cap, int img_h, int img_w, float* xyz_raw, float* chol_raw, float* features,
                        float* adan_state, const void* target, int target_format, void* work, size_t work_bytes,
                        int step, float lr, float beta1, float beta2, float beta3, float eps, float weight_decay,
-                       int precounted, int tile_row_begin, int tile_row_end, int phases, float* out_img,
-                       float* param_grads_out, int32_t* ids_sorted_out, gs2d_fit_report* report_host,
-                       gs2d_stream_t stream) {
+                       int precounted, int tile_row_begin, int tile_row_end, int phases,
+                       const gs2d_grad_exchange* exchange, float* out_img, float* param_grads_out,
+                       int32_t* ids_sorted_out, gs2d_fit_report* report_host, gs2d_stream_t stream) {
     gs2d_fit_layout L;
     int rc = fit_layout(n, cap, img_h, img_w, &L);
     if (rc != GS2D_OK) return rc;
@@ -736,6 +766,18 @@ int gs2d_fit_step_band(int n, int cap, int img_h, int img_w, float* xyz_raw, flo
     int32_t* status = (int32_t*)(w + L.off_status);
     double* loss = (double*)(w + L.off_loss);
     float* grads = (float*)(w + L.off_grads);
+    const float* const* peer_grads = nullptr;
+    int num_peers = 0;
+    float* grads_zero = nullptr;
+    if (exchange) {
+        GS2D_REQUIRE(exchange->accumulate != nullptr, "fit_step: exchange without an accumulate buffer");
+        GS2D_REQUIRE(exchange->num_peers >= 0 && (exchange->num_peers == 0 || exchange->peers != nullptr),
+                     "fit_step: bad peer list");
+        grads = exchange->accumulate;
+        peer_grads = exchange->peers;
+        num_peers = exchange->num_peers;
+        grads_zero = exchange->zero;
+    }
     if (phases & GS2D_FIT_PHASE_GRADS) {
         GS2D_REQUIRE(target != nullptr, "fit_step: null target");
         rc = launch_bin(n, xyz_raw, chol_raw, features, nullptr, 1, img_h, img_w, row0, row1, cap, step, L, w, s,
@@ -770,7 +812,7 @@ int gs2d_fit_step_band(int n, int cap, int img_h, int img_w, float* xyz_raw, flo
             n, xyz_raw, chol_raw, features, adan_state, grads, half_w, half_h, tx, ty, h, status,
             loss + (step % GS2D_FIT_LOSS_SLOTS), loss + ((step + 1) % GS2D_FIT_LOSS_SLOTS), param_grads_out, cap,
             step + 1, (int32_t*)(w + L.off_tile_count), (int32_t*)(w + L.off_tile_off), report_host, row0, row1,
-            banded ? 1 : 0);
+            banded ? 1 : 0, peer_grads, num_peers, grads_zero);
         GS2D_CHECK_LAUNCH("fit_update");
     }
     return GS2D_OK;
@@ -784,7 +826,7 @@ int gs2d_fit_step(int n, int cap, int img_h, int img_w, float* xyz_raw, float* c
     GS2D_REQUIRE(img_h > 0, "fit_step: bad sizes");
     return gs2d_fit_step_band(n, cap, img_h, img_w, xyz_raw, chol_raw, features, adan_state, target, target_format,
                               work, work_bytes, step, lr, beta1, beta2, beta3, eps, weight_decay, precounted, 0,
-                              div_up(img_h, GS2D_TILE), GS2D_FIT_PHASE_GRADS | GS2D_FIT_PHASE_UPDATE, out_img,
+                              div_up(img_h, GS2D_TILE), GS2D_FIT_PHASE_GRADS | GS2D_FIT_PHASE_UPDATE, nullptr, out_img,
                               param_grads_out, ids_sorted_out, report_host, stream);
 }
 

@@ -347,14 +347,23 @@ class SpatialFrameFit(FusedFrameFit):
     bands: list of (row_begin, row_end) per rank (default: equal split); `emulate_world` runs all
     bands in this one process on one GPU and sums in place of the all-reduce (tests)."""
 
-    path_name = "tile-row bands per rank; scatter-pack + tile kernel on the band, NCCL all-reduce of the [N,12] gradient rows, replicated update"
+    path_name = "tile-row bands per rank; scatter-pack + tile kernel on the band, gradient rows summed across ranks, replicated update"
 
-    def __init__(self, H, W, num_points, device, group=None, bands=None, emulate_world: int = 0, **kw):
+    def __init__(self, H, W, num_points, device, group=None, bands=None, emulate_world: int = 0,
+                 exchange: str = "nccl", **kw):
+        """exchange: "nccl" -- one all-reduce call on the gradient rows between the two phases;
+        "peer" -- the rows live in symmetric (peer-mapped) memory and the update kernel itself sums
+        them over NVLink in rank order after a device-side barrier: no collective kernel, no extra
+        pass over the rows, bit-identical results on every rank by construction."""
         super().__init__(H, W, num_points, device, **kw)
+        import ctypes
         import torch.distributed as dist
-        self._dist = dist
+        self._dist, self._ctypes = dist, ctypes
         self.group = group
         self.emulate_world = int(emulate_world)
+        if exchange not in ("nccl", "peer"):
+            raise ValueError("exchange must be 'nccl' or 'peer'")
+        self.exchange = exchange
         if self.emulate_world:
             self.world, self.rank = self.emulate_world, 0
         else:
@@ -366,8 +375,44 @@ class SpatialFrameFit(FusedFrameFit):
             raise ValueError("bands must tile [0, tile_rows) contiguously, one per rank")
         lay = self.layout
         self._grads = self.work[lay.off_grads:lay.off_grads + self.n * 48].view(torch.float32)
+        self._hdl = None
+        if exchange == "peer":
+            self._setup_peer_buffers()
 
-    def _band_call(self, gt, fmt, band, phases, precounted, dbg):
+    def _setup_peer_buffers(self):
+        dev, n = self.device, self.n
+        row_bytes = n * 48
+        if self.emulate_world:
+            # one process, one GPU: every emulated rank gets its own pair of buffers
+            self._xbuf = torch.zeros((self.world, 2, n, 12), dtype=torch.float32, device=dev)
+            ptrs = [[self._xbuf[r, b].data_ptr() for r in range(self.world)] for b in range(2)]
+            self._own = [[self._xbuf[r, b].data_ptr() for b in range(2)] for r in range(self.world)]
+        else:
+            import torch.distributed._symmetric_memory as symm
+            grp = self.group if self.group is not None else self._dist.group.WORLD
+            self._xbuf = symm.empty((2, n, 12), dtype=torch.float32, device=dev)
+            self._xbuf.zero_()
+            self._hdl = symm.rendezvous(self._xbuf, grp)
+            base = [int(p) for p in self._hdl.buffer_ptrs]
+            ptrs = [[base[r] + b * row_bytes for r in range(self.world)] for b in range(2)]
+            self._own = [[base[self.rank] + b * row_bytes for b in range(2)]]
+            torch.cuda.current_stream(dev).synchronize()
+            self._hdl.barrier(channel=0)            # every rank's buffers are zero before anyone adds
+        self._peer_lists = torch.tensor(ptrs, dtype=torch.int64, device=dev)   # [2][world] device pointers
+
+    def _exchange_struct(self, rank_slot: int, with_peers: bool):
+        """gs2d_grad_exchange for this step: accumulate into buffer step&1, zero the other one"""
+        if self.exchange != "peer":
+            return None
+        x = self.step_index & 1
+        ex = self._lib.GradExchange()
+        ex.accumulate = self._own[rank_slot][x]
+        ex.peers = self._peer_lists[x].data_ptr() if with_peers else None
+        ex.num_peers = self.world if with_peers else 0
+        ex.zero = self._own[rank_slot][1 - x]
+        return ex
+
+    def _band_call(self, gt, fmt, band, phases, precounted, dbg, ex=None):
         b1, b2, b3 = self.betas
         slot = self.step_index % self._lib.FIT_LOSS_SLOTS
         out_img, grads_out, ids_out = dbg.get("out_img"), dbg.get("grads_out"), dbg.get("ids_out")
@@ -375,7 +420,8 @@ class SpatialFrameFit(FusedFrameFit):
             self.n, self.cap, self.H, self.W, self._xyz.data_ptr(), self._cholesky.data_ptr(),
             self._features_dc.data_ptr(), self.adan_state.data_ptr(), gt.data_ptr(), fmt, self.work.data_ptr(),
             self.layout.total_bytes, self.step_index, self.current_lr(), b1, b2, b3, self.eps, self.weight_decay,
-            1 if precounted else 0, band[0], band[1], phases, None if out_img is None else out_img.data_ptr(),
+            1 if precounted else 0, band[0], band[1], phases,
+            None if ex is None else self._ctypes.addressof(ex), None if out_img is None else out_img.data_ptr(),
             None if grads_out is None else grads_out.data_ptr(), None if ids_out is None else ids_out.data_ptr(),
             self._report_ptr + 24 * slot, torch.cuda.current_stream(self.device).cuda_stream), "fit_step_band")
 
@@ -383,15 +429,24 @@ class SpatialFrameFit(FusedFrameFit):
         self.step_index += 1
         G, U = self._lib.FIT_PHASE_GRADS, self._lib.FIT_PHASE_UPDATE
         if self.emulate_world:
-            for band in self.bands:                      # every "rank" adds into the one gradient buffer
-                self._band_call(gt, fmt, band, G, False, dbg)
-            self._band_call(gt, fmt, self.bands[0], U, False, dbg)
+            for r, band in enumerate(self.bands):        # every "rank" adds into its (or the one) gradient buffer
+                self._band_call(gt, fmt, band, G, False, dbg, self._exchange_struct(r, False))
+            ex = self._exchange_struct(0, True)
+            self._band_call(gt, fmt, self.bands[0], U, False, dbg, ex)
+            if self.exchange == "peer":                  # the other emulated ranks re-zero their buffers too
+                x = self.step_index & 1
+                self._xbuf[1:, 1 - x].zero_()
             self._counted_for = None                     # the pre-count covered band 0 only
             return
         band = self.bands[self.rank]
-        self._band_call(gt, fmt, band, G, self._precount_valid(), dbg)
-        self._dist.all_reduce(self._grads, op=self._dist.ReduceOp.SUM, group=self.group)
-        self._band_call(gt, fmt, band, U, False, dbg)
+        if self.exchange == "peer":
+            self._band_call(gt, fmt, band, G, self._precount_valid(), dbg, self._exchange_struct(0, False))
+            self._hdl.barrier(channel=0)                 # device-side, on the current stream: all bands are in
+            self._band_call(gt, fmt, band, U, False, dbg, self._exchange_struct(0, True))
+        else:
+            self._band_call(gt, fmt, band, G, self._precount_valid(), dbg)
+            self._dist.all_reduce(self._grads, op=self._dist.ReduceOp.SUM, group=self.group)
+            self._band_call(gt, fmt, band, U, False, dbg)
         self._counted_for = self._versions()
 
     @torch.no_grad()

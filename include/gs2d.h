@@ -240,12 +240,27 @@ int gs2d_fit_step(int n, int cap, int img_h, int img_w, float* xyz_raw, float* c
  * bit-identical parameters.  gs2d_fit_step == full band, both phases. */
 #define GS2D_FIT_PHASE_GRADS 1
 #define GS2D_FIT_PHASE_UPDATE 2
+/* Optional: exchange the gradients through peer-mapped memory (NVLink / NVSwitch) instead of a
+ * collective call.  The tile kernel accumulates into `accumulate` (this rank's buffer for this
+ * step, fp32 [n][12], zero on entry); after a cross-rank barrier issued by the caller on the same
+ * stream, the UPDATE phase reads row i of every buffer in `peers` (a DEVICE array of num_peers
+ * device pointers, own buffer included, all mapped into this rank's address space) in list order
+ * and sums them -- the all-reduce is that read, fused into the per-Gaussian update kernel -- and
+ * re-zeroes row i of `zero`.  With two buffers per rank used alternately (accumulate = buf[step&1],
+ * zero = buf[(step+1)&1]) one barrier per step suffices: a buffer is only re-zeroed two steps
+ * after peers read it.  exchange == NULL: gradients live in the workspace (off_grads). */
+typedef struct {
+    float* accumulate;
+    const float* const* peers;
+    int num_peers;
+    float* zero;
+} gs2d_grad_exchange;
 int gs2d_fit_step_band(int n, int cap, int img_h, int img_w, float* xyz_raw, float* chol_raw, float* features,
                        float* adan_state, const void* target, int target_format, void* work, size_t work_bytes,
                        int step, float lr, float beta1, float beta2, float beta3, float eps, float weight_decay,
-                       int precounted, int tile_row_begin, int tile_row_end, int phases, float* out_img,
-                       float* param_grads_out, int32_t* ids_sorted_out, gs2d_fit_report* report_host,
-                       gs2d_stream_t stream);
+                       int precounted, int tile_row_begin, int tile_row_end, int phases,
+                       const gs2d_grad_exchange* exchange, float* out_img, float* param_grads_out,
+                       int32_t* ids_sorted_out, gs2d_fit_report* report_host, gs2d_stream_t stream);
 /* Render-only (decode): project_gaussians_2d + rasterize_gaussians_sum forward of the reference
  * (GaussianSplats_Represent.py:83-90) as three kernels, sync-free.  activate != 0: inputs are
  * the raw parameters (tanh / bound applied here); else means2d / L_elements as the projection

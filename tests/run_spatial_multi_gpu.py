@@ -1,8 +1,9 @@
 """Multi-GPU check of the spatial mode (run under torchrun on N GPUs of one box):
     python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 \
         --master-port 29533 tests/run_spatial_multi_gpu.py [--h 2160 --w 3840 --n 200000 --iters 20]
-Every rank fits the same frame on its band of tile rows with one NCCL all-reduce of the gradient
-rows per iteration; rank 0 also runs the whole-frame fit alone and compares losses / parameters,
+Every rank fits the same frame on its band of tile rows; the gradient rows are summed across ranks
+either by one NCCL all-reduce per iteration (--exchange nccl) or inside the update kernel through
+peer-mapped memory (--exchange peer); rank 0 also runs the whole-frame fit alone and compares losses / parameters,
 then prints one JSON line with the timing of both (CUDA events, max over ranks)."""
 import argparse
 import json
@@ -22,6 +23,7 @@ def main():
     ap.add_argument("--n", type=int, default=200_000)
     ap.add_argument("--iters", type=int, default=50)
     ap.add_argument("--warmup", type=int, default=10)
+    ap.add_argument("--exchange", default="nccl", choices=["nccl", "peer"])
     a = ap.parse_args()
     rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
     torch.cuda.set_device(local)
@@ -32,7 +34,7 @@ def main():
 
     init = synth.gaussians(a.n, seed=1)
     gt = (synth.target_frame(a.h, a.w)[0] * 255).round().to(torch.uint8).permute(1, 2, 0).contiguous().to(dev)
-    fit = SpatialFrameFit(a.h, a.w, a.n, dev, init=init)
+    fit = SpatialFrameFit(a.h, a.w, a.n, dev, init=init, exchange=a.exchange)
     fit.train_iters(gt, a.warmup)
     dist.barrier(); torch.cuda.synchronize()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -60,10 +62,10 @@ def main():
         ref_ms = e0.elapsed_time(e1) / a.iters
         ref_loss = ref.loss()
         d = (ref._features_dc - fit._features_dc).abs()
-        out = {"world": world, "H": a.h, "W": a.w, "gaussians": a.n, "iters": a.iters, "bands": fit.bands,
+        out = {"world": world, "exchange": a.exchange, "H": a.h, "W": a.w, "gaussians": a.n, "iters": a.iters, "bands": fit.bands,
                "spatial_ms_per_iter": float(ms), "single_gpu_ms_per_iter": ref_ms, "speedup": ref_ms / float(ms),
                "loss_spatial": loss, "loss_single": ref_loss, "params_identical_across_ranks": identical,
-               "median_abs_param_diff_vs_single": float(d.median()), "allreduce_bytes": a.n * 48}
+               "median_abs_param_diff_vs_single": float(d.median()), "exchange_bytes_per_rank": a.n * 48}
         assert identical, "ranks diverged"
         assert abs(loss - ref_loss) <= 2e-3 * ref_loss, (loss, ref_loss)
         print(json.dumps(out), flush=True)

@@ -305,14 +305,17 @@ def test_fit_stream_equals_resident_loop():
     assert a.step_index == K
 
 
+@pytest.mark.parametrize("exchange", ["nccl", "peer"])
 @pytest.mark.parametrize("H,W,n,world", [(256, 256, 10_000, 2), (200, 328, 3_000, 3), (1080, 1920, 50_000, 4)])
-def test_tile_row_bands_sum_to_the_whole_frame(H, W, n, world):
+def test_tile_row_bands_sum_to_the_whole_frame(H, W, n, world, exchange):
     """spatial mode on ONE GPU: every band's gradients (and loss) added into the same buffer in
     place of the all-reduce must reproduce the whole-frame step"""
     from gsvc_b200.fit import SpatialFrameFit
     from gsvc_b200 import synth
     init, gt, full = _setup(H, W, n, seed=17)
-    banded = SpatialFrameFit(H, W, n, cuda, init=init, emulate_world=world)
+    # "nccl": all bands add into one buffer (what the all-reduce would produce); "peer": one buffer
+    # per emulated rank, summed in rank order inside the update kernel (the NVLink exchange path)
+    banded = SpatialFrameFit(H, W, n, cuda, init=init, emulate_world=world, exchange=exchange)
     gtd = gt.to(cuda)
     ga = torch.empty((n, 8), device=cuda)
     gb = torch.empty((n, 8), device=cuda)
