@@ -52,6 +52,13 @@ class GradExchange(Structure):
     _fields_ = [("accumulate", c_void_p), ("peers", c_void_p), ("num_peers", c_int), ("zero", c_void_p)]
 
 
+class FitOptions(Structure):
+    """mirror of gs2d_fit_options (include/gs2d.h)"""
+
+    _fields_ = [("rgb_w", c_void_p), ("adan_state_w", c_void_p), ("rgb_w_grad_out", c_void_p), ("adan_step", c_int),
+                ("adan_fresh", c_int), ("skip_update", c_int)]
+
+
 FIT_LOSS_SLOTS = 64
 TARGET_F32_CHW, TARGET_U8_HWC = 0, 1
 FIT_PHASE_GRADS, FIT_PHASE_UPDATE = 1, 2
@@ -87,7 +94,9 @@ _SIGNATURES = {
                               c_float, c_float, c_float, c_float, c_float, c_float, c_int, _P, _P, _P, _P, _P]),
     "gs2d_fit_step_band": (c_int, [c_int, c_int, c_int, c_int, _P, _P, _P, _P, _P, c_int, _P, c_size_t, c_int,
                                    c_float, c_float, c_float, c_float, c_float, c_float, c_int, c_int, c_int, c_int,
-                                   _P, _P, _P, _P, _P, _P]),
+                                   _P, _P, _P, _P, _P, _P, _P]),
+    "gs2d_prune_scratch_bytes": (c_size_t, [c_int]),
+    "gs2d_prune_lowest": (c_int, [c_int, c_int, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, c_size_t, _P]),
     "gs2d_render_chol": (c_int, [c_int, c_int, c_int, c_int, _P, _P, _P, _P, c_int, _P, c_size_t, _P, c_int, c_int,
                                  _P, _P, _P]),
 }

@@ -184,7 +184,8 @@ k_fit_count(int n, const float* __restrict__ xyz_raw, const float* __restrict__ 
 // ------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(kFitThreads)
 k_fit_scatter(int n, const float* __restrict__ xyz_raw, const float* __restrict__ chol_raw,
-              const float* __restrict__ feat, const float* __restrict__ opac, int activate, float half_w, float half_h,
+              const float* __restrict__ feat, const float* __restrict__ opac, const float* __restrict__ rgb_w,
+              int activate, float half_w, float half_h,
               int tx, int ty, int row0, int row1, int W, int H, const int32_t* __restrict__ tile_off,
               int32_t* tile_fill, const int32_t* __restrict__ status, float4* __restrict__ packed) {
     if (status[kStOverflow] != 0) return;
@@ -194,7 +195,9 @@ k_fit_scatter(int n, const float* __restrict__ xyz_raw, const float* __restrict_
     fit_project(i, xyz_raw, chol_raw, activate, half_w, half_h, tx, ty, p, m, L);
     if (p.nth <= 0) return;
     const float o = opac ? opac[i] : 1.f;
-    const float r = feat[3 * i], g = feat[3 * i + 1], b = feat[3 * i + 2];
+    // colours = _features_dc * rgb_W (GaussianSplats_Represent.py:62-63); plain fp32 products
+    const float cw = rgb_w ? rgb_w[i] : 1.f;
+    const float r = mulf(feat[3 * i], cw), g = mulf(feat[3 * i + 1], cw), b = mulf(feat[3 * i + 2], cw);
     for (int y = max(p.y0, row0); y < min(p.y1, row1); ++y)
         for (int x = p.x0; x < p.x1; ++x) {
             const int t = y * tx + x;
@@ -572,7 +575,9 @@ k_fit_update(int n, float* __restrict__ xyz_raw, float* __restrict__ chol_raw, f
              AdanHyper h, int32_t* status, const double* loss_this, double* loss_next,
              float* __restrict__ grads_out, int cap, int next_step, int32_t* tile_count,
              int32_t* __restrict__ tile_off, gs2d_fit_report* report_host, int row0, int row1, int loss_in_grads,
-             const float* const* __restrict__ peer_grads, int num_peers, float* __restrict__ grads_zero) {
+             const float* const* __restrict__ peer_grads, int num_peers, float* __restrict__ grads_zero,
+             float* __restrict__ rgb_w, float* __restrict__ adan_w, float* __restrict__ rgb_w_grad_out,
+             int skip_update) {
     __shared__ int sh[8];
     __shared__ int s_last;
     const int i = blockIdx.x * kFitThreads + threadIdx.x;
@@ -626,6 +631,13 @@ k_fit_update(int n, float* __restrict__ xyz_raw, float* __restrict__ chol_raw, f
             zrow[0] = z; zrow[1] = z; zrow[2] = z;
         }
         float g[8] = {0.f, 0.f, 0.f, 0.f, 0.f, g1.y, g1.z, g1.w};   // xyz(2) chol(3) feat(3)
+        float gw = 0.f, cw = 1.f;
+        if (rgb_w) {   // colours = feat * w: d feat = d colour * w, d w = <d colour, feat>
+            cw = rgb_w[i];
+            gw = g1.y * feat[3 * i] + g1.z * feat[3 * i + 1] + g1.w * feat[3 * i + 2];
+            g[5] = g1.y * cw; g[6] = g1.z * cw; g[7] = g1.w * cw;
+            if (rgb_w_grad_out) rgb_w_grad_out[i] = gw;
+        }
         if (p.ok && (int)p.radius > 0) {   // backward2d.cu:23-25
             const float3 vc = conic_vjp(p.conic, make_float3(g0.z, g0.w, g1.x));
             const float3 vl = chol_vjp(L.x, L.y, L.z, vc);
@@ -638,6 +650,7 @@ k_fit_update(int n, float* __restrict__ xyz_raw, float* __restrict__ chol_raw, f
 #pragma unroll
             for (int k = 0; k < 8; ++k) grads_out[(size_t)i * 8 + k] = g[k];
         }
+        if (skip_update) return;   // uniform over the grid: nobody reaches the scan below
         float par[8] = {xyz_raw[2 * i], xyz_raw[2 * i + 1], chol_raw[3 * i], chol_raw[3 * i + 1], chol_raw[3 * i + 2],
                         feat[3 * i], feat[3 * i + 1], feat[3 * i + 2]};
         const size_t plane = (size_t)n * 8;
@@ -659,6 +672,11 @@ k_fit_update(int n, float* __restrict__ xyz_raw, float* __restrict__ chol_raw, f
         xyz_raw[2 * i] = par[0]; xyz_raw[2 * i + 1] = par[1];
         chol_raw[3 * i] = par[2]; chol_raw[3 * i + 1] = par[3]; chol_raw[3 * i + 2] = par[4];
         feat[3 * i] = par[5]; feat[3 * i + 1] = par[6]; feat[3 * i + 2] = par[7];
+        if (rgb_w) {
+            float wm = adan_w[i], wn = adan_w[(size_t)n + i], wd = adan_w[2 * (size_t)n + i], wp = adan_w[3 * (size_t)n + i];
+            rgb_w[i] = adan_one(cw, gw, wm, wn, wd, wp, h);
+            adan_w[i] = wm; adan_w[(size_t)n + i] = wn; adan_w[2 * (size_t)n + i] = wd; adan_w[3 * (size_t)n + i] = wp;
+        }
         // the next iteration's binning starts here: project the updated parameters and count tiles
         // (same arithmetic as k_fit_count / k_fit_scatter, so the ranges match what scatter fills)
         Proj2d pn;
@@ -666,6 +684,7 @@ k_fit_update(int n, float* __restrict__ xyz_raw, float* __restrict__ chol_raw, f
                      half_h, tx, ty, pn);
         count_tiles(pn, tx, row0, row1, tile_count);
     }
+    if (skip_update) return;
     scan_tiles_by_last_block(tx, ty, cap, next_step, tile_count, tile_off, status, sh, &s_last);
 }
 
@@ -714,7 +733,8 @@ int gs2d_fit_init(int n, int cap, int img_h, int img_w, void* work, size_t work_
     return GS2D_OK;
 }
 
-static int launch_bin(int n, const float* xyz, const float* chol, const float* feat, const float* opac, int activate,
+static int launch_bin(int n, const float* xyz, const float* chol, const float* feat, const float* opac,
+                      const float* rgb_w, int activate,
                       int img_h, int img_w, int row0, int row1, int cap, int step, const gs2d_fit_layout& L, char* w,
                       cudaStream_t s, bool precounted = false) {
     const int tx = div_up(img_w, GS2D_TILE), ty = div_up(img_h, GS2D_TILE);
@@ -731,8 +751,8 @@ static int launch_bin(int n, const float* xyz, const float* chol, const float* f
     }
     {
         ProfScope ps_(GS2D_STAGE_EDGES_PACK, s);
-        k_fit_scatter<<<blocks, kFitThreads, 0, s>>>(n, xyz, chol, feat, opac, activate, half_w, half_h, tx, ty, row0,
-                                                     row1, img_w, img_h, tile_off, tile_count, status,
+        k_fit_scatter<<<blocks, kFitThreads, 0, s>>>(n, xyz, chol, feat, opac, rgb_w, activate, half_w, half_h, tx, ty,
+                                                     row0, row1, img_w, img_h, tile_off, tile_count, status,
                                                      (float4*)(w + L.off_packed));
         GS2D_CHECK_LAUNCH("fit_scatter");
     }
@@ -743,8 +763,9 @@ int gs2d_fit_step_band(int n, int cap, int img_h, int img_w, float* xyz_raw, flo
                        float* adan_state, const void* target, int target_format, void* work, size_t work_bytes,
                        int step, float lr, float beta1, float beta2, float beta3, float eps, float weight_decay,
                        int precounted, int tile_row_begin, int tile_row_end, int phases,
-                       const gs2d_grad_exchange* exchange, float* out_img, float* param_grads_out,
-                       int32_t* ids_sorted_out, gs2d_fit_report* report_host, gs2d_stream_t stream) {
+                       const gs2d_grad_exchange* exchange, const gs2d_fit_options* options, float* out_img,
+                       float* param_grads_out, int32_t* ids_sorted_out, gs2d_fit_report* report_host,
+                       gs2d_stream_t stream) {
     gs2d_fit_layout L;
     int rc = fit_layout(n, cap, img_h, img_w, &L);
     if (rc != GS2D_OK) return rc;
@@ -778,9 +799,19 @@ int gs2d_fit_step_band(int n, int cap, int img_h, int img_w, float* xyz_raw, flo
         num_peers = exchange->num_peers;
         grads_zero = exchange->zero;
     }
+    float* rgb_w = nullptr; float* adan_w = nullptr; float* rgb_w_grad_out = nullptr;
+    int adan_step = step, adan_fresh = step == 1, skip_update = 0;
+    if (options) {
+        GS2D_REQUIRE(options->rgb_w == nullptr || options->adan_state_w != nullptr,
+                     "fit_step: rgb_w without its optimizer state");
+        GS2D_REQUIRE(options->adan_step >= 0, "fit_step: negative adan_step");
+        rgb_w = options->rgb_w; adan_w = options->adan_state_w; rgb_w_grad_out = options->rgb_w_grad_out;
+        if (options->adan_step > 0) { adan_step = options->adan_step; adan_fresh = options->adan_fresh != 0; }
+        skip_update = options->skip_update != 0;
+    }
     if (phases & GS2D_FIT_PHASE_GRADS) {
         GS2D_REQUIRE(target != nullptr, "fit_step: null target");
-        rc = launch_bin(n, xyz_raw, chol_raw, features, nullptr, 1, img_h, img_w, row0, row1, cap, step, L, w, s,
+        rc = launch_bin(n, xyz_raw, chol_raw, features, nullptr, rgb_w, 1, img_h, img_w, row0, row1, cap, step, L, w, s,
                         precounted != 0);
         if (rc != GS2D_OK) return rc;
         const float grad_scale = (float)(2.0 / (3.0 * (double)img_h * (double)img_w));   // the WHOLE frame's mean
@@ -801,18 +832,18 @@ int gs2d_fit_step_band(int n, int cap, int img_h, int img_w, float* xyz_raw, flo
     if (phases & GS2D_FIT_PHASE_UPDATE) {
         AdanHyper h;
         h.b1 = beta1; h.b2 = beta2; h.b3 = beta3;
-        h.step_size = (float)((double)lr / (1.0 - pow((double)beta1, step)));
-        h.step_size_diff = (float)((double)lr * (double)beta2 / (1.0 - pow((double)beta2, step)));
-        h.inv_bc3_sqrt = (float)(1.0 / sqrt(1.0 - pow((double)beta3, step)));
+        h.step_size = (float)((double)lr / (1.0 - pow((double)beta1, adan_step)));
+        h.step_size_diff = (float)((double)lr * (double)beta2 / (1.0 - pow((double)beta2, adan_step)));
+        h.inv_bc3_sqrt = (float)(1.0 / sqrt(1.0 - pow((double)beta3, adan_step)));
         h.eps = eps;
         h.decay_div = 1.f + lr * weight_decay;
-        h.first = step == 1;
+        h.first = adan_fresh;
         ProfScope ps_(GS2D_STAGE_ADAN, s);
         k_fit_update<<<div_up(n, kFitThreads), kFitThreads, 0, s>>>(
             n, xyz_raw, chol_raw, features, adan_state, grads, half_w, half_h, tx, ty, h, status,
             loss + (step % GS2D_FIT_LOSS_SLOTS), loss + ((step + 1) % GS2D_FIT_LOSS_SLOTS), param_grads_out, cap,
             step + 1, (int32_t*)(w + L.off_tile_count), (int32_t*)(w + L.off_tile_off), report_host, row0, row1,
-            banded ? 1 : 0, peer_grads, num_peers, grads_zero);
+            banded ? 1 : 0, peer_grads, num_peers, grads_zero, rgb_w, adan_w, rgb_w_grad_out, skip_update);
         GS2D_CHECK_LAUNCH("fit_update");
     }
     return GS2D_OK;
@@ -826,8 +857,8 @@ int gs2d_fit_step(int n, int cap, int img_h, int img_w, float* xyz_raw, float* c
     GS2D_REQUIRE(img_h > 0, "fit_step: bad sizes");
     return gs2d_fit_step_band(n, cap, img_h, img_w, xyz_raw, chol_raw, features, adan_state, target, target_format,
                               work, work_bytes, step, lr, beta1, beta2, beta3, eps, weight_decay, precounted, 0,
-                              div_up(img_h, GS2D_TILE), GS2D_FIT_PHASE_GRADS | GS2D_FIT_PHASE_UPDATE, nullptr, out_img,
-                              param_grads_out, ids_sorted_out, report_host, stream);
+                              div_up(img_h, GS2D_TILE), GS2D_FIT_PHASE_GRADS | GS2D_FIT_PHASE_UPDATE, nullptr, nullptr,
+                              out_img, param_grads_out, ids_sorted_out, report_host, stream);
 }
 
 int gs2d_render_chol(int n, int cap, int img_h, int img_w, const float* means_or_xyz_raw, const float* chol,
@@ -843,7 +874,7 @@ int gs2d_render_chol(int n, int cap, int img_h, int img_w, const float* means_or
     cudaStream_t s = (cudaStream_t)stream;
     char* w = (char*)work;
     const int tx = div_up(img_w, GS2D_TILE), ty = div_up(img_h, GS2D_TILE);
-    rc = launch_bin(n, means_or_xyz_raw, chol, colors, opacities, activate, img_h, img_w, 0, ty, cap, 0, L, w, s);
+    rc = launch_bin(n, means_or_xyz_raw, chol, colors, opacities, nullptr, activate, img_h, img_w, 0, ty, cap, 0, L, w, s);
     if (rc != GS2D_OK) return rc;
     {
         ProfScope ps_(GS2D_STAGE_RASTER_FWD, s);

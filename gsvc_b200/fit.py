@@ -21,9 +21,17 @@ from .rasterize_sum import rasterize_gaussians_sum
 
 
 class FrameFit(torch.nn.Module):
+    """GaussianVideo_frame on the drop-in operators.  With isdensity / isremoval the colour weight
+    rgb_W is learnable and the prune / add control of GaussianSplats_Represent.py:98-172 runs
+    between backward() and the optimizer step, as train_iter :199-204 does (schedule:
+    gsvc_b200.density.DensityPlan)."""
+
     def __init__(self, H: int, W: int, num_points: int, device, lr: float = 1e-3, seed: int = 1,
-                 init: dict | None = None):
+                 init: dict | None = None, isdensity: bool = False, isremoval: bool = False,
+                 removal_rate: float = 0.1, max_num_points: int | None = None, densification_interval: int = 100,
+                 plan=None):
         super().__init__()
+        from .density import DensityPlan
         self.H, self.W = int(H), int(W)
         self.tile_bounds = ((self.W + 15) // 16, (self.H + 15) // 16, 1)
         self.device = torch.device(device)
@@ -34,11 +42,18 @@ class FrameFit(torch.nn.Module):
         self._xyz = torch.nn.Parameter(init["_xyz"].clone().to(self.device))
         self._cholesky = torch.nn.Parameter(init["_cholesky"].clone().to(self.device))
         self._features_dc = torch.nn.Parameter(init["_features_dc"].clone().to(self.device))
+        n = self._xyz.shape[0]
+        self.plan = plan or DensityPlan(max_num_points or n, removal_rate, densification_interval, isdensity, isremoval)
+        if self.plan.learns_rgb_w:      # :31-36
+            self.rgb_W = torch.nn.Parameter(torch.full((n, 1), self.plan.rgb_w_init, device=self.device))
+        else:
+            self.register_buffer("rgb_W", torch.ones((n, 1), device=self.device))
         self.register_buffer("cholesky_bound", torch.tensor([0.5, 0.0, 0.5], device=self.device).view(1, 3))
         self.register_buffer("background", torch.ones(3, device=self.device))
-        self.register_buffer("opacity", torch.ones(num_points, 1, device=self.device))
+        self.lr = lr
         self.optimizer = Adan(self.parameters(), lr=lr)
         self.scheduler = torch.optim.lr_scheduler.StepLR(self.optimizer, step_size=20000, gamma=0.5)
+        self.iter = 0
 
     path_name = "autograd drop-in ops (project_gaussians_2d + rasterize_gaussians_sum) + torch glue + foreach Adan"
 
@@ -47,21 +62,74 @@ class FrameFit(torch.nn.Module):
         from .rasterize_sum import _device_ctx
         return _device_ctx(self.device).last_num_intersects
 
+    @property
+    def get_features(self):
+        return self._features_dc * self.rgb_W      # :62-63
+
+    def _render(self, means2d, L_elements, colors):
+        """[H,W,3] unclamped; the one place that touches the operators (tests swap it out)"""
+        xys, depths, radii, conics, nth = project_gaussians_2d(means2d, L_elements, self.H, self.W, self.tile_bounds)
+        opacity = torch.ones(means2d.shape[0], 1, device=means2d.device)
+        return rasterize_gaussians_sum(xys, depths, radii, conics, nth, colors, opacity, self.H, self.W, 16, 16,
+                                       background=self.background, return_alpha=False)
+
     def forward(self):
-        xys, depths, radii, conics, nth = project_gaussians_2d(
-            torch.tanh(self._xyz), self._cholesky + self.cholesky_bound, self.H, self.W, self.tile_bounds)
-        out = rasterize_gaussians_sum(xys, depths, radii, conics, nth, self._features_dc, self.opacity, self.H,
-                                      self.W, 16, 16, background=self.background, return_alpha=False)
+        out = self._render(torch.tanh(self._xyz), self._cholesky + self.cholesky_bound, self.get_features)
         out = torch.clamp(out, 0, 1)
         return out.view(-1, self.H, self.W, 3).permute(0, 3, 1, 2).contiguous()
 
-    def train_iter(self, gt_image: torch.Tensor):
-        """one iteration of GaussianSplats_Represent.py:191-207 (no prune / add)"""
+    def _reattach(self):
+        for group in self.optimizer.param_groups:       # :115-116
+            group["params"] = [p for p in self.parameters() if p.requires_grad]
+
+    @torch.no_grad()
+    def _prune(self, count: int):
+        # torch.norm + torch.sort + boolean mask, :103-114.  torch.sort leaves the order of equal
+        # keys open; this package fixes it to lowest index first (as gs2d_prune_lowest does)
+        _, order = torch.sort(torch.norm(self.rgb_W, dim=1), stable=True)
+        keep = torch.ones(self._xyz.shape[0], dtype=torch.bool, device=self._xyz.device)
+        keep[order[:count]] = False
+        self.last_keep = keep
+        self._xyz = torch.nn.Parameter(self._xyz[keep])
+        self._cholesky = torch.nn.Parameter(self._cholesky[keep])
+        self._features_dc = torch.nn.Parameter(self._features_dc[keep])
+        self.rgb_W = torch.nn.Parameter(self.rgb_W[keep])
+
+    @torch.no_grad()
+    def _add(self, count: int):
+        # :134-144 -- drawn from the CPU generator in this order, then moved to the device
+        dev = self._xyz.device
+        new_xyz = torch.atanh(2 * (torch.rand(count, 2) - 0.5)).to(dev)
+        new_cholesky = torch.rand(count, 3).to(dev)
+        new_features_dc = torch.rand(count, 3).to(dev)
+        new_rgb_W = 0.01 * torch.ones(count, 1).to(dev)
+        self._xyz = torch.nn.Parameter(torch.cat((self._xyz, new_xyz), dim=0))
+        self._cholesky = torch.nn.Parameter(torch.cat((self._cholesky, new_cholesky), dim=0))
+        self._features_dc = torch.nn.Parameter(torch.cat((self._features_dc, new_features_dc), dim=0))
+        self.rgb_W = torch.nn.Parameter(torch.cat((self.rgb_W, new_rgb_W), dim=0))
+
+    def _control(self, it: int):
+        act = self.plan.action(it, self._xyz.shape[0])
+        if act.kind == "prune":
+            self._prune(act.count)
+        elif act.kind == "add":
+            self._add(act.count)
+        if act.rebuild:
+            self.optimizer = Adan(self.parameters(), lr=self.lr)       # update_optimizer(), :93-97
+        elif act.replaces_parameters:
+            self._reattach()
+        return act
+
+    def train_iter(self, gt_image: torch.Tensor, iter: int | None = None):
+        """one iteration of GaussianSplats_Represent.py:191-207"""
+        self.iter = self.iter + 1 if iter is None else int(iter)
         image = self.forward()
         loss = F.mse_loss(image, gt_image)
         loss.backward()
         with torch.no_grad():
             psnr = 10 * math.log10(1.0 / loss.item())
+        if self.plan.learns_rgb_w:
+            self._control(self.iter)
         self.optimizer.step()
         self.optimizer.zero_grad(set_to_none=True)
         self.scheduler.step()
@@ -421,7 +489,8 @@ class SpatialFrameFit(FusedFrameFit):
             self._features_dc.data_ptr(), self.adan_state.data_ptr(), gt.data_ptr(), fmt, self.work.data_ptr(),
             self.layout.total_bytes, self.step_index, self.current_lr(), b1, b2, b3, self.eps, self.weight_decay,
             1 if precounted else 0, band[0], band[1], phases,
-            None if ex is None else self._ctypes.addressof(ex), None if out_img is None else out_img.data_ptr(),
+            None if ex is None else self._ctypes.addressof(ex), None,
+            None if out_img is None else out_img.data_ptr(),
             None if grads_out is None else grads_out.data_ptr(), None if ids_out is None else ids_out.data_ptr(),
             self._report_ptr + 24 * slot, torch.cuda.current_stream(self.device).cuda_stream), "fit_step_band")
 

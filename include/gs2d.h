@@ -255,12 +255,51 @@ typedef struct {
     int num_peers;
     float* zero;
 } gs2d_grad_exchange;
+/* Optional extras of a step: the learnable colour weight and the optimizer bookkeeping that the
+ * reference's prune / add control needs (GaussianSplats_Represent.py:31-36 rgb_W, :62-67
+ * colours = _features_dc * rgb_W, :98-172 removal_control / adaptive_control).
+ *   rgb_w [n]            learnable per-Gaussian colour weight; NULL: weight 1, not a parameter
+ *   adan_state_w [4][n]  its Adan state (exp_avg, exp_avg_sq, exp_avg_diff, previous gradient)
+ *   rgb_w_grad_out [n]   parity tests: d loss / d rgb_w (may be NULL)
+ *   adan_step            the optimizer's group['step'] used for the bias corrections
+ *                        (optimizer.py:165-172); 0: use `step`.  It differs from the iteration
+ *                        number once update_optimizer() rebuilt the optimizer (:93-97)
+ *   adan_fresh           != 0: the optimizer state was (re)created since the last update, so the
+ *                        previous gradient := this gradient (optimizer.py:183-185; the state
+ *                        planes must have been zeroed by the caller).  Ignored when adan_step == 0
+ *                        (then `step == 1` decides, as gs2d_fit_step does)
+ *   skip_update          != 0: the UPDATE phase reports the loss and re-zeroes the gradient rows
+ *                        but leaves parameters and optimizer state untouched and does not
+ *                        pre-count the next step -- the reference's iterations in which the
+ *                        control replaced the parameter tensors after backward(), so that
+ *                        optimizer.step() saw no gradients (train_iter :199-204) */
+typedef struct {
+    float* rgb_w;
+    float* adan_state_w;
+    float* rgb_w_grad_out;
+    int adan_step;
+    int adan_fresh;
+    int skip_update;
+} gs2d_fit_options;
 int gs2d_fit_step_band(int n, int cap, int img_h, int img_w, float* xyz_raw, float* chol_raw, float* features,
                        float* adan_state, const void* target, int target_format, void* work, size_t work_bytes,
                        int step, float lr, float beta1, float beta2, float beta3, float eps, float weight_decay,
                        int precounted, int tile_row_begin, int tile_row_end, int phases,
-                       const gs2d_grad_exchange* exchange, float* out_img, float* param_grads_out,
-                       int32_t* ids_sorted_out, gs2d_fit_report* report_host, gs2d_stream_t stream);
+                       const gs2d_grad_exchange* exchange, const gs2d_fit_options* options, float* out_img,
+                       float* param_grads_out, int32_t* ids_sorted_out, gs2d_fit_report* report_host,
+                       gs2d_stream_t stream);
+/* The reference's prune (GaussianSplats_Represent.py:98-128, :147-171): drop the `remove_count`
+ * Gaussians with the smallest |rgb_w| (torch.norm over dim 1 of an [N,1] tensor, then torch.sort,
+ * :103-104 / :146-147; ties -- which torch.sort leaves unspecified -- go lowest index first) and
+ * compact the four parameter tensors in index order (boolean-mask indexing, :111-114).  Built
+ * from this library's own onesweep sort (32 key bits) and look-back scan plus two small kernels;
+ * sync-free.  Outputs hold n - remove_count rows and must not alias the inputs.  keep_index_out
+ * [n - remove_count] (may be NULL) receives the surviving rows' old indices.
+ * scratch: gs2d_prune_scratch_bytes(n). */
+size_t gs2d_prune_scratch_bytes(int n);
+int gs2d_prune_lowest(int n, int remove_count, const float* rgb_w, const float* xyz_raw, const float* chol_raw,
+                      const float* features, float* rgb_w_out, float* xyz_out, float* chol_out, float* features_out,
+                      int32_t* keep_index_out, void* scratch, size_t scratch_bytes, gs2d_stream_t stream);
 /* Render-only (decode): project_gaussians_2d + rasterize_gaussians_sum forward of the reference
  * (GaussianSplats_Represent.py:83-90) as three kernels, sync-free.  activate != 0: inputs are
  * the raw parameters (tanh / bound applied here); else means2d / L_elements as the projection

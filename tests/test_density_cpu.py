@@ -1,0 +1,98 @@
+"""CPU tests of the prune / add control (BASELINE config 4's "pruning and random add"):
+the schedule (gsvc_b200.density) and FrameFit's restatement of the control are replayed against
+trajectories recorded from the reference's own GaussianVideo_frame + Adan
+(tests/golden/make_golden_control.py -> tests/golden/control.npz)."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from tests import surrogate
+from gsvc_b200.density import Action, DensityPlan, OptimizerClock
+from gsvc_b200.fit import FrameFit
+
+G = np.load(os.path.join(os.path.dirname(__file__), "golden", "control.npz"))
+KEYS = ("_xyz", "_cholesky", "_features_dc", "rgb_W")
+
+
+class _SurrogateFit(FrameFit):
+    def _render(self, means2d, L_elements, colors):
+        xys, depths, radii, conics, nth = surrogate.project(means2d, L_elements, self.H, self.W, self.tile_bounds)
+        return surrogate.rasterize(xys, depths, radii, conics, nth, colors, torch.ones(means2d.shape[0], 1), self.H,
+                                   self.W)
+
+
+def _fit(mode):
+    init = {k: torch.from_numpy(G[f"{mode}.init.{k}"]) for k in KEYS}
+    n = init["_xyz"].shape[0]
+    kw = dict(isremoval=True, densification_interval=500) if mode == "removal" else dict(isdensity=True)
+    m = _SurrogateFit(8, 8, n, "cpu", init=init, max_num_points=48, removal_rate=0.25, **kw)
+    assert torch.equal(m.rgb_W.detach(), init["rgb_W"])        # 0.01 / ones, as the reference initialises it
+    return m
+
+
+@pytest.mark.parametrize("mode,iters", [("removal", 4100), ("density", 1100)])
+def test_framefit_control_reproduces_the_reference_class(mode, iters):
+    m = _fit(mode)
+    gt = torch.from_numpy(G["gt"])
+    torch.set_rng_state(torch.from_numpy(G[f"{mode}.rng_state"]))      # the add draws from the global CPU generator
+    ns = G[f"{mode}.n"]
+    losses = G[f"{mode}.loss"]
+    snaps = sorted(int(k.split(".")[1][2:]) for k in G.files if k.startswith(f"{mode}.it") and k.endswith("._xyz"))
+    for it in range(1, iters + 1):
+        loss, _ = m.train_iter(gt, it)
+        assert m._xyz.shape[0] == ns[it - 1], f"iteration {it}: Gaussian count"
+        assert float(loss.detach()) == pytest.approx(losses[it - 1], rel=2e-4, abs=1e-7), f"iteration {it}: loss"
+        if it in snaps:
+            for k in KEYS:
+                want = G[f"{mode}.it{it}.{k}"]
+                got = getattr(m, k).detach().numpy()
+                assert got.shape == want.shape, (it, k)
+                np.testing.assert_allclose(got, want, rtol=2e-3, atol=2e-5, err_msg=f"iteration {it}: {k}")
+
+
+def test_plan_matches_the_recorded_counts():
+    """the schedule alone (no model): Gaussian counts after every iteration"""
+    for mode, kw, n0 in (("removal", dict(isremoval=True, densification_interval=500), 48),
+                         ("density", dict(isdensity=True, densification_interval=100), 36)):
+        plan = DensityPlan(48, 0.25, **kw)
+        n = n0
+        for it, want in enumerate(G[f"{mode}.n"], start=1):
+            a = plan.action(it, n)
+            n += a.count if a.kind == "add" else -a.count if a.kind == "prune" else 0
+            assert n == want, (mode, it)
+
+
+def test_plan_actions_at_reference_defaults():
+    # train_video_Represent.py defaults: removal_rate 0.1, densification_interval 100
+    rm = DensityPlan(50_000, 0.1, 100, isremoval=True)
+    assert rm.action(50, 50_000) == Action()
+    assert rm.action(100, 50_000) == Action("prune", int(0.1 / 40 * 50_000))        # 125 per control step
+    assert rm.action(4000, 50_000 - 39 * 125) == Action("prune", 125, True)           # lands on max*(1-rate)
+    assert rm.action(4000, 45_000) == Action("none", 0, True)                         # nothing left to drop: rebuild only
+    assert rm.action(4100, 45_000) == Action()
+    ad = DensityPlan(50_000, 0.1, 100, isdensity=True)
+    assert ad.action(1, 45_000) == Action("add", 5000)
+    assert ad.action(100, 50_000) == Action() and ad.action(400, 50_000) == Action()
+    assert ad.action(500, 50_000) == Action("prune", 1000)
+    assert ad.action(900, 46_000) == Action("prune", 1000)
+    assert ad.action(1000, 45_000) == Action("none", 0, True)
+    assert ad.action(1100, 45_000) == Action()
+    assert DensityPlan(100, 0.1).action(100, 100) == Action()                         # neither mode: rgb_W is a buffer
+    assert not DensityPlan(100, 0.1).learns_rgb_w
+    with pytest.raises(ZeroDivisionError):                                            # int(500 / 600) == 0, as the reference
+        DensityPlan(100, 0.1, 600, isdensity=True).action(600, 100)
+
+
+def test_optimizer_clock():
+    c = OptimizerClock()
+    assert c.begin(Action()) == (1, True, False)                   # first step: previous gradient := gradient
+    assert c.begin(Action()) == (2, False, False)
+    assert c.begin(Action("prune", 3)) == (3, True, True)          # replaced: no update, the step still counts
+    assert c.begin(Action()) == (4, True, False)                   # fresh state, but bias corrections continue
+    assert c.begin(Action()) == (5, False, False)
+    assert c.begin(Action("none", 0, True)) == (1, True, False)    # rebuilt optimizer steps right away
+    assert c.lr_frozen
+    assert c.begin(Action("prune", 2, True)) == (1, True, True)    # rebuilt and replaced: its first step sees no grads
+    assert c.begin(Action()) == (2, True, False)
