@@ -45,7 +45,8 @@ class FrameFit(torch.nn.Module):
         n = self._xyz.shape[0]
         self.plan = plan or DensityPlan(max_num_points or n, removal_rate, densification_interval, isdensity, isremoval)
         if self.plan.learns_rgb_w:      # :31-36
-            self.rgb_W = torch.nn.Parameter(torch.full((n, 1), self.plan.rgb_w_init, device=self.device))
+            w0 = init["rgb_W"].clone().float() if "rgb_W" in init else torch.full((n, 1), self.plan.rgb_w_init)
+            self.rgb_W = torch.nn.Parameter(w0.to(self.device))
         else:
             self.register_buffer("rgb_W", torch.ones((n, 1), device=self.device))
         self.register_buffer("cholesky_bound", torch.tensor([0.5, 0.0, 0.5], device=self.device).view(1, 3))
@@ -77,6 +78,11 @@ class FrameFit(torch.nn.Module):
         out = self._render(torch.tanh(self._xyz), self._cholesky + self.cholesky_bound, self.get_features)
         out = torch.clamp(out, 0, 1)
         return out.view(-1, self.H, self.W, 3).permute(0, 3, 1, 2).contiguous()
+
+    def frame_state(self) -> dict:
+        """train_video_Represent.py:107-114: what a fitted frame hands to the next one"""
+        return {"_xyz": self._xyz.detach().clone(), "_cholesky": self._cholesky.detach().clone(),
+                "_features_dc": self.get_features.detach().clone()}
 
     def _reattach(self):
         for group in self.optimizer.param_groups:       # :115-116
@@ -151,11 +157,15 @@ class FusedFrameFit(torch.nn.Module):
 
     def __init__(self, H: int, W: int, num_points: int, device, lr: float = 1e-3, seed: int = 1,
                  init: dict | None = None, betas=(0.98, 0.92, 0.99), eps: float = 1e-8, weight_decay: float = 0.0,
-                 cap: int | None = None, lr_step_size: int = 20000, lr_gamma: float = 0.5):
+                 cap: int | None = None, lr_step_size: int = 20000, lr_gamma: float = 0.5, isdensity: bool = False,
+                 isremoval: bool = False, removal_rate: float = 0.1, max_num_points: int | None = None,
+                 densification_interval: int = 100, plan=None):
         super().__init__()
+        import ctypes
         from . import _lib
         from . import cuda as _C
-        self._lib, self._C = _lib, _C
+        from .density import DensityPlan, OptimizerClock
+        self._lib, self._C, self._ctypes = _lib, _C, ctypes
         self.H, self.W, self.n = int(H), int(W), int(num_points)
         self.device = torch.device(device)
         if self.device.index is None:
@@ -168,10 +178,21 @@ class FusedFrameFit(torch.nn.Module):
         self._cholesky = torch.nn.Parameter(init["_cholesky"].clone().float().contiguous().to(dev), requires_grad=False)
         self._features_dc = torch.nn.Parameter(init["_features_dc"].clone().float().contiguous().to(dev),
                                                requires_grad=False)
+        self.n = int(self._xyz.shape[0])
+        # prune / add control (GaussianSplats_Represent.py:98-172): rgb_W is a parameter only then (:31-36)
+        self.plan = plan or DensityPlan(max_num_points or self.n, removal_rate, densification_interval, isdensity,
+                                        isremoval)
+        if self.plan.learns_rgb_w:
+            w0 = init["rgb_W"].clone().float() if "rgb_W" in init else torch.full((self.n, 1), self.plan.rgb_w_init)
+            self.rgb_W = torch.nn.Parameter(w0.contiguous().to(dev), requires_grad=False)
+        else:
+            self.rgb_W = None
+        self.clock = OptimizerClock()
         self.lr, self.betas, self.eps, self.weight_decay = float(lr), tuple(betas), float(eps), float(weight_decay)
         self.lr_step_size, self.lr_gamma = int(lr_step_size), float(lr_gamma)
         self.step_index = 0
-        self.cap = int(cap) if cap else max(8 * self.n, 1 << 18)
+        self._ckpt = (0, 0, True, False)     # (iteration, clock.step, clock.fresh, clock.lr_frozen) at the last sync
+        self.cap = int(cap) if cap else max(8 * max(self.n, self.plan.max_num_points), 1 << 18)
         self._alloc()
 
     def _alloc(self):
@@ -181,22 +202,22 @@ class FusedFrameFit(torch.nn.Module):
         self.layout = lay
         dev = self.device
         self.work = torch.empty((lay.total_bytes,), dtype=torch.uint8, device=dev)
-        if not hasattr(self, "adan_state"):
-            self.adan_state = torch.empty((4, self.n, 8), dtype=torch.float32, device=dev)
-            adan_ptr = self.adan_state.data_ptr()
-        else:
-            adan_ptr = None   # regrowing the workspace keeps the optimizer state
+        if getattr(self, "adan_state", None) is None or self.adan_state.shape[1] != self.n:
+            # new model or new Gaussian count: fresh optimizer state (regrowing the workspace keeps it)
+            self.adan_state = torch.zeros((4, self.n, 8), dtype=torch.float32, device=dev)
+            self.adan_state_w = torch.zeros((4, self.n), dtype=torch.float32, device=dev) if self.rgb_W is not None else None
         with self._C._guard(dev):
             self._lib.check(lib.gs2d_fit_init(self.n, self.cap, self.H, self.W, self.work.data_ptr(), lay.total_bytes,
-                                              adan_ptr, torch.cuda.current_stream(dev).cuda_stream), "fit_init")
+                                              None, torch.cuda.current_stream(dev).cuda_stream), "fit_init")
         self._status = self.work[lay.off_status:lay.off_status + 64].view(torch.int32)
         self._loss = self.work[lay.off_loss:lay.off_loss + 8 * self._lib.FIT_LOSS_SLOTS].view(torch.float64)
-        # ring of gs2d_fit_report records (24 B each) in pinned host memory, written by the device
-        self._report = torch.zeros((self._lib.FIT_LOSS_SLOTS, 6), dtype=torch.int32).pin_memory()
-        self._report[:, 5] = -1
-        self._report_np = self._report.numpy()
-        self._report_f64 = self._report_np.view("float64")     # [slots, 3]; column 0 = loss_sum
-        self._report_ptr = self._report.data_ptr()
+        if not hasattr(self, "_report"):
+            # ring of gs2d_fit_report records (24 B each) in pinned host memory, written by the device
+            self._report = torch.zeros((self._lib.FIT_LOSS_SLOTS, 6), dtype=torch.int32).pin_memory()
+            self._report[:, 5] = -1
+            self._report_np = self._report.numpy()
+            self._report_f64 = self._report_np.view("float64")     # [slots, 3]; column 0 = loss_sum
+            self._report_ptr = self._report.data_ptr()
         self._render_img = None
         self._counted_for = None   # nothing pre-counted in a fresh workspace
 
@@ -210,26 +231,108 @@ class FusedFrameFit(torch.nn.Module):
         return gt.contiguous(), self._lib.TARGET_F32_CHW
 
     def current_lr(self) -> float:
-        # torch.optim.lr_scheduler.StepLR(step_size=20000, gamma=0.5), GaussianSplats_Represent.py:52
+        # torch.optim.lr_scheduler.StepLR(step_size=20000, gamma=0.5), GaussianSplats_Represent.py:52;
+        # the optimizer update_optimizer() builds (:93-97) has no scheduler: constant lr from then on
+        if self.clock.lr_frozen:
+            return self.lr
         return self.lr * self.lr_gamma ** (self.step_index // self.lr_step_size)
 
-    def _issue(self, gt, fmt, out_img=None, grads_out=None, ids_out=None):
+    def _options(self, adan_step: int, fresh: bool, skip: bool, w_grad_out=None):
+        o = self._lib.FitOptions()
+        if self.rgb_W is not None:
+            o.rgb_w, o.adan_state_w = self.rgb_W.data_ptr(), self.adan_state_w.data_ptr()
+            o.rgb_w_grad_out = None if w_grad_out is None else w_grad_out.data_ptr()
+        o.adan_step, o.adan_fresh, o.skip_update = int(adan_step), int(fresh), int(skip)
+        return o
+
+    def _issue(self, gt, fmt, out_img=None, grads_out=None, ids_out=None, w_grad_out=None):
+        from .density import Action
         self.step_index += 1
+        act = self.plan.action(self.step_index, self.n) if self.rgb_W is not None else Action()
+        if act.rebuild or act.replaces_parameters:
+            self._control_sync()                    # the one host wait of the control: once per interval
+        if act.rebuild and not act.replaces_parameters:
+            self._zero_optimizer_state()            # update_optimizer() precedes this iteration's step
+        adan_step, fresh, skip = self.clock.begin(act)
+        opts = self._options(adan_step, fresh, skip, w_grad_out)
         b1, b2, b3 = self.betas
         lib = self._lib.load()
         slot = self.step_index % self._lib.FIT_LOSS_SLOTS
-        self._lib.check(lib.gs2d_fit_step(
+        self._lib.check(lib.gs2d_fit_step_band(
             self.n, self.cap, self.H, self.W, self._xyz.data_ptr(), self._cholesky.data_ptr(),
             self._features_dc.data_ptr(), self.adan_state.data_ptr(), gt.data_ptr(), fmt, self.work.data_ptr(),
             self.layout.total_bytes, self.step_index, self.current_lr(), b1, b2, b3, self.eps, self.weight_decay,
-            1 if self._precount_valid() else 0, None if out_img is None else out_img.data_ptr(),
+            1 if self._precount_valid() else 0, 0, (self.H + 15) // 16,
+            self._lib.FIT_PHASE_GRADS | self._lib.FIT_PHASE_UPDATE, None, self._ctypes.addressof(opts),
+            None if out_img is None else out_img.data_ptr(),
             None if grads_out is None else grads_out.data_ptr(), None if ids_out is None else ids_out.data_ptr(),
             self._report_ptr + 24 * slot, torch.cuda.current_stream(self.device).cuda_stream), "fit_step")
-        self._counted_for = self._versions()
+        if skip:
+            self._counted_for = None                # a skipped update pre-counts nothing
+            self._replace_parameters(act)
+        else:
+            self._counted_for = self._versions()
+        if act.rebuild or act.replaces_parameters:
+            self._ckpt = (self.step_index, self.clock.step, self.clock.fresh, self.clock.lr_frozen)
+
+    def _control_sync(self):
+        """before a prune / add / optimizer rebuild: all earlier steps must have really happened
+        (an overflowed workspace turns steps into no-ops; see _recover)"""
+        if self.step_index <= 1:
+            return
+        torch.cuda.current_stream(self.device).synchronize()
+        prev = self.step_index - 1
+        _, _i, overflow, _m = self._read_report(prev)
+        if overflow != 0:
+            self.step_index = prev
+            self._recover(overflow)
+            raise RuntimeError(
+                f"intersections exceeded the workspace capacity at step {overflow}; the workspace was regrown "
+                f"to {self.cap} and the model rewound to step {self.step_index}: re-issue the remaining iterations")
+
+    def _zero_optimizer_state(self):
+        self.adan_state.zero_()
+        if self.adan_state_w is not None:
+            self.adan_state_w.zero_()
+
+    @torch.no_grad()
+    def _replace_parameters(self, act):
+        """the prune (gs2d_prune_lowest) or the random add of GaussianSplats_Represent.py:134-144,
+        after the step that only reported the loss; optimizer state starts afresh for every row"""
+        dev, n = self.device, self.n
+        if act.kind == "prune":
+            m = n - act.count
+            if m < 1:
+                raise RuntimeError("the prune would remove every Gaussian")
+            lib = self._lib.load()
+            scratch = torch.empty((lib.gs2d_prune_scratch_bytes(n),), dtype=torch.uint8, device=dev)
+            new = [torch.empty((m, c), dtype=torch.float32, device=dev) for c in (1, 2, 3, 3)]
+            self.last_keep_index = torch.empty((m,), dtype=torch.int32, device=dev)
+            self._lib.check(lib.gs2d_prune_lowest(
+                n, act.count, self.rgb_W.data_ptr(), self._xyz.data_ptr(), self._cholesky.data_ptr(),
+                self._features_dc.data_ptr(), new[0].data_ptr(), new[1].data_ptr(), new[2].data_ptr(),
+                new[3].data_ptr(), self.last_keep_index.data_ptr(), scratch.data_ptr(), scratch.numel(),
+                torch.cuda.current_stream(dev).cuda_stream), "prune_lowest")
+        else:
+            # same draws, in the same order, from the global CPU generator as the reference
+            c = act.count
+            add = [torch.atanh(2 * (torch.rand(c, 2) - 0.5)), torch.rand(c, 3), torch.rand(c, 3), 0.01 * torch.ones(c, 1)]
+            old = [self._xyz, self._cholesky, self._features_dc, self.rgb_W]
+            cat = [torch.cat((o, a.to(dev)), dim=0) for o, a in zip(old, add)]
+            new = [cat[3], cat[0], cat[1], cat[2]]
+        self.rgb_W = torch.nn.Parameter(new[0], requires_grad=False)
+        self._xyz = torch.nn.Parameter(new[1], requires_grad=False)
+        self._cholesky = torch.nn.Parameter(new[2], requires_grad=False)
+        self._features_dc = torch.nn.Parameter(new[3], requires_grad=False)
+        self.n = int(self._xyz.shape[0])
+        self.adan_state = None                      # new tensors, new (zero) optimizer state
+        self._alloc()
 
     def _versions(self):
+        w = self.rgb_W
         return (self._xyz._version, self._cholesky._version, self._features_dc._version,
-                self._xyz.data_ptr(), self._cholesky.data_ptr(), self._features_dc.data_ptr())
+                self._xyz.data_ptr(), self._cholesky.data_ptr(), self._features_dc.data_ptr(),
+                None if w is None else (w._version, w.data_ptr()))
 
     def _precount_valid(self) -> bool:
         """the previous step pre-counted the tiles of the parameters it wrote; that is still valid
@@ -277,8 +380,12 @@ class FusedFrameFit(torch.nn.Module):
         return loss_sum / (3.0 * self.H * self.W)
 
     def _recover(self, overflow_step: int):
-        # steps >= overflow_step were no-ops (parameters and optimizer state untouched)
+        # steps >= overflow_step were no-ops (parameters and optimizer state untouched); the
+        # optimizer clock goes back with them (nothing but plain steps since the last control sync)
         self.step_index = overflow_step - 1
+        it0, t0, fresh0, frozen0 = self._ckpt
+        d = max(self.step_index - it0, 0)
+        self.clock.step, self.clock.fresh, self.clock.lr_frozen = t0 + d, fresh0 and d == 0, frozen0
         self.cap *= 2
         self._alloc()
 
@@ -345,6 +452,17 @@ class FusedFrameFit(torch.nn.Module):
     def last_num_intersects(self) -> int:
         return self.status()[0]
 
+    @property
+    def get_features(self):
+        """colours as rendered: _features_dc * rgb_W (GaussianSplats_Represent.py:62-63)"""
+        return self._features_dc if self.rgb_W is None else (self._features_dc * self.rgb_W).contiguous()
+
+    def frame_state(self) -> dict:
+        """what the reference keeps of a fitted frame and hands to the next one
+        (train_video_Represent.py:107-114): _xyz, _cholesky and the weighted colours"""
+        return {"_xyz": self._xyz.detach().clone(), "_cholesky": self._cholesky.detach().clone(),
+                "_features_dc": self.get_features.detach().clone()}
+
     @torch.no_grad()
     def forward(self):
         if self._render_img is None:
@@ -358,10 +476,11 @@ class FusedFrameFit(torch.nn.Module):
                                                   torch.cuda.current_stream(self.device).cuda_stream), "fit_init")
             self._render_img = True
         out = torch.empty((1, 3, self.H, self.W), dtype=torch.float32, device=self.device)
+        colors = self.get_features
         with self._C._guard(self.device):
             self._lib.check(self._lib.load().gs2d_render_chol(
                 self.n, self.cap, self.H, self.W, self._xyz.data_ptr(), self._cholesky.data_ptr(),
-                self._features_dc.data_ptr(), None, 1, self._render_work.data_ptr(), self._render_work.numel(),
+                colors.data_ptr(), None, 1, self._render_work.data_ptr(), self._render_work.numel(),
                 out.data_ptr(), 1, 1, None, None, torch.cuda.current_stream(self.device).cuda_stream), "render_chol")
         return out
 
@@ -424,9 +543,10 @@ class SpatialFrameFit(FusedFrameFit):
         them over NVLink in rank order after a device-side barrier: no collective kernel, no extra
         pass over the rows, bit-identical results on every rank by construction."""
         super().__init__(H, W, num_points, device, **kw)
-        import ctypes
         import torch.distributed as dist
-        self._dist, self._ctypes = dist, ctypes
+        self._dist = dist
+        if self.rgb_W is not None:
+            raise NotImplementedError("the prune / add control is not wired into the tile-row split yet")
         self.group = group
         self.emulate_world = int(emulate_world)
         if exchange not in ("nccl", "peer"):

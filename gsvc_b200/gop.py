@@ -8,9 +8,10 @@ per-frame parameter dicts (`_xyz`, `_cholesky`, `_features_dc` -- the reference'
 gmodels_state_dict entries, train_video_Represent.py:107-114,379) are gathered to rank 0 once at
 the end.  The reference itself is single-GPU (`cuda:0`); this module is new design, not a mirror.
 
-Prune / random-add inside a frame's fit (GaussianSplats_Represent.py:98-172) needs the learnable
-`rgb_W`, which the fused step does not carry yet: P-frames here start from the previous frame's
-Gaussians and keep their count (listed as "next" in DESIGN.md).
+Prune / random-add inside a frame's fit (GaussianSplats_Represent.py:98-172) is the fitter's
+business (FusedFrameFit(isremoval=...) for key frames, FusedFrameFit(isdensity=...) for predicted
+frames, as train_video_Represent.py:362-366 builds them); the Gaussian count of a frame then
+follows from the previous one (`num_gaussian_points`, :365).
 """
 from __future__ import annotations
 
@@ -58,7 +59,9 @@ def fit_gop(get_frame: Callable[[int], torch.Tensor], gop: Gop, make_fitter: Cal
         gt = get_frame(f)
         fit.train_iters(gt, iters)
         loss = fit.loss()
-        prev = {k: v.detach().clone() for k, v in fit.state_dict().items()}
+        # the reference hands on _xyz, _cholesky and the WEIGHTED colours (train_video_Represent.py:107-114)
+        state = fit.frame_state() if hasattr(fit, "frame_state") else fit.state_dict()
+        prev = {k: v.detach().clone() for k, v in state.items()}
         out[f] = {"state": {k: v.cpu() for k, v in prev.items()}, "psnr": 10 * math.log10(1.0 / max(loss, 1e-20)),
                   "iters": iters}
         if on_frame is not None:

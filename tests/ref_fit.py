@@ -5,13 +5,13 @@ tests/ref_gpu.py, driven by the same loop as gsvc_b200.fit.FrameFit.  Used by
 `bench.py --impl reference-gpu` and by the trajectory parity test."""
 from __future__ import annotations
 
-import math
-
 import torch
-import torch.nn.functional as F
 
-import ref_gpu
-from gsvc_b200.adan import Adan
+try:
+    from tests import ref_gpu
+except ImportError:          # bench.py puts tests/ itself on sys.path
+    import ref_gpu
+from gsvc_b200.fit import FrameFit
 
 
 class _RefProject(torch.autograd.Function):
@@ -57,39 +57,15 @@ class _RefRasterSum(torch.autograd.Function):
         return v_xy, None, None, v_conic, None, v_col, v_op, None, None, None
 
 
-class RefFrameFit(torch.nn.Module):
+class RefFrameFit(FrameFit):
+    """gsvc_b200.fit.FrameFit (the loop, rgb_W and the prune / add control, pinned against the
+    reference's model class by tests/test_density_cpu.py) with the two operators swapped for the
+    reference's own kernels"""
+
     path_name = "reference CUDA kernels (oracle/_ref, sm_100a, --use_fast_math) + torch cumsum/.item()/sort/gather glue"
     last_num_intersects = 0
 
-    def __init__(self, H, W, num_points, device, lr=1e-3, seed=1, init=None):
-        super().__init__()
-        from gsvc_b200 import synth
-        self.H, self.W = H, W
-        self.tb = ((W + 15) // 16, (H + 15) // 16, 1)
-        self.device = torch.device(device)
-        init = init or synth.gaussians(num_points, seed=seed)
-        self._xyz = torch.nn.Parameter(init["_xyz"].clone().to(device))
-        self._cholesky = torch.nn.Parameter(init["_cholesky"].clone().to(device))
-        self._features_dc = torch.nn.Parameter(init["_features_dc"].clone().to(device))
-        self.register_buffer("cholesky_bound", torch.tensor([0.5, 0.0, 0.5], device=device).view(1, 3))
-        self.optimizer = Adan(self.parameters(), lr=lr)
-        self.scheduler = torch.optim.lr_scheduler.StepLR(self.optimizer, step_size=20000, gamma=0.5)
-
-    def forward(self):
-        opacity = torch.ones(self._xyz.shape[0], 1).to(self.device)   # as the reference: new tensor every call
-        xys, depths, radii, conics, nth = _RefProject.apply(torch.tanh(self._xyz), self._cholesky + self.cholesky_bound,
-                                                            self.H, self.W, self.tb)
-        out = _RefRasterSum.apply(xys, depths, radii, conics, nth, self._features_dc, opacity, self.H, self.W, self.tb)
-        out = torch.clamp(out, 0, 1)
-        return out.view(-1, self.H, self.W, 3).permute(0, 3, 1, 2).contiguous()
-
-    def train_iter(self, gt_image):
-        image = self.forward()
-        loss = F.mse_loss(image, gt_image)
-        loss.backward()
-        with torch.no_grad():
-            psnr = 10 * math.log10(1.0 / loss.item())
-        self.optimizer.step()
-        self.optimizer.zero_grad(set_to_none=True)
-        self.scheduler.step()
-        return loss, psnr
+    def _render(self, means2d, L_elements, colors):
+        opacity = torch.ones(means2d.shape[0], 1).to(self.device)   # as the reference: new tensor every call
+        xys, depths, radii, conics, nth = _RefProject.apply(means2d, L_elements, self.H, self.W, self.tile_bounds)
+        return _RefRasterSum.apply(xys, depths, radii, conics, nth, colors, opacity, self.H, self.W, self.tile_bounds)

@@ -1,0 +1,179 @@
+"""GPU parity of the prune / add control on the fused path (FusedFrameFit with isremoval /
+isdensity: rgb_W inside gs2d_fit_step_band, gs2d_prune_lowest, optimizer clock) against the
+reference's kernels driven by FrameFit's restatement of the control (tests/ref_fit.RefFrameFit;
+the restatement itself is pinned against the reference's model class on CPU,
+tests/test_density_cpu.py)."""
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+cuda = torch.device("cuda:0")
+KEYS = ("_xyz", "_cholesky", "_features_dc", "rgb_W")
+GRAD_RTOL = 1e-4
+
+
+def _rel(a, b):
+    return float((a - b).abs().max() / max(float(b.abs().max()), 1e-30))
+
+
+def _assert_params_close(fused, ref):
+    """two runs of the same trajectory on different kernels: atomic order differs, and Adan turns
+    a near-zero gradient's noise into a full +-lr step, so a few elements may differ by O(lr)"""
+    for k in KEYS:
+        a, b = getattr(fused, k), getattr(ref, k).detach()
+        assert a.shape == b.shape, k
+        d = (a - b).abs()
+        assert float(d.median()) <= 5e-6, k
+        assert float((d > 1e-4).float().mean()) <= 0.01, k
+        assert float(d.max()) <= 2e-2, k
+
+
+def _init(n, seed, spread_w=True):
+    from gsvc_b200 import synth
+    init = synth.gaussians(n, seed=seed)
+    if spread_w:
+        # distinct colour weights: which Gaussians a prune drops is then decided by the values, not
+        # by float noise between two implementations of the same update
+        g = torch.Generator().manual_seed(seed + 100)
+        init["rgb_W"] = 0.01 + 0.2 * torch.rand(n, 1, generator=g)
+    return init
+
+
+def _pair(H, W, n, init, plan_kw, seed=5):
+    from gsvc_b200 import synth
+    from gsvc_b200.density import DensityPlan
+    from gsvc_b200.fit import FusedFrameFit
+    from tests.ref_fit import RefFrameFit
+    gt = synth.target_frame(H, W, seed=seed).to(cuda)
+    fused = FusedFrameFit(H, W, n, cuda, init=init, plan=DensityPlan(**plan_kw))
+    ref = RefFrameFit(H, W, n, cuda, init=init, plan=DensityPlan(**plan_kw))
+    return gt, fused, ref
+
+
+def test_rgb_w_first_step_gradients_and_update():
+    H, W, n = 256, 256, 6000
+    init = _init(n, 11)
+    gt, fused, ref = _pair(H, W, n, init, dict(max_num_points=n, removal_rate=0.1, isremoval=True))
+    # reference gradients of the four parameter tensors
+    loss = torch.nn.functional.mse_loss(ref.forward(), gt)
+    loss.backward()
+    want = [ref._xyz.grad, ref._cholesky.grad, ref._features_dc.grad, ref.rgb_W.grad]
+    g8 = torch.empty((n, 8), device=cuda)
+    gw = torch.empty((n,), device=cuda)
+    fused.train_iters(gt, 1, grads_out=g8, w_grad_out=gw)
+    assert fused.loss() == pytest.approx(float(loss.detach()), rel=2e-6)
+    got = [g8[:, 0:2], g8[:, 2:5], g8[:, 5:8], gw.view(n, 1)]
+    for a, b, name in zip(got, want, KEYS):
+        assert _rel(a, b) <= GRAD_RTOL, name
+    ref.optimizer.step()
+    for k in KEYS:        # first Adan step: every element moves by ~lr
+        a, b = getattr(fused, k), getattr(ref, k).detach()
+        assert float((a - b).abs().max()) <= 2e-6, k
+    # the render uses the weighted colours
+    img = fused.forward()
+    assert float((img - ref.forward().detach()).abs().max()) <= 1e-5
+
+
+@pytest.mark.parametrize("n0,final_prune", [(2000, True), (1875, False)])
+def test_removal_schedule_matches_the_reference_loop(n0, final_prune):
+    """K-frame mode (isremoval): prune every 10 iterations up to 40, optimizer rebuild at 40 -- with
+    (n0 = 2000) and without (n0 = 1875: already at max*(1-rate)) a last prune"""
+    H, W = 128, 160
+    kw = dict(max_num_points=2000, removal_rate=0.25, densification_interval=10, isremoval=True, removal_until=40)
+    gt, fused, ref = _pair(H, W, n0, _init(n0, 21), kw)
+    for it in range(1, 56):
+        before = ref._xyz.shape[0]
+        lr_, _ = ref.train_iter(gt, it)
+        lf, _ = fused.train_iter(gt)
+        assert fused.n == ref._xyz.shape[0], it
+        assert lf == pytest.approx(float(lr_.detach()), rel=5e-4), it
+        if ref._xyz.shape[0] != before:
+            kept = torch.nonzero(ref.last_keep).flatten().to(torch.int32)
+            assert torch.equal(kept, fused.last_keep_index), f"iteration {it}: different Gaussians pruned"
+    assert fused.n == 1500 and (n0 - 1500 - 3 * 125 > 0) == final_prune
+    assert fused.clock.lr_frozen and fused.clock.step == 55 - 40 + 1
+    _assert_params_close(fused, ref)
+
+
+def test_density_schedule_matches_the_reference_loop():
+    """P-frame mode (isdensity): initialised from a previous frame, random add at iteration 1 (same
+    draws from the CPU generator), prune at 10/15, rebuild at 20"""
+    H, W, n_prev, n_max = 128, 160, 1500, 2000
+    from gsvc_b200 import synth
+    prev = synth.gaussians(n_prev, seed=31)
+    kw = dict(max_num_points=n_max, removal_rate=0.25, densification_interval=5, isdensity=True, density_from=10,
+              density_for=10)
+    gt, fused, ref = _pair(H, W, n_prev, prev, kw)
+    assert float(fused.rgb_W.min()) == 1.0 and float(ref.rgb_W.min()) == 1.0       # :33-34
+    state = torch.get_rng_state()
+    losses = []
+    for it in range(1, 31):
+        l, _ = ref.train_iter(gt, it)
+        losses.append(float(l.detach()))
+    torch.set_rng_state(state)
+    ns = []
+    for it in range(1, 31):
+        l, _ = fused.train_iter(gt)
+        ns.append(fused.n)
+        assert l == pytest.approx(losses[it - 1], rel=5e-4), it
+    assert ns[0] == 2000 and ns[8] == 2000 and ns[9] == 1750 and ns[14] == 1500 and ns[-1] == 1500
+    assert fused.n == ref._xyz.shape[0]
+    _assert_params_close(fused, ref)
+    # what the next frame starts from: weighted colours
+    fs = fused.frame_state()
+    assert torch.allclose(fs["_features_dc"], fused._features_dc * fused.rgb_W)
+
+
+def test_prune_lowest_against_torch():
+    from gsvc_b200 import _lib
+    lib = _lib.load()
+    g = torch.Generator().manual_seed(3)
+    for n, k in ((1, 0), (257, 1), (5000, 0), (5000, 1234), (100_000, 99_999), (70_001, 35_000)):
+        w = torch.randn(n, 1, generator=g)
+        m7 = w[3::7].shape[0]
+        w[0:7 * m7:7] = w[3::7]                                          # exact ties
+        if n > 20:
+            w[5], w[6] = 0.0, -0.0
+        xyz, chol, feat = torch.randn(n, 2, generator=g), torch.randn(n, 3, generator=g), torch.randn(n, 3, generator=g)
+        d = [t.to(cuda).contiguous() for t in (w, xyz, chol, feat)]
+        m = n - k
+        out = [torch.full((m, c), float("nan"), device=cuda) for c in (1, 2, 3, 3)]
+        idx = torch.empty((m,), dtype=torch.int32, device=cuda)
+        scratch = torch.empty((lib.gs2d_prune_scratch_bytes(n),), dtype=torch.uint8, device=cuda)
+        _lib.check(lib.gs2d_prune_lowest(n, k, d[0].data_ptr(), d[1].data_ptr(), d[2].data_ptr(), d[3].data_ptr(),
+                                         out[0].data_ptr(), out[1].data_ptr(), out[2].data_ptr(), out[3].data_ptr(),
+                                         idx.data_ptr(), scratch.data_ptr(), scratch.numel(),
+                                         torch.cuda.current_stream().cuda_stream), "prune_lowest")
+        _, order = torch.sort(torch.norm(d[0], dim=1), stable=True)
+        keep = torch.ones(n, dtype=torch.bool, device=cuda)
+        keep[order[:k]] = False
+        assert torch.equal(idx.long(), torch.nonzero(keep).flatten()), (n, k)
+        for o, src in zip(out, d):
+            assert torch.equal(o, src[keep]), (n, k)
+
+
+def test_overflow_before_a_prune_rewinds_the_clock():
+    from gsvc_b200 import synth
+    from gsvc_b200.density import DensityPlan
+    from gsvc_b200.fit import FusedFrameFit
+    H, W, n = 256, 256, 4000
+    gt = synth.target_frame(H, W, seed=2).to(cuda)
+    plan = dict(max_num_points=n, removal_rate=0.25, densification_interval=10, isremoval=True, removal_until=40)
+    init = _init(n, 41)
+    small = FusedFrameFit(H, W, n, cuda, init=init, plan=DensityPlan(**plan), cap=1024)   # far too small
+    with pytest.raises(RuntimeError, match="capacity"):
+        small.train_iters(gt, 12)            # detected at the control sync of iteration 10
+    assert small.step_index == 0 and small.clock.step == 0 and small.clock.fresh
+    while True:                              # regrow until it fits, as a caller would
+        try:
+            small.train_iters(gt, 12 - small.step_index)
+            small.loss()
+            break
+        except RuntimeError:
+            continue
+    ok = FusedFrameFit(H, W, n, cuda, init=init, plan=DensityPlan(**plan))
+    ok.train_iters(gt, 12)
+    assert small.n == ok.n == n - 250
+    for k in KEYS:
+        assert torch.equal(getattr(small, k), getattr(ok, k)) or float((getattr(small, k) - getattr(ok, k)).abs().max()) < 1e-5
