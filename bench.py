@@ -134,11 +134,22 @@ def ncu_traffic(stage: str):
 # ------------------------------------------------------------------------------------------
 # CPU arm: the oracle port on the host cores
 # ------------------------------------------------------------------------------------------
+def raw_frame(seed=1):
+    """the synthetic frame as the reference's input file would hold it: planar I420, uint8 [H*3/2, W]"""
+    import torch
+    from gsvc_b200 import synth, yuv
+    rgb = (synth.target_frame(H, W, seed=seed)[0] * 255).round().to(torch.uint8).permute(1, 2, 0).contiguous()
+    return yuv.rgb_to_i420(rgb).contiguous()
+
+
 def make_cpu_fit(seed=1):
+    import numpy as np
     from gsvc_b200 import synth
+    from oracle import yuv as oracle_yuv
     from oracle.fit_cpu import CpuFit
     g = synth.gaussians(NPTS, seed=seed)
-    gt = synth.target_frame(H, W, seed=seed)[0].permute(1, 2, 0).contiguous().numpy()
+    # the same frame every arm fits: the raw I420 frame decoded as the reference's loader does
+    gt = oracle_yuv.i420_to_rgb(raw_frame(seed).numpy(), H, W).astype(np.float32) / np.float32(255)
     return CpuFit(H, W, {k: g[k].numpy() for k in ("_xyz", "_cholesky", "_features_dc")}, gt)
 
 
@@ -205,13 +216,16 @@ def main_gpu(args, rank: int, world: int, local_rank: int):
     mine = args.impl in ("b200", "b200-dropin")
     fused = args.impl == "b200"
     fit = make_fitter(args.impl, dev, seed=1 + rank, trained_like=args.trained_like)
-    frame = synth.target_frame(H, W, seed=1 + rank)                      # [1,3,H,W] fp32 in [0,1]
+    raw = raw_frame(seed=1 + rank)                                       # uint8 [H*3/2, W] planar I420
     if fused:
-        # the fused path takes the raw RGB frame (uint8 [H,W,3], what the YUV loader decodes to)
-        gt_host = (frame[0] * 255).round().to(torch.uint8).permute(1, 2, 0).contiguous().pin_memory()
+        # the fused path takes the raw frame of the .yuv file and decodes it inside the tile kernel
+        gt_host = raw.pin_memory()
         step_resident = lambda g: fit.train_iters(g, 1)                  # nothing read back
     else:
-        gt_host = frame.pin_memory()                                     # fp32 NCHW, what the reference's loader yields
+        # fp32 NCHW in [0,1]: what the reference's loader (cv2 decode + ToTensor) hands its loop
+        from gsvc_b200 import yuv as _yuv
+        rgb = _yuv.i420_to_rgb(raw.to(dev), H, W)
+        gt_host = (rgb.permute(2, 0, 1).float() / 255).unsqueeze(0).contiguous().cpu().pin_memory()
         step_resident = fit.train_iter                                   # reads the loss back every step, as the reference
     gt = gt_host.to(dev)
     flush = torch.empty(L2_FLUSH_BYTES, dtype=torch.uint8, device=dev)
@@ -273,6 +287,15 @@ def main_gpu(args, rank: int, world: int, local_rank: int):
     e2e_ms = a.elapsed_time(b) / K
     clocks = sampler.stop() if rank == 0 else None
 
+    # ---- what the host link gives this frame alone (explains e2e; not part of any metric) ----
+    barrier()
+    a.record()
+    for _ in range(20):
+        gt.copy_(gt_host, non_blocking=True)
+    b.record()
+    barrier()
+    h2d_ms = a.elapsed_time(b) / 20
+
     # ---- render-only fps (config 3), device-resident -----------------------------------------
     with torch.no_grad():
         for _ in range(3):
@@ -312,11 +335,13 @@ def main_gpu(args, rank: int, world: int, local_rank: int):
             "config": {"workload": WORKLOAD, "H": H, "W": W, "gaussians": NPTS, "intersections": I,
                        "l2": f"flushed between timed steps ({L2_FLUSH_BYTES >> 20} MiB memset outside the event pair)",
                        "path": getattr(fit, "path_name", "autograd drop-in ops + torch glue"),
-                       "e2e_path": "FusedFrameFit.fit_stream: pinned-host uint8 frame per step, copy overlapped with the previous step, loss reported into pinned memory" if fused else "train_iter per step: H2D of the fp32 frame, loss.item()",
+                       "e2e_path": "FusedFrameFit.fit_stream: pinned-host raw I420 frame per step (decoded in the tile kernel), copy overlapped with the previous step, loss reported into pinned memory" if fused else "train_iter per step: H2D of the fp32 frame, loss.item()",
                        "parallelism": f"{world} independent GOP chains, one per GPU, no collective"},
             "clocks": clocks,
             "e2e": {"value": world * 1e3 / e2e_ms, "unit": UNIT, "h2d_bytes_per_step": gt_host.numel() * gt_host.element_size(),
-                    "d2h_bytes_per_step": 24 if fused else 4, "ms_per_step": e2e_ms},
+                    "d2h_bytes_per_step": 24 if fused else 4, "ms_per_step": e2e_ms,
+                    "h2d_copy_alone_ms": h2d_ms,
+                    "h2d_copy_alone_gbs": gt_host.numel() * gt_host.element_size() / (h2d_ms * 1e-3) / 1e9},
             "gpu_launches": launches,
             "l2_warm": {"value": world * 1e3 / warm_ms, "unit": UNIT, "ms_per_step": warm_ms},
             "render": {"value": world * 1e3 / render_ms, "unit": "frames/s", "ms_per_frame": render_ms},
@@ -354,8 +379,100 @@ def main_gpu(args, rank: int, world: int, local_rank: int):
         dist.destroy_process_group()
 
 
+# ------------------------------------------------------------------------------------------
+# --workload gop: BASELINE config 4 (not the headline line; run explicitly)
+# ------------------------------------------------------------------------------------------
+def main_gop(args, rank: int, world: int, local_rank: int):
+    """120-frame 1080p sequence with scene cuts, key frames fitted from scratch with the removal
+    control, predicted frames from the previous frame with random add + prune; key-frame-delimited
+    GOPs sharded over the ranks with no data-path collective (gsvc_b200.gop).  Strong scaling:
+    value = frames of the whole sequence / max-over-ranks time.  Frames are pre-decoded into
+    pinned host memory per rank (raw I420); the timed region holds every frame's H2D copy, fit,
+    and the final gather of the per-frame Gaussians to rank 0."""
+    import torch
+    import torch.distributed as dist
+    from gsvc_b200 import _lib, gop
+
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+        gather_group = dist.new_group(backend="gloo")       # gather_object of CPU dicts
+    else:
+        gather_group = None
+    F, cut = args.gop_frames, args.gop_cut
+    frame_fn, keyframes = gop.synthetic_sequence(H, W, F, cut_every=cut)
+    gops = gop.gops_from_keyframes(keyframes, F)
+    cost = lambda g: args.gop_iters_key + (g[1] - g[0] - 1) * args.gop_iters_pred
+    mine = gop.assign_gops(gops, world, cost=cost)[rank]
+    from gsvc_b200 import yuv
+    # raw I420 frames, as the reference's .yuv input holds them; decoded inside the tile kernel
+    host = {f: yuv.rgb_to_i420((frame_fn(f)[0] * 255).round().to(torch.uint8).permute(1, 2, 0).contiguous())
+            .contiguous().pin_memory() for g in mine for f in range(*g)}
+    get = lambda f: host[f].to(dev, non_blocking=True)
+    make = gop.reference_fitters(H, W, NPTS, dev)
+    # warm-up: one short key frame + predicted frame chain (allocator, kernels, prune path)
+    if mine:
+        f0 = mine[0][0]
+        gop.fit_gop(lambda f: get(f0), (f0, f0 + 2), make, 120, 120)
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize(dev)
+    launches0 = _lib.launch_count()
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    wall0 = time.perf_counter()
+    a.record()
+    out = gop.fit_sequence(get, F, keyframes, make, args.gop_iters_key, args.gop_iters_pred, group=gather_group)
+    b.record()
+    torch.cuda.synchronize(dev)
+    if world > 1:
+        dist.barrier()
+    wall = time.perf_counter() - wall0
+    launches = _lib.launch_count() - launches0
+    t = torch.tensor([a.elapsed_time(b)], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms = float(t)
+    clocks = sampler.stop() if rank == 0 else None
+    if rank == 0:
+        iters = sum(r["iters"] for r in out.values())
+        psnrs = [out[f]["psnr"] for f in sorted(out)]
+        npts = [out[f]["num_points"] for f in sorted(out)]
+        line = {
+            "metric": "gop_frames_per_s_1080p_50k", "value": F / (ms * 1e-3), "unit": "frames/s", "n_gpus": world,
+            "steps": F, "warmup": 2, "ms_per_step": ms / F, "higher_is_better": True, "scaling": "strong",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": f"C4: {F}-frame 1080p synthetic sequence, scene cut every {cut} frames, "
+                                   f"{NPTS} Gaussians, key frames {args.gop_iters_key} iters with removal control, "
+                                   f"predicted frames {args.gop_iters_pred} iters with random add + prune",
+                       "H": H, "W": W, "gaussians": NPTS, "gops": len(gops),
+                       "gops_per_rank": [len(x) for x in gop.assign_gops(gops, world, cost=cost)],
+                       "parallelism": f"{len(gops)} key-frame-delimited GOPs over {world} GPU(s), no data-path collective"},
+            "clocks": clocks, "gpu_launches": launches, "fit_iterations": iters,
+            "fit_iters_per_s": iters / (ms * 1e-3), "wall_s_timed_region": wall,
+            "psnr_mean": sum(psnrs) / len(psnrs), "psnr_min": min(psnrs),
+            "num_points_first_last": [npts[0], npts[-1]], "num_points_max": max(npts),
+            "e2e": {"value": F / wall, "unit": "frames/s", "h2d_bytes_per_step": 3 * H * W // 2,
+                    "d2h_bytes_per_step": 36 * NPTS},
+        }
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
 def main():
     ap = argparse.ArgumentParser()
+    ap.add_argument("--workload", default="fit", choices=["fit", "gop"],
+                    help="fit: the headline line (C2 + C3 render); gop: BASELINE config 4 (sequence, GOP sharding)")
+    ap.add_argument("--gop-frames", type=int, default=120)
+    ap.add_argument("--gop-cut", type=int, default=30, help="scene cut (key frame) every this many frames")
+    ap.add_argument("--gop-iters-key", type=int, default=4100,
+                    help="iterations per key frame (the removal control runs to iteration 4000)")
+    ap.add_argument("--gop-iters-pred", type=int, default=1000,
+                    help="iterations per predicted frame (add at 1, prune 500..900, rebuild at 1000)")
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=200)
     ap.add_argument("--warmup", type=int, default=20)
@@ -366,7 +483,9 @@ def main():
                     help="informational: wide Gaussians (L = 4*rand + bound, ~10x the intersections, tiles beyond 256)")
     args = ap.parse_args()
     rank, world, local_rank = _env_int("RANK", 0), _env_int("WORLD_SIZE", 1), _env_int("LOCAL_RANK", 0)
-    if args.impl == "reference":
+    if args.workload == "gop":
+        main_gop(args, rank, world, local_rank)
+    elif args.impl == "reference":
         main_reference(args, rank)
     else:
         main_gpu(args, rank, world, local_rank)

@@ -60,7 +60,7 @@ class FitOptions(Structure):
 
 
 FIT_LOSS_SLOTS = 64
-TARGET_F32_CHW, TARGET_U8_HWC = 0, 1
+TARGET_F32_CHW, TARGET_U8_HWC, TARGET_I420 = 0, 1, 2
 FIT_PHASE_GRADS, FIT_PHASE_UPDATE = 1, 2
 
 _P = c_void_p
@@ -95,6 +95,12 @@ _SIGNATURES = {
     "gs2d_fit_step_band": (c_int, [c_int, c_int, c_int, c_int, _P, _P, _P, _P, _P, c_int, _P, c_size_t, c_int,
                                    c_float, c_float, c_float, c_float, c_float, c_float, c_int, c_int, c_int, c_int,
                                    _P, _P, _P, _P, _P, _P, _P]),
+    "gs2d_i420_to_rgb": (c_int, [c_int, c_int, _P, _P, _P]),
+    "gs2d_frame_pipe_create": (c_int, [_P, c_size_t, c_int, POINTER(c_void_p)]),
+    "gs2d_frame_pipe_destroy": (c_int, [_P]),
+    "gs2d_frame_pipe_push": (c_int, [_P, _P, POINTER(c_int)]),
+    "gs2d_frame_pipe_acquire": (c_int, [_P, c_int, _P, POINTER(c_void_p)]),
+    "gs2d_frame_pipe_release": (c_int, [_P, c_int, _P]),
     "gs2d_prune_scratch_bytes": (c_size_t, [c_int]),
     "gs2d_prune_lowest": (c_int, [c_int, c_int, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, c_size_t, _P]),
     "gs2d_render_chol": (c_int, [c_int, c_int, c_int, c_int, _P, _P, _P, _P, c_int, _P, c_size_t, _P, c_int, c_int,

@@ -49,6 +49,17 @@ __device__ __forceinline__ float u8_over_255(uint32_t v) {
     return fmaf_(fmaf_(-q, 255.f, x), r, q);
 }
 
+// cv2.COLOR_YUV2RGB_I420 for one pixel (utils.py:150 of the reference; OpenCV's BT.601 limited-range
+// 20-bit fixed point; pinned against cv2 by tests/test_yuv_cpu.py) -> r | g << 8 | b << 16
+__device__ __forceinline__ uint32_t yuv_to_rgb_packed(int y, int u, int v) {
+    const int yy = max(y - 16, 0) * 1220542 + (1 << 19);
+    const int uu = u - 128, vv = v - 128;
+    const int r = (yy + 1673527 * vv) >> 20;
+    const int g = (yy - 852492 * vv - 409993 * uu) >> 20;
+    const int b = (yy + 2116026 * uu) >> 20;
+    return (uint32_t)min(max(r, 0), 255) | ((uint32_t)min(max(g, 0), 255) << 8) | ((uint32_t)min(max(b, 0), 255) << 16);
+}
+
 // activations of the reference's frame model (GaussianSplats_Represent.py:56-70) + projection
 __device__ __forceinline__ void fit_project(int i, const float* __restrict__ xyz_raw, const float* __restrict__ chol_raw,
                                             int activate, float half_w, float half_h, int tx, int ty, Proj2d& p,
@@ -304,7 +315,8 @@ __device__ __forceinline__ float group8_reduce8_t(float (&v)[8], int lane) {
 // MODE 0: fit (loss + backward, no image written unless out_img != NULL)
 // MODE 1: render only (image [+ final_idx] written, no target, no backward)
 // GT: 0 = target is fp32 planar [3][H][W] (what torchvision's ToTensor / the reference's loader
-//         yields), 1 = uint8 interleaved [H][W][3] (raw frame; compared as value / 255)
+//         yields), 1 = uint8 interleaved [H][W][3] (raw frame; compared as value / 255),
+//         2 = planar I420 as the .yuv file holds it (converted here as the reference's loader does)
 //
 // One CTA of two warps per tile.  Warp w owns tile rows 8w .. 8w+7; a lane owns one column of
 // two interleaved row sets: pixel j (0..3) of lane l is (x = l & 15, y = 8w + 2j + (l >> 4)), so
@@ -348,9 +360,14 @@ k_fit_tiles(int W, int H, int tx, int row0, const int32_t* __restrict__ tile_off
                     const float* g = (const float*)gt;
                     const size_t plane = (size_t)H * W;
                     tgt[j] = make_float3(__ldg(g + pid), __ldg(g + plane + pid), __ldg(g + 2 * plane + pid));
-                } else {
+                } else if (GT == 1) {
                     const uint8_t* g = (const uint8_t*)gt + 3 * pid;
                     tgt_u8[j] = (uint32_t)__ldg(g) | ((uint32_t)__ldg(g + 1) << 8) | ((uint32_t)__ldg(g + 2) << 16);
+                } else {   // I420: luma plane, then the two quarter-size chroma planes
+                    const uint8_t* g = (const uint8_t*)gt;
+                    const size_t plane = (size_t)H * W, cid = (size_t)(py_i >> 1) * (W >> 1) + (px_i >> 1);
+                    tgt_u8[j] = yuv_to_rgb_packed(__ldg(g + pid), __ldg(g + plane + cid),
+                                                  __ldg(g + plane + (plane >> 2) + cid));
                 }
             }
         }
@@ -437,7 +454,7 @@ k_fit_tiles(int W, int H, int tx, int row0, const int32_t* __restrict__ tile_off
 #pragma unroll
     for (int j = 0; j < 4; ++j) {
         float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (GT == 1) tgt[j] = make_float3(u8_over_255(tgt_u8[j] & 255u), u8_over_255((tgt_u8[j] >> 8) & 255u),
+        if (GT != 0) tgt[j] = make_float3(u8_over_255(tgt_u8[j] & 255u), u8_over_255((tgt_u8[j] >> 8) & 255u),
                                           u8_over_255((tgt_u8[j] >> 16) & 255u));
         if (inside[j]) {
             const float cr = fminf(fmaxf(pix[j].x, 0.f), 1.f), cg = fminf(fmaxf(pix[j].y, 0.f), 1.f),
@@ -688,6 +705,28 @@ k_fit_update(int n, float* __restrict__ xyz_raw, float* __restrict__ chol_raw, f
     scan_tiles_by_last_block(tx, ty, cap, next_step, tile_count, tile_off, status, sh, &s_last);
 }
 
+// the loader as a pass of its own (drop-in path: the model files want an RGB tensor): one thread
+// per 2x2 block -- two 2-byte luma loads, one U, one V, two 6-byte row segments out
+__global__ void __launch_bounds__(kFitThreads)
+k_i420_to_rgb(int H, int W, const uint8_t* __restrict__ yuv, uint8_t* __restrict__ rgb) {
+    const int bw = W >> 1, bh = H >> 1;
+    const int b = blockIdx.x * kFitThreads + threadIdx.x;
+    if (b >= bw * bh) return;
+    const int by = b / bw, bx = b - by * bw;
+    const size_t plane = (size_t)H * W;
+    const int u = __ldg(yuv + plane + b), v = __ldg(yuv + plane + (plane >> 2) + b);
+#pragma unroll
+    for (int r = 0; r < 2; ++r) {
+        const size_t pid = (size_t)(2 * by + r) * W + 2 * bx;
+        const uint16_t yy = __ldg(reinterpret_cast<const uint16_t*>(yuv + pid));   // pid is even
+        const uint32_t a = yuv_to_rgb_packed(yy & 255, u, v), c = yuv_to_rgb_packed(yy >> 8, u, v);
+        uint16_t* o = reinterpret_cast<uint16_t*>(rgb + 3 * pid);                  // 3 * pid is even
+        o[0] = (uint16_t)(a & 0xffffu);
+        o[1] = (uint16_t)((a >> 16) | ((c & 255u) << 8));
+        o[2] = (uint16_t)(c >> 8);
+    }
+}
+
 static inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 
 static int fit_layout(int n, int cap, int img_h, int img_w, gs2d_fit_layout* L) {
@@ -772,8 +811,10 @@ int gs2d_fit_step_band(int n, int cap, int img_h, int img_w, float* xyz_raw, flo
     const int tx = div_up(img_w, GS2D_TILE), ty = div_up(img_h, GS2D_TILE);
     GS2D_REQUIRE(n > 0 && step >= 1, "fit_step: n and step must be positive");
     GS2D_REQUIRE(work != nullptr && work_bytes >= L.total_bytes, "fit_step: workspace too small");
-    GS2D_REQUIRE(target_format == GS2D_TARGET_F32_CHW || target_format == GS2D_TARGET_U8_HWC,
-                 "fit_step: unknown target format");
+    GS2D_REQUIRE(target_format == GS2D_TARGET_F32_CHW || target_format == GS2D_TARGET_U8_HWC ||
+                     target_format == GS2D_TARGET_I420, "fit_step: unknown target format");
+    GS2D_REQUIRE(target_format != GS2D_TARGET_I420 || (img_h % 2 == 0 && img_w % 2 == 0),
+                 "fit_step: an I420 frame needs even width and height");
     GS2D_REQUIRE(xyz_raw && chol_raw && features && adan_state, "fit_step: null pointer");
     GS2D_REQUIRE(0 <= tile_row_begin && tile_row_begin < tile_row_end && tile_row_end <= ty,
                  "fit_step: tile row band out of range");
@@ -822,8 +863,13 @@ int gs2d_fit_step_band(int n, int cap, int img_h, int img_w, float* xyz_raw, flo
                 img_w, img_h, tx, row0, (const int32_t*)(w + L.off_tile_off), (int32_t*)(w + L.off_tile_count),
                 (const float4*)(w + L.off_packed), target, grad_scale, grads, loss + (step % GS2D_FIT_LOSS_SLOTS),
                 status, out_img, 1, 1, nullptr, ids_sorted_out, 0, banded ? 1 : 0);
-        else
+        else if (target_format == GS2D_TARGET_U8_HWC)
             k_fit_tiles<0, 1><<<grid, kTileThreads, 0, s>>>(
+                img_w, img_h, tx, row0, (const int32_t*)(w + L.off_tile_off), (int32_t*)(w + L.off_tile_count),
+                (const float4*)(w + L.off_packed), target, grad_scale, grads, loss + (step % GS2D_FIT_LOSS_SLOTS),
+                status, out_img, 1, 1, nullptr, ids_sorted_out, 0, banded ? 1 : 0);
+        else
+            k_fit_tiles<0, 2><<<grid, kTileThreads, 0, s>>>(
                 img_w, img_h, tx, row0, (const int32_t*)(w + L.off_tile_off), (int32_t*)(w + L.off_tile_count),
                 (const float4*)(w + L.off_packed), target, grad_scale, grads, loss + (step % GS2D_FIT_LOSS_SLOTS),
                 status, out_img, 1, 1, nullptr, ids_sorted_out, 0, banded ? 1 : 0);
@@ -859,6 +905,18 @@ int gs2d_fit_step(int n, int cap, int img_h, int img_w, float* xyz_raw, float* c
                               work, work_bytes, step, lr, beta1, beta2, beta3, eps, weight_decay, precounted, 0,
                               div_up(img_h, GS2D_TILE), GS2D_FIT_PHASE_GRADS | GS2D_FIT_PHASE_UPDATE, nullptr, nullptr,
                               out_img, param_grads_out, ids_sorted_out, report_host, stream);
+}
+
+int gs2d_i420_to_rgb(int img_h, int img_w, const uint8_t* yuv, uint8_t* rgb, gs2d_stream_t stream) {
+    GS2D_REQUIRE(img_h > 0 && img_w > 0 && img_h % 2 == 0 && img_w % 2 == 0, "i420_to_rgb: width and height must be even");
+    GS2D_REQUIRE(yuv && rgb, "i420_to_rgb: null pointer");
+    GS2D_REQUIRE((((uintptr_t)yuv | (uintptr_t)rgb) & 1) == 0, "i420_to_rgb: buffers must be 2-byte aligned");
+    cudaStream_t s = (cudaStream_t)stream;
+    const int blocks2x2 = (img_h / 2) * (img_w / 2);
+    ProfScope ps_(GS2D_STAGE_OTHER, s);
+    k_i420_to_rgb<<<div_up(blocks2x2, kFitThreads), kFitThreads, 0, s>>>(img_h, img_w, yuv, rgb);
+    GS2D_CHECK_LAUNCH("i420_to_rgb");
+    return GS2D_OK;
 }
 
 int gs2d_render_chol(int n, int cap, int img_h, int img_w, const float* means_or_xyz_raw, const float* chol,

@@ -142,6 +142,13 @@ class FrameFit(torch.nn.Module):
         return loss, psnr
 
 
+class _NoAction:
+    kind, count, rebuild, replaces_parameters = "none", 0, False, False
+
+
+_NO_ACTION = _NoAction()
+
+
 class FusedFrameFit(torch.nn.Module):
     """The same fit loop on the fused C-ABI entry point gs2d_fit_step (include/gs2d.h): four
     kernels per iteration, nothing synchronises the host until a loss is read.  Parameters keep
@@ -151,7 +158,9 @@ class FusedFrameFit(torch.nn.Module):
         .train_iter(gt)          one iteration; returns (loss, psnr) -- reads the loss back
         .train_iters(gt, k)      k iterations, nothing read back; .loss(step) reads lazily
         .forward()               render [1,3,H,W] (clamped), sync-free
-    gt: fp32 [1,3,H,W] / [3,H,W] in [0,1] (the reference loader's format) or uint8 [H,W,3]."""
+    gt: fp32 [1,3,H,W] / [3,H,W] in [0,1] (the reference loader's format), uint8 RGB [H,W,3], or
+    the raw uint8 I420 frame [H*3/2,W] of the .yuv file (decoded inside the tile kernel exactly as
+    the reference's cv2 loader would)."""
 
     path_name = "fused C-ABI fit step (scatter-pack, tile kernel fwd+L2+bwd, projection-bwd+Adan+next count/scan): 3 kernels/iter"
 
@@ -188,6 +197,10 @@ class FusedFrameFit(torch.nn.Module):
         else:
             self.rgb_W = None
         self.clock = OptimizerClock()
+        self._opts = _lib.FitOptions()
+        self._cdll = _lib.load()
+        self._tile_rows = (self.H + 15) // 16
+        self._both_phases = _lib.FIT_PHASE_GRADS | _lib.FIT_PHASE_UPDATE
         self.lr, self.betas, self.eps, self.weight_decay = float(lr), tuple(betas), float(eps), float(weight_decay)
         self.lr_step_size, self.lr_gamma = int(lr_step_size), float(lr_gamma)
         self.step_index = 0
@@ -223,8 +236,13 @@ class FusedFrameFit(torch.nn.Module):
 
     def _target(self, gt: torch.Tensor):
         if gt.dtype == torch.uint8:
+            if gt.numel() * 2 == 3 * self.H * self.W and gt.dim() <= 2:
+                # the raw I420 frame of the .yuv file ([H*3/2, W] as utils.py:148 shapes it, or flat)
+                if self.H % 2 or self.W % 2:
+                    raise ValueError("an I420 target needs even width and height")
+                return gt.contiguous(), self._lib.TARGET_I420
             if gt.dim() != 3 or gt.shape != (self.H, self.W, 3):
-                raise ValueError("uint8 target must be [H,W,3]")
+                raise ValueError("uint8 target must be RGB [H,W,3] or a raw I420 frame [H*3/2,W]")
             return gt.contiguous(), self._lib.TARGET_U8_HWC
         if gt.dtype != torch.float32 or gt.numel() != 3 * self.H * self.W:
             raise ValueError("target must be fp32 [1,3,H,W] / [3,H,W] or uint8 [H,W,3]")
@@ -238,17 +256,17 @@ class FusedFrameFit(torch.nn.Module):
         return self.lr * self.lr_gamma ** (self.step_index // self.lr_step_size)
 
     def _options(self, adan_step: int, fresh: bool, skip: bool, w_grad_out=None):
-        o = self._lib.FitOptions()
+        o = self._opts
         if self.rgb_W is not None:
             o.rgb_w, o.adan_state_w = self.rgb_W.data_ptr(), self.adan_state_w.data_ptr()
             o.rgb_w_grad_out = None if w_grad_out is None else w_grad_out.data_ptr()
         o.adan_step, o.adan_fresh, o.skip_update = int(adan_step), int(fresh), int(skip)
         return o
 
-    def _issue(self, gt, fmt, out_img=None, grads_out=None, ids_out=None, w_grad_out=None):
-        from .density import Action
+    def _issue(self, gt, fmt, out_img=None, grads_out=None, ids_out=None, w_grad_out=None, stream=None):
+        """gt: the target on the device (tensor, or a raw device address)"""
         self.step_index += 1
-        act = self.plan.action(self.step_index, self.n) if self.rgb_W is not None else Action()
+        act = self.plan.action(self.step_index, self.n) if self.rgb_W is not None else _NO_ACTION
         if act.rebuild or act.replaces_parameters:
             self._control_sync()                    # the one host wait of the control: once per interval
         if act.rebuild and not act.replaces_parameters:
@@ -256,17 +274,20 @@ class FusedFrameFit(torch.nn.Module):
         adan_step, fresh, skip = self.clock.begin(act)
         opts = self._options(adan_step, fresh, skip, w_grad_out)
         b1, b2, b3 = self.betas
-        lib = self._lib.load()
         slot = self.step_index % self._lib.FIT_LOSS_SLOTS
-        self._lib.check(lib.gs2d_fit_step_band(
+        rc = self._cdll.gs2d_fit_step_band(
             self.n, self.cap, self.H, self.W, self._xyz.data_ptr(), self._cholesky.data_ptr(),
-            self._features_dc.data_ptr(), self.adan_state.data_ptr(), gt.data_ptr(), fmt, self.work.data_ptr(),
+            self._features_dc.data_ptr(), self.adan_state.data_ptr(), gt if isinstance(gt, int) else gt.data_ptr(),
+            fmt, self.work.data_ptr(),
             self.layout.total_bytes, self.step_index, self.current_lr(), b1, b2, b3, self.eps, self.weight_decay,
-            1 if self._precount_valid() else 0, 0, (self.H + 15) // 16,
-            self._lib.FIT_PHASE_GRADS | self._lib.FIT_PHASE_UPDATE, None, self._ctypes.addressof(opts),
+            1 if self._precount_valid() else 0, 0, self._tile_rows,
+            self._both_phases, None, self._ctypes.addressof(opts),
             None if out_img is None else out_img.data_ptr(),
             None if grads_out is None else grads_out.data_ptr(), None if ids_out is None else ids_out.data_ptr(),
-            self._report_ptr + 24 * slot, torch.cuda.current_stream(self.device).cuda_stream), "fit_step")
+            self._report_ptr + 24 * slot,
+            torch.cuda.current_stream(self.device).cuda_stream if stream is None else stream)
+        if rc:
+            self._lib.check(rc, "fit_step")
         if skip:
             self._counted_for = None                # a skipped update pre-counts nothing
             self._replace_parameters(act)
@@ -394,59 +415,87 @@ class FusedFrameFit(torch.nn.Module):
         loss = self.loss()
         return loss, 10 * math.log10(1.0 / loss)
 
-    def fit_stream(self, host_frames, prefetch: int = 2):
-        """One iteration per frame of `host_frames` (an iterable of pinned-host targets, uint8
-        [H,W,3] or fp32 [1,3,H,W]); yields (loss, psnr) of every step.  The copy of frame i+1 runs
-        on a side stream while step i computes (double-buffered device targets), and a step's loss
-        arrives in pinned memory with the step itself, so per step the host only waits on one event."""
+    def _await_report(self, step: int, stream: int):
+        """the step's report lands in pinned host memory with the step's last kernel: poll it
+        (cheaper and sooner than an event wait); falls back to a stream sync so that a failed
+        launch surfaces as an error instead of a hang"""
+        rec = self._report_np[step % self._lib.FIT_LOSS_SLOTS]
+        spins = 0
+        while rec[5] != step:
+            spins += 1
+            if spins > 2_000_000:
+                torch.cuda.current_stream(self.device).synchronize()
+                if rec[5] != step:
+                    raise RuntimeError(f"step {step} finished without reporting")
+
+    def fit_stream(self, host_frames, prefetch: int = 2, lag: int = 1):
+        """One iteration per frame of `host_frames` (an iterable of PINNED host targets of one
+        format: raw I420 [H*3/2,W], uint8 RGB [H,W,3] or fp32 [1,3,H,W]); yields (loss, psnr) of
+        every step, in order.  Frames travel through the library's frame pipe (include/gs2d.h):
+        the copy of frame i+1 runs on the pipe's stream under step i, and a step's loss arrives in
+        pinned memory with the step itself.  lag: how many steps may be in flight when a result is
+        handed back -- lag=1 (default) issues step i+1 before waiting for step i, so the host's
+        work on the next step hides under the device's; lag=0 is strictly synchronous."""
         dev = self.device
-        copy_stream = torch.cuda.Stream(device=dev)
-        main = torch.cuda.current_stream(dev)
-        bufs, copied, freed = [None] * prefetch, [None] * prefetch, [None] * prefetch
+        ct, lib, check = self._ctypes, self._cdll, self._lib.check
         it = iter(host_frames)
+        first = next(it, None)
+        if first is None:
+            return
+        if not first.is_pinned():
+            raise ValueError("fit_stream wants pinned host frames (tensor.pin_memory())")
+        fmt = self._target(first)[1]
+        frame_bytes = first.numel() * first.element_size()
+        depth = max(2, min(int(prefetch), 8))
+        slots = torch.empty((depth, frame_bytes), dtype=torch.uint8, device=dev)
+        pipe = ct.c_void_p()
+        check(lib.gs2d_frame_pipe_create(slots.data_ptr(), frame_bytes, depth, ct.byref(pipe)), "frame_pipe_create")
+        slot_out, ptr_out = ct.c_int(), ct.c_void_p()
+        stream = torch.cuda.current_stream(dev).cuda_stream
+        queued, inflight = [], []        # (slot, host frame) copied but not consumed; (step, host frame) issued
 
-        def stage(j, frame):
-            b = j % prefetch
-            if bufs[b] is None or bufs[b].shape != frame.shape or bufs[b].dtype != frame.dtype:
-                bufs[b] = torch.empty(frame.shape, dtype=frame.dtype, device=dev)
-            with torch.cuda.stream(copy_stream):
-                if freed[b] is not None:
-                    copy_stream.wait_event(freed[b])       # the step that read this buffer is done
-                bufs[b].copy_(frame, non_blocking=True)
-                ev = torch.cuda.Event()
-                ev.record(copy_stream)
-            copied[b] = ev
+        def push(frame):
+            if frame.numel() * frame.element_size() != frame_bytes or not frame.is_pinned():
+                raise ValueError("fit_stream: every frame must be pinned and of the first frame's size")
+            rc = lib.gs2d_frame_pipe_push(pipe, frame.data_ptr(), ct.byref(slot_out))
+            if rc:
+                check(rc, "frame_pipe_push")
+            queued.append((slot_out.value, frame))
 
-        pending = []
-        j = 0
-        for frame in it:
-            pending.append(frame)
-            stage(j, frame)
-            j += 1
-            if len(pending) >= prefetch:
-                break
-        i = 0
-        done_ev = torch.cuda.Event()
-        while pending:
-            pending.pop(0)
-            b = i % prefetch
-            main.wait_event(copied[b])
-            gt, fmt = self._target(bufs[b])
-            with self._C._guard(dev):
-                self._issue(gt, fmt)
-            step = self.step_index
-            fr = torch.cuda.Event()
-            fr.record(main)
-            freed[b] = fr
-            nxt = next(it, None)
-            if nxt is not None:                             # next frame's copy overlaps this step
-                pending.append(nxt)
-                stage(j, nxt)
-                j += 1
-            fr.synchronize()
+        def result(step):
+            self._await_report(step, stream)
             loss = self.loss(step, wait=False)
-            yield loss, 10 * math.log10(1.0 / max(loss, 1e-20))
-            i += 1
+            return loss, 10 * math.log10(1.0 / max(loss, 1e-20))
+
+        try:
+            with self._C._guard(dev):
+                push(first)
+                for _ in range(depth - 1):
+                    nxt = next(it, None)
+                    if nxt is None:
+                        break
+                    push(nxt)
+            while queued:
+                slot, frame = queued.pop(0)
+                with self._C._guard(dev):
+                    rc = lib.gs2d_frame_pipe_acquire(pipe, slot, stream, ct.byref(ptr_out))
+                    if rc:
+                        check(rc, "frame_pipe_acquire")
+                    self._issue(ptr_out.value, fmt, stream=stream)
+                    rc = lib.gs2d_frame_pipe_release(pipe, slot, stream)
+                    if rc:
+                        check(rc, "frame_pipe_release")
+                    inflight.append((self.step_index, frame))   # the frame stays alive until its step reported
+                    nxt = next(it, None)
+                    if nxt is not None:                          # its copy overlaps the step just issued
+                        push(nxt)
+                while len(inflight) > lag:
+                    yield result(inflight.pop(0)[0])
+            while inflight:
+                yield result(inflight.pop(0)[0])
+        finally:
+            torch.cuda.current_stream(dev).synchronize()
+            lib.gs2d_frame_pipe_destroy(pipe)
 
     @property
     def last_num_intersects(self) -> int:

@@ -63,7 +63,7 @@ def fit_gop(get_frame: Callable[[int], torch.Tensor], gop: Gop, make_fitter: Cal
         state = fit.frame_state() if hasattr(fit, "frame_state") else fit.state_dict()
         prev = {k: v.detach().clone() for k, v in state.items()}
         out[f] = {"state": {k: v.cpu() for k, v in prev.items()}, "psnr": 10 * math.log10(1.0 / max(loss, 1e-20)),
-                  "iters": iters}
+                  "iters": iters, "num_points": int(prev["_xyz"].shape[0])}
         if on_frame is not None:
             on_frame(f, fit)
     return out
@@ -94,3 +94,38 @@ def fit_sequence(get_frame: Callable[[int], torch.Tensor], num_frames: int, keyf
         merged.update(part)
     assert sorted(merged) == list(range(num_frames)), "GOP sharding lost or duplicated frames"
     return merged
+
+
+def synthetic_sequence(H: int, W: int, num_frames: int = 120, cut_every: int = 30, shift_px: float = 2.0,
+                       seed: int = 1):
+    """BASELINE config 4's sequence: one pattern translated by `shift_px` per frame with
+    a hard scene cut (new pattern) every `cut_every` frames.  -> (frame(f) -> [1,3,H,W] fp32,
+    key frame indices)."""
+    from . import synth
+
+    def frame(f: int) -> torch.Tensor:
+        return synth.target_frame(H, W, seed=seed, shift=shift_px * (f % cut_every), pattern=f // cut_every)
+
+    return frame, list(range(0, num_frames, cut_every))
+
+
+def reference_fitters(H: int, W: int, num_points: int, device, is_rm: bool = True, is_ad: bool = True,
+                      removal_rate: float = 0.1, densification_interval: int = 100, lr: float = 1e-3, seed: int = 1,
+                      cls=None, **kw):
+    """make_fitter for fit_gop / fit_sequence, built the way train_video_Represent.py:358-366 builds
+    its trainers: a key frame starts from `num_points` fresh Gaussians with the removal control
+    (isremoval = --is_rm); a predicted frame starts from the previous frame's Gaussians (their
+    count, their weighted colours) with the adaptive add / prune control (isdensity = --is_ad) and
+    max_num_points = num_points."""
+    if cls is None:
+        from .fit import FusedFrameFit as cls
+
+    def make(prev: Optional[dict]):
+        if prev is None:
+            return cls(H, W, num_points, device, lr=lr, seed=seed, isremoval=is_rm, removal_rate=removal_rate,
+                       max_num_points=num_points, densification_interval=densification_interval, **kw)
+        return cls(H, W, int(prev["_xyz"].shape[0]), device, lr=lr, init=prev, isdensity=is_ad,
+                   removal_rate=removal_rate, max_num_points=num_points,
+                   densification_interval=densification_interval, **kw)
+
+    return make

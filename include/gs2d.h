@@ -178,7 +178,12 @@ int gs2d_rasterize_sum_bwd_binned(int n, int num_intersects, const int32_t* gaus
  *               control region once (and the Adan state);
  *   adan_state  fp32 [4][n][8]: m, n, d, previous gradient of (xyz 2, chol 3, features 3);
  *   target      the frame to fit: GS2D_TARGET_F32_CHW fp32 planar [3][H][W] in [0,1], or
- *               GS2D_TARGET_U8_HWC uint8 interleaved [H][W][3] (compared as value / 255).
+ *               GS2D_TARGET_U8_HWC uint8 interleaved [H][W][3] (compared as value / 255), or
+ *               GS2D_TARGET_I420 the raw frame as the reference's .yuv file holds it (planar
+ *               YUV 4:2:0, 8 bit: H*W luma bytes, then (H/2)*(W/2) U, then V; H and W even),
+ *               converted per pixel inside the tile kernel exactly as the reference's loader
+ *               does (cv2.COLOR_YUV2RGB_I420, utils.py:134-156; see gs2d_i420_to_rgb) and
+ *               compared as value / 255 -- half the bytes of the RGB frame to move and read.
  * precounted: every step ends by projecting the UPDATED parameters and counting/scanning their
  * tiles, i.e. it pre-computes the next step's binning; pass precounted = 1 when the previous call
  * on this workspace was gs2d_fit_step and neither the parameters nor the workspace were touched
@@ -197,6 +202,7 @@ int gs2d_rasterize_sum_bwd_binned(int n, int num_intersects, const int32_t* gaus
 #define GS2D_FIT_LOSS_SLOTS 64
 #define GS2D_TARGET_F32_CHW 0
 #define GS2D_TARGET_U8_HWC 1
+#define GS2D_TARGET_I420 2
 typedef struct {
     size_t total_bytes;
     size_t off_status;      /* int32[16] */
@@ -300,6 +306,28 @@ size_t gs2d_prune_scratch_bytes(int n);
 int gs2d_prune_lowest(int n, int remove_count, const float* rgb_w, const float* xyz_raw, const float* chol_raw,
                       const float* features, float* rgb_w_out, float* xyz_out, float* chol_out, float* features_out,
                       int32_t* keep_index_out, void* scratch, size_t scratch_bytes, gs2d_stream_t stream);
+/* Frame pipe: raw frames from PINNED host memory into a ring of `depth` device slots
+ * (device_slots: depth * frame_bytes bytes, caller-owned) on the pipe's own copy stream, so the
+ * copy of the next frame runs under the current frame's fit step.  No counterpart in the
+ * reference, which decodes all frames on the CPU up front (utils.py:134-156) and moves each to
+ * the GPU synchronously (train_video_Represent.py:43).  Per frame:
+ *   push(host_frame) -> slot     copy queued (after the slot's previous consumer released it)
+ *   acquire(slot, stream)        `stream` waits for that copy; returns the slot's device pointer
+ *   ... enqueue the work that reads the frame on `stream` (gs2d_fit_step, gs2d_i420_to_rgb) ...
+ *   release(slot, stream)        the slot may be overwritten once the work queued so far is done
+ * Nothing here blocks the host.  The host frame must stay valid until its copy ran. */
+#define GS2D_PIPE_MAX_DEPTH 8
+typedef struct gs2d_frame_pipe gs2d_frame_pipe;
+int gs2d_frame_pipe_create(void* device_slots, size_t frame_bytes, int depth, gs2d_frame_pipe** out);
+int gs2d_frame_pipe_destroy(gs2d_frame_pipe* pipe);
+int gs2d_frame_pipe_push(gs2d_frame_pipe* pipe, const void* host_frame, int* slot_out);
+int gs2d_frame_pipe_acquire(gs2d_frame_pipe* pipe, int slot, gs2d_stream_t stream, void** device_frame);
+int gs2d_frame_pipe_release(gs2d_frame_pipe* pipe, int slot, gs2d_stream_t stream);
+/* The reference's frame loader arithmetic, process_yuv_video (utils.py:134-156):
+ * cv2.cvtColor(yuv, cv2.COLOR_YUV2RGB_I420) of one planar I420 frame -> uint8 RGB [H][W][3].
+ * OpenCV's BT.601 limited-range 20-bit fixed-point formula, chroma of the pixel's 2x2 block
+ * (oracle/yuv.py states it; bit-exact against cv2 over all 2^24 triples).  H and W even. */
+int gs2d_i420_to_rgb(int img_h, int img_w, const uint8_t* yuv, uint8_t* rgb, gs2d_stream_t stream);
 /* Render-only (decode): project_gaussians_2d + rasterize_gaussians_sum forward of the reference
  * (GaussianSplats_Represent.py:83-90) as three kernels, sync-free.  activate != 0: inputs are
  * the raw parameters (tanh / bound applied here); else means2d / L_elements as the projection

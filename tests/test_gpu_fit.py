@@ -288,15 +288,27 @@ def test_u8_target_all_values_match_ieee_division():
     assert fa.loss() == pytest.approx(fb.loss(), rel=1e-12)
 
 
-def test_fit_stream_equals_resident_loop():
-    """pinned-host frames streamed with overlapped copies give the same losses as the resident loop"""
-    H, W, n, K = 128, 160, 2_000, 12
+@pytest.mark.parametrize("fmt,lag,prefetch", [("rgb", 1, 2), ("rgb", 0, 2), ("i420", 1, 3), ("f32", 2, 4)])
+def test_fit_stream_equals_resident_loop(fmt, lag, prefetch):
+    """pinned-host frames streamed through the frame pipe (copies overlapped, results handed back
+    `lag` steps late) give the same losses, in order, as the resident loop"""
+    from gsvc_b200 import yuv
+    H, W, n, K = 128, 160, 2_000, 13
     init, gt, a = _setup(H, W, n, seed=4)
     _, _, b = _setup(H, W, n, seed=4)
     u8 = (gt[0] * 255).round().to(torch.uint8).permute(1, 2, 0).contiguous()
-    frames = [((u8.int() + 3 * i) % 256).to(torch.uint8).pin_memory() for i in range(3)]   # three different frames
+    rgbs = [((u8.int() + 3 * i) % 256).to(torch.uint8) for i in range(3)]                  # three different frames
+    if fmt == "rgb":
+        frames = [f.pin_memory() for f in rgbs]
+    elif fmt == "i420":
+        frames = [yuv.rgb_to_i420(f).contiguous().pin_memory() for f in rgbs]
+    else:
+        frames = [(f.permute(2, 0, 1).float() / 255).unsqueeze(0).contiguous().pin_memory() for f in rgbs]
     seq = [frames[i % 3] for i in range(K)]
-    la = [l for l, _ in a.fit_stream(seq)]
+    la = [l for l, _ in a.fit_stream(iter(seq), prefetch=prefetch, lag=lag)]
+    assert len(la) == K
+    with pytest.raises(ValueError):
+        next(a.fit_stream([frames[0].clone()]))          # not pinned
     lb = []
     for f in seq:
         l, _ = b.train_iter(f.to(cuda))
