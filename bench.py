@@ -215,7 +215,7 @@ def main_gpu(args, rank: int, world: int, local_rank: int):
 
     mine = args.impl in ("b200", "b200-dropin")
     fused = args.impl == "b200"
-    fit = make_fitter(args.impl, dev, seed=1 + rank, trained_like=args.trained_like)
+    fit = None
     raw = raw_frame(seed=1 + rank)                                       # uint8 [H*3/2, W] planar I420
     if fused:
         # the fused path takes the raw frame of the .yuv file and decodes it inside the tile kernel
@@ -226,7 +226,7 @@ def main_gpu(args, rank: int, world: int, local_rank: int):
         from gsvc_b200 import yuv as _yuv
         rgb = _yuv.i420_to_rgb(raw.to(dev), H, W)
         gt_host = (rgb.permute(2, 0, 1).float() / 255).unsqueeze(0).contiguous().cpu().pin_memory()
-        step_resident = fit.train_iter                                   # reads the loss back every step, as the reference
+        step_resident = lambda g: fit.train_iter(g)                                   # reads the loss back every step, as the reference
     gt = gt_host.to(dev)
     flush = torch.empty(L2_FLUSH_BYTES, dtype=torch.uint8, device=dev)
     K, Wm = args.steps, max(args.warmup, 3)
@@ -236,10 +236,16 @@ def main_gpu(args, rank: int, world: int, local_rank: int):
             dist.barrier()
         torch.cuda.synchronize(dev)
 
-    # ---- warm-up ---------------------------------------------------------------------------
-    for _ in range(Wm):
-        step_resident(gt)
-    barrier()
+    def fresh_model():
+        """every timed phase starts from the same state: the model as initialised + Wm warm-up
+        iterations, so `value`, `l2_warm`, `e2e` and the stage pass time the same K iterations"""
+        nonlocal fit
+        fit = make_fitter(args.impl, dev, seed=1 + rank, trained_like=args.trained_like)
+        for _ in range(Wm):
+            step_resident(gt)
+        barrier()
+
+    fresh_model()
 
     # ---- value: HBM-resident inputs, L2 flushed between steps, per-step CUDA events ------------
     sampler = ClockSampler(local_rank)
@@ -261,7 +267,7 @@ def main_gpu(args, rank: int, world: int, local_rank: int):
 
     # ---- same loop back to back (L2 warm: what a real fit loop sees), one event pair -----------
     a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    barrier()
+    fresh_model()
     a.record()
     for _ in range(K):
         step_resident(gt)
@@ -270,7 +276,7 @@ def main_gpu(args, rank: int, world: int, local_rank: int):
     warm_ms = a.elapsed_time(b) / K
 
     # ---- e2e: target frame in pinned host memory every step, loss read back every step -------
-    barrier()
+    fresh_model()
     a.record()
     psnr = 0.0
     if fused:
@@ -311,6 +317,7 @@ def main_gpu(args, rank: int, world: int, local_rank: int):
     # ---- per-stage timing pass (CUDA events inside the library, on the launching stream) ------
     stages = {}
     if mine:
+        fresh_model()
         _lib.prof_enable(True)
         for _ in range(K):
             flush.zero_()

@@ -7,7 +7,8 @@ import os
 from ctypes import POINTER, Structure, c_char_p, c_float, c_int, c_size_t, c_void_p
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "lib", "libgs2d.so")
+# GS2D_LIB: kernel-variant A/B runs only (profiles/build_variant.py); the product loads the in-tree build
+LIB_PATH = os.environ.get("GS2D_LIB") or os.path.join(_HERE, "lib", "libgs2d.so")
 
 GS2D_OK = 0
 

@@ -323,15 +323,20 @@ __device__ __forceinline__ float group8_reduce8_t(float (&v)[8], int lane) {
 // one warp instruction on pixel j covers the row pair {8w+2j, 8w+2j+1} -- the granularity of the
 // rectangle culling -- while dx, conic.x*dx and conic.y*dx are computed once per Gaussian and
 // reused by the four pixels (same operations as the reference's expression, so bit-identical).
+#ifndef GS2D_TILE_MIN_BLOCKS
+#define GS2D_TILE_MIN_BLOCKS 1
+#endif
 template <int MODE, int GT>
-__global__ void __launch_bounds__(kTileThreads)
+__global__ void __launch_bounds__(kTileThreads, GS2D_TILE_MIN_BLOCKS)
 k_fit_tiles(int W, int H, int tx, int row0, const int32_t* __restrict__ tile_off, int32_t* tile_fill,
             const float4* __restrict__ packed, const void* __restrict__ gt, float grad_scale,
             float* __restrict__ grads, double* loss_acc, const int32_t* __restrict__ status,
             float* __restrict__ out_img, int out_chw, int out_clamp, int32_t* __restrict__ final_idx,
             int32_t* __restrict__ ids_sorted_dbg, int want_opacity_grad, int loss_in_grads) {
     __shared__ float4 sq[GS2D_MAX_PER_TILE * 3];
-    __shared__ float4 sv[GS2D_TILE_PIX];          // v_out of the tile; before that, the id chunk of the staging
+    // v_out of the tile (rows 0..15; before that, the id chunk of the staging) + 16 rows of zeros:
+    // the backward's row walk may run past the tile for lanes whose pair has a shorter rectangle
+    __shared__ float4 sv[2 * GS2D_TILE_PIX];
     __shared__ float sred[kTileThreads / 32];
     int* sid = reinterpret_cast<int*>(sv);
     static_assert(sizeof(float4) * GS2D_TILE_PIX >= sizeof(int) * kIdChunk, "id chunk must fit in sv");
@@ -341,6 +346,11 @@ k_fit_tiles(int W, int H, int tx, int row0, const int32_t* __restrict__ tile_off
     const int t = tile_y * tx + blockIdx.x;
     const int lo = tile_off[t], cnt = tile_off[t + 1] - lo;
     if (tid == 0) tile_fill[t] = 0;   // ready for the next iteration's scatter
+    if (MODE == 0) {
+#pragma unroll
+        for (int j = 0; j < GS2D_TILE_PIX / kTileThreads; ++j)
+            sv[GS2D_TILE_PIX + j * kTileThreads + tid] = make_float4(0.f, 0.f, 0.f, 0.f);
+    }
 
     const int lx = lane & 15, ly0 = 8 * warp + (lane >> 4);   // pixel j: (lx, ly0 + 2j)
     const int ox = blockIdx.x * GS2D_TILE, oy = tile_y * GS2D_TILE;
@@ -504,7 +514,6 @@ k_fit_tiles(int W, int H, int tx, int row0, const int32_t* __restrict__ tile_off
         const float4 q0 = sq[3 * k], q2 = sq[3 * k + 2];
         const float gx = q0.x, gy = q0.y, cx = q0.z, cy = q0.w, cz = q1.x, opac = q1.y;
         float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-        float acc_op = 0.f;
         for (int cb0 = 0; cb0 < 2; ++cb0) {
             int max_h = (cb0 < ncol) ? h : 0;
             max_h = max(max_h, __shfl_xor_sync(0xffffffffu, max_h, 8));
@@ -512,51 +521,53 @@ k_fit_tiles(int W, int H, int tx, int row0, const int32_t* __restrict__ tile_off
             if (max_h == 0) break;
             const int lxp = rx0 + l8 + 8 * cb0;
             const bool col_ok = (cb0 < ncol) && lxp <= rx1;
+            const int lxs = min(lxp, GS2D_TILE - 1);                   // a readable column for lanes outside the rectangle
             const float dx = subf(gx, (float)(ox + lxp));
             const float t1 = mulf(cx, dx), t3 = mulf(cy, dx);
-            const float cxdx = cx * dx, cydx = cy * dx, dx2 = dx * dx;
+            // Straight-line inner loop: a lane outside its pair's rectangle (column beyond rx1, row
+            // beyond ry1) or a pixel that fails the reference's test contributes vis = alpha = 0.
+            // Per pixel only the moments of v_sigma over dy are accumulated (dx is the lane's
+            // constant): S0 = sum v_sigma, S1 = sum v_sigma*dy, S2 = sum v_sigma*dy^2; v_xy and
+            // v_conic (backward.cu:828-832) are linear in them and folded in after the column.
+            const float fy_last = col_ok ? (float)(oy + ry1) : -1.f;   // last row this lane really owns
+            float S0 = 0.f, S1 = 0.f, S2 = 0.f, cr = 0.f, cg = 0.f, cbl = 0.f;
+            float fy = (float)(oy + ry0);                              // row coordinate as a float (exact)
+            const float4* svc = sv + ry0 * GS2D_TILE + lxs;
             // kBwdRows rows per trip: that many independent sigma / ex2 chains in flight per lane
             // (the loop is latency-bound, not issue-bound: profiles/r1 notes)
             for (int ry = 0; ry < max_h; ry += kBwdRows) {
-                float dy[kBwdRows], sg[kBwdRows], vis[kBwdRows], al[kBwdRows];
 #pragma unroll
                 for (int u = 0; u < kBwdRows; ++u) {
-                    dy[u] = subf(gy, (float)(oy + ry0 + ry + u));
-                    const float q = fmaf_(dx, t1, mulf(mulf(cz, dy[u]), dy[u]));
-                    sg[u] = fmaf_(dy[u], t3, mulf(q, 0.5f));
-                }
-#pragma unroll
-                for (int u = 0; u < kBwdRows; ++u) {
-                    vis[u] = gauss_vis(sg[u]);
-                    al[u] = minf(mulf(opac, vis[u]), 1.f);
-                }
-#pragma unroll
-                for (int u = 0; u < kBwdRows; ++u) {
-                    if (!(col_ok && ry + u < h && gauss_pass(sg[u], al[u]))) continue;
-                    const float4 vo = sv[(ry0 + ry + u) * GS2D_TILE + lxp];
+                    const float fyu = fy + (float)u;
+                    const float dy = subf(gy, fyu);
+                    const float q = fmaf_(dx, t1, mulf(mulf(cz, dy), dy));
+                    const float sg = fmaf_(dy, t3, mulf(q, 0.5f));
+                    const float vis = gauss_vis(sg);
+                    const float al = minf(mulf(opac, vis), 1.f);
+                    const bool ok = (fyu <= fy_last) && gauss_pass(sg, al);
+                    const float visk = ok ? vis : 0.f, alk = ok ? al : 0.f;
+                    const float4 vo = svc[(ry + u) * GS2D_TILE];          // rows past the tile read the zero rows
                     const float v_alpha = q2.x * vo.x + q2.y * vo.y + q2.z * vo.z;   // backward.cu:821-825
-                    const float v_sigma = -opac * vis[u] * v_alpha;                   // :827
-                    acc[0] += v_sigma * (cxdx + cy * dy[u]);                          // v_xy     :831-832
-                    acc[1] += v_sigma * (cydx + cz * dy[u]);
-                    const float hs = 0.5f * v_sigma;
-                    acc[2] += hs * dx2;                                               // v_conic  :828-830
-                    acc[3] += hs * dx * dy[u];
-                    acc[4] += hs * dy[u] * dy[u];
-                    acc[5] += al[u] * vo.x;                                           // v_rgb    :817
-                    acc[6] += al[u] * vo.y;
-                    acc[7] += al[u] * vo.z;
-                    acc_op += vis[u] * v_alpha;                                       // v_opacity :833
+                    const float v_sigma = -opac * visk * v_alpha;                     // :827
+                    const float t = v_sigma * dy;
+                    S0 += v_sigma;
+                    S1 += t;
+                    S2 = fmaf(t, dy, S2);
+                    cr = fmaf(alk, vo.x, cr);                                         // v_rgb    :817
+                    cg = fmaf(alk, vo.y, cg);
+                    cbl = fmaf(alk, vo.z, cbl);
                 }
+                fy += (float)kBwdRows;
             }
+            acc[0] += cx * dx * S0 + cy * S1;                                         // v_xy     :831-832
+            acc[1] += cy * dx * S0 + cz * S1;
+            acc[2] += 0.5f * dx * dx * S0;                                            // v_conic  :828-830
+            acc[3] += 0.5f * dx * S1;
+            acc[4] += 0.5f * S2;
+            acc[5] += cr; acc[6] += cg; acc[7] += cbl;
         }
         const float tot = group8_reduce8_t(acc, lane);
         float* row = grads + (size_t)__float_as_int(q1.w) * 12;
-        if (want_opacity_grad) {   // the frame model keeps opacity fixed at 1: not needed by the fit step
-            acc_op += __shfl_xor_sync(0xffffffffu, acc_op, 4);
-            acc_op += __shfl_xor_sync(0xffffffffu, acc_op, 2);
-            acc_op += __shfl_xor_sync(0xffffffffu, acc_op, 1);
-            if (l8 == 0 && live && acc_op != 0.f) atomicAdd(row + 8, acc_op);
-        }
         if (live && tot != 0.f) atomicAdd(row + l8, tot);   // 4 pairs x 8 consecutive floats
     }
 }
