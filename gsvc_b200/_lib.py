@@ -50,7 +50,8 @@ class FitLayout(Structure):
 class GradExchange(Structure):
     """mirror of gs2d_grad_exchange (include/gs2d.h)"""
 
-    _fields_ = [("accumulate", c_void_p), ("peers", c_void_p), ("num_peers", c_int), ("zero", c_void_p)]
+    _fields_ = [("accumulate", c_void_p), ("peers", c_void_p), ("num_peers", c_int), ("zero", c_void_p),
+                ("multicast", c_void_p)]
 
 
 class FitOptions(Structure):

@@ -575,6 +575,19 @@ k_fit_tiles(int W, int H, int tx, int row0, const int32_t* __restrict__ tile_off
 // ------------------------------------------------------------------------------------------
 // K4: projection backward + tanh backward + Adan + gradient re-zeroing
 // ------------------------------------------------------------------------------------------
+// one 16-byte row segment summed over all ranks by the NVLink switch (NVLS)
+__device__ __forceinline__ float4 multimem_sum4(const float* mc) {
+    float4 v;
+    asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0, %1, %2, %3}, [%4];"
+                 : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(mc) : "memory");
+    return v;
+}
+__device__ __forceinline__ float multimem_sum1(const float* mc) {
+    float v;
+    asm volatile("multimem.ld_reduce.relaxed.sys.global.add.f32 %0, [%1];" : "=f"(v) : "l"(mc) : "memory");
+    return v;
+}
+
 struct AdanHyper {
     float b1, b2, b3;
     float step_size;        // lr / (1 - b1^t)
@@ -605,7 +618,7 @@ k_fit_update(int n, float* __restrict__ xyz_raw, float* __restrict__ chol_raw, f
              int32_t* __restrict__ tile_off, gs2d_fit_report* report_host, int row0, int row1, int loss_in_grads,
              const float* const* __restrict__ peer_grads, int num_peers, float* __restrict__ grads_zero,
              float* __restrict__ rgb_w, float* __restrict__ adan_w, float* __restrict__ rgb_w_grad_out,
-             int skip_update) {
+             int skip_update, const float* __restrict__ mc_grads) {
     __shared__ int sh[8];
     __shared__ int s_last;
     const int i = blockIdx.x * kFitThreads + threadIdx.x;
@@ -614,7 +627,9 @@ k_fit_update(int n, float* __restrict__ xyz_raw, float* __restrict__ chol_raw, f
         // for but the kernel itself); written before the scan below replaces status[0]
         double ls = *loss_this;
         if (loss_in_grads) {
-            if (num_peers > 0) {
+            if (mc_grads) {
+                ls = (double)multimem_sum1(mc_grads + 9);
+            } else if (num_peers > 0) {
                 float acc = 0.f;
                 for (int r = 0; r < num_peers; ++r) acc += __ldcg(peer_grads[r] + 9);
                 ls = (double)acc;
@@ -636,7 +651,11 @@ k_fit_update(int n, float* __restrict__ xyz_raw, float* __restrict__ chol_raw, f
         Proj2d p; float2 m; float3 L;
         fit_project(i, xyz_raw, chol_raw, 1, half_w, half_h, tx, ty, p, m, L);
         float4 g0, g1;   // v_xy(2) v_conic(3) v_rgb(3) | v_opacity(1) pad(3) unused here
-        if (num_peers > 0) {
+        if (mc_grads) {
+            // spatial mode over the switch: one load returns the row summed over all ranks
+            g0 = multimem_sum4(mc_grads + (size_t)i * 12);
+            g1 = multimem_sum4(mc_grads + (size_t)i * 12 + 4);
+        } else if (num_peers > 0) {
             // spatial mode over peer memory: the all-reduce IS this read -- every rank sums the
             // ranks' gradient rows (NVLink peer loads) in rank order, so all ranks compute
             // bit-identical updates with no collective kernel and no extra pass over the rows
@@ -842,6 +861,7 @@ int gs2d_fit_step_band(int n, int cap, int img_h, int img_w, float* xyz_raw, flo
     const float* const* peer_grads = nullptr;
     int num_peers = 0;
     float* grads_zero = nullptr;
+    const float* mc_grads = nullptr;
     if (exchange) {
         GS2D_REQUIRE(exchange->accumulate != nullptr, "fit_step: exchange without an accumulate buffer");
         GS2D_REQUIRE(exchange->num_peers >= 0 && (exchange->num_peers == 0 || exchange->peers != nullptr),
@@ -850,6 +870,8 @@ int gs2d_fit_step_band(int n, int cap, int img_h, int img_w, float* xyz_raw, flo
         peer_grads = exchange->peers;
         num_peers = exchange->num_peers;
         grads_zero = exchange->zero;
+        mc_grads = exchange->multicast;
+        if (mc_grads) { peer_grads = nullptr; num_peers = 0; }
     }
     float* rgb_w = nullptr; float* adan_w = nullptr; float* rgb_w_grad_out = nullptr;
     int adan_step = step, adan_fresh = step == 1, skip_update = 0;
@@ -900,7 +922,8 @@ int gs2d_fit_step_band(int n, int cap, int img_h, int img_w, float* xyz_raw, flo
             n, xyz_raw, chol_raw, features, adan_state, grads, half_w, half_h, tx, ty, h, status,
             loss + (step % GS2D_FIT_LOSS_SLOTS), loss + ((step + 1) % GS2D_FIT_LOSS_SLOTS), param_grads_out, cap,
             step + 1, (int32_t*)(w + L.off_tile_count), (int32_t*)(w + L.off_tile_off), report_host, row0, row1,
-            banded ? 1 : 0, peer_grads, num_peers, grads_zero, rgb_w, adan_w, rgb_w_grad_out, skip_update);
+            banded ? 1 : 0, peer_grads, num_peers, grads_zero, rgb_w, adan_w, rgb_w_grad_out, skip_update,
+            mc_grads);
         GS2D_CHECK_LAUNCH("fit_update");
     }
     return GS2D_OK;

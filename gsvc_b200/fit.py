@@ -598,8 +598,10 @@ class SpatialFrameFit(FusedFrameFit):
             raise NotImplementedError("the prune / add control is not wired into the tile-row split yet")
         self.group = group
         self.emulate_world = int(emulate_world)
-        if exchange not in ("nccl", "peer"):
-            raise ValueError("exchange must be 'nccl' or 'peer'")
+        if exchange not in ("nccl", "peer", "nvls"):
+            raise ValueError("exchange must be 'nccl', 'peer' or 'nvls'")
+        if exchange == "nvls" and emulate_world:
+            raise ValueError("the switch reduction needs real ranks (no single-GPU emulation)")
         self.exchange = exchange
         if self.emulate_world:
             self.world, self.rank = self.emulate_world, 0
@@ -613,7 +615,7 @@ class SpatialFrameFit(FusedFrameFit):
         lay = self.layout
         self._grads = self.work[lay.off_grads:lay.off_grads + self.n * 48].view(torch.float32)
         self._hdl = None
-        if exchange == "peer":
+        if exchange in ("peer", "nvls"):
             self._setup_peer_buffers()
 
     def _setup_peer_buffers(self):
@@ -633,13 +635,16 @@ class SpatialFrameFit(FusedFrameFit):
             base = [int(p) for p in self._hdl.buffer_ptrs]
             ptrs = [[base[r] + b * row_bytes for r in range(self.world)] for b in range(2)]
             self._own = [[base[self.rank] + b * row_bytes for b in range(2)]]
+            self._mc = int(self._hdl.multicast_ptr or 0)
+            if self.exchange == "nvls" and not self._mc:
+                raise RuntimeError("exchange='nvls': this process group has no NVLink-switch multicast (NVLS) mapping")
             torch.cuda.current_stream(dev).synchronize()
             self._hdl.barrier(channel=0)            # every rank's buffers are zero before anyone adds
         self._peer_lists = torch.tensor(ptrs, dtype=torch.int64, device=dev)   # [2][world] device pointers
 
     def _exchange_struct(self, rank_slot: int, with_peers: bool):
         """gs2d_grad_exchange for this step: accumulate into buffer step&1, zero the other one"""
-        if self.exchange != "peer":
+        if self.exchange == "nccl":
             return None
         x = self.step_index & 1
         ex = self._lib.GradExchange()
@@ -647,6 +652,7 @@ class SpatialFrameFit(FusedFrameFit):
         ex.peers = self._peer_lists[x].data_ptr() if with_peers else None
         ex.num_peers = self.world if with_peers else 0
         ex.zero = self._own[rank_slot][1 - x]
+        ex.multicast = (self._mc + x * self.n * 48) if (with_peers and self.exchange == "nvls") else None
         return ex
 
     def _band_call(self, gt, fmt, band, phases, precounted, dbg, ex=None):
@@ -677,7 +683,7 @@ class SpatialFrameFit(FusedFrameFit):
             self._counted_for = None                     # the pre-count covered band 0 only
             return
         band = self.bands[self.rank]
-        if self.exchange == "peer":
+        if self.exchange in ("peer", "nvls"):
             self._band_call(gt, fmt, band, G, self._precount_valid(), dbg, self._exchange_struct(0, False))
             self._hdl.barrier(channel=0)                 # device-side, on the current stream: all bands are in
             self._band_call(gt, fmt, band, U, False, dbg, self._exchange_struct(0, True))

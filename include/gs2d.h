@@ -260,6 +260,11 @@ typedef struct {
     const float* const* peers;
     int num_peers;
     float* zero;
+    const float* multicast;   /* != NULL: the NVLink-switch multicast address of this step's buffers
+                               * (all ranks' `accumulate` bound to one multicast object): the update
+                               * kernel sums the rows with multimem.ld_reduce -- the switch adds the
+                               * ranks' copies and returns one row, so a rank reads n*48 bytes
+                               * whatever the world size.  peers / num_peers are then ignored. */
 } gs2d_grad_exchange;
 /* Optional extras of a step: the learnable colour weight and the optimizer bookkeeping that the
  * reference's prune / add control needs (GaussianSplats_Represent.py:31-36 rgb_W, :62-67

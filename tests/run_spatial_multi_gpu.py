@@ -23,7 +23,7 @@ def main():
     ap.add_argument("--n", type=int, default=200_000)
     ap.add_argument("--iters", type=int, default=50)
     ap.add_argument("--warmup", type=int, default=10)
-    ap.add_argument("--exchange", default="nccl", choices=["nccl", "peer"])
+    ap.add_argument("--exchange", default="nccl", choices=["nccl", "peer", "nvls"])
     a = ap.parse_args()
     rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
     torch.cuda.set_device(local)
