@@ -187,12 +187,13 @@ def main_reference(args, rank: int):
 # ------------------------------------------------------------------------------------------
 # GPU arms
 # ------------------------------------------------------------------------------------------
-def make_fitter(impl: str, dev, seed: int, trained_like: bool = False):
+def make_fitter(impl: str, dev, seed: int, trained_like: bool = False, slots: bool = True):
     import torch
     if trained_like:
         from gsvc_b200 import synth
         from gsvc_b200.fit import FusedFrameFit
-        return FusedFrameFit(H, W, NPTS, dev, init=synth.gaussians(NPTS, seed=seed, trained_like=True), cap=1 << 22)
+        return FusedFrameFit(H, W, NPTS, dev, init=synth.gaussians(NPTS, seed=seed, trained_like=True), cap=1 << 22,
+                             slots=slots)
     if impl == "reference-gpu":
         sys.path.insert(0, os.path.join(ROOT, "tests"))
         import ref_fit
@@ -200,7 +201,7 @@ def make_fitter(impl: str, dev, seed: int, trained_like: bool = False):
     from gsvc_b200.fit import FrameFit, FusedFrameFit
     if impl == "b200-dropin":
         return FrameFit(H, W, NPTS, dev, seed=seed)
-    return FusedFrameFit(H, W, NPTS, dev, seed=seed)
+    return FusedFrameFit(H, W, NPTS, dev, seed=seed, slots=slots)
 
 
 def main_gpu(args, rank: int, world: int, local_rank: int):
@@ -240,7 +241,7 @@ def main_gpu(args, rank: int, world: int, local_rank: int):
         """every timed phase starts from the same state: the model as initialised + Wm warm-up
         iterations, so `value`, `l2_warm`, `e2e` and the stage pass time the same K iterations"""
         nonlocal fit
-        fit = make_fitter(args.impl, dev, seed=1 + rank, trained_like=args.trained_like)
+        fit = make_fitter(args.impl, dev, seed=1 + rank, trained_like=args.trained_like, slots=not args.ranges)
         for _ in range(Wm):
             step_resident(gt)
         barrier()
@@ -486,6 +487,8 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "b200-dropin", "reference", "reference-gpu"])
     ap.add_argument("--cpu-steps", type=int, default=20, help="fit iterations of the cpu_baseline leg")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--ranges", action="store_true",
+                    help="tile ranges (count + scan + scatter, 3 kernels/iter) instead of fixed tile slots (2 kernels/iter)")
     ap.add_argument("--trained-like", action="store_true",
                     help="informational: wide Gaussians (L = 4*rand + bound, ~10x the intersections, tiles beyond 256)")
     args = ap.parse_args()

@@ -31,6 +31,14 @@ constexpr int kStNumIntersects = 0;   // status words (int32[16])
 constexpr int kStOverflow = 1;        // first step index whose intersections exceeded cap (0 = none)
 constexpr int kStTicket = 2;
 constexpr int kStMaxPerTile = 3;      // max entries of any tile in the last step
+constexpr int kStSlotIsect = 4;       // [4], [5]: slot mode, intersections of the step with that parity
+constexpr int kStSlotMax = 32;        // slot mode's running max per tile: one reduction per CTA, so it lives on
+                                      // a cache line of its own (every CTA's first load is the flag in line 0)
+constexpr int kScatterBatch = 8;      // slot claims a thread keeps in flight before it writes records
+#ifndef GS2D_SLOT_STRIDE
+#define GS2D_SLOT_STRIDE GS2D_MAX_PER_TILE
+#endif
+constexpr int kSlotStride = GS2D_SLOT_STRIDE;   // records between two tiles' slots (experiments only: < 256 drops the Q1 guarantee)
 
 __device__ __forceinline__ void cp_async16(void* smem, const void* gmem) {
     const unsigned sa = (unsigned)__cvta_generic_to_shared(smem);
@@ -190,35 +198,115 @@ k_fit_count(int n, const float* __restrict__ xyz_raw, const float* __restrict__ 
 }
 
 // ------------------------------------------------------------------------------------------
-// K2: scatter the packed records into their tiles' ranges
+// K2: scatter the packed records into their tiles
 // packed[pos] = { x, y, conic.x, conic.y | conic.z, opacity, rect, gaussian id | r, g, b, tile }
+// Two addressings of the same records:
+//   ranges (SLOT = false)  tile t owns [tile_off[t], tile_off[t+1]) -- needs the count + scan first;
+//   slots  (SLOT = true)   tile t owns [t*256, t*256 + 256): no count, no scan, so the update kernel
+//                          can scatter the NEXT step's records itself (two kernels per iteration).
+//                          256 is all the reference ever renders of a tile; WHICH 256
+//                          of a fuller tile needs all its ids, so a 257th claim flags the step
+//                          (status[kStOverflow] = -step) and the caller redoes it with ranges.
+// The claims (atomics that return a position) of up to kScatterBatch tiles are issued back to back
+// before the first record is written: a Gaussian's tiles then cost one round trip to L2, not one each.
+// Returns the number of tiles claimed.
 // ------------------------------------------------------------------------------------------
+template <bool SLOT>
+__device__ __forceinline__ int scatter_records(const Proj2d& p, int i, float o, float r, float g, float b, int tx,
+                                               int row0, int row1, int W, int H, const int32_t* __restrict__ tile_off,
+                                               int32_t* tile_fill, float4* __restrict__ packed, int32_t* status,
+                                               int flag_step) {
+    if (p.nth <= 0) return 0;
+    const int ya = max(p.y0, row0), yb = min(p.y1, row1);
+    const int bw = p.x1 - p.x0;
+    const int nt = (yb - ya) * bw;
+    if (nt <= 0) return 0;
+    int x = p.x0, y = ya;
+    for (int base = 0; base < nt; base += kScatterBatch) {
+        int pos[kScatterBatch];
+        const int xs = x, ys = y;
+#pragma unroll
+        for (int k = 0; k < kScatterBatch; ++k) {
+            if (base + k < nt) {
+                pos[k] = atomicAdd(&tile_fill[y * tx + x], 1);
+                if (++x == p.x1) { x = p.x0; ++y; }
+            }
+        }
+        int xr = xs, yr = ys;
+#pragma unroll
+        for (int k = 0; k < kScatterBatch; ++k) {
+            if (base + k < nt) {
+                const int t = yr * tx + xr;
+                size_t at;
+                bool ok = true;
+                if (SLOT) {
+                    ok = pos[k] < kSlotStride;
+                    if (!ok) atomicCAS(&status[kStOverflow], 0, -flag_step);
+                    at = (size_t)t * kSlotStride + pos[k];
+                } else {
+                    at = (size_t)tile_off[t] + pos[k];
+                }
+                if (ok) {
+                    const uint32_t rect = pair_rect(p.cx, p.cy, o, p.conic.x, p.conic.y, p.conic.z, xr * GS2D_TILE,
+                                                    yr * GS2D_TILE, W, H);
+                    packed[3 * at + 0] = make_float4(p.cx, p.cy, p.conic.x, p.conic.y);
+                    packed[3 * at + 1] = make_float4(p.conic.z, o, __uint_as_float(rect), __int_as_float(i));
+                    packed[3 * at + 2] = make_float4(r, g, b, __uint_as_float((uint32_t)t));
+                }
+                if (++xr == p.x1) { xr = p.x0; ++yr; }
+            }
+        }
+    }
+    return nt;
+}
+
+// block sum of one int per thread -> one atomic per block (slot mode's intersection count)
+__device__ __forceinline__ void block_add(int v, int32_t* dst, int* sh) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    __syncthreads();
+    if ((threadIdx.x & 31) == 0) sh[threadIdx.x >> 5] = v;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        int s = 0;
+        for (int w = 0; w < kFitThreads / 32; ++w) s += sh[w];
+        if (s) atomicAdd(dst, s);
+    }
+}
+
 __global__ void __launch_bounds__(kFitThreads)
 k_fit_scatter(int n, const float* __restrict__ xyz_raw, const float* __restrict__ chol_raw,
               const float* __restrict__ feat, const float* __restrict__ opac, const float* __restrict__ rgb_w,
               int activate, float half_w, float half_h,
               int tx, int ty, int row0, int row1, int W, int H, const int32_t* __restrict__ tile_off,
-              int32_t* tile_fill, const int32_t* __restrict__ status, float4* __restrict__ packed) {
-    if (status[kStOverflow] != 0) return;
+              int32_t* tile_fill, int32_t* status, float4* __restrict__ packed, int slots, int step) {
+    __shared__ int sh[8];
+    // not an early return: in slot mode another block may raise the flag while this one runs, and
+    // every thread must reach the block sum below
+    const bool dead = status[kStOverflow] != 0;
     const int i = blockIdx.x * kFitThreads + threadIdx.x;
-    if (i >= n) return;
-    Proj2d p; float2 m; float3 L;
-    fit_project(i, xyz_raw, chol_raw, activate, half_w, half_h, tx, ty, p, m, L);
-    if (p.nth <= 0) return;
-    const float o = opac ? opac[i] : 1.f;
-    // colours = _features_dc * rgb_W (GaussianSplats_Represent.py:62-63); plain fp32 products
-    const float cw = rgb_w ? rgb_w[i] : 1.f;
-    const float r = mulf(feat[3 * i], cw), g = mulf(feat[3 * i + 1], cw), b = mulf(feat[3 * i + 2], cw);
-    for (int y = max(p.y0, row0); y < min(p.y1, row1); ++y)
-        for (int x = p.x0; x < p.x1; ++x) {
-            const int t = y * tx + x;
-            const int pos = tile_off[t] + atomicAdd(&tile_fill[t], 1);
-            const uint32_t rect = pair_rect(p.cx, p.cy, o, p.conic.x, p.conic.y, p.conic.z, x * GS2D_TILE,
-                                            y * GS2D_TILE, W, H);
-            packed[3 * (size_t)pos + 0] = make_float4(p.cx, p.cy, p.conic.x, p.conic.y);
-            packed[3 * (size_t)pos + 1] = make_float4(p.conic.z, o, __uint_as_float(rect), __int_as_float(i));
-            packed[3 * (size_t)pos + 2] = make_float4(r, g, b, __uint_as_float((uint32_t)t));
-        }
+    int claimed = 0;
+    if (i < n && !dead) {
+        Proj2d p; float2 m; float3 L;
+        fit_project(i, xyz_raw, chol_raw, activate, half_w, half_h, tx, ty, p, m, L);
+        const float o = opac ? opac[i] : 1.f;
+        // colours = _features_dc * rgb_W (GaussianSplats_Represent.py:62-63); plain fp32 products
+        const float cw = rgb_w ? rgb_w[i] : 1.f;
+        const float r = mulf(feat[3 * i], cw), g = mulf(feat[3 * i + 1], cw), b = mulf(feat[3 * i + 2], cw);
+        if (slots)
+            claimed = scatter_records<true>(p, i, o, r, g, b, tx, row0, row1, W, H, nullptr, tile_fill, packed, status, step);
+        else
+            scatter_records<false>(p, i, o, r, g, b, tx, row0, row1, W, H, tile_off, tile_fill, packed, status, step);
+    }
+    if (slots) block_add(claimed, &status[kStSlotIsect + (step & 1)], sh);
+}
+
+// slot mode, parameters changed behind the library's back: forget the stale scatter
+__global__ void __launch_bounds__(kFitThreads)
+k_fit_reset_slots(int tiles, int32_t* tile_fill, int32_t* status) {
+    const int t = blockIdx.x * kFitThreads + threadIdx.x;
+    if (t < tiles) tile_fill[t] = 0;
+    if (t == 0) { status[kStSlotIsect] = 0; status[kStSlotIsect + 1] = 0; status[kStSlotMax] = 0; }
 }
 
 // ------------------------------------------------------------------------------------------
@@ -330,9 +418,9 @@ template <int MODE, int GT>
 __global__ void __launch_bounds__(kTileThreads, GS2D_TILE_MIN_BLOCKS)
 k_fit_tiles(int W, int H, int tx, int row0, const int32_t* __restrict__ tile_off, int32_t* tile_fill,
             const float4* __restrict__ packed, const void* __restrict__ gt, float grad_scale,
-            float* __restrict__ grads, double* loss_acc, const int32_t* __restrict__ status,
+            float* __restrict__ grads, double* loss_acc, int32_t* __restrict__ status,
             float* __restrict__ out_img, int out_chw, int out_clamp, int32_t* __restrict__ final_idx,
-            int32_t* __restrict__ ids_sorted_dbg, int want_opacity_grad, int loss_in_grads) {
+            int32_t* __restrict__ ids_sorted_dbg, int step, int loss_in_grads) {
     __shared__ float4 sq[GS2D_MAX_PER_TILE * 3];
     // v_out of the tile (rows 0..15; before that, the id chunk of the staging) + 16 rows of zeros:
     // the backward's row walk may run past the tile for lanes whose pair has a shorter rectangle
@@ -344,8 +432,12 @@ k_fit_tiles(int W, int H, int tx, int row0, const int32_t* __restrict__ tile_off
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int tile_y = (int)blockIdx.y + row0;
     const int t = tile_y * tx + blockIdx.x;
-    const int lo = tile_off[t], cnt = tile_off[t + 1] - lo;
-    if (tid == 0) tile_fill[t] = 0;   // ready for the next iteration's scatter
+    // ranges: the tile's records are [tile_off[t], tile_off[t+1]); slots (tile_off == NULL): the
+    // first tile_fill[t] of [t*256, t*256+256) (a fuller tile flagged the step: not reached)
+    const int lo = tile_off ? tile_off[t] : t * kSlotStride;
+    const int cnt = tile_off ? tile_off[t + 1] - lo : tile_fill[t];
+    // (tile_fill[t] is re-zeroed further down, after the staging's barrier: a store to the address
+    // of the load in flight would park this warp on it before its target loads are even issued)
     if (MODE == 0) {
 #pragma unroll
         for (int j = 0; j < GS2D_TILE_PIX / kTileThreads; ++j)
@@ -357,6 +449,7 @@ k_fit_tiles(int W, int H, int tx, int row0, const int32_t* __restrict__ tile_off
     const int px_i = ox + lx;
     const bool in_x = px_i < W;
     uint32_t tgt_u8[4] = {0u, 0u, 0u, 0u};
+    uint8_t raw_y[4] = {0, 0, 0, 0}, raw_u[4] = {0, 0, 0, 0}, raw_v[4] = {0, 0, 0, 0};   // I420: decoded where the target is used
     float3 tgt[4];
 #pragma unroll
     for (int j = 0; j < 4; ++j) tgt[j] = make_float3(0.f, 0.f, 0.f);
@@ -376,14 +469,25 @@ k_fit_tiles(int W, int H, int tx, int row0, const int32_t* __restrict__ tile_off
                 } else {   // I420: luma plane, then the two quarter-size chroma planes
                     const uint8_t* g = (const uint8_t*)gt;
                     const size_t plane = (size_t)H * W, cid = (size_t)(py_i >> 1) * (W >> 1) + (px_i >> 1);
-                    tgt_u8[j] = yuv_to_rgb_packed(__ldg(g + pid), __ldg(g + plane + cid),
-                                                  __ldg(g + plane + (plane >> 2) + cid));
+                    // only loaded here: touching the bytes now would park the warp on DRAM latency
+                    // before the batch is even requested
+                    raw_y[j] = __ldg(g + pid);
+                    raw_u[j] = __ldg(g + plane + cid);
+                    raw_v[j] = __ldg(g + plane + (plane >> 2) + cid);
                 }
             }
         }
     }
 
     const int nb = stage_tile_sorted(packed + 3 * (size_t)lo, cnt, sq, sid, tid);
+    if (tid == 0) {                   // every thread is past a barrier that it reached knowing cnt
+        tile_fill[t] = 0;             // ready for the next iteration's scatter
+        if (!tile_off && MODE == 0) {
+            atomicMax(&status[kStSlotMax], cnt);   // result unused: a reduction the CTA never waits for
+            if (blockIdx.x == 0 && blockIdx.y == 0)                    // the update kernel counts the next step into it
+                status[kStSlotIsect + ((step + 1) & 1)] = 0;
+        }
+    }
     if (ids_sorted_dbg) {   // parity tests: the order the batch is rendered in
         for (int r = tid; r < nb; r += kTileThreads) ids_sorted_dbg[lo + r] = __float_as_int(sq[3 * r + 1].w);
         for (int r = nb + tid; r < cnt; r += kTileThreads) ids_sorted_dbg[lo + r] = -1;
@@ -464,6 +568,7 @@ k_fit_tiles(int W, int H, int tx, int row0, const int32_t* __restrict__ tile_off
 #pragma unroll
     for (int j = 0; j < 4; ++j) {
         float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (GT == 2) tgt_u8[j] = yuv_to_rgb_packed(raw_y[j], raw_u[j], raw_v[j]);
         if (GT != 0) tgt[j] = make_float3(u8_over_255(tgt_u8[j] & 255u), u8_over_255((tgt_u8[j] >> 8) & 255u),
                                           u8_over_255((tgt_u8[j] >> 16) & 255u));
         if (inside[j]) {
@@ -618,10 +723,15 @@ k_fit_update(int n, float* __restrict__ xyz_raw, float* __restrict__ chol_raw, f
              int32_t* __restrict__ tile_off, gs2d_fit_report* report_host, int row0, int row1, int loss_in_grads,
              const float* const* __restrict__ peer_grads, int num_peers, float* __restrict__ grads_zero,
              float* __restrict__ rgb_w, float* __restrict__ adan_w, float* __restrict__ rgb_w_grad_out,
-             int skip_update, const float* __restrict__ mc_grads) {
+             int skip_update, const float* __restrict__ mc_grads, int slots, float4* __restrict__ packed, int W,
+             int H) {
     __shared__ int sh[8];
     __shared__ int s_last;
     const int i = blockIdx.x * kFitThreads + threadIdx.x;
+    // a flag for a LATER step (slot mode: another block may be raising it right now for the step
+    // being scattered below) must not stop this step's update half way
+    const int of = status[kStOverflow];
+    const bool dead = of != 0 && abs(of) < next_step;
     if (i == 0 && report_host) {
         // the step's result straight into pinned host memory (no copy to issue, nothing to wait
         // for but the kernel itself); written before the scan below replaces status[0]
@@ -638,15 +748,17 @@ k_fit_update(int n, float* __restrict__ xyz_raw, float* __restrict__ chol_raw, f
             }
         }
         report_host->loss_sum = ls;
-        report_host->num_intersects = status[kStNumIntersects];
-        report_host->overflow_step = status[kStOverflow];
-        report_host->max_per_tile = status[kStMaxPerTile];
+        report_host->num_intersects = slots ? status[kStSlotIsect + ((next_step - 1) & 1)] : status[kStNumIntersects];
+        report_host->overflow_step = of;
+        report_host->max_per_tile = slots ? status[kStSlotMax] : status[kStMaxPerTile];
+        if (slots) status[kStSlotMax] = 0;   // the tile kernel of the next step raises it again
         __threadfence_system();
         report_host->step = next_step - 1;   // written last: the host treats it as the valid flag
         __threadfence_system();
     }
-    if (status[kStOverflow] != 0) return;
+    if (dead) return;
     if (i == 0 && loss_next) *loss_next = 0.0;
+    int claimed = 0;
     if (i < n) {
         Proj2d p; float2 m; float3 L;
         fit_project(i, xyz_raw, chol_raw, 1, half_w, half_h, tx, ty, p, m, L);
@@ -721,7 +833,8 @@ k_fit_update(int n, float* __restrict__ xyz_raw, float* __restrict__ chol_raw, f
         feat[3 * i] = par[5]; feat[3 * i + 1] = par[6]; feat[3 * i + 2] = par[7];
         if (rgb_w) {
             float wm = adan_w[i], wn = adan_w[(size_t)n + i], wd = adan_w[2 * (size_t)n + i], wp = adan_w[3 * (size_t)n + i];
-            rgb_w[i] = adan_one(cw, gw, wm, wn, wd, wp, h);
+            cw = adan_one(cw, gw, wm, wn, wd, wp, h);
+            rgb_w[i] = cw;
             adan_w[i] = wm; adan_w[(size_t)n + i] = wn; adan_w[2 * (size_t)n + i] = wd; adan_w[3 * (size_t)n + i] = wp;
         }
         // the next iteration's binning starts here: project the updated parameters and count tiles
@@ -729,9 +842,20 @@ k_fit_update(int n, float* __restrict__ xyz_raw, float* __restrict__ chol_raw, f
         Proj2d pn;
         project_chol(tanhf(par[0]), tanhf(par[1]), addf(par[2], 0.5f), addf(par[3], 0.f), addf(par[4], 0.5f), half_w,
                      half_h, tx, ty, pn);
-        count_tiles(pn, tx, row0, row1, tile_count);
+        if (slots) {
+            // ... and with fixed slots per tile there is nothing to count or scan first: the records
+            // of the next iteration are written right here (tile_count is the tiles' fill level)
+            claimed = scatter_records<true>(pn, i, 1.f, mulf(par[5], cw), mulf(par[6], cw), mulf(par[7], cw), tx, row0,
+                                            row1, W, H, nullptr, tile_count, packed, status, next_step);
+        } else {
+            count_tiles(pn, tx, row0, row1, tile_count);
+        }
     }
     if (skip_update) return;
+    if (slots) {
+        block_add(claimed, &status[kStSlotIsect + (next_step & 1)], sh);
+        return;
+    }
     scan_tiles_by_last_block(tx, ty, cap, next_step, tile_count, tile_off, status, sh, &s_last);
 }
 
@@ -766,7 +890,7 @@ static int fit_layout(int n, int cap, int img_h, int img_w, gs2d_fit_layout* L) 
     }
     const long long tiles = (long long)div_up(img_w, GS2D_TILE) * div_up(img_h, GS2D_TILE);
     size_t o = 0;
-    L->off_status = o;      o = align_up(o + 16 * sizeof(int32_t), 256);
+    L->off_status = o;      o = align_up(o + 64 * sizeof(int32_t), 256);
     L->off_loss = o;        o = align_up(o + GS2D_FIT_LOSS_SLOTS * sizeof(double), 256);
     L->off_tile_count = o;  o = align_up(o + (size_t)tiles * sizeof(int32_t), 256);
     L->off_tile_off = o;    o = align_up(o + (size_t)(tiles + 1) * sizeof(int32_t), 256);
@@ -822,7 +946,7 @@ static int launch_bin(int n, const float* xyz, const float* chol, const float* f
         ProfScope ps_(GS2D_STAGE_EDGES_PACK, s);
         k_fit_scatter<<<blocks, kFitThreads, 0, s>>>(n, xyz, chol, feat, opac, rgb_w, activate, half_w, half_h, tx, ty,
                                                      row0, row1, img_w, img_h, tile_off, tile_count, status,
-                                                     (float4*)(w + L.off_packed));
+                                                     (float4*)(w + L.off_packed), 0, step);
         GS2D_CHECK_LAUNCH("fit_scatter");
     }
     return GS2D_OK;
@@ -874,8 +998,11 @@ int gs2d_fit_step_band(int n, int cap, int img_h, int img_w, float* xyz_raw, flo
         if (mc_grads) { peer_grads = nullptr; num_peers = 0; }
     }
     float* rgb_w = nullptr; float* adan_w = nullptr; float* rgb_w_grad_out = nullptr;
-    int adan_step = step, adan_fresh = step == 1, skip_update = 0;
+    int adan_step = step, adan_fresh = step == 1, skip_update = 0, slots = 0;
     if (options) {
+        slots = options->slots != 0;
+        GS2D_REQUIRE(!slots || (long long)cap >= (long long)L.tiles * GS2D_MAX_PER_TILE,
+                     "fit_step: slot mode needs cap >= tiles * 256");
         GS2D_REQUIRE(options->rgb_w == nullptr || options->adan_state_w != nullptr,
                      "fit_step: rgb_w without its optimizer state");
         GS2D_REQUIRE(options->adan_step >= 0, "fit_step: negative adan_step");
@@ -885,27 +1012,41 @@ int gs2d_fit_step_band(int n, int cap, int img_h, int img_w, float* xyz_raw, flo
     }
     if (phases & GS2D_FIT_PHASE_GRADS) {
         GS2D_REQUIRE(target != nullptr, "fit_step: null target");
-        rc = launch_bin(n, xyz_raw, chol_raw, features, nullptr, rgb_w, 1, img_h, img_w, row0, row1, cap, step, L, w, s,
-                        precounted != 0);
-        if (rc != GS2D_OK) return rc;
+        if (slots) {
+            if (!precounted) {   // nothing scattered for these parameters yet (first step, or they were modified)
+                ProfScope ps_(GS2D_STAGE_EDGES_PACK, s);
+                k_fit_reset_slots<<<div_up(L.tiles, kFitThreads), kFitThreads, 0, s>>>(
+                    L.tiles, (int32_t*)(w + L.off_tile_count), status);
+                GS2D_CHECK_LAUNCH("fit_reset_slots");
+                k_fit_scatter<<<div_up(n, kFitThreads), kFitThreads, 0, s>>>(
+                    n, xyz_raw, chol_raw, features, nullptr, rgb_w, 1, half_w, half_h, tx, ty, row0, row1, img_w, img_h,
+                    nullptr, (int32_t*)(w + L.off_tile_count), status, (float4*)(w + L.off_packed), 1, step);
+                GS2D_CHECK_LAUNCH("fit_scatter_slots");
+            }
+        } else {
+            rc = launch_bin(n, xyz_raw, chol_raw, features, nullptr, rgb_w, 1, img_h, img_w, row0, row1, cap, step, L, w,
+                            s, precounted != 0);
+            if (rc != GS2D_OK) return rc;
+        }
+        const int32_t* tile_off_arg = slots ? nullptr : (const int32_t*)(w + L.off_tile_off);
         const float grad_scale = (float)(2.0 / (3.0 * (double)img_h * (double)img_w));   // the WHOLE frame's mean
         ProfScope ps_(GS2D_STAGE_FIT_TILES, s);
         const dim3 grid(tx, row1 - row0);
         if (target_format == GS2D_TARGET_F32_CHW)
             k_fit_tiles<0, 0><<<grid, kTileThreads, 0, s>>>(
-                img_w, img_h, tx, row0, (const int32_t*)(w + L.off_tile_off), (int32_t*)(w + L.off_tile_count),
+                img_w, img_h, tx, row0, tile_off_arg, (int32_t*)(w + L.off_tile_count),
                 (const float4*)(w + L.off_packed), target, grad_scale, grads, loss + (step % GS2D_FIT_LOSS_SLOTS),
-                status, out_img, 1, 1, nullptr, ids_sorted_out, 0, banded ? 1 : 0);
+                status, out_img, 1, 1, nullptr, ids_sorted_out, step, banded ? 1 : 0);
         else if (target_format == GS2D_TARGET_U8_HWC)
             k_fit_tiles<0, 1><<<grid, kTileThreads, 0, s>>>(
-                img_w, img_h, tx, row0, (const int32_t*)(w + L.off_tile_off), (int32_t*)(w + L.off_tile_count),
+                img_w, img_h, tx, row0, tile_off_arg, (int32_t*)(w + L.off_tile_count),
                 (const float4*)(w + L.off_packed), target, grad_scale, grads, loss + (step % GS2D_FIT_LOSS_SLOTS),
-                status, out_img, 1, 1, nullptr, ids_sorted_out, 0, banded ? 1 : 0);
+                status, out_img, 1, 1, nullptr, ids_sorted_out, step, banded ? 1 : 0);
         else
             k_fit_tiles<0, 2><<<grid, kTileThreads, 0, s>>>(
-                img_w, img_h, tx, row0, (const int32_t*)(w + L.off_tile_off), (int32_t*)(w + L.off_tile_count),
+                img_w, img_h, tx, row0, tile_off_arg, (int32_t*)(w + L.off_tile_count),
                 (const float4*)(w + L.off_packed), target, grad_scale, grads, loss + (step % GS2D_FIT_LOSS_SLOTS),
-                status, out_img, 1, 1, nullptr, ids_sorted_out, 0, banded ? 1 : 0);
+                status, out_img, 1, 1, nullptr, ids_sorted_out, step, banded ? 1 : 0);
         GS2D_CHECK_LAUNCH("fit_tiles");
     }
     if (phases & GS2D_FIT_PHASE_UPDATE) {
@@ -923,7 +1064,7 @@ int gs2d_fit_step_band(int n, int cap, int img_h, int img_w, float* xyz_raw, flo
             loss + (step % GS2D_FIT_LOSS_SLOTS), loss + ((step + 1) % GS2D_FIT_LOSS_SLOTS), param_grads_out, cap,
             step + 1, (int32_t*)(w + L.off_tile_count), (int32_t*)(w + L.off_tile_off), report_host, row0, row1,
             banded ? 1 : 0, peer_grads, num_peers, grads_zero, rgb_w, adan_w, rgb_w_grad_out, skip_update,
-            mc_grads);
+            mc_grads, slots, (float4*)(w + L.off_packed), img_w, img_h);
         GS2D_CHECK_LAUNCH("fit_update");
     }
     return GS2D_OK;
@@ -972,7 +1113,7 @@ int gs2d_render_chol(int n, int cap, int img_h, int img_w, const float* means_or
         ProfScope ps_(GS2D_STAGE_RASTER_FWD, s);
         k_fit_tiles<1, 0><<<dim3(tx, ty), kTileThreads, 0, s>>>(
             img_w, img_h, tx, 0, (const int32_t*)(w + L.off_tile_off), (int32_t*)(w + L.off_tile_count),
-            (const float4*)(w + L.off_packed), nullptr, 0.f, nullptr, nullptr, (const int32_t*)(w + L.off_status),
+            (const float4*)(w + L.off_packed), nullptr, 0.f, nullptr, nullptr, (int32_t*)(w + L.off_status),
             out_img, out_chw, out_clamp, final_idx, ids_sorted_out, 0, 0);
         GS2D_CHECK_LAUNCH("render_tiles");
     }

@@ -168,7 +168,10 @@ class FusedFrameFit(torch.nn.Module):
                  init: dict | None = None, betas=(0.98, 0.92, 0.99), eps: float = 1e-8, weight_decay: float = 0.0,
                  cap: int | None = None, lr_step_size: int = 20000, lr_gamma: float = 0.5, isdensity: bool = False,
                  isremoval: bool = False, removal_rate: float = 0.1, max_num_points: int | None = None,
-                 densification_interval: int = 100, plan=None):
+                 densification_interval: int = 100, plan=None, slots: bool = True):
+        """slots: fixed 256-record slots per tile instead of tile ranges (include/gs2d.h,
+        gs2d_fit_options.slots): two kernels per iteration instead of three.  The first tile that
+        would need a 257th record switches the model to ranges for good (same results, see _recover)."""
         super().__init__()
         import ctypes
         from . import _lib
@@ -205,7 +208,10 @@ class FusedFrameFit(torch.nn.Module):
         self.lr_step_size, self.lr_gamma = int(lr_step_size), float(lr_gamma)
         self.step_index = 0
         self._ckpt = (0, 0, True, False)     # (iteration, clock.step, clock.fresh, clock.lr_frozen) at the last sync
-        self.cap = int(cap) if cap else max(8 * max(self.n, self.plan.max_num_points), 1 << 18)
+        self.slots = bool(slots)
+        self._cap_ranges = int(cap) if cap else max(8 * max(self.n, self.plan.max_num_points), 1 << 18)
+        tiles = ((self.H + 15) // 16) * ((self.W + 15) // 16)
+        self.cap = max(self._cap_ranges, tiles * 256) if self.slots else self._cap_ranges
         self._alloc()
 
     def _alloc(self):
@@ -261,6 +267,7 @@ class FusedFrameFit(torch.nn.Module):
             o.rgb_w, o.adan_state_w = self.rgb_W.data_ptr(), self.adan_state_w.data_ptr()
             o.rgb_w_grad_out = None if w_grad_out is None else w_grad_out.data_ptr()
         o.adan_step, o.adan_fresh, o.skip_update = int(adan_step), int(fresh), int(skip)
+        o.slots = int(self.slots)
         return o
 
     def _issue(self, gt, fmt, out_img=None, grads_out=None, ids_out=None, w_grad_out=None, stream=None):
@@ -306,10 +313,7 @@ class FusedFrameFit(torch.nn.Module):
         _, _i, overflow, _m = self._read_report(prev)
         if overflow != 0:
             self.step_index = prev
-            self._recover(overflow)
-            raise RuntimeError(
-                f"intersections exceeded the workspace capacity at step {overflow}; the workspace was regrown "
-                f"to {self.cap} and the model rewound to step {self.step_index}: re-issue the remaining iterations")
+            raise RuntimeError(self._recover(overflow))
 
     def _zero_optimizer_state(self):
         self.adan_state.zero_()
@@ -394,21 +398,30 @@ class FusedFrameFit(torch.nn.Module):
             torch.cuda.current_stream(self.device).synchronize()
         loss_sum, _i, overflow, _m = self._read_report(step)
         if overflow != 0:
-            self._recover(overflow)
-            raise RuntimeError(
-                f"intersections exceeded the workspace capacity at step {overflow}; the workspace was regrown "
-                f"to {self.cap} and the model rewound to step {self.step_index}: re-issue the remaining iterations")
+            raise RuntimeError(self._recover(overflow))
         return loss_sum / (3.0 * self.H * self.W)
 
-    def _recover(self, overflow_step: int):
-        # steps >= overflow_step were no-ops (parameters and optimizer state untouched); the
-        # optimizer clock goes back with them (nothing but plain steps since the last control sync)
-        self.step_index = overflow_step - 1
+    def _recover(self, overflow_step: int) -> str:
+        """steps >= |overflow_step| were no-ops (parameters and optimizer state untouched); the
+        optimizer clock goes back with them (nothing but plain steps since the last control sync).
+        Positive: the intersections outgrew `cap` -> double it.  Negative: slot mode met a tile with
+        more than 256 Gaussians -> tile ranges from here on (which 256 the reference renders of such
+        a tile needs all of its ids)."""
+        self.step_index = abs(overflow_step) - 1
         it0, t0, fresh0, frozen0 = self._ckpt
         d = max(self.step_index - it0, 0)
         self.clock.step, self.clock.fresh, self.clock.lr_frozen = t0 + d, fresh0 and d == 0, frozen0
-        self.cap *= 2
+        if overflow_step < 0:
+            self.slots = False
+            self.cap = self._cap_ranges
+            what = "a tile outgrew its 256 slots: the model switched to tile ranges"
+        else:
+            self.cap *= 2
+            self._cap_ranges = max(self._cap_ranges, self.cap)
+            what = f"intersections exceeded the workspace capacity: the workspace was regrown to {self.cap}"
         self._alloc()
+        return (f"step {abs(overflow_step)}: {what} and the model rewound to step {self.step_index}: "
+                f"re-issue the remaining iterations")
 
     def train_iter(self, gt_image: torch.Tensor):
         self.train_iters(gt_image, 1)
@@ -586,12 +599,14 @@ class SpatialFrameFit(FusedFrameFit):
     path_name = "tile-row bands per rank; scatter-pack + tile kernel on the band, gradient rows summed across ranks, replicated update"
 
     def __init__(self, H, W, num_points, device, group=None, bands=None, emulate_world: int = 0,
-                 exchange: str = "nccl", **kw):
+                 exchange: str = "nccl", slots: bool = False, **kw):
         """exchange: "nccl" -- one all-reduce call on the gradient rows between the two phases;
         "peer" -- the rows live in symmetric (peer-mapped) memory and the update kernel itself sums
         them over NVLink in rank order after a device-side barrier: no collective kernel, no extra
         pass over the rows, bit-identical results on every rank by construction."""
-        super().__init__(H, W, num_points, device, **kw)
+        if slots:
+            raise NotImplementedError("tile slots are not wired into the tile-row split yet")
+        super().__init__(H, W, num_points, device, slots=False, **kw)
         import torch.distributed as dist
         self._dist = dist
         if self.rgb_W is not None:

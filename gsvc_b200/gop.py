@@ -47,13 +47,18 @@ def assign_gops(gops: Sequence[Gop], world: int, cost: Optional[Callable[[Gop], 
 
 
 def fit_gop(get_frame: Callable[[int], torch.Tensor], gop: Gop, make_fitter: Callable[[Optional[dict]], object],
-            iters_key: int, iters_pred: int, on_frame: Optional[Callable[[int, object], None]] = None) -> Dict[int, dict]:
+            iters_key: int, iters_pred: int, on_frame: Optional[Callable[[int, object], None]] = None,
+            seed: Optional[int] = None) -> Dict[int, dict]:
     """Fit one GOP: the keyframe from scratch (`make_fitter(None)`), every following frame from
     the previous frame's parameters (`make_fitter(prev_state)`).  Returns frame -> {"state": the
     three parameter tensors on the CPU, "psnr": float, "iters": int}."""
     out: Dict[int, dict] = {}
     prev = None
     for f in range(gop[0], gop[1]):
+        if seed is not None:
+            # every frame draws (fresh Gaussians, the random add) from its own stream, so the result
+            # of a frame does not depend on which rank fitted which other frames before it
+            torch.manual_seed(int(seed) * 100003 + f)
         fit = make_fitter(prev)
         iters = iters_key if prev is None else iters_pred
         gt = get_frame(f)
@@ -71,7 +76,7 @@ def fit_gop(get_frame: Callable[[int], torch.Tensor], gop: Gop, make_fitter: Cal
 
 def fit_sequence(get_frame: Callable[[int], torch.Tensor], num_frames: int, keyframes: Sequence[int],
                  make_fitter: Callable[[Optional[dict]], object], iters_key: int, iters_pred: int,
-                 group=None) -> Optional[Dict[int, dict]]:
+                 group=None, seed: Optional[int] = 1) -> Optional[Dict[int, dict]]:
     """Every rank fits its share of the GOPs; rank 0 returns {frame: result} for the whole
     sequence (other ranks return None).  Works without torch.distributed (one process)."""
     distributed = dist.is_available() and dist.is_initialized()
@@ -82,7 +87,7 @@ def fit_sequence(get_frame: Callable[[int], torch.Tensor], num_frames: int, keyf
     mine = assign_gops(gops, world, cost=lambda g: iters_key + (g[1] - g[0] - 1) * iters_pred)[rank]
     local: Dict[int, dict] = {}
     for g in mine:
-        local.update(fit_gop(get_frame, g, make_fitter, iters_key, iters_pred))
+        local.update(fit_gop(get_frame, g, make_fitter, iters_key, iters_pred, seed=seed))
     if not distributed:
         return local
     gathered = [None] * world if rank == 0 else None

@@ -283,7 +283,18 @@ typedef struct {
  *                        but leaves parameters and optimizer state untouched and does not
  *                        pre-count the next step -- the reference's iterations in which the
  *                        control replaced the parameter tensors after backward(), so that
- *                        optimizer.step() saw no gradients (train_iter :199-204) */
+ *                        optimizer.step() saw no gradients (train_iter :199-204)
+ *   slots                != 0: fixed-capacity tile slots instead of tile ranges -- tile t owns records
+ *                        [t*256, t*256+256) of the packed region (256 = all the reference renders
+ *                        of a tile, forward.cu:552), so nothing has to be counted or scanned before
+ *                        the scatter and the UPDATE phase writes the next step's records itself: a
+ *                        steady-state iteration is TWO kernels.  Needs cap >= tiles*256 and the same
+ *                        value on every call of a workspace; `precounted` then means "the previous
+ *                        UPDATE already scattered these parameters".  A tile that would take a 257th
+ *                        record makes the step a no-op like a cap overflow, reported as a NEGATIVE
+ *                        overflow_step: re-initialise the workspace and continue with slots = 0
+ *                        (only ranges can tell WHICH 256 ids a fuller tile renders).  ids_sorted_out
+ *                        is then indexed by slot (t*256 + rank). */
 typedef struct {
     float* rgb_w;
     float* adan_state_w;
@@ -291,6 +302,7 @@ typedef struct {
     int adan_step;
     int adan_fresh;
     int skip_update;
+    int slots;
 } gs2d_fit_options;
 int gs2d_fit_step_band(int n, int cap, int img_h, int img_w, float* xyz_raw, float* chol_raw, float* features,
                        float* adan_state, const void* target, int target_format, void* work, size_t work_bytes,

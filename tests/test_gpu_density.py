@@ -105,7 +105,7 @@ def test_density_schedule_matches_the_reference_loop():
     kw = dict(max_num_points=n_max, removal_rate=0.25, densification_interval=5, isdensity=True, density_from=10,
               density_for=10)
     gt, fused, ref = _pair(H, W, n_prev, prev, kw)
-    assert float(fused.rgb_W.min()) == 1.0 and float(ref.rgb_W.min()) == 1.0       # :33-34
+    assert float(fused.rgb_W.min()) == 1.0 and float(ref.rgb_W.detach().min()) == 1.0       # :33-34
     state = torch.get_rng_state()
     losses = []
     for it in range(1, 31):
@@ -161,7 +161,7 @@ def test_overflow_before_a_prune_rewinds_the_clock():
     gt = synth.target_frame(H, W, seed=2).to(cuda)
     plan = dict(max_num_points=n, removal_rate=0.25, densification_interval=10, isremoval=True, removal_until=40)
     init = _init(n, 41)
-    small = FusedFrameFit(H, W, n, cuda, init=init, plan=DensityPlan(**plan), cap=1024)   # far too small
+    small = FusedFrameFit(H, W, n, cuda, init=init, plan=DensityPlan(**plan), cap=1024, slots=False)   # far too small
     with pytest.raises(RuntimeError, match="capacity"):
         small.train_iters(gt, 12)            # detected at the control sync of iteration 10
     assert small.step_index == 0 and small.clock.step == 0 and small.clock.fresh

@@ -25,13 +25,28 @@ def _oracle_fit(H, W, init, gt_chw):
                   gt_chw.permute(1, 2, 0).contiguous().numpy(), tanh=_device_tanh)
 
 
-def _setup(H, W, n, seed=3, trained_like=False, cap=None):
+def _setup(H, W, n, seed=3, trained_like=False, cap=None, slots=False):
+    """slots=False: tile ranges (the layout whose order / ranges compare one to one with the
+    reference's sorted arrays); slots=True: the two-kernel iteration on fixed tile slots"""
     from gsvc_b200 import synth
     from gsvc_b200.fit import FusedFrameFit
     init = synth.gaussians(n, seed=seed, trained_like=trained_like)
     gt = synth.target_frame(H, W, seed=seed)      # [1,3,H,W]
-    fit = FusedFrameFit(H, W, n, cuda, init=init, cap=cap)
+    fit = FusedFrameFit(H, W, n, cuda, init=init, cap=cap, slots=slots)
     return init, gt, fit
+
+
+def _ids_in_reference_order(ids, tile_bins, tiles, slots):
+    """the debug id output as one array in the reference's sorted order: ranges are already that;
+    slots hold tile t's ids at [t*256, t*256 + count)"""
+    ids = ids.cpu().numpy()
+    if not slots:
+        return ids
+    out = np.full_like(ids, -7)
+    for t in range(tiles):
+        lo, hi = (int(v) for v in tile_bins[t])
+        out[lo:hi] = ids[t * 256:t * 256 + (hi - lo)]
+    return out
 
 
 def _rel(a, b):
@@ -61,9 +76,10 @@ def _ref_gpu_param_grads(init, gt, H, W):
     return [t.cpu().numpy() for t in g], r
 
 
+@pytest.mark.parametrize("slots", [False, True])
 @pytest.mark.parametrize("H,W,n", [(256, 256, 10_000), (200, 328, 3_000), (1080, 1920, 50_000)])
-def test_first_step_grads_binning_loss_and_update(H, W, n):
-    init, gt, fit = _setup(H, W, n)
+def test_first_step_grads_binning_loss_and_update(H, W, n, slots):
+    init, gt, fit = _setup(H, W, n, slots=slots)
     o = _oracle_fit(H, W, init, gt[0])
     o_loss, o_g, r = o.grads()
     grads = torch.full((n, 8), float("nan"), device=cuda)
@@ -73,8 +89,10 @@ def test_first_step_grads_binning_loss_and_update(H, W, n):
     # binning of this step: the rendering order of every tile range is bit-exact (the tile ranges
     # themselves are compared in test_render_matches_reference_kernels_and_oracle)
     I = r["num_intersects"]
+    ids = torch.from_numpy(_ids_in_reference_order(ids, r["tile_bins"], fit.layout.tiles, slots))
     assert np.array_equal(ids[:I].cpu().numpy(), r["gaussian_ids_sorted"])
     assert (ids[I:] == -7).all()
+    assert fit.slots == slots
     # loss and gradients
     loss = fit.loss()
     assert abs(loss - o_loss) <= 2e-6 * max(o_loss, 1e-12) + 1e-9, (loss, o_loss)
@@ -99,9 +117,91 @@ def test_first_step_grads_binning_loss_and_update(H, W, n):
         assert (d > 2e-5).mean() <= 2e-3 and d.max() <= 2.1e-3, (name, d.max(), (d > 2e-5).mean())
 
 
+@pytest.mark.parametrize("H,W,n,trained", [(256, 256, 10_000, False), (1080, 1920, 50_000, False),
+                                           (1080, 1920, 50_000, True), (200, 328, 3_000, False)])
+def test_slot_iteration_follows_the_range_iteration(H, W, n, trained):
+    """two kernels per iteration on fixed tile slots (the update kernel scatters the next step's
+    records) against three kernels on tile ranges: same losses, same intersection counts, same
+    per-tile maxima, step after step; then an edit of the parameters behind the library's back"""
+    init, gt, a = _setup(H, W, n, seed=8, trained_like=trained, slots=True)
+    _, _, b = _setup(H, W, n, seed=8, trained_like=trained, slots=False, cap=1 << 21)
+    gtd = gt.to(cuda)
+    for it in range(10):
+        la, _ = a.train_iter(gtd)
+        lb, _ = b.train_iter(gtd)
+        assert la == pytest.approx(lb, rel=2e-5), it
+        assert a.status() == b.status(), it                 # (num_intersects, overflow, max_per_tile)
+    assert a.slots and a.status()[0] > 0
+    for k in ("_xyz", "_cholesky", "_features_dc"):
+        d = (getattr(a, k) - getattr(b, k)).abs()
+        assert float(d.median()) <= 1e-6 and float((d > 1e-4).float().mean()) <= 0.01, k
+    snap = {k: getattr(b, k).detach().clone() for k in ("_xyz", "_cholesky", "_features_dc")}
+    snap["_xyz"][::3, 1] += 0.2                             # and moved: the stale scatter must not be used
+    with torch.no_grad():
+        for m in (a, b):
+            for k, v in snap.items():
+                getattr(m, k).copy_(v)                      # identical parameters, versions bumped
+    a.adan_state.copy_(b.adan_state)
+    for it in range(3):
+        la, _ = a.train_iter(gtd)
+        lb, _ = b.train_iter(gtd)
+        assert la == pytest.approx(lb, rel=1e-5), it
+        assert a.status() == b.status(), it
+
+
+def test_slot_overflow_falls_back_to_ranges():
+    """a tile with more than 256 Gaussians cannot be rendered from slots (which 256 needs all ids):
+    the step is a no-op, the model switches to ranges and continues with identical results"""
+    H, W, n = 96, 128, 6_000
+    init, gt, a = _setup(H, W, n, seed=11, trained_like=True, slots=True)
+    _, _, b = _setup(H, W, n, seed=11, trained_like=True, slots=False)
+    gtd = gt.to(cuda)
+    before = a._xyz.clone()
+    a.train_iters(gtd, 3)
+    with pytest.raises(RuntimeError, match="tile ranges"):
+        a.loss()
+    assert not a.slots and a.step_index == 0 and torch.equal(before, a._xyz)
+    a.train_iters(gtd, 3)
+    b.train_iters(gtd, 3)
+    assert a.loss() == pytest.approx(b.loss(), rel=1e-6)
+    assert a.status() == b.status() and a.status()[2] > 256
+
+
+def test_slot_overflow_in_a_later_step():
+    """the overflow is met by the update kernel while it scatters step s+1: step s must be
+    complete and valid, step s+1 the first no-op"""
+    H, W, n = 64, 64, 3_000
+    from gsvc_b200 import synth
+    from gsvc_b200.fit import FusedFrameFit
+    init = synth.gaussians(n, seed=2)
+    init["_xyz"] = init["_xyz"] * 0.05            # everything near the centre: ~190 per tile at the start
+    init["_cholesky"] = init["_cholesky"] * 0 + torch.tensor([1.2, 0.0, 1.2])
+    gt = synth.target_frame(H, W, seed=2).to(cuda)
+    a = FusedFrameFit(H, W, n, cuda, init=init, slots=True, lr=0.05)
+    b = FusedFrameFit(H, W, n, cuda, init=init, slots=False, lr=0.05)
+    hit = None
+    for it in range(1, 200):
+        try:
+            la, _ = a.train_iter(gt)
+        except RuntimeError as e:
+            assert "tile ranges" in str(e)
+            hit = it
+            break
+        lb, _ = b.train_iter(gt)
+        assert la == pytest.approx(lb, rel=1e-4), it
+    if hit is None:
+        pytest.skip("the Gaussians never crowded a tile beyond 256 in 200 iterations")
+    assert not a.slots and a.step_index in (hit - 1, hit - 2)   # hit-2: step hit-1's own report already carried the flag
+    while a.step_index < hit + 3:
+        la, _ = a.train_iter(gt)
+    while b.step_index < hit + 3:
+        lb, _ = b.train_iter(gt)
+    assert la == pytest.approx(lb, rel=1e-3)
+
+
 def test_trajectory_follows_the_oracle():
     H, W, n, K = 256, 256, 10_000, 25
-    init, gt, fit = _setup(H, W, n, seed=5)
+    init, gt, fit = _setup(H, W, n, seed=5, slots=True)
     o = _oracle_fit(H, W, init, gt[0])
     gtd = gt.to(cuda)
     losses, o_losses = [], []
