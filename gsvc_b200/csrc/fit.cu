@@ -40,6 +40,15 @@ constexpr int kScatterBatch = 8;      // slot claims a thread keeps in flight be
 #endif
 constexpr int kSlotStride = GS2D_SLOT_STRIDE;   // records between two tiles' slots (experiments only: < 256 drops the Q1 guarantee)
 
+// Programmatic dependent launch (PDL): a kernel launched with the attribute may start while the
+// kernel before it in the stream is still running; it must not touch what that kernel writes until
+// pdl_wait() returns (= the predecessor finished and its writes are visible).  pdl_release() lets
+// the NEXT kernel in the stream start early in turn; it is called after pdl_wait(), so a kernel's
+// prologue never overlaps anything older than its direct predecessor.  Both are no-ops for a
+// kernel launched the ordinary way.
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_release() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
 __device__ __forceinline__ void cp_async16(void* smem, const void* gmem) {
     const unsigned sa = (unsigned)__cvta_generic_to_shared(smem);
     asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(sa), "l"(gmem) : "memory");
@@ -428,16 +437,9 @@ k_fit_tiles(int W, int H, int tx, int row0, const int32_t* __restrict__ tile_off
     __shared__ float sred[kTileThreads / 32];
     int* sid = reinterpret_cast<int*>(sv);
     static_assert(sizeof(float4) * GS2D_TILE_PIX >= sizeof(int) * kIdChunk, "id chunk must fit in sv");
-    if (status[kStOverflow] != 0) return;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int tile_y = (int)blockIdx.y + row0;
     const int t = tile_y * tx + blockIdx.x;
-    // ranges: the tile's records are [tile_off[t], tile_off[t+1]); slots (tile_off == NULL): the
-    // first tile_fill[t] of [t*256, t*256+256) (a fuller tile flagged the step: not reached)
-    const int lo = tile_off ? tile_off[t] : t * kSlotStride;
-    const int cnt = tile_off ? tile_off[t + 1] - lo : tile_fill[t];
-    // (tile_fill[t] is re-zeroed further down, after the staging's barrier: a store to the address
-    // of the load in flight would park this warp on it before its target loads are even issued)
     if (MODE == 0) {
 #pragma unroll
         for (int j = 0; j < GS2D_TILE_PIX / kTileThreads; ++j)
@@ -479,6 +481,17 @@ k_fit_tiles(int W, int H, int tx, int row0, const int32_t* __restrict__ tile_off
         }
     }
 
+    // ---- everything above is independent of the kernel before this one (the target frame is not
+    // its output): under PDL it runs while that kernel drains ----------------------------------
+    pdl_wait();
+    pdl_release();
+    if (status[kStOverflow] != 0) return;
+    // ranges: the tile's records are [tile_off[t], tile_off[t+1]); slots (tile_off == NULL): the
+    // first tile_fill[t] of [t*256, t*256+256) (a fuller tile flagged the step: not reached)
+    const int lo = tile_off ? tile_off[t] : t * kSlotStride;
+    const int cnt = tile_off ? tile_off[t + 1] - lo : tile_fill[t];
+    // (tile_fill[t] is re-zeroed after the staging's barrier: a store to the address of the load in
+    // flight would park this warp on it)
     const int nb = stage_tile_sorted(packed + 3 * (size_t)lo, cnt, sq, sid, tid);
     if (tid == 0) {                   // every thread is past a barrier that it reached knowing cnt
         tile_fill[t] = 0;             // ready for the next iteration's scatter
@@ -728,6 +741,35 @@ k_fit_update(int n, float* __restrict__ xyz_raw, float* __restrict__ chol_raw, f
     __shared__ int sh[8];
     __shared__ int s_last;
     const int i = blockIdx.x * kFitThreads + threadIdx.x;
+    // ---- prologue: parameters and optimizer state were last written by the PREVIOUS update kernel,
+    // not by the tile kernel this one follows -- under PDL all of this (the bulk of the kernel's
+    // memory traffic and both tanh) runs while the tile kernel's last wave drains ----------------
+    Proj2d p; float2 m; float3 L;
+    float par[8], am[8], an[8], ad[8], ap[8];
+    float cw = 1.f, wm = 0.f, wn = 0.f, wd = 0.f, wp = 0.f;
+    const size_t plane = (size_t)n * 8;
+    float4* sm = reinterpret_cast<float4*>(adan + (size_t)i * 8);
+    float4* sn = reinterpret_cast<float4*>(adan + plane + (size_t)i * 8);
+    float4* sd = reinterpret_cast<float4*>(adan + 2 * plane + (size_t)i * 8);
+    float4* sp = reinterpret_cast<float4*>(adan + 3 * plane + (size_t)i * 8);
+    if (i < n) {
+        fit_project(i, xyz_raw, chol_raw, 1, half_w, half_h, tx, ty, p, m, L);
+        par[0] = xyz_raw[2 * i]; par[1] = xyz_raw[2 * i + 1];
+        par[2] = chol_raw[3 * i]; par[3] = chol_raw[3 * i + 1]; par[4] = chol_raw[3 * i + 2];
+        par[5] = feat[3 * i]; par[6] = feat[3 * i + 1]; par[7] = feat[3 * i + 2];
+        if (!skip_update) {
+            *reinterpret_cast<float4*>(am) = sm[0]; *reinterpret_cast<float4*>(am + 4) = sm[1];
+            *reinterpret_cast<float4*>(an) = sn[0]; *reinterpret_cast<float4*>(an + 4) = sn[1];
+            *reinterpret_cast<float4*>(ad) = sd[0]; *reinterpret_cast<float4*>(ad + 4) = sd[1];
+            *reinterpret_cast<float4*>(ap) = sp[0]; *reinterpret_cast<float4*>(ap + 4) = sp[1];
+        }
+        if (rgb_w) {
+            cw = rgb_w[i];
+            if (!skip_update) { wm = adan_w[i]; wn = adan_w[(size_t)n + i]; wd = adan_w[2 * (size_t)n + i]; wp = adan_w[3 * (size_t)n + i]; }
+        }
+    }
+    pdl_wait();
+    pdl_release();
     // a flag for a LATER step (slot mode: another block may be raising it right now for the step
     // being scattered below) must not stop this step's update half way
     const int of = status[kStOverflow];
@@ -760,8 +802,6 @@ k_fit_update(int n, float* __restrict__ xyz_raw, float* __restrict__ chol_raw, f
     if (i == 0 && loss_next) *loss_next = 0.0;
     int claimed = 0;
     if (i < n) {
-        Proj2d p; float2 m; float3 L;
-        fit_project(i, xyz_raw, chol_raw, 1, half_w, half_h, tx, ty, p, m, L);
         float4 g0, g1;   // v_xy(2) v_conic(3) v_rgb(3) | v_opacity(1) pad(3) unused here
         if (mc_grads) {
             // spatial mode over the switch: one load returns the row summed over all ranks
@@ -790,10 +830,9 @@ k_fit_update(int n, float* __restrict__ xyz_raw, float* __restrict__ chol_raw, f
             zrow[0] = z; zrow[1] = z; zrow[2] = z;
         }
         float g[8] = {0.f, 0.f, 0.f, 0.f, 0.f, g1.y, g1.z, g1.w};   // xyz(2) chol(3) feat(3)
-        float gw = 0.f, cw = 1.f;
+        float gw = 0.f;
         if (rgb_w) {   // colours = feat * w: d feat = d colour * w, d w = <d colour, feat>
-            cw = rgb_w[i];
-            gw = g1.y * feat[3 * i] + g1.z * feat[3 * i + 1] + g1.w * feat[3 * i + 2];
+            gw = g1.y * par[5] + g1.z * par[6] + g1.w * par[7];
             g[5] = g1.y * cw; g[6] = g1.z * cw; g[7] = g1.w * cw;
             if (rgb_w_grad_out) rgb_w_grad_out[i] = gw;
         }
@@ -810,18 +849,6 @@ k_fit_update(int n, float* __restrict__ xyz_raw, float* __restrict__ chol_raw, f
             for (int k = 0; k < 8; ++k) grads_out[(size_t)i * 8 + k] = g[k];
         }
         if (skip_update) return;   // uniform over the grid: nobody reaches the scan below
-        float par[8] = {xyz_raw[2 * i], xyz_raw[2 * i + 1], chol_raw[3 * i], chol_raw[3 * i + 1], chol_raw[3 * i + 2],
-                        feat[3 * i], feat[3 * i + 1], feat[3 * i + 2]};
-        const size_t plane = (size_t)n * 8;
-        float4* sm = reinterpret_cast<float4*>(adan + (size_t)i * 8);
-        float4* sn = reinterpret_cast<float4*>(adan + plane + (size_t)i * 8);
-        float4* sd = reinterpret_cast<float4*>(adan + 2 * plane + (size_t)i * 8);
-        float4* sp = reinterpret_cast<float4*>(adan + 3 * plane + (size_t)i * 8);
-        float am[8], an[8], ad[8], ap[8];
-        *reinterpret_cast<float4*>(am) = sm[0]; *reinterpret_cast<float4*>(am + 4) = sm[1];
-        *reinterpret_cast<float4*>(an) = sn[0]; *reinterpret_cast<float4*>(an + 4) = sn[1];
-        *reinterpret_cast<float4*>(ad) = sd[0]; *reinterpret_cast<float4*>(ad + 4) = sd[1];
-        *reinterpret_cast<float4*>(ap) = sp[0]; *reinterpret_cast<float4*>(ap + 4) = sp[1];
 #pragma unroll
         for (int k = 0; k < 8; ++k) par[k] = adan_one(par[k], g[k], am[k], an[k], ad[k], ap[k], h);
         sm[0] = *reinterpret_cast<float4*>(am); sm[1] = *reinterpret_cast<float4*>(am + 4);
@@ -832,7 +859,6 @@ k_fit_update(int n, float* __restrict__ xyz_raw, float* __restrict__ chol_raw, f
         chol_raw[3 * i] = par[2]; chol_raw[3 * i + 1] = par[3]; chol_raw[3 * i + 2] = par[4];
         feat[3 * i] = par[5]; feat[3 * i + 1] = par[6]; feat[3 * i + 2] = par[7];
         if (rgb_w) {
-            float wm = adan_w[i], wn = adan_w[(size_t)n + i], wd = adan_w[2 * (size_t)n + i], wp = adan_w[3 * (size_t)n + i];
             cw = adan_one(cw, gw, wm, wn, wd, wp, h);
             rgb_w[i] = cw;
             adan_w[i] = wm; adan_w[(size_t)n + i] = wn; adan_w[2 * (size_t)n + i] = wd; adan_w[3 * (size_t)n + i] = wp;
@@ -882,6 +908,25 @@ k_i420_to_rgb(int H, int W, const uint8_t* __restrict__ yuv, uint8_t* __restrict
 }
 
 static inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+// Launch with programmatic stream serialization: the kernel may begin (up to its pdl_wait()) while
+// its predecessor in the stream is still running.  GS2D_NO_PDL=1 in the environment turns it off
+// (A/B runs).
+template <typename... KArgs, typename... Args>
+static cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, cudaStream_t s, Args&&... args) {
+    static const bool off = [] { const char* e = getenv("GS2D_NO_PDL"); return e && e[0] == '1'; }();
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid;
+    cfg.blockDim = block;
+    cfg.dynamicSmemBytes = 0;
+    cfg.stream = s;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = off ? 0 : 1;
+    return cudaLaunchKernelEx(&cfg, kernel, KArgs(std::forward<Args>(args))...);
+}
 
 static int fit_layout(int n, int cap, int img_h, int img_w, gs2d_fit_layout* L) {
     if (n < 0 || cap < 1 || img_h < 1 || img_w < 1) {
@@ -1033,20 +1078,20 @@ int gs2d_fit_step_band(int n, int cap, int img_h, int img_w, float* xyz_raw, flo
         ProfScope ps_(GS2D_STAGE_FIT_TILES, s);
         const dim3 grid(tx, row1 - row0);
         if (target_format == GS2D_TARGET_F32_CHW)
-            k_fit_tiles<0, 0><<<grid, kTileThreads, 0, s>>>(
+            GS2D_CHECK_CUDA(launch_pdl(k_fit_tiles<0, 0>, grid, dim3(kTileThreads), s,
                 img_w, img_h, tx, row0, tile_off_arg, (int32_t*)(w + L.off_tile_count),
                 (const float4*)(w + L.off_packed), target, grad_scale, grads, loss + (step % GS2D_FIT_LOSS_SLOTS),
-                status, out_img, 1, 1, nullptr, ids_sorted_out, step, banded ? 1 : 0);
+                status, out_img, 1, 1, (int32_t*)nullptr, ids_sorted_out, step, banded ? 1 : 0));
         else if (target_format == GS2D_TARGET_U8_HWC)
-            k_fit_tiles<0, 1><<<grid, kTileThreads, 0, s>>>(
+            GS2D_CHECK_CUDA(launch_pdl(k_fit_tiles<0, 1>, grid, dim3(kTileThreads), s,
                 img_w, img_h, tx, row0, tile_off_arg, (int32_t*)(w + L.off_tile_count),
                 (const float4*)(w + L.off_packed), target, grad_scale, grads, loss + (step % GS2D_FIT_LOSS_SLOTS),
-                status, out_img, 1, 1, nullptr, ids_sorted_out, step, banded ? 1 : 0);
+                status, out_img, 1, 1, (int32_t*)nullptr, ids_sorted_out, step, banded ? 1 : 0));
         else
-            k_fit_tiles<0, 2><<<grid, kTileThreads, 0, s>>>(
+            GS2D_CHECK_CUDA(launch_pdl(k_fit_tiles<0, 2>, grid, dim3(kTileThreads), s,
                 img_w, img_h, tx, row0, tile_off_arg, (int32_t*)(w + L.off_tile_count),
                 (const float4*)(w + L.off_packed), target, grad_scale, grads, loss + (step % GS2D_FIT_LOSS_SLOTS),
-                status, out_img, 1, 1, nullptr, ids_sorted_out, step, banded ? 1 : 0);
+                status, out_img, 1, 1, (int32_t*)nullptr, ids_sorted_out, step, banded ? 1 : 0));
         GS2D_CHECK_LAUNCH("fit_tiles");
     }
     if (phases & GS2D_FIT_PHASE_UPDATE) {
@@ -1059,12 +1104,12 @@ int gs2d_fit_step_band(int n, int cap, int img_h, int img_w, float* xyz_raw, flo
         h.decay_div = 1.f + lr * weight_decay;
         h.first = adan_fresh;
         ProfScope ps_(GS2D_STAGE_ADAN, s);
-        k_fit_update<<<div_up(n, kFitThreads), kFitThreads, 0, s>>>(
+        GS2D_CHECK_CUDA(launch_pdl(k_fit_update, dim3(div_up(n, kFitThreads)), dim3(kFitThreads), s,
             n, xyz_raw, chol_raw, features, adan_state, grads, half_w, half_h, tx, ty, h, status,
             loss + (step % GS2D_FIT_LOSS_SLOTS), loss + ((step + 1) % GS2D_FIT_LOSS_SLOTS), param_grads_out, cap,
             step + 1, (int32_t*)(w + L.off_tile_count), (int32_t*)(w + L.off_tile_off), report_host, row0, row1,
             banded ? 1 : 0, peer_grads, num_peers, grads_zero, rgb_w, adan_w, rgb_w_grad_out, skip_update,
-            mc_grads, slots, (float4*)(w + L.off_packed), img_w, img_h);
+            mc_grads, slots, (float4*)(w + L.off_packed), img_w, img_h));
         GS2D_CHECK_LAUNCH("fit_update");
     }
     return GS2D_OK;
