@@ -321,7 +321,8 @@ def main_gpu(args, rank: int, world: int, local_rank: int):
         fresh_model()
         _lib.prof_enable(True)
         for _ in range(K):
-            flush.zero_()
+            if not args.warm_stages:
+                flush.zero_()
             step_resident(gt)
         torch.cuda.synchronize(dev)
         _lib.prof_enable(False)
@@ -487,6 +488,8 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "b200-dropin", "reference", "reference-gpu"])
     ap.add_argument("--cpu-steps", type=int, default=20, help="fit iterations of the cpu_baseline leg")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--warm-stages", action="store_true",
+                    help="per-stage timing pass without the L2 flush (what the back-to-back loop sees); diagnostics")
     ap.add_argument("--ranges", action="store_true",
                     help="tile ranges (count + scan + scatter, 3 kernels/iter) instead of fixed tile slots (2 kernels/iter)")
     ap.add_argument("--trained-like", action="store_true",
