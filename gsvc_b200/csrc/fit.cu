@@ -335,18 +335,15 @@ constexpr int kBwdRows = GS2D_BWD_ROWS;   // rows of a pair's rectangle a lane e
 // in flight while the ids land).  cnt > 256 (rare; the reference then renders only the 256
 // lowest ids): ranks are computed against all cnt ids in chunks and the 256
 // lowest-ranked records are kept.
-// `pre` (slot mode): record `tid` of the tile was already requested -- its address does not depend on
-// the count, so the load went out together with the loads of the flag and of the count.
 __device__ __forceinline__ int stage_tile_sorted(const float4* __restrict__ src, int cnt, float4* sq, int* sid,
-                                                 int tid, bool pre, float4 r0, float4 r1, float4 r2) {
+                                                 int tid) {
     const int nb = min(cnt, GS2D_MAX_PER_TILE);
     if (cnt <= GS2D_MAX_PER_TILE) {
+        float4 r0, r1, r2;
         if (tid < cnt) {
-            if (!pre) {
-                r0 = __ldg(&src[3 * (size_t)tid + 0]);
-                r1 = __ldg(&src[3 * (size_t)tid + 1]);
-                r2 = __ldg(&src[3 * (size_t)tid + 2]);
-            }
+            r0 = __ldg(&src[3 * (size_t)tid + 0]);
+            r1 = __ldg(&src[3 * (size_t)tid + 1]);
+            r2 = __ldg(&src[3 * (size_t)tid + 2]);
             sid[tid] = __float_as_int(r1.w);
         }
         for (int j = tid + kTileThreads; j < cnt; j += kTileThreads)
@@ -490,21 +487,17 @@ k_fit_tiles(int W, int H, int tx, int row0, const int32_t* __restrict__ tile_off
     pdl_release();
     // ranges: the tile's records are [tile_off[t], tile_off[t+1]); slots (tile_off == NULL): the
     // first tile_fill[t] of [t*256, t*256+256) (a fuller tile flagged the step: not reached).
-    // With slots the flag, the count and the first 64 records are independent loads: one round
-    // trip to L2 instead of three (a record beyond the count is loaded and ignored).
+    // The flag and the count are independent loads: one round trip.  (Requesting the first 64
+    // records speculatively as well -- their address does not depend on the count -- was measured:
+    // no gain, and 25 MB per step of never-written slots pulled from DRAM.)
     const bool slot = tile_off == nullptr;
-    float4 r0 = make_float4(0.f, 0.f, 0.f, 0.f), r1 = r0, r2 = r0;
-    if (slot) {
-        const float4* src = packed + 3 * ((size_t)t * kSlotStride + tid);
-        r0 = __ldg(src); r1 = __ldg(src + 1); r2 = __ldg(src + 2);
-    }
     const int of = status[kStOverflow];
     const int lo = slot ? t * kSlotStride : tile_off[t];
     const int cnt = slot ? tile_fill[t] : tile_off[t + 1] - lo;
     if (of != 0) return;
     // (tile_fill[t] is re-zeroed after the staging's barrier: a store to the address of the load in
     // flight would park this warp on it)
-    const int nb = stage_tile_sorted(packed + 3 * (size_t)lo, cnt, sq, sid, tid, slot, r0, r1, r2);
+    const int nb = stage_tile_sorted(packed + 3 * (size_t)lo, cnt, sq, sid, tid);
     if (tid == 0) {                   // every thread is past a barrier that it reached knowing cnt
         tile_fill[t] = 0;             // ready for the next iteration's scatter
         if (!tile_off && MODE == 0) {
