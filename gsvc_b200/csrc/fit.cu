@@ -1,26 +1,27 @@
-// fit.cu -- the fit iteration of one frame as three (first: four) kernels, no host synchronisation, no
-// allocation, no memset:
+// fit.cu -- the fit iteration of one frame as TWO kernels (tile slots) or three (tile ranges), no host
+// synchronisation, no allocation, no memset:
 //
-//   k_fit_count    per Gaussian: tanh / Cholesky-bound activations, projection, one atomic per
-//                  touched tile into tile_count; the last block to finish scans tile_count into
-//                  tile_off (= the reference's tile_bins) and publishes num_intersects.
-//   k_fit_scatter  per Gaussian: same projection, claims a slot in each touched tile's range and
-//                  writes the 48-byte packed record there.  Order inside a tile is restored in
-//                  the tile kernel by ranking the records on Gaussian id, which is exactly the
-//                  order the reference's stable sort on tile id produces.
 //   k_fit_tiles    one CTA per 16x16 tile: sum-rasterise forward (forward.cu:512-627, first 256
 //                  entries only), clamp + L2 loss against the target and its
 //                  gradient (GaussianSplats_Represent.py:88-89,194 + utils.py:21-26 of the
 //                  reference) kept in shared memory, then the rasteriser backward
-//                  (backward.cu:696-862) warp-per-Gaussian from shared memory: one 9-float
-//                  reduction per (Gaussian, tile) pair.
+//                  (backward.cu:696-862) eight lanes per (Gaussian, tile) pair from shared memory:
+//                  one 8-float reduction per pair.
 //   k_fit_update   per Gaussian: projection backward (backward2d.cu:8-51, reference formula,
-//                  SURVEY Q12), tanh backward, Adan update of the 8 parameters, re-zeroing of the
-//                  gradient row, and -- with the updated parameters still in registers -- the
-//                  NEXT iteration's projection + tile count + scan, so a steady-state iteration
-//                  is three kernels (scatter, tiles, update) and k_fit_count runs only first.
+//                  SURVEY Q12), tanh backward, Adan update of the 8 (9 with rgb_W) parameters,
+//                  re-zeroing of the gradient row, and -- with the updated parameters still in
+//                  registers -- the NEXT iteration's binning: with tile slots it writes that
+//                  iteration's packed records itself; with tile ranges it counts tiles and the last
+//                  block scans the counts, and
+//   k_fit_scatter  (ranges: every step; slots: only when nothing is pre-scattered) claims a position
+//                  in each touched tile and writes the 48-byte packed record there.  Order inside a
+//                  tile is restored in the tile kernel by ranking the records on Gaussian id, which
+//                  is exactly the order the reference's stable sort on tile id produces.
+//   k_fit_count    (ranges, first step only) per Gaussian: activations, projection, one atomic per
+//                  touched tile; the last block to finish scans tile_count into tile_off (= the
+//                  reference's tile_bins) and publishes num_intersects.
 //
-// The same count/scatter/tile kernels without the loss and backward are the render-only path.
+// The count/scatter/tile kernels without the loss and backward are the render-only path.
 #include "gs2d_internal.h"
 #include "gs2d_math.cuh"
 

@@ -171,9 +171,9 @@ int gs2d_rasterize_sum_bwd_binned(int n, int num_intersects, const int32_t* gaus
  * gs2d_fit_step runs ONE iteration of GaussianVideo_frame.train_iter
  * (GaussianSplats_Represent.py:191-207: forward :83-90, L2 loss utils.py:21-26, backward,
  * Adan step optimizer.py:125-236 with the reference's defaults) as three or four kernels on `stream`
- * with no host synchronisation, no allocation and no memset: project+count+scan,
- * scatter-pack, tile kernel (rasterise forward + clamp/L2 + rasterise backward) and
- * projection-backward+Adan.  Everything lives in caller-owned memory:
+ * (two with gs2d_fit_options.slots, gs2d_fit_step_band) with no host synchronisation, no allocation
+ * and no memset: project+count+scan, scatter-pack, tile kernel (rasterise forward + clamp/L2 +
+ * rasterise backward) and projection-backward+Adan.  Everything lives in caller-owned memory:
  *   work        gs2d_fit_layout_for(...).total_bytes, 256-byte aligned; gs2d_fit_init zeroes its
  *               control region once (and the Adan state);
  *   adan_state  fp32 [4][n][8]: m, n, d, previous gradient of (xyz 2, chol 3, features 3);
