@@ -315,6 +315,23 @@ def main_gpu(args, rank: int, world: int, local_rank: int):
         barrier()
     render_ms = a.elapsed_time(b) / K
 
+    # ---- config 3 as BASELINE.json words it: render from the QUANTISED Gaussians (wire format) ----
+    renderq_ms = None
+    if fused:
+        from gsvc_b200.decode import QuantizedFrame
+        books = torch.rand(2, 8, 3, generator=torch.Generator().manual_seed(1)) * torch.tensor([1.0, 0.3]).view(2, 1, 1)
+        qf = QuantizedFrame.from_state(fit.frame_state(), books, device=dev)
+        with torch.no_grad():
+            for _ in range(3):
+                qf.render(H, W)
+            barrier()
+            a.record()
+            for _ in range(K):
+                qf.render(H, W)
+            b.record()
+            barrier()
+        renderq_ms = a.elapsed_time(b) / K
+
     # ---- per-stage timing pass (CUDA events inside the library, on the launching stream) ------
     stages = {}
     if mine:
@@ -330,10 +347,10 @@ def main_gpu(args, rank: int, world: int, local_rank: int):
         stages = {k: {"ms_per_step": v[0] / K, "launches_per_step": v[1] / K} for k, v in prof.items() if v[1]}
 
     # ---- max over ranks ----------------------------------------------------------------------
-    t = torch.tensor([step_ms, warm_ms, e2e_ms, render_ms], dtype=torch.float64, device=dev)
+    t = torch.tensor([step_ms, warm_ms, e2e_ms, render_ms, renderq_ms or 0.0], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    step_ms, warm_ms, e2e_ms, render_ms = (float(x) for x in t.tolist())
+    step_ms, warm_ms, e2e_ms, render_ms, renderq_ms = (float(x) for x in t.tolist())
 
     if rank == 0:
         I = int(getattr(fit, "last_num_intersects", 0)) or None
@@ -356,6 +373,10 @@ def main_gpu(args, rank: int, world: int, local_rank: int):
             "render": {"value": world * 1e3 / render_ms, "unit": "frames/s", "ms_per_frame": render_ms},
             "wall_s_timed_region": wall, "final_psnr": psnr,
         }
+        if renderq_ms:
+            line["render_quantized"] = {"value": world * 1e3 / renderq_ms, "unit": "frames/s", "ms_per_frame": renderq_ms,
+                                        "bytes_per_gaussian": 9,
+                                        "what": "C3: gs2d_render_quantized from fp16 means + 6-bit Cholesky codes + 2x3-bit VQ colour indices"}
         if args.impl != "b200":
             line["impl"] = args.impl
         if args.trained_like:

@@ -61,6 +61,13 @@ class FitOptions(Structure):
                 ("adan_fresh", c_int), ("skip_update", c_int), ("slots", c_int)]
 
 
+class QuantizedFrame(Structure):
+    """mirror of gs2d_quantized_frame (include/gs2d.h)"""
+
+    _fields_ = [("xyz_half", c_void_p), ("chol_code", c_void_p), ("color_index", c_void_p), ("codebooks", c_void_p),
+                ("chol_scale", c_float * 3), ("chol_beta", c_float * 3)]
+
+
 FIT_LOSS_SLOTS = 64
 TARGET_F32_CHW, TARGET_U8_HWC, TARGET_I420 = 0, 1, 2
 FIT_PHASE_GRADS, FIT_PHASE_UPDATE = 1, 2
@@ -98,6 +105,8 @@ _SIGNATURES = {
                                    c_float, c_float, c_float, c_float, c_float, c_float, c_int, c_int, c_int, c_int,
                                    _P, _P, _P, _P, _P, _P, _P]),
     "gs2d_i420_to_rgb": (c_int, [c_int, c_int, _P, _P, _P]),
+    "gs2d_render_quantized": (c_int, [c_int, c_int, c_int, c_int, _P, _P, c_size_t, _P, c_int, c_int, _P, _P, _P]),
+    "gs2d_dequantize": (c_int, [c_int, _P, _P, _P, _P, _P]),
     "gs2d_frame_pipe_create": (c_int, [_P, c_size_t, c_int, POINTER(c_void_p)]),
     "gs2d_frame_pipe_destroy": (c_int, [_P]),
     "gs2d_frame_pipe_push": (c_int, [_P, _P, POINTER(c_int)]),

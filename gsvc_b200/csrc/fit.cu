@@ -22,6 +22,8 @@
 //                  reference's tile_bins) and publishes num_intersects.
 //
 // The count/scatter/tile kernels without the loss and backward are the render-only path.
+#include <cuda_fp16.h>
+
 #include "gs2d_internal.h"
 #include "gs2d_math.cuh"
 
@@ -78,19 +80,56 @@ __device__ __forceinline__ uint32_t yuv_to_rgb_packed(int y, int u, int v) {
     return (uint32_t)min(max(r, 0), 255) | ((uint32_t)min(max(g, 0), 255) << 8) | ((uint32_t)min(max(b, 0), 255) << 16);
 }
 
-// activations of the reference's frame model (GaussianSplats_Represent.py:56-70) + projection
+// Where a Gaussian's parameters come from (`activate`):
+//   0  means2d / L_elements / colours as the projection API takes them
+//   1  the raw parameters of the frame model: tanh and the Cholesky bound applied here
+//      (GaussianSplats_Represent.py:56-70)
+//   2  the quantised wire format of the codec (forward_quantize, GaussianSplats_Compress.py:71-84):
+//      xyz as fp16 bits (FakeQuantizationHalf, quantize.py:15-24), Cholesky as 6-bit codes with a
+//      per-channel scale / beta (UniformQuantizer.compress / decompress, quantize.py:82-88:
+//      code * scale + beta, then the bound), colours as two 3-bit residual-VQ indices into two
+//      8-entry codebooks (VectorQuantizer.decompress, quantize.py:146-150: 0 + e0[i0] + e1[i1]).
+//      The pointers then hold uint16 [n][2], uint8 [n][3] and uint8 [n][2]: 9 bytes per Gaussian
+//      instead of 32, decoded in registers -- no fp32 copy of the frame's Gaussians ever exists.
+struct QuantConst {
+    float scale[3], beta[3];
+    const float* codebooks;   // [2][8][3]
+};
+
 __device__ __forceinline__ void fit_project(int i, const float* __restrict__ xyz_raw, const float* __restrict__ chol_raw,
                                             int activate, float half_w, float half_h, int tx, int ty, Proj2d& p,
-                                            float2& means, float3& L) {
-    const float2 r = reinterpret_cast<const float2*>(xyz_raw)[i];
-    L = make_float3(chol_raw[3 * i], chol_raw[3 * i + 1], chol_raw[3 * i + 2]);
-    if (activate) {
-        means = make_float2(tanhf(r.x), tanhf(r.y));
-        L.x = addf(L.x, 0.5f); L.y = addf(L.y, 0.f); L.z = addf(L.z, 0.5f);
+                                            float2& means, float3& L, const QuantConst& qc) {
+    if (activate == 2) {
+        const uint32_t hx = reinterpret_cast<const uint32_t*>(xyz_raw)[i];          // two fp16
+        const uint8_t* c = reinterpret_cast<const uint8_t*>(chol_raw) + 3 * (size_t)i;
+        means = make_float2(tanhf(__half2float(__ushort_as_half((unsigned short)(hx & 0xffffu)))),
+                            tanhf(__half2float(__ushort_as_half((unsigned short)(hx >> 16)))));
+        L.x = addf(addf(mulf((float)c[0], qc.scale[0]), qc.beta[0]), 0.5f);
+        L.y = addf(addf(mulf((float)c[1], qc.scale[1]), qc.beta[1]), 0.f);
+        L.z = addf(addf(mulf((float)c[2], qc.scale[2]), qc.beta[2]), 0.5f);
     } else {
-        means = r;
+        const float2 r = reinterpret_cast<const float2*>(xyz_raw)[i];
+        L = make_float3(chol_raw[3 * i], chol_raw[3 * i + 1], chol_raw[3 * i + 2]);
+        if (activate) {
+            means = make_float2(tanhf(r.x), tanhf(r.y));
+            L.x = addf(L.x, 0.5f); L.y = addf(L.y, 0.f); L.z = addf(L.z, 0.5f);
+        } else {
+            means = r;
+        }
     }
     project_chol(means.x, means.y, L.x, L.y, L.z, half_w, half_h, tx, ty, p);
+}
+
+__device__ __forceinline__ float3 fit_colour(int i, const float* __restrict__ feat, const float* __restrict__ rgb_w,
+                                             int activate, const QuantConst& qc) {
+    if (activate == 2) {
+        const uint8_t* ix = reinterpret_cast<const uint8_t*>(feat) + 2 * (size_t)i;
+        const float* e0 = qc.codebooks + 3 * (ix[0] & 7), * e1 = qc.codebooks + 24 + 3 * (ix[1] & 7);
+        return make_float3(addf(__ldg(e0), __ldg(e1)), addf(__ldg(e0 + 1), __ldg(e1 + 1)), addf(__ldg(e0 + 2), __ldg(e1 + 2)));
+    }
+    // colours = _features_dc * rgb_W (GaussianSplats_Represent.py:62-63); plain fp32 products
+    const float cw = rgb_w ? rgb_w[i] : 1.f;
+    return make_float3(mulf(feat[3 * i], cw), mulf(feat[3 * i + 1], cw), mulf(feat[3 * i + 2], cw));
 }
 
 // ------------------------------------------------------------------------------------------
@@ -195,13 +234,13 @@ __device__ __forceinline__ void scan_tiles_by_last_block(int tx, int ty, int cap
 __global__ void __launch_bounds__(kFitThreads)
 k_fit_count(int n, const float* __restrict__ xyz_raw, const float* __restrict__ chol_raw, int activate, float half_w,
             float half_h, int tx, int ty, int row0, int row1, int cap, int step, int32_t* tile_count,
-            int32_t* __restrict__ tile_off, int32_t* status) {
+            int32_t* __restrict__ tile_off, int32_t* status, QuantConst qc) {
     __shared__ int sh[8];
     __shared__ int s_last;
     const int i = blockIdx.x * kFitThreads + threadIdx.x;
     if (i < n) {
         Proj2d p; float2 m; float3 L;
-        fit_project(i, xyz_raw, chol_raw, activate, half_w, half_h, tx, ty, p, m, L);
+        fit_project(i, xyz_raw, chol_raw, activate, half_w, half_h, tx, ty, p, m, L, qc);
         count_tiles(p, tx, row0, row1, tile_count);
     }
     scan_tiles_by_last_block(tx, ty, cap, step, tile_count, tile_off, status, sh, &s_last);
@@ -289,7 +328,7 @@ k_fit_scatter(int n, const float* __restrict__ xyz_raw, const float* __restrict_
               const float* __restrict__ feat, const float* __restrict__ opac, const float* __restrict__ rgb_w,
               int activate, float half_w, float half_h,
               int tx, int ty, int row0, int row1, int W, int H, const int32_t* __restrict__ tile_off,
-              int32_t* tile_fill, int32_t* status, float4* __restrict__ packed, int slots, int step) {
+              int32_t* tile_fill, int32_t* status, float4* __restrict__ packed, int slots, int step, QuantConst qc) {
     __shared__ int sh[8];
     // not an early return: in slot mode another block may raise the flag while this one runs, and
     // every thread must reach the block sum below
@@ -298,11 +337,10 @@ k_fit_scatter(int n, const float* __restrict__ xyz_raw, const float* __restrict_
     int claimed = 0;
     if (i < n && !dead) {
         Proj2d p; float2 m; float3 L;
-        fit_project(i, xyz_raw, chol_raw, activate, half_w, half_h, tx, ty, p, m, L);
+        fit_project(i, xyz_raw, chol_raw, activate, half_w, half_h, tx, ty, p, m, L, qc);
         const float o = opac ? opac[i] : 1.f;
-        // colours = _features_dc * rgb_W (GaussianSplats_Represent.py:62-63); plain fp32 products
-        const float cw = rgb_w ? rgb_w[i] : 1.f;
-        const float r = mulf(feat[3 * i], cw), g = mulf(feat[3 * i + 1], cw), b = mulf(feat[3 * i + 2], cw);
+        const float3 col = fit_colour(i, feat, rgb_w, activate, qc);
+        const float r = col.x, g = col.y, b = col.z;
         if (slots)
             claimed = scatter_records<true>(p, i, o, r, g, b, tx, row0, row1, W, H, nullptr, tile_fill, packed, status, step);
         else
@@ -759,7 +797,7 @@ k_fit_update(int n, float* __restrict__ xyz_raw, float* __restrict__ chol_raw, f
     float4* sd = reinterpret_cast<float4*>(adan + 2 * plane + (size_t)i * 8);
     float4* sp = reinterpret_cast<float4*>(adan + 3 * plane + (size_t)i * 8);
     if (i < n) {
-        fit_project(i, xyz_raw, chol_raw, 1, half_w, half_h, tx, ty, p, m, L);
+        fit_project(i, xyz_raw, chol_raw, 1, half_w, half_h, tx, ty, p, m, L, QuantConst());
         par[0] = xyz_raw[2 * i]; par[1] = xyz_raw[2 * i + 1];
         par[2] = chol_raw[3 * i]; par[3] = chol_raw[3 * i + 1]; par[4] = chol_raw[3 * i + 2];
         par[5] = feat[3 * i]; par[6] = feat[3 * i + 1]; par[7] = feat[3 * i + 2];
@@ -891,6 +929,24 @@ k_fit_update(int n, float* __restrict__ xyz_raw, float* __restrict__ chol_raw, f
     scan_tiles_by_last_block(tx, ty, cap, next_step, tile_count, tile_off, status, sh, &s_last);
 }
 
+// wire format -> the fp32 parameter tensors of the frame model (what forward_quantize feeds the two
+// operators BEFORE tanh / bound: fp16-rounded _xyz, code*scale+beta, e0+e1): for a decoder that goes
+// on fitting (P-frames start from the decoded previous frame) and for the parity tests
+__global__ void __launch_bounds__(kFitThreads)
+k_dequantize(int n, const uint16_t* __restrict__ xyz_half, const uint8_t* __restrict__ chol_code,
+             const uint8_t* __restrict__ color_index, QuantConst qc, float* __restrict__ xyz_raw,
+             float* __restrict__ chol_raw, float* __restrict__ features) {
+    const int i = blockIdx.x * kFitThreads + threadIdx.x;
+    if (i >= n) return;
+    xyz_raw[2 * i] = __half2float(__ushort_as_half(xyz_half[2 * i]));
+    xyz_raw[2 * i + 1] = __half2float(__ushort_as_half(xyz_half[2 * i + 1]));
+#pragma unroll
+    for (int c = 0; c < 3; ++c)
+        chol_raw[3 * i + c] = addf(mulf((float)chol_code[3 * i + c], qc.scale[c]), qc.beta[c]);
+    const float3 col = fit_colour(i, reinterpret_cast<const float*>(color_index), nullptr, 2, qc);
+    features[3 * i] = col.x; features[3 * i + 1] = col.y; features[3 * i + 2] = col.z;
+}
+
 // the loader as a pass of its own (drop-in path: the model files want an RGB tensor): one thread
 // per 2x2 block -- two 2-byte luma loads, one U, one V, two 6-byte row segments out
 __global__ void __launch_bounds__(kFitThreads)
@@ -980,7 +1036,7 @@ int gs2d_fit_init(int n, int cap, int img_h, int img_w, void* work, size_t work_
 static int launch_bin(int n, const float* xyz, const float* chol, const float* feat, const float* opac,
                       const float* rgb_w, int activate,
                       int img_h, int img_w, int row0, int row1, int cap, int step, const gs2d_fit_layout& L, char* w,
-                      cudaStream_t s, bool precounted = false) {
+                      cudaStream_t s, bool precounted = false, const QuantConst& qc = QuantConst()) {
     const int tx = div_up(img_w, GS2D_TILE), ty = div_up(img_h, GS2D_TILE);
     const float half_w = 0.5f * (float)(unsigned)img_w, half_h = 0.5f * (float)(unsigned)img_h;
     int32_t* status = (int32_t*)(w + L.off_status);
@@ -990,14 +1046,14 @@ static int launch_bin(int n, const float* xyz, const float* chol, const float* f
     if (!precounted) {
         ProfScope ps_(GS2D_STAGE_SCAN_MAP, s);
         k_fit_count<<<blocks, kFitThreads, 0, s>>>(n, xyz, chol, activate, half_w, half_h, tx, ty, row0, row1, cap,
-                                                   step, tile_count, tile_off, status);
+                                                   step, tile_count, tile_off, status, qc);
         GS2D_CHECK_LAUNCH("fit_count");
     }
     {
         ProfScope ps_(GS2D_STAGE_EDGES_PACK, s);
         k_fit_scatter<<<blocks, kFitThreads, 0, s>>>(n, xyz, chol, feat, opac, rgb_w, activate, half_w, half_h, tx, ty,
                                                      row0, row1, img_w, img_h, tile_off, tile_count, status,
-                                                     (float4*)(w + L.off_packed), 0, step);
+                                                     (float4*)(w + L.off_packed), 0, step, qc);
         GS2D_CHECK_LAUNCH("fit_scatter");
     }
     return GS2D_OK;
@@ -1071,7 +1127,7 @@ int gs2d_fit_step_band(int n, int cap, int img_h, int img_w, float* xyz_raw, flo
                 GS2D_CHECK_LAUNCH("fit_reset_slots");
                 k_fit_scatter<<<div_up(n, kFitThreads), kFitThreads, 0, s>>>(
                     n, xyz_raw, chol_raw, features, nullptr, rgb_w, 1, half_w, half_h, tx, ty, row0, row1, img_w, img_h,
-                    nullptr, (int32_t*)(w + L.off_tile_count), status, (float4*)(w + L.off_packed), 1, step);
+                    nullptr, (int32_t*)(w + L.off_tile_count), status, (float4*)(w + L.off_packed), 1, step, QuantConst());
                 GS2D_CHECK_LAUNCH("fit_scatter_slots");
             }
         } else {
@@ -1131,6 +1187,58 @@ int gs2d_fit_step(int n, int cap, int img_h, int img_w, float* xyz_raw, float* c
                               work, work_bytes, step, lr, beta1, beta2, beta3, eps, weight_decay, precounted, 0,
                               div_up(img_h, GS2D_TILE), GS2D_FIT_PHASE_GRADS | GS2D_FIT_PHASE_UPDATE, nullptr, nullptr,
                               out_img, param_grads_out, ids_sorted_out, report_host, stream);
+}
+
+static int quant_const(const gs2d_quantized_frame* q, QuantConst& qc) {
+    GS2D_REQUIRE(q != nullptr && q->xyz_half && q->chol_code && q->color_index && q->codebooks,
+                 "quantized frame: null pointer");
+    GS2D_REQUIRE(((uintptr_t)q->xyz_half & 3) == 0, "quantized frame: xyz_half must be 4-byte aligned");
+    for (int c = 0; c < 3; ++c) { qc.scale[c] = q->chol_scale[c]; qc.beta[c] = q->chol_beta[c]; }
+    qc.codebooks = q->codebooks;
+    return GS2D_OK;
+}
+
+int gs2d_render_quantized(int n, int cap, int img_h, int img_w, const gs2d_quantized_frame* q, void* work,
+                          size_t work_bytes, float* out_img, int out_chw, int out_clamp, int32_t* final_idx,
+                          int32_t* ids_sorted_out, gs2d_stream_t stream) {
+    gs2d_fit_layout L;
+    int rc = fit_layout(n, cap, img_h, img_w, &L);
+    if (rc != GS2D_OK) return rc;
+    GS2D_REQUIRE(n > 0, "render_quantized: n must be positive");
+    GS2D_REQUIRE(work != nullptr && work_bytes >= L.total_bytes, "render_quantized: workspace too small");
+    GS2D_REQUIRE(out_img != nullptr, "render_quantized: null output");
+    QuantConst qc;
+    rc = quant_const(q, qc);
+    if (rc != GS2D_OK) return rc;
+    cudaStream_t s = (cudaStream_t)stream;
+    char* w = (char*)work;
+    const int tx = div_up(img_w, GS2D_TILE), ty = div_up(img_h, GS2D_TILE);
+    rc = launch_bin(n, (const float*)q->xyz_half, (const float*)q->chol_code, (const float*)q->color_index, nullptr,
+                    nullptr, 2, img_h, img_w, 0, ty, cap, 0, L, w, s, false, qc);
+    if (rc != GS2D_OK) return rc;
+    {
+        ProfScope ps_(GS2D_STAGE_RASTER_FWD, s);
+        k_fit_tiles<1, 0><<<dim3(tx, ty), kTileThreads, 0, s>>>(
+            img_w, img_h, tx, 0, (const int32_t*)(w + L.off_tile_off), (int32_t*)(w + L.off_tile_count),
+            (const float4*)(w + L.off_packed), nullptr, 0.f, nullptr, nullptr, (int32_t*)(w + L.off_status),
+            out_img, out_chw, out_clamp, final_idx, ids_sorted_out, 0, 0);
+        GS2D_CHECK_LAUNCH("render_tiles");
+    }
+    return GS2D_OK;
+}
+
+int gs2d_dequantize(int n, const gs2d_quantized_frame* q, float* xyz_raw, float* chol_raw, float* features,
+                    gs2d_stream_t stream) {
+    GS2D_REQUIRE(n > 0 && xyz_raw && chol_raw && features, "dequantize: bad arguments");
+    QuantConst qc;
+    const int rc = quant_const(q, qc);
+    if (rc != GS2D_OK) return rc;
+    cudaStream_t s = (cudaStream_t)stream;
+    ProfScope ps_(GS2D_STAGE_OTHER, s);
+    k_dequantize<<<div_up(n, kFitThreads), kFitThreads, 0, s>>>(n, q->xyz_half, q->chol_code, q->color_index, qc,
+                                                               xyz_raw, chol_raw, features);
+    GS2D_CHECK_LAUNCH("dequantize");
+    return GS2D_OK;
 }
 
 int gs2d_i420_to_rgb(int img_h, int img_w, const uint8_t* yuv, uint8_t* rgb, gs2d_stream_t stream) {

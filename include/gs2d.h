@@ -323,6 +323,34 @@ size_t gs2d_prune_scratch_bytes(int n);
 int gs2d_prune_lowest(int n, int remove_count, const float* rgb_w, const float* xyz_raw, const float* chol_raw,
                       const float* features, float* rgb_w_out, float* xyz_out, float* chol_out, float* features_out,
                       int32_t* keep_index_out, void* scratch, size_t scratch_bytes, gs2d_stream_t stream);
+/* Decode side: the quantised wire format of the codec, rendered without ever
+ * materialising fp32 Gaussians.  Same result as the reference's forward_quantize in eval mode
+ * (GaussianSplats_Compress.py:71-84) fed with the same codes:
+ *   xyz_half     uint16 [n][2]  IEEE fp16 bits of _xyz (FakeQuantizationHalf, quantize.py:15-24);
+ *                               means2d = tanh(float(xyz_half))
+ *   chol_code    uint8  [n][3]  6-bit codes 0..63 (UniformQuantizer.compress, quantize.py:82-84);
+ *                               L = code * chol_scale[c] + chol_beta[c] (+ the Cholesky bound)
+ *   color_index  uint8  [n][2]  residual-VQ indices of layer 0 and 1, 0..7 each;
+ *                               colour = codebooks[0][i0] + codebooks[1][i1]   (quantize.py:146-150)
+ *   codebooks    fp32 [2][8][3] device memory
+ * 9 bytes per Gaussian instead of 32.  Opacity is 1 (the model's `_opacity` buffer).  Entropy
+ * decoding of the code streams (constriction ANS, quantize.py:152-180) stays on the CPU. */
+typedef struct {
+    const uint16_t* xyz_half;
+    const uint8_t* chol_code;
+    const uint8_t* color_index;
+    const float* codebooks;
+    float chol_scale[3];
+    float chol_beta[3];
+} gs2d_quantized_frame;
+/* gs2d_render_chol on the wire format (work / outputs as there). */
+int gs2d_render_quantized(int n, int cap, int img_h, int img_w, const gs2d_quantized_frame* frame, void* work,
+                          size_t work_bytes, float* out_img, int out_chw, int out_clamp, int32_t* final_idx,
+                          int32_t* ids_sorted_out, gs2d_stream_t stream);
+/* The fp32 parameter tensors the wire format stands for (_xyz [n][2] before tanh, _cholesky [n][3]
+ * before the bound, colours [n][3]): what a P-frame fit starts from after decoding frame i-1. */
+int gs2d_dequantize(int n, const gs2d_quantized_frame* frame, float* xyz_raw, float* chol_raw, float* features,
+                    gs2d_stream_t stream);
 /* Frame pipe: raw frames from PINNED host memory into a ring of `depth` device slots
  * (device_slots: depth * frame_bytes bytes, caller-owned) on the pipe's own copy stream, so the
  * copy of the next frame runs under the current frame's fit step.  No counterpart in the
