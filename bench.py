@@ -432,6 +432,33 @@ def main_gop(args, rank: int, world: int, local_rank: int):
         gather_group = None
     F, cut = args.gop_frames, args.gop_cut
     frame_fn, keyframes = gop.synthetic_sequence(H, W, F, cut_every=cut)
+    prepass = None
+    if args.gop_detect:
+        # the reference's key-frame detection pre-pass (train_video_Represent.py:312-355): 5000-point
+        # probe fits, 500 iterations fresh / 100 from the previous frame, frames sharded with a halo
+        from gsvc_b200 import yuv as _y
+        from gsvc_b200.fit import FusedFrameFit
+        edges = [round(r * F / world) for r in range(world + 1)]
+        lo_f, hi_f = max(edges[rank] - 1, 0), edges[rank + 1]
+        probe_host = {f: _y.rgb_to_i420((frame_fn(f)[0] * 255).round().to(torch.uint8).permute(1, 2, 0).contiguous())
+                      .contiguous().pin_memory() for f in range(lo_f, hi_f)}
+        probe = lambda prev: FusedFrameFit(H, W, 5000, dev, init=prev) if prev is not None else FusedFrameFit(H, W, 5000, dev, seed=int(torch.initial_seed() % (1 << 30)))
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize(dev)
+        t0 = time.perf_counter()
+        scores = gop.keyframe_scores(lambda f: probe_host[f].to(dev, non_blocking=True), F, probe, 500, 100,
+                                     group=gather_group)
+        torch.cuda.synchronize(dev)
+        if world > 1:
+            dist.barrier()
+        dt = time.perf_counter() - t0
+        found = [sorted(set(gop.keyframes_from_scores(scores)))] if rank == 0 else [None]
+        if world > 1:
+            dist.broadcast_object_list(found, src=0, group=gather_group)
+        prepass = {"seconds": dt, "frames_per_s": F / dt, "probe_points": 5000, "iters": [500, 100],
+                   "keyframes_found": found[0], "scene_cuts": keyframes, "matches_scene_cuts": found[0] == keyframes}
+        keyframes = found[0]
     gops = gop.gops_from_keyframes(keyframes, F)
     cost = lambda g: args.gop_iters_key + (g[1] - g[0] - 1) * args.gop_iters_pred
     mine = gop.assign_gops(gops, world, cost=cost)[rank]
@@ -485,6 +512,7 @@ def main_gop(args, rank: int, world: int, local_rank: int):
             "fit_iters_per_s": iters / (ms * 1e-3), "wall_s_timed_region": wall,
             "psnr_mean": sum(psnrs) / len(psnrs), "psnr_min": min(psnrs),
             "num_points_first_last": [npts[0], npts[-1]], "num_points_max": max(npts),
+            "keyframe_prepass": prepass,
             "e2e": {"value": F / wall, "unit": "frames/s", "h2d_bytes_per_step": 3 * H * W // 2,
                     "d2h_bytes_per_step": 36 * NPTS},
         }
@@ -499,6 +527,8 @@ def main():
                     help="fit: the headline line (C2 + C3 render); gop: BASELINE config 4 (sequence, GOP sharding)")
     ap.add_argument("--gop-frames", type=int, default=120)
     ap.add_argument("--gop-cut", type=int, default=30, help="scene cut (key frame) every this many frames")
+    ap.add_argument("--gop-detect", action="store_true",
+                    help="run the key-frame detection pre-pass first and shard by the key frames it finds")
     ap.add_argument("--gop-iters-key", type=int, default=4100,
                     help="iterations per key frame (the removal control runs to iteration 4000)")
     ap.add_argument("--gop-iters-pred", type=int, default=1000,

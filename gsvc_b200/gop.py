@@ -134,3 +134,82 @@ def reference_fitters(H: int, W: int, num_points: int, device, is_rm: bool = Tru
                    densification_interval=densification_interval, **kw)
 
     return make
+
+
+# ------------------------------------------------------------------------------------------
+# Key-frame detection pre-pass (train_video_Represent.py:312-355)
+# ------------------------------------------------------------------------------------------
+def detect_outliers_mean_diff(values: Sequence[float], window_size: int = 10, threshold: float = 3) -> List[int]:
+    """utils.py:214-229 of the reference: index i is an outlier if it exceeds the mean of the window
+    [i - window_size, i + window_size) by `threshold` standard deviations, or `threshold` times that mean"""
+    import numpy as np
+    v = np.asarray(values, dtype=np.float64)
+    out = []
+    for i in range(len(v)):
+        w = v[max(0, i - window_size):min(len(v), i + window_size)]
+        mean, std = np.mean(w), np.std(w)
+        if (v[i] - mean) > threshold * std or v[i] > mean * threshold:
+            out.append(i)
+    return out
+
+
+def keyframes_from_scores(scores: Sequence[float]) -> List[int]:
+    """scores[i] = loss_P - loss_K of frame i (scores[0] = 0) -> 0-based key-frame indices, frame 0
+    first: min-max normalisation of scores[1:] (:336-341), outlier detection (:347), frame 1
+    (here: 0) always a key frame (:349)"""
+    import numpy as np
+    s = np.asarray(scores, dtype=np.float64)
+    rest = s[1:]
+    if rest.size == 0:
+        return [0]
+    lo, hi = float(rest.min()), float(rest.max())
+    norm = [float(s[0])] + [float((x - lo) / (hi - lo)) if hi > lo else 0.0 for x in rest]
+    ks = [int(i) for i in detect_outliers_mean_diff(norm)]
+    return [0] + ks       # np.insert(K_frames, 0, 1) in the reference's 1-based numbering: frame 0 may repeat
+
+
+def keyframe_scores(get_frame: Callable[[int], torch.Tensor], num_frames: int,
+                    make_probe: Callable[[Optional[dict]], object], iters_key: int = 500, iters_pred: int = 100,
+                    group=None, seed: Optional[int] = 1) -> Optional[List[float]]:
+    """The probe fits of the reference's pre-pass: for every frame a fresh small model fitted for
+    `iters_key` iterations (loss_K, :322-323 / :328-329) and a model started from the PREVIOUS
+    frame's fresh fit, fitted for `iters_pred` (loss_P, :330-331); score = loss_P - loss_K (:334).
+    The fresh fit of frame i depends on frame i alone, so the frames are sharded in contiguous blocks
+    over the ranks with a one-frame halo (a rank refits the frame before its block) and no data-path
+    collective; rank 0 gets the scores (others None)."""
+    distributed = dist.is_available() and dist.is_initialized()
+    world = dist.get_world_size(group) if distributed else 1
+    rank = dist.get_rank(group) if distributed else 0
+    edges = [round(r * num_frames / world) for r in range(world + 1)]
+    a, b = edges[rank], edges[rank + 1]
+    local: Dict[int, float] = {}
+
+    def fresh(f: int):
+        if seed is not None:
+            torch.manual_seed(int(seed) * 100003 + f)
+        fit = make_probe(None)
+        fit.train_iters(get_frame(f), iters_key)
+        state = fit.frame_state() if hasattr(fit, "frame_state") else fit.state_dict()
+        return {k: v.detach().clone() for k, v in state.items()}, fit.loss()
+
+    prev = fresh(a - 1)[0] if (a > 0 and b > a) else None          # the halo
+    for f in range(a, b):
+        cur, loss_k = fresh(f)
+        if f == 0:
+            local[f] = 0.0                                          # :324-326
+        else:
+            p = make_probe(prev)
+            p.train_iters(get_frame(f), iters_pred)
+            local[f] = p.loss() - loss_k
+        prev = cur
+    if not distributed:
+        return [local[f] for f in range(num_frames)]
+    gathered = [None] * world if rank == 0 else None
+    dist.gather_object(local, gathered, dst=0, group=group)
+    if rank != 0:
+        return None
+    merged: Dict[int, float] = {}
+    for part in gathered:
+        merged.update(part)
+    assert sorted(merged) == list(range(num_frames)), "key-frame pre-pass lost or duplicated frames"
+    return [merged[f] for f in range(num_frames)]

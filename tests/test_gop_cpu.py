@@ -129,3 +129,96 @@ def test_split_tile_rows():
     assert split_tile_rows(6, 2, [0] * 6) == [(0, 3), (3, 6)]
     with pytest.raises(ValueError):
         split_tile_rows(3, 4)
+
+
+# ---- key-frame detection pre-pass (train_video_Represent.py:312-355) -------------------------
+def test_keyframe_decision_matches_the_reference_functions():
+    import numpy as np
+    G = np.load(os.path.join(os.path.dirname(__file__), "golden", "keyframes.npz"))
+    for case in range(6):
+        got = gop.keyframes_from_scores(G[f"scores{case}"])
+        assert [k + 1 for k in got] == [int(k) for k in G[f"kframes{case}"]], case      # the reference numbers frames from 1
+
+
+class _ProbeFit:
+    """probe stand-in: the loss of a fit depends on the frame, on where it started and on how long
+    it ran, so a wrong halo or a wrong pairing of frames shows in the score"""
+
+    def __init__(self, prev):
+        self.start = None if prev is None else float(prev["_xyz"][0, 0])
+        self.frame_val, self.iters = None, 0
+
+    def train_iters(self, gt, iters):
+        self.frame_val = float(gt.flatten()[0])
+        self.iters += iters
+
+    def loss(self):
+        base = 0.01 * (1 + 0.01 * (self.frame_val % 7))
+        if self.start is None:
+            return base / self.iters
+        return base / self.iters + 0.001 * abs(self.frame_val - self.start)     # far from the previous frame: worse
+
+    def frame_state(self):
+        return {"_xyz": torch.full((2, 2), self.frame_val)}
+
+
+def _frame_values(n):
+    vals, v = [], 0.0
+    for f in range(n):
+        v += 9.0 if f in (7, 19) else 1.0          # two scene cuts
+        vals.append(v)
+    return vals
+
+
+def _expected_scores(n, ik, ip):
+    vals = _frame_values(n)
+    out = [0.0]
+    for f in range(1, n):
+        base = 0.01 * (1 + 0.01 * (vals[f] % 7))
+        out.append(base / ip + 0.001 * abs(vals[f] - vals[f - 1]) - base / ik)
+    return out
+
+
+def test_keyframe_scores_single_process():
+    n = 24
+    vals = _frame_values(n)
+    s = gop.keyframe_scores(lambda f: torch.full((3, 2, 2), vals[f]), n, _ProbeFit, 50, 10)
+    assert s == pytest.approx(_expected_scores(n, 50, 10))
+    assert gop.keyframes_from_scores(s) == [0, 7, 19]
+
+
+def _kf_worker(rank, world, port, q):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        n = 24
+        vals = _frame_values(n)
+        seen = []
+        get = lambda f: (seen.append(f), torch.full((3, 2, 2), vals[f]))[1]
+        scores = gop.keyframe_scores(get, n, _ProbeFit, 50, 10)
+        q.put((rank, sorted(set(seen)), scores))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_keyframe_scores_world_size_3_gloo_with_halo():
+    world = 3
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_kf_worker, args=(r, world, port, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    res = {}
+    for _ in range(world):
+        rank, seen, out = q.get(timeout=120)
+        res[rank] = (seen, out)
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    assert res[0][1] == pytest.approx(_expected_scores(24, 50, 10))      # identical to the unsharded pass
+    assert res[1][1] is None and res[2][1] is None
+    assert res[0][0] == list(range(0, 8))                               # block [0, 8)
+    assert res[1][0] == list(range(7, 16))                              # block [8, 16) + the frame before it
+    assert res[2][0] == list(range(15, 24))

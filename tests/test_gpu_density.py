@@ -177,3 +177,19 @@ def test_overflow_before_a_prune_rewinds_the_clock():
     assert small.n == ok.n == n - 250
     for k in KEYS:
         assert torch.equal(getattr(small, k), getattr(ok, k)) or float((getattr(small, k) - getattr(ok, k)).abs().max()) < 1e-5
+
+
+def test_keyframe_prepass_finds_the_scene_cuts():
+    """train_video_Represent.py:312-355 on the fused fitter: probe fits per frame, score = loss of the
+    fit started from the previous frame minus loss of the fresh fit, outliers = key frames"""
+    from gsvc_b200 import gop
+    from gsvc_b200.fit import FusedFrameFit
+    H, W, F = 128, 160, 12
+    frame, cuts = gop.synthetic_sequence(H, W, F, cut_every=4, seed=3)
+    frames = [frame(f).to(cuda) for f in range(F)]
+    probe = lambda prev: FusedFrameFit(H, W, 600, cuda, init=prev) if prev is not None else FusedFrameFit(H, W, 600, cuda, seed=5)
+    scores = gop.keyframe_scores(lambda f: frames[f], F, probe, iters_key=300, iters_pred=60)
+    assert scores[0] == 0.0 and len(scores) == F
+    assert gop.keyframes_from_scores(scores) == cuts == [0, 4, 8]
+    at_cuts = min(scores[4], scores[8])
+    assert at_cuts > 3 * max(s for i, s in enumerate(scores) if i not in (0, 4, 8))
