@@ -4,7 +4,7 @@ from __future__ import annotations
 
 import ctypes
 import os
-from ctypes import POINTER, Structure, c_char_p, c_float, c_int, c_size_t, c_void_p
+from ctypes import POINTER, Structure, c_char_p, c_float, c_int, c_size_t, c_uint32, c_void_p
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 # GS2D_LIB: kernel-variant A/B runs only (profiles/build_variant.py); the product loads the in-tree build
@@ -51,7 +51,9 @@ class GradExchange(Structure):
     """mirror of gs2d_grad_exchange (include/gs2d.h)"""
 
     _fields_ = [("accumulate", c_void_p), ("peers", c_void_p), ("num_peers", c_int), ("zero", c_void_p),
-                ("multicast", c_void_p)]
+                ("multicast", c_void_p), ("shard_begin", c_int), ("shard_end", c_int), ("xyz_peers", c_void_p),
+                ("chol_peers", c_void_p), ("feat_peers", c_void_p), ("status_peers", c_void_p),
+                ("barrier_pads", c_void_p), ("rank", c_int), ("barrier_epoch", c_uint32)]
 
 
 class FitOptions(Structure):

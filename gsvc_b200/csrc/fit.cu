@@ -260,11 +260,22 @@ k_fit_count(int n, const float* __restrict__ xyz_raw, const float* __restrict__ 
 // before the first record is written: a Gaussian's tiles then cost one round trip to L2, not one each.
 // Returns the number of tiles claimed.
 // ------------------------------------------------------------------------------------------
+// Sharded update (include/gs2d.h, gs2d_grad_exchange): the peers' parameter tensors (the update
+// kernel stores its shard's new values into all of them) and status words (an overflowing tile is
+// flagged on every rank); R == 0: not sharded.
+struct Route {
+    float* const* xyz;
+    float* const* chol;
+    float* const* feat;
+    int32_t* const* status;
+    int R;
+};
+
 template <bool SLOT>
 __device__ __forceinline__ int scatter_records(const Proj2d& p, int i, float o, float r, float g, float b, int tx,
                                                int row0, int row1, int W, int H, const int32_t* __restrict__ tile_off,
                                                int32_t* tile_fill, float4* __restrict__ packed, int32_t* status,
-                                               int flag_step) {
+                                               int flag_step, const Route& rt = Route()) {
     if (p.nth <= 0) return 0;
     const int ya = max(p.y0, row0), yb = min(p.y1, row1);
     const int bw = p.x1 - p.x0;
@@ -290,7 +301,11 @@ __device__ __forceinline__ int scatter_records(const Proj2d& p, int i, float o, 
                 bool ok = true;
                 if (SLOT) {
                     ok = pos[k] < kSlotStride;
-                    if (!ok) atomicCAS(&status[kStOverflow], 0, -flag_step);
+                    if (!ok) {
+                        atomicCAS(&status[kStOverflow], 0, -flag_step);
+                        for (int q = 0; q < rt.R; ++q)   // sharded update: every rank must stop at this step
+                            if (rt.status[q] != status) atomicCAS_system(&rt.status[q][kStOverflow], 0, -flag_step);
+                    }
                     at = (size_t)t * kSlotStride + pos[k];
                 } else {
                     at = (size_t)tile_off[t] + pos[k];
@@ -328,7 +343,8 @@ k_fit_scatter(int n, const float* __restrict__ xyz_raw, const float* __restrict_
               const float* __restrict__ feat, const float* __restrict__ opac, const float* __restrict__ rgb_w,
               int activate, float half_w, float half_h,
               int tx, int ty, int row0, int row1, int W, int H, const int32_t* __restrict__ tile_off,
-              int32_t* tile_fill, int32_t* status, float4* __restrict__ packed, int slots, int step, QuantConst qc) {
+              int32_t* tile_fill, int32_t* status, float4* __restrict__ packed, int slots, int step, QuantConst qc,
+              Route rt) {
     __shared__ int sh[8];
     // not an early return: in slot mode another block may raise the flag while this one runs, and
     // every thread must reach the block sum below
@@ -342,7 +358,7 @@ k_fit_scatter(int n, const float* __restrict__ xyz_raw, const float* __restrict_
         const float3 col = fit_colour(i, feat, rgb_w, activate, qc);
         const float r = col.x, g = col.y, b = col.z;
         if (slots)
-            claimed = scatter_records<true>(p, i, o, r, g, b, tx, row0, row1, W, H, nullptr, tile_fill, packed, status, step);
+            claimed = scatter_records<true>(p, i, o, r, g, b, tx, row0, row1, W, H, nullptr, tile_fill, packed, status, step, rt);
         else
             scatter_records<false>(p, i, o, r, g, b, tx, row0, row1, W, H, tile_off, tile_fill, packed, status, step);
     }
@@ -781,10 +797,14 @@ k_fit_update(int n, float* __restrict__ xyz_raw, float* __restrict__ chol_raw, f
              const float* const* __restrict__ peer_grads, int num_peers, float* __restrict__ grads_zero,
              float* __restrict__ rgb_w, float* __restrict__ adan_w, float* __restrict__ rgb_w_grad_out,
              int skip_update, const float* __restrict__ mc_grads, int slots, float4* __restrict__ packed, int W,
-             int H) {
+             int H, int shard_begin, int shard_end, Route rt) {
     __shared__ int sh[8];
     __shared__ int s_last;
-    const int i = blockIdx.x * kFitThreads + threadIdx.x;
+    __shared__ float s_par[8 * kFitThreads];
+    // this launch updates Gaussians [shard_begin, shard_end) -- [0, n) unless the update is sharded
+    // over the ranks; all arrays are indexed by the global Gaussian index
+    const int gtid = blockIdx.x * kFitThreads + threadIdx.x;
+    const int i = shard_begin + gtid;
     // ---- prologue: parameters and optimizer state were last written by the PREVIOUS update kernel,
     // not by the tile kernel this one follows -- under PDL all of this (the bulk of the kernel's
     // memory traffic and both tanh) runs while the tile kernel's last wave drains ----------------
@@ -796,7 +816,7 @@ k_fit_update(int n, float* __restrict__ xyz_raw, float* __restrict__ chol_raw, f
     float4* sn = reinterpret_cast<float4*>(adan + plane + (size_t)i * 8);
     float4* sd = reinterpret_cast<float4*>(adan + 2 * plane + (size_t)i * 8);
     float4* sp = reinterpret_cast<float4*>(adan + 3 * plane + (size_t)i * 8);
-    if (i < n) {
+    if (i < shard_end) {
         fit_project(i, xyz_raw, chol_raw, 1, half_w, half_h, tx, ty, p, m, L, QuantConst());
         par[0] = xyz_raw[2 * i]; par[1] = xyz_raw[2 * i + 1];
         par[2] = chol_raw[3 * i]; par[3] = chol_raw[3 * i + 1]; par[4] = chol_raw[3 * i + 2];
@@ -818,7 +838,7 @@ k_fit_update(int n, float* __restrict__ xyz_raw, float* __restrict__ chol_raw, f
     // being scattered below) must not stop this step's update half way
     const int of = status[kStOverflow];
     const bool dead = of != 0 && abs(of) < next_step;
-    if (i == 0 && report_host) {
+    if (gtid == 0 && report_host) {
         // the step's result straight into pinned host memory (no copy to issue, nothing to wait
         // for but the kernel itself); written before the scan below replaces status[0]
         double ls = *loss_this;
@@ -843,9 +863,16 @@ k_fit_update(int n, float* __restrict__ xyz_raw, float* __restrict__ chol_raw, f
         __threadfence_system();
     }
     if (dead) return;
-    if (i == 0 && loss_next) *loss_next = 0.0;
+    if (gtid == 0 && loss_next) *loss_next = 0.0;
+    if (rt.R > 0 && grads_zero) {
+        // sharded: this rank reads (and would re-zero) only its shard's rows, but its tile kernel
+        // adds into every row of its own buffer -- clear the whole spare buffer for the step after next
+        const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
+        float4* zb = reinterpret_cast<float4*>(grads_zero);
+        for (size_t q = gtid; q < (size_t)n * 3; q += (size_t)gridDim.x * kFitThreads) zb[q] = z;
+    }
     int claimed = 0;
-    if (i < n) {
+    if (i < shard_end) {
         float4 g0, g1;   // v_xy(2) v_conic(3) v_rgb(3) | v_opacity(1) pad(3) unused here
         if (mc_grads) {
             // spatial mode over the switch: one load returns the row summed over all ranks
@@ -857,17 +884,29 @@ k_fit_update(int n, float* __restrict__ xyz_raw, float* __restrict__ chol_raw, f
             // bit-identical updates with no collective kernel and no extra pass over the rows
             g0 = make_float4(0.f, 0.f, 0.f, 0.f);
             g1 = g0;
-            for (int r = 0; r < num_peers; ++r) {
-                const float4* prow = reinterpret_cast<const float4*>(peer_grads[r] + (size_t)i * 12);
-                const float4 a = __ldcg(prow), b = __ldcg(prow + 1);
-                g0.x += a.x; g0.y += a.y; g0.z += a.z; g0.w += a.w;
-                g1.x += b.x; g1.y += b.y; g1.z += b.z; g1.w += b.w;
+            // up to eight peers' rows in flight at once: one NVLink round trip, not one per rank
+            for (int r0 = 0; r0 < num_peers; r0 += 8) {
+                float4 a[8], b[8];
+#pragma unroll
+                for (int k = 0; k < 8; ++k) {
+                    if (r0 + k < num_peers) {
+                        const float4* prow = reinterpret_cast<const float4*>(peer_grads[r0 + k] + (size_t)i * 12);
+                        a[k] = __ldcg(prow); b[k] = __ldcg(prow + 1);
+                    }
+                }
+#pragma unroll
+                for (int k = 0; k < 8; ++k) {
+                    if (r0 + k < num_peers) {
+                        g0.x += a[k].x; g0.y += a[k].y; g0.z += a[k].z; g0.w += a[k].w;
+                        g1.x += b[k].x; g1.y += b[k].y; g1.z += b[k].z; g1.w += b[k].w;
+                    }
+                }
             }
         } else {
             const float4* grow = reinterpret_cast<const float4*>(grads + (size_t)i * 12);
             g0 = grow[0]; g1 = grow[1];
         }
-        {   // re-zero a gradient row for a later step: this step's buffer, or (peer exchange) the
+        if (rt.R == 0) {   // re-zero a gradient row for a later step: this step's buffer, or (peer exchange) the
             // OTHER buffer of the pair, which no peer can still be reading (see SpatialFrameFit)
             float4* zrow = reinterpret_cast<float4*>((grads_zero ? grads_zero : grads) + (size_t)i * 12);
             const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -902,31 +941,86 @@ k_fit_update(int n, float* __restrict__ xyz_raw, float* __restrict__ chol_raw, f
         xyz_raw[2 * i] = par[0]; xyz_raw[2 * i + 1] = par[1];
         chol_raw[3 * i] = par[2]; chol_raw[3 * i + 1] = par[3]; chol_raw[3 * i + 2] = par[4];
         feat[3 * i] = par[5]; feat[3 * i + 1] = par[6]; feat[3 * i + 2] = par[7];
+        if (rt.R > 0) {   // sharded update: staged for the block's stores into the peers' tensors (below)
+            s_par[2 * threadIdx.x] = par[0]; s_par[2 * threadIdx.x + 1] = par[1];
+#pragma unroll
+            for (int k = 0; k < 3; ++k) {
+                s_par[2 * kFitThreads + 3 * threadIdx.x + k] = par[2 + k];
+                s_par[5 * kFitThreads + 3 * threadIdx.x + k] = par[5 + k];
+            }
+        }
         if (rgb_w) {
             cw = adan_one(cw, gw, wm, wn, wd, wp, h);
             rgb_w[i] = cw;
             adan_w[i] = wm; adan_w[(size_t)n + i] = wn; adan_w[2 * (size_t)n + i] = wd; adan_w[3 * (size_t)n + i] = wp;
         }
         // the next iteration's binning starts here: project the updated parameters and count tiles
-        // (same arithmetic as k_fit_count / k_fit_scatter, so the ranges match what scatter fills)
-        Proj2d pn;
-        project_chol(tanhf(par[0]), tanhf(par[1]), addf(par[2], 0.5f), addf(par[3], 0.f), addf(par[4], 0.5f), half_w,
-                     half_h, tx, ty, pn);
-        if (slots) {
-            // ... and with fixed slots per tile there is nothing to count or scan first: the records
-            // of the next iteration are written right here (tile_count is the tiles' fill level)
-            claimed = scatter_records<true>(pn, i, 1.f, mulf(par[5], cw), mulf(par[6], cw), mulf(par[7], cw), tx, row0,
-                                            row1, W, H, nullptr, tile_count, packed, status, next_step);
-        } else {
-            count_tiles(pn, tx, row0, row1, tile_count);
+        // (same arithmetic as k_fit_count / k_fit_scatter, so the ranges match what scatter fills);
+        // not when the update is sharded: each rank bins its band from the gathered parameters
+        if (rt.R == 0) {
+            Proj2d pn;
+            project_chol(tanhf(par[0]), tanhf(par[1]), addf(par[2], 0.5f), addf(par[3], 0.f), addf(par[4], 0.5f),
+                         half_w, half_h, tx, ty, pn);
+            if (slots) {
+                // ... and with fixed slots per tile there is nothing to count or scan first: the records
+                // of the next iteration are written right here (tile_count is the tiles' fill level)
+                claimed = scatter_records<true>(pn, i, 1.f, mulf(par[5], cw), mulf(par[6], cw), mulf(par[7], cw), tx,
+                                                row0, row1, W, H, nullptr, tile_count, packed, status, next_step);
+            } else {
+                count_tiles(pn, tx, row0, row1, tile_count);
+            }
         }
     }
     if (skip_update) return;
+    if (rt.R > 0) {
+        // sharded update: the all-gather is these stores (NVLink, fire and forget; the peers read
+        // them after the barrier that follows this kernel).  A block's Gaussians are contiguous in
+        // each of the three tensors, so every store instruction of a warp fills one 128-byte line.
+        __syncthreads();
+        const size_t i0 = (size_t)shard_begin + (size_t)blockIdx.x * kFitThreads;
+        const int c = min(kFitThreads, shard_end - (int)i0);
+        for (int q = 0; q < rt.R; ++q) {
+            float* px = rt.xyz[q];
+            if (px == xyz_raw) continue;   // this rank's own copy was written above
+            float* pc = rt.chol[q]; float* pf = rt.feat[q];
+            for (int k = threadIdx.x; k < 2 * c; k += kFitThreads) px[2 * i0 + k] = s_par[k];
+            for (int k = threadIdx.x; k < 3 * c; k += kFitThreads) {
+                pc[3 * i0 + k] = s_par[2 * kFitThreads + k];
+                pf[3 * i0 + k] = s_par[5 * kFitThreads + k];
+            }
+        }
+        return;
+    }
     if (slots) {
         block_add(claimed, &status[kStSlotIsect + (next_step & 1)], sh);
         return;
     }
     scan_tiles_by_last_block(tx, ty, cap, next_step, tile_count, tile_off, status, sh, &s_last);
+}
+
+// Cross-rank barrier on the stream (include/gs2d.h, gs2d_grad_exchange.barrier_pads): one warp, lane
+// q signals rank q and waits for rank q.  The kernels before it on this stream have completed, so
+// their writes (local REDs, stores into peer memory) precede the fence; the release / acquire pair
+// at system scope hands them to whoever passes the barrier on the other side.  The kernel that
+// follows may be launched programmatically: its prologue runs under the wait.
+__global__ void __launch_bounds__(32)
+k_rank_barrier(uint32_t* const* __restrict__ pads, int R, int rank, uint32_t epoch) {
+    pdl_release();
+    const int q = threadIdx.x;
+    if (q >= R) return;
+    __threadfence_system();
+    uint32_t* dst = pads[q] + rank;
+    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(dst), "r"(epoch) : "memory");
+    const uint32_t* src = pads[rank] + q;
+    unsigned long long t0, t1;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+    uint32_t v;
+    for (;;) {
+        asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(src) : "memory");
+        if ((int32_t)(v - epoch) >= 0) break;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
+        if (t1 - t0 > 10000000000ull) __trap();   // 10 s: a peer is gone
+    }
 }
 
 // wire format -> the fp32 parameter tensors of the frame model (what forward_quantize feeds the two
@@ -1053,7 +1147,7 @@ static int launch_bin(int n, const float* xyz, const float* chol, const float* f
         ProfScope ps_(GS2D_STAGE_EDGES_PACK, s);
         k_fit_scatter<<<blocks, kFitThreads, 0, s>>>(n, xyz, chol, feat, opac, rgb_w, activate, half_w, half_h, tx, ty,
                                                      row0, row1, img_w, img_h, tile_off, tile_count, status,
-                                                     (float4*)(w + L.off_packed), 0, step, qc);
+                                                     (float4*)(w + L.off_packed), 0, step, qc, Route());
         GS2D_CHECK_LAUNCH("fit_scatter");
     }
     return GS2D_OK;
@@ -1093,6 +1187,8 @@ int gs2d_fit_step_band(int n, int cap, int img_h, int img_w, float* xyz_raw, flo
     int num_peers = 0;
     float* grads_zero = nullptr;
     const float* mc_grads = nullptr;
+    Route rt = Route();
+    int shard_begin = 0, shard_end = n;
     if (exchange) {
         GS2D_REQUIRE(exchange->accumulate != nullptr, "fit_step: exchange without an accumulate buffer");
         GS2D_REQUIRE(exchange->num_peers >= 0 && (exchange->num_peers == 0 || exchange->peers != nullptr),
@@ -1103,7 +1199,21 @@ int gs2d_fit_step_band(int n, int cap, int img_h, int img_w, float* xyz_raw, flo
         grads_zero = exchange->zero;
         mc_grads = exchange->multicast;
         if (mc_grads) { peer_grads = nullptr; num_peers = 0; }
+        if (exchange->shard_end > exchange->shard_begin) {
+            GS2D_REQUIRE(exchange->shard_begin >= 0 && exchange->shard_end <= n, "fit_step: shard out of range");
+            GS2D_REQUIRE(num_peers > 0 && exchange->xyz_peers && exchange->chol_peers && exchange->feat_peers &&
+                             exchange->status_peers && grads_zero,
+                         "fit_step: a sharded update needs peers, their parameter pointers and a spare buffer");
+            shard_begin = exchange->shard_begin;
+            shard_end = exchange->shard_end;
+            rt.xyz = exchange->xyz_peers;
+            rt.chol = exchange->chol_peers;
+            rt.feat = exchange->feat_peers;
+            rt.status = exchange->status_peers;
+            rt.R = num_peers;
+        }
     }
+    const bool sharded = rt.R > 0;
     float* rgb_w = nullptr; float* adan_w = nullptr; float* rgb_w_grad_out = nullptr;
     int adan_step = step, adan_fresh = step == 1, skip_update = 0, slots = 0;
     if (options) {
@@ -1117,17 +1227,26 @@ int gs2d_fit_step_band(int n, int cap, int img_h, int img_w, float* xyz_raw, flo
         if (options->adan_step > 0) { adan_step = options->adan_step; adan_fresh = options->adan_fresh != 0; }
         skip_update = options->skip_update != 0;
     }
+    GS2D_REQUIRE(!sharded || (slots && rgb_w == nullptr && !skip_update),
+                 "fit_step: a sharded update needs tile slots (and has no prune / add control)");
     if (phases & GS2D_FIT_PHASE_GRADS) {
         GS2D_REQUIRE(target != nullptr, "fit_step: null target");
         if (slots) {
-            if (!precounted) {   // nothing scattered for these parameters yet (first step, or they were modified)
+            // precounted == 0: nothing scattered for these parameters yet (first step, or they were
+            // modified).  A sharded update never scatters: the band's records are written here, every
+            // step, from the parameters the ranks stored into this rank's tensors (the fill levels
+            // are zero already: the previous tile kernel left them so)
+            if (!precounted || sharded) {
                 ProfScope ps_(GS2D_STAGE_EDGES_PACK, s);
-                k_fit_reset_slots<<<div_up(L.tiles, kFitThreads), kFitThreads, 0, s>>>(
-                    L.tiles, (int32_t*)(w + L.off_tile_count), status);
-                GS2D_CHECK_LAUNCH("fit_reset_slots");
+                if (!precounted) {
+                    k_fit_reset_slots<<<div_up(L.tiles, kFitThreads), kFitThreads, 0, s>>>(
+                        L.tiles, (int32_t*)(w + L.off_tile_count), status);
+                    GS2D_CHECK_LAUNCH("fit_reset_slots");
+                }
                 k_fit_scatter<<<div_up(n, kFitThreads), kFitThreads, 0, s>>>(
                     n, xyz_raw, chol_raw, features, nullptr, rgb_w, 1, half_w, half_h, tx, ty, row0, row1, img_w, img_h,
-                    nullptr, (int32_t*)(w + L.off_tile_count), status, (float4*)(w + L.off_packed), 1, step, QuantConst());
+                    nullptr, (int32_t*)(w + L.off_tile_count), status, (float4*)(w + L.off_packed), 1, step, QuantConst(),
+                    rt);
                 GS2D_CHECK_LAUNCH("fit_scatter_slots");
             }
         } else {
@@ -1156,6 +1275,15 @@ int gs2d_fit_step_band(int n, int cap, int img_h, int img_w, float* xyz_raw, flo
                 status, out_img, 1, 1, (int32_t*)nullptr, ids_sorted_out, step, banded ? 1 : 0));
         GS2D_CHECK_LAUNCH("fit_tiles");
     }
+    const bool own_barrier = exchange && exchange->barrier_pads &&
+                             phases == (GS2D_FIT_PHASE_GRADS | GS2D_FIT_PHASE_UPDATE);
+    if (own_barrier) {
+        GS2D_REQUIRE(exchange->num_peers > 0 && exchange->num_peers <= 32 && exchange->rank >= 0 &&
+                         exchange->rank < exchange->num_peers, "fit_step: bad barrier description");
+        k_rank_barrier<<<1, 32, 0, s>>>(exchange->barrier_pads, exchange->num_peers, exchange->rank,
+                                        exchange->barrier_epoch);
+        GS2D_CHECK_LAUNCH("rank_barrier");
+    }
     if (phases & GS2D_FIT_PHASE_UPDATE) {
         AdanHyper h;
         h.b1 = beta1; h.b2 = beta2; h.b3 = beta3;
@@ -1166,13 +1294,18 @@ int gs2d_fit_step_band(int n, int cap, int img_h, int img_w, float* xyz_raw, flo
         h.decay_div = 1.f + lr * weight_decay;
         h.first = adan_fresh;
         ProfScope ps_(GS2D_STAGE_ADAN, s);
-        GS2D_CHECK_CUDA(launch_pdl(k_fit_update, dim3(div_up(n, kFitThreads)), dim3(kFitThreads), s,
+        GS2D_CHECK_CUDA(launch_pdl(k_fit_update, dim3(div_up(shard_end - shard_begin, kFitThreads)), dim3(kFitThreads), s,
             n, xyz_raw, chol_raw, features, adan_state, grads, half_w, half_h, tx, ty, h, status,
             loss + (step % GS2D_FIT_LOSS_SLOTS), loss + ((step + 1) % GS2D_FIT_LOSS_SLOTS), param_grads_out, cap,
             step + 1, (int32_t*)(w + L.off_tile_count), (int32_t*)(w + L.off_tile_off), report_host, row0, row1,
             banded ? 1 : 0, peer_grads, num_peers, grads_zero, rgb_w, adan_w, rgb_w_grad_out, skip_update,
-            mc_grads, slots, (float4*)(w + L.off_packed), img_w, img_h));
+            mc_grads, slots, (float4*)(w + L.off_packed), img_w, img_h, shard_begin, shard_end, rt));
         GS2D_CHECK_LAUNCH("fit_update");
+    }
+    if (own_barrier && sharded) {   // the peers' stores into this rank's parameters precede its next scatter
+        k_rank_barrier<<<1, 32, 0, s>>>(exchange->barrier_pads, exchange->num_peers, exchange->rank,
+                                        exchange->barrier_epoch + 1u);
+        GS2D_CHECK_LAUNCH("rank_barrier");
     }
     return GS2D_OK;
 }

@@ -599,22 +599,24 @@ class SpatialFrameFit(FusedFrameFit):
     path_name = "tile-row bands per rank; scatter-pack + tile kernel on the band, gradient rows summed across ranks, replicated update"
 
     def __init__(self, H, W, num_points, device, group=None, bands=None, emulate_world: int = 0,
-                 exchange: str = "nccl", slots: bool = False, **kw):
+                 exchange: str = "nccl", slots: bool = False, own_barrier: bool = True, **kw):
         """exchange: "nccl" -- one all-reduce call on the gradient rows between the two phases;
         "peer" -- the rows live in symmetric (peer-mapped) memory and the update kernel itself sums
         them over NVLink in rank order after a device-side barrier: no collective kernel, no extra
         pass over the rows, bit-identical results on every rank by construction."""
-        if slots:
-            raise NotImplementedError("tile slots are not wired into the tile-row split yet")
-        super().__init__(H, W, num_points, device, slots=False, **kw)
+        sharded = exchange == "sharded"
+        if slots and not sharded:
+            raise NotImplementedError("tile slots are wired into the tile-row split for exchange='sharded' only")
+        super().__init__(H, W, num_points, device, slots=sharded, **kw)
         import torch.distributed as dist
         self._dist = dist
         if self.rgb_W is not None:
             raise NotImplementedError("the prune / add control is not wired into the tile-row split yet")
         self.group = group
+        self.own_barrier = bool(own_barrier)     # False: torch's symmetric-memory barrier between two host calls
         self.emulate_world = int(emulate_world)
-        if exchange not in ("nccl", "peer", "nvls"):
-            raise ValueError("exchange must be 'nccl', 'peer' or 'nvls'")
+        if exchange not in ("nccl", "peer", "nvls", "sharded"):
+            raise ValueError("exchange must be 'nccl', 'peer', 'nvls' or 'sharded'")
         if exchange == "nvls" and emulate_world:
             raise ValueError("the switch reduction needs real ranks (no single-GPU emulation)")
         self.exchange = exchange
@@ -630,8 +632,55 @@ class SpatialFrameFit(FusedFrameFit):
         lay = self.layout
         self._grads = self.work[lay.off_grads:lay.off_grads + self.n * 48].view(torch.float32)
         self._hdl = None
-        if exchange in ("peer", "nvls"):
+        if sharded:
+            self._setup_sharded()
+        if exchange in ("peer", "nvls", "sharded"):
             self._setup_peer_buffers()
+
+    def _setup_sharded(self):
+        """Sharded update: rank r owns Gaussians shards[r] (optimizer state, gradient reduction,
+        update) and rasterises bands[r].  Its update kernel stores the new parameters into every
+        rank's parameter tensors, and a tile that outgrows its slots is flagged in every rank's
+        status words: both move into symmetric (peer-mapped) memory."""
+        dev, n, lay, R = self.device, self.n, self.layout, self.world
+        edges = [round(r * n / R) for r in range(R + 1)]
+        self.shards = [(edges[r], edges[r + 1]) for r in range(R)]
+        if any(b <= a for a, b in self.shards):
+            raise ValueError("need at least one Gaussian per rank")
+        lib = self._lib.load()
+        if self.emulate_world:
+            # one process: the "ranks" share the parameter tensors, each has a workspace of its own
+            self._works = [self.work] + [torch.empty_like(self.work) for _ in range(R - 1)]
+            with self._C._guard(dev):
+                for wk in self._works[1:]:
+                    self._lib.check(lib.gs2d_fit_init(n, self.cap, self.H, self.W, wk.data_ptr(), lay.total_bytes, None,
+                                                      torch.cuda.current_stream(dev).cuda_stream), "fit_init")
+            par = [[t.data_ptr()] * R for t in (self._xyz, self._cholesky, self._features_dc)]
+            status = [wk.data_ptr() + lay.off_status for wk in self._works]
+        else:
+            import torch.distributed._symmetric_memory as symm
+            grp = self.group if self.group is not None else self._dist.group.WORLD
+            buf = symm.empty((8 * n,), dtype=torch.float32, device=dev)
+            self._par_hdl = symm.rendezvous(buf, grp)
+            views = (buf[:2 * n].view(n, 2), buf[2 * n:5 * n].view(n, 3), buf[5 * n:8 * n].view(n, 3))
+            for v, name in zip(views, ("_xyz", "_cholesky", "_features_dc")):
+                v.copy_(getattr(self, name).data)
+                setattr(self, name, torch.nn.Parameter(v, requires_grad=False))
+            wk = symm.empty((lay.total_bytes,), dtype=torch.uint8, device=dev)
+            self._work_hdl = symm.rendezvous(wk, grp)
+            with self._C._guard(dev):
+                self._lib.check(lib.gs2d_fit_init(n, self.cap, self.H, self.W, wk.data_ptr(), lay.total_bytes, None,
+                                                  torch.cuda.current_stream(dev).cuda_stream), "fit_init")
+            self.work = wk
+            self._status = wk[lay.off_status:lay.off_status + 64].view(torch.int32)
+            self._loss = wk[lay.off_loss:lay.off_loss + 8 * self._lib.FIT_LOSS_SLOTS].view(torch.float64)
+            self._grads = wk[lay.off_grads:lay.off_grads + n * 48].view(torch.float32)
+            self._works = [wk]
+            bases = [int(p) for p in self._par_hdl.buffer_ptrs]
+            par = [[b + 4 * off for b in bases] for off in (0, 2 * n, 5 * n)]
+            status = [int(p) + lay.off_status for p in self._work_hdl.buffer_ptrs]
+        self._route_ptrs = torch.tensor(par + [status], dtype=torch.int64, device=dev)   # xyz, chol, feat, status
+        self._route_ptr = [self._route_ptrs[k].data_ptr() for k in range(4)]
 
     def _setup_peer_buffers(self):
         dev, n = self.device, self.n
@@ -653,9 +702,16 @@ class SpatialFrameFit(FusedFrameFit):
             self._mc = int(self._hdl.multicast_ptr or 0)
             if self.exchange == "nvls" and not self._mc:
                 raise RuntimeError("exchange='nvls': this process group has no NVLink-switch multicast (NVLS) mapping")
+            # pads of the library's own cross-rank barrier (gs2d_grad_exchange.barrier_pads)
+            self._pads = symm.empty((64,), dtype=torch.int32, device=dev)
+            self._pads.zero_()
+            self._pads_hdl = symm.rendezvous(self._pads, grp)
+            self._pad_ptrs = torch.tensor([int(p) for p in self._pads_hdl.buffer_ptrs], dtype=torch.int64, device=dev)
+            self._barriers = 0                      # barriers issued so far (same on every rank)
             torch.cuda.current_stream(dev).synchronize()
             self._hdl.barrier(channel=0)            # every rank's buffers are zero before anyone adds
         self._peer_lists = torch.tensor(ptrs, dtype=torch.int64, device=dev)   # [2][world] device pointers
+        self._peer_list_ptr = [self._peer_lists[b].data_ptr() for b in range(2)]
 
     def _exchange_struct(self, rank_slot: int, with_peers: bool):
         """gs2d_grad_exchange for this step: accumulate into buffer step&1, zero the other one"""
@@ -664,29 +720,97 @@ class SpatialFrameFit(FusedFrameFit):
         x = self.step_index & 1
         ex = self._lib.GradExchange()
         ex.accumulate = self._own[rank_slot][x]
-        ex.peers = self._peer_lists[x].data_ptr() if with_peers else None
+        ex.peers = self._peer_list_ptr[x] if with_peers else None
         ex.num_peers = self.world if with_peers else 0
         ex.zero = self._own[rank_slot][1 - x]
         ex.multicast = (self._mc + x * self.n * 48) if (with_peers and self.exchange == "nvls") else None
+        if self.exchange == "sharded":
+            ex.peers, ex.num_peers = self._peer_list_ptr[x], self.world
+            ex.shard_begin, ex.shard_end = self.shards[rank_slot if self.emulate_world else self.rank]
+            ex.xyz_peers, ex.chol_peers, ex.feat_peers, ex.status_peers = self._route_ptr
         return ex
 
-    def _band_call(self, gt, fmt, band, phases, precounted, dbg, ex=None):
+    def _with_barrier(self, ex):
+        """the library issues the step's barriers itself (one host call per step)"""
+        count = 2 if self.exchange == "sharded" else 1
+        ex.barrier_pads, ex.rank, ex.barrier_epoch = self._pad_ptrs.data_ptr(), self.rank, self._barriers + 1
+        self._barriers += count
+        return ex
+
+    def _band_call(self, gt, fmt, band, phases, precounted, dbg, ex=None, work=None):
         b1, b2, b3 = self.betas
+        opts = None
+        if self.slots:
+            opts = self._opts
+            opts.adan_step, opts.adan_fresh, opts.skip_update, opts.slots = 0, 0, 0, 1   # 0: the step's own clock
+        work = self.work if work is None else work
         slot = self.step_index % self._lib.FIT_LOSS_SLOTS
         out_img, grads_out, ids_out = dbg.get("out_img"), dbg.get("grads_out"), dbg.get("ids_out")
-        self._lib.check(self._lib.load().gs2d_fit_step_band(
+        self._lib.check(self._cdll.gs2d_fit_step_band(
             self.n, self.cap, self.H, self.W, self._xyz.data_ptr(), self._cholesky.data_ptr(),
-            self._features_dc.data_ptr(), self.adan_state.data_ptr(), gt.data_ptr(), fmt, self.work.data_ptr(),
+            self._features_dc.data_ptr(), self.adan_state.data_ptr(), gt.data_ptr(), fmt, work.data_ptr(),
             self.layout.total_bytes, self.step_index, self.current_lr(), b1, b2, b3, self.eps, self.weight_decay,
             1 if precounted else 0, band[0], band[1], phases,
-            None if ex is None else self._ctypes.addressof(ex), None,
+            None if ex is None else self._ctypes.addressof(ex),
+            None if opts is None else self._ctypes.addressof(opts),
             None if out_img is None else out_img.data_ptr(),
             None if grads_out is None else grads_out.data_ptr(), None if ids_out is None else ids_out.data_ptr(),
             self._report_ptr + 24 * slot, torch.cuda.current_stream(self.device).cuda_stream), "fit_step_band")
 
+    def _issue_sharded(self, gt, fmt, dbg):
+        """GRADS on the band (records of the band from the local parameter copy, tile kernel) |
+        barrier | UPDATE of the shard (sums its rows from every rank's buffer, Adan, new parameters
+        stored into every rank's tensors) | barrier.  The emulation runs each phase for all "ranks"
+        in turn; a phase boundary is then a barrier by construction."""
+        P = self._lib
+        ranks = range(self.world) if self.emulate_world else (self.rank,)
+        precounted = self._precount_valid()             # False: first step, or the parameters were edited
+        if self.own_barrier and not self.emulate_world:
+            self._band_call(gt, fmt, self.bands[self.rank], self._both_phases, precounted, dbg,
+                            self._with_barrier(self._exchange_struct(0, True)))
+            self._counted_for = self._versions()
+            return
+        for ph in (P.FIT_PHASE_GRADS, P.FIT_PHASE_UPDATE):
+            for r in ranks:
+                slot = r if self.emulate_world else 0
+                self._band_call(gt, fmt, self.bands[r], ph, precounted, dbg, self._exchange_struct(slot, True),
+                                self._works[slot])
+            if not self.emulate_world:
+                self._hdl.barrier(channel=0)            # device-side, on the current stream
+        self._counted_for = self._versions()
+
+    def gather_optimizer_state(self):
+        """sharded update: the optimizer state of a Gaussian is current on its owner only (the
+        parameters are current everywhere) -- bring every rank's copy up to date, e.g. before a
+        checkpoint or a switch of the exchange"""
+        if self.exchange != "sharded" or self.emulate_world:
+            return
+        for r, (a, b) in enumerate(self.shards):
+            src = self._dist.get_global_rank(self.group, r) if self.group is not None else r
+            for k in range(4):
+                self._dist.broadcast(self.adan_state[k, a:b], src=src, group=self.group)
+
+    def _recover(self, overflow_step: int) -> str:
+        if self.exchange != "sharded":
+            return super()._recover(overflow_step)
+        # a tile outgrew its slots (every rank saw the flag): go on with tile ranges, which only the
+        # replicated update has.  EVERY rank must get here (read the loss on all ranks).
+        self.gather_optimizer_state()
+        self.exchange = "peer"
+        msg = super()._recover(overflow_step)
+        lay = self.layout
+        self._grads = self.work[lay.off_grads:lay.off_grads + self.n * 48].view(torch.float32)
+        self._xbuf.zero_()
+        if not self.emulate_world:
+            torch.cuda.current_stream(self.device).synchronize()
+            self._hdl.barrier(channel=0)
+        return msg + " (sharded update -> replicated update over peer memory)"
+
     def _issue(self, gt, fmt, **dbg):
         self.step_index += 1
         G, U = self._lib.FIT_PHASE_GRADS, self._lib.FIT_PHASE_UPDATE
+        if self.exchange == "sharded":
+            return self._issue_sharded(gt, fmt, dbg)
         if self.emulate_world:
             for r, band in enumerate(self.bands):        # every "rank" adds into its (or the one) gradient buffer
                 self._band_call(gt, fmt, band, G, False, dbg, self._exchange_struct(r, False))
@@ -698,7 +822,10 @@ class SpatialFrameFit(FusedFrameFit):
             self._counted_for = None                     # the pre-count covered band 0 only
             return
         band = self.bands[self.rank]
-        if self.exchange in ("peer", "nvls"):
+        if self.exchange in ("peer", "nvls") and self.own_barrier:
+            self._band_call(gt, fmt, band, G | U, self._precount_valid(), dbg,
+                            self._with_barrier(self._exchange_struct(0, True)))
+        elif self.exchange in ("peer", "nvls"):
             self._band_call(gt, fmt, band, G, self._precount_valid(), dbg, self._exchange_struct(0, False))
             self._hdl.barrier(channel=0)                 # device-side, on the current stream: all bands are in
             self._band_call(gt, fmt, band, U, False, dbg, self._exchange_struct(0, True))

@@ -265,6 +265,40 @@ typedef struct {
                                * kernel sums the rows with multimem.ld_reduce -- the switch adds the
                                * ranks' copies and returns one row, so a rank reads n*48 bytes
                                * whatever the world size.  peers / num_peers are then ignored. */
+    /* ---- sharded update (shard_end > shard_begin; needs tile slots and `peers`) ------------------
+     * The replicated update does not scale: every rank reads every rank's rows and redoes the
+     * per-Gaussian work of the whole model.  Here rank r owns Gaussians [shard_begin, shard_end):
+     * its UPDATE phase reduces only those rows (a reduce-scatter fused into the kernel), runs Adan
+     * on them (the optimizer state of a Gaussian lives on its owner only), and stores the new
+     * parameters into EVERY rank's parameter tensors (an all-gather fused into the kernel: plain
+     * NVLink stores, 32 bytes per Gaussian and peer).  After a second barrier the next GRADS phase
+     * scatters the records of its own tile-row band from its now complete local copy.
+     * Two cross-rank barriers per step (after GRADS, after UPDATE), issued by the caller.
+     *   xyz_peers / chol_peers / feat_peers   DEVICE arrays of num_peers pointers: rank q's
+     *                    xyz_raw / chol_raw / features tensors (this rank's own included)
+     *   status_peers     DEVICE array of num_peers pointers: rank q's status words (its work +
+     *                    layout.off_status): a tile that outgrows its slots is flagged on every
+     *                    rank, so that all of them stop at the same step */
+    int shard_begin, shard_end;
+    float* const* xyz_peers;
+    float* const* chol_peers;
+    float* const* feat_peers;
+    int32_t* const* status_peers;
+    /* ---- cross-rank barrier issued by the library (optional; any peer exchange) -------------------
+     * With `barrier_pads` set and both phases in one call, the barrier between GRADS and UPDATE (and,
+     * for a sharded update, the one after UPDATE) is a one-warp kernel of this library on the same
+     * stream: the whole step is then ONE host call, which matters once a step is down to ~100 us.
+     *   barrier_pads   DEVICE array of num_peers pointers: rank q's pad, uint32[num_peers] in peer-mapped
+     *                  memory, zero before the first step.  Barrier number e: rank r stores e into
+     *                  pad_q[r] of every q (release, system scope), then waits until its own pad holds
+     *                  >= e in every slot (acquire).  Epochs only grow, so nothing is ever reset.
+     *   rank           this rank's index into the peer arrays
+     *   barrier_epoch  number of the first barrier of this call (the caller counts: 1, 2, ... -- every
+     *                  rank must issue the same sequence of calls); a sharded step uses two
+     * A rank that waits longer than 10 s traps (a peer died): an error, not a hang. */
+    uint32_t* const* barrier_pads;
+    int rank;
+    uint32_t barrier_epoch;
 } gs2d_grad_exchange;
 /* Optional extras of a step: the learnable colour weight and the optimizer bookkeeping that the
  * reference's prune / add control needs (GaussianSplats_Represent.py:31-36 rgb_W, :62-67

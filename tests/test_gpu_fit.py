@@ -417,7 +417,7 @@ def test_fit_stream_equals_resident_loop(fmt, lag, prefetch):
     assert a.step_index == K
 
 
-@pytest.mark.parametrize("exchange", ["nccl", "peer"])
+@pytest.mark.parametrize("exchange", ["nccl", "peer", "sharded"])
 @pytest.mark.parametrize("H,W,n,world", [(256, 256, 10_000, 2), (200, 328, 3_000, 3), (1080, 1920, 50_000, 4)])
 def test_tile_row_bands_sum_to_the_whole_frame(H, W, n, world, exchange):
     """spatial mode on ONE GPU: every band's gradients (and loss) added into the same buffer in
@@ -426,7 +426,9 @@ def test_tile_row_bands_sum_to_the_whole_frame(H, W, n, world, exchange):
     from gsvc_b200 import synth
     init, gt, full = _setup(H, W, n, seed=17)
     # "nccl": all bands add into one buffer (what the all-reduce would produce); "peer": one buffer
-    # per emulated rank, summed in rank order inside the update kernel (the NVLink exchange path)
+    # per emulated rank, summed in rank order inside the update kernel (the NVLink exchange path);
+    # "sharded": as "peer", but rank r updates only its share of the Gaussians and writes their next
+    # records into the tile slots of the rank that owns each tile row (one workspace per rank)
     banded = SpatialFrameFit(H, W, n, cuda, init=init, emulate_world=world, exchange=exchange)
     gtd = gt.to(cuda)
     ga = torch.empty((n, 8), device=cuda)
