@@ -17,6 +17,7 @@ from typing import Any
 
 import torch
 
+from .options import options
 from .project_gaussians_2d import project_gaussians_2d
 from .project_gaussians_2d_scale_rot import project_gaussians_2d_scale_rot
 from .rasterize_sum import rasterize_gaussians_sum
@@ -49,6 +50,7 @@ __all__ = [
     "GetTileBinEdges",
     "MapGaussiansToIntersects",
     "install_as_gsplat",
+    "options",
 ]
 
 

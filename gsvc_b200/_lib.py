@@ -60,7 +60,7 @@ class FitOptions(Structure):
     """mirror of gs2d_fit_options (include/gs2d.h)"""
 
     _fields_ = [("rgb_w", c_void_p), ("adan_state_w", c_void_p), ("rgb_w_grad_out", c_void_p), ("adan_step", c_int),
-                ("adan_fresh", c_int), ("skip_update", c_int), ("slots", c_int)]
+                ("adan_fresh", c_int), ("skip_update", c_int), ("slots", c_int), ("analytic_grad", c_int)]
 
 
 class QuantizedFrame(Structure):
@@ -86,6 +86,8 @@ _SIGNATURES = {
     "gs2d_project_scalerot_fwd": (c_int, [c_int, _P, _P, _P, c_int, c_int, c_int, c_int, c_float, _P, _P, _P, _P, _P, _P]),
     "gs2d_project_chol_bwd": (c_int, [c_int, _P, c_int, c_int, _P, _P, _P, c_int, _P, c_int, _P, _P, _P, _P]),
     "gs2d_project_scalerot_bwd": (c_int, [c_int, _P, _P, c_int, c_int, _P, _P, _P, c_int, _P, c_int, _P, _P, _P, _P, _P]),
+    "gs2d_project_chol_bwd_analytic": (c_int, [c_int, _P, c_int, c_int, _P, _P, _P, c_int, _P, c_int, _P, _P, _P, _P]),
+    "gs2d_project_scalerot_bwd_analytic": (c_int, [c_int, _P, _P, c_int, c_int, _P, _P, _P, c_int, _P, c_int, _P, _P, _P, _P, _P]),
     "gs2d_cov2d_bounds": (c_int, [c_int, _P, _P, _P, _P]),
     "gs2d_scan_scratch_bytes": (c_size_t, [c_int]),
     "gs2d_cumsum_tiles_hit": (c_int, [c_int, _P, _P, _P, _P, _P, c_size_t, _P]),
@@ -99,6 +101,8 @@ _SIGNATURES = {
     "gs2d_rasterize_sum_fwd_binned": (c_int, [c_int, c_int, _P, _P, _P, _P, _P, _P, c_int, c_int, _P, _P, _P, _P, c_size_t, _P]),
     "gs2d_rasterize_sum_bwd": (c_int, [c_int, c_int, c_int, c_int, _P, c_size_t, _P, _P, _P, _P]),
     "gs2d_rasterize_sum_bwd_binned": (c_int, [c_int, c_int, _P, _P, _P, _P, _P, _P, c_int, c_int, _P, _P, _P, _P, c_size_t, _P]),
+    "gs2d_rasterize_sum_nd_fwd": (c_int, [c_int, c_int, _P, _P, _P, _P, _P, _P, _P, c_int, c_int, c_int, c_int, _P, c_size_t, _P, _P, _P, _P, _P]),
+    "gs2d_rasterize_sum_nd_bwd": (c_int, [c_int, c_int, c_int, c_int, c_int, c_int, _P, c_size_t, _P, _P, _P, _P, _P, _P]),
     "gs2d_fit_layout_for": (c_int, [c_int, c_int, c_int, c_int, POINTER(FitLayout)]),
     "gs2d_fit_init": (c_int, [c_int, c_int, c_int, c_int, _P, c_size_t, _P, _P]),
     "gs2d_fit_step": (c_int, [c_int, c_int, c_int, c_int, _P, _P, _P, _P, _P, c_int, _P, c_size_t, c_int,

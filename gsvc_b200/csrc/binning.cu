@@ -403,7 +403,9 @@ k_edges_pack(const int32_t* __restrict__ n_dev, int n_static, const uint32_t* __
     const float2 xy = reinterpret_cast<const float2*>(xys)[g];
     const float cx = conics[3 * g], cy = conics[3 * g + 1], cz = conics[3 * g + 2];
     const float o = opac[g];
-    const float r = colors[3 * g], gg = colors[3 * g + 1], b = colors[3 * g + 2];
+    // colors == nullptr: the N-channel rasteriser reads its colours by Gaussian id instead
+    const float r = colors ? colors[3 * g] : 0.f, gg = colors ? colors[3 * g + 1] : 0.f,
+                b = colors ? colors[3 * g + 2] : 0.f;
     const int ox = (int)(cur % (uint32_t)tx) * GS2D_TILE, oy = (int)(cur / (uint32_t)tx) * GS2D_TILE;
     const uint32_t rect = pair_rect(xy.x, xy.y, o, cx, cy, cz, ox, oy, W, H);
     packed[3 * (size_t)i + 0] = make_float4(xy.x, xy.y, cx, cy);
@@ -439,7 +441,8 @@ k_pack_binned(int num_intersects, const int32_t* __restrict__ ids_sorted, const 
         packed[3 * (size_t)i + 0] = make_float4(xy.x, xy.y, cx, cy);
         packed[3 * (size_t)i + 1] = make_float4(cz, o, __uint_as_float(rect), __int_as_float(g));
         packed[3 * (size_t)i + 2] =
-            make_float4(colors[3 * g], colors[3 * g + 1], colors[3 * g + 2], __uint_as_float((uint32_t)t));
+            colors ? make_float4(colors[3 * g], colors[3 * g + 1], colors[3 * g + 2], __uint_as_float((uint32_t)t))
+                   : make_float4(0.f, 0.f, 0.f, __uint_as_float((uint32_t)t));
     }
 }
 

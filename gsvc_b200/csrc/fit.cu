@@ -774,6 +774,7 @@ struct AdanHyper {
     float eps;
     float decay_div;        // 1 + lr * weight_decay
     int first;              // t == 1: previous gradient := gradient
+    float offdiag;          // 2: the reference's projection backward; 1: analytic gradient
 };
 
 __device__ __forceinline__ float adan_one(float p, float g, float& m, float& nn, float& d, float& prev,
@@ -921,7 +922,7 @@ k_fit_update(int n, float* __restrict__ xyz_raw, float* __restrict__ chol_raw, f
         }
         if (p.ok && (int)p.radius > 0) {   // backward2d.cu:23-25
             const float3 vc = conic_vjp(p.conic, make_float3(g0.z, g0.w, g1.x));
-            const float3 vl = chol_vjp(L.x, L.y, L.z, vc);
+            const float3 vl = chol_vjp(L.x, L.y, L.z, vc, h.offdiag);
             const float vmx = g0.x * half_w, vmy = g0.y * half_h;            // backward2d.cu:48-49
             g[0] = vmx * (1.f - m.x * m.x);                                   // d tanh
             g[1] = vmy * (1.f - m.y * m.y);
@@ -1215,7 +1216,7 @@ int gs2d_fit_step_band(int n, int cap, int img_h, int img_w, float* xyz_raw, flo
     }
     const bool sharded = rt.R > 0;
     float* rgb_w = nullptr; float* adan_w = nullptr; float* rgb_w_grad_out = nullptr;
-    int adan_step = step, adan_fresh = step == 1, skip_update = 0, slots = 0;
+    int adan_step = step, adan_fresh = step == 1, skip_update = 0, slots = 0, analytic = 0;
     if (options) {
         slots = options->slots != 0;
         GS2D_REQUIRE(!slots || (long long)cap >= (long long)L.tiles * GS2D_MAX_PER_TILE,
@@ -1226,6 +1227,7 @@ int gs2d_fit_step_band(int n, int cap, int img_h, int img_w, float* xyz_raw, flo
         rgb_w = options->rgb_w; adan_w = options->adan_state_w; rgb_w_grad_out = options->rgb_w_grad_out;
         if (options->adan_step > 0) { adan_step = options->adan_step; adan_fresh = options->adan_fresh != 0; }
         skip_update = options->skip_update != 0;
+        analytic = options->analytic_grad != 0;
     }
     GS2D_REQUIRE(!sharded || (slots && rgb_w == nullptr && !skip_update),
                  "fit_step: a sharded update needs tile slots (and has no prune / add control)");
@@ -1293,6 +1295,7 @@ int gs2d_fit_step_band(int n, int cap, int img_h, int img_w, float* xyz_raw, flo
         h.eps = eps;
         h.decay_div = 1.f + lr * weight_decay;
         h.first = adan_fresh;
+        h.offdiag = analytic ? 1.f : 2.f;
         ProfScope ps_(GS2D_STAGE_ADAN, s);
         GS2D_CHECK_CUDA(launch_pdl(k_fit_update, dim3(div_up(shard_end - shard_begin, kFitThreads)), dim3(kFitThreads), s,
             n, xyz_raw, chol_raw, features, adan_state, grads, half_w, half_h, tx, ty, h, status,

@@ -80,7 +80,7 @@ __global__ void __launch_bounds__(kProjThreads)
 k_project_chol_bwd(int n, const float* __restrict__ L, float half_w, float half_h, const int32_t* __restrict__ radii,
                    const float* __restrict__ conics, const float* __restrict__ v_xy, int ld_xy,
                    const float* __restrict__ v_conic, int ld_conic, float* __restrict__ v_cov2d,
-                   float* __restrict__ v_mean2d, float* __restrict__ v_L) {
+                   float* __restrict__ v_mean2d, float* __restrict__ v_L, float offdiag) {
     const int i = blockIdx.x * kProjThreads + threadIdx.x;
     if (i >= n) return;
     float3 vc = make_float3(0.f, 0.f, 0.f), vl = make_float3(0.f, 0.f, 0.f);
@@ -90,8 +90,8 @@ k_project_chol_bwd(int n, const float* __restrict__ L, float half_w, float half_
         const float* gp = v_conic + (size_t)i * ld_conic;
         vc = conic_vjp(x, make_float3(gp[0], gp[1], gp[2]));
         const float l11 = L[3 * i], l21 = L[3 * i + 1], l22 = L[3 * i + 2];
-        // reference formula (backward2d.cu:39-41), off-diagonal counted twice
-        vl = chol_vjp(l11, l21, l22, vc);
+        // reference formula (backward2d.cu:39-41): offdiag = 2, off-diagonal counted twice
+        vl = chol_vjp(l11, l21, l22, vc, offdiag);
         const float* xp = v_xy + (size_t)i * ld_xy;
         vm = make_float2(xp[0] * half_w, xp[1] * half_h);   // backward2d.cu:48-49
     }
@@ -105,7 +105,7 @@ k_project_scalerot_bwd(int n, const float* __restrict__ scales, const float* __r
                        float half_h, const int32_t* __restrict__ radii, const float* __restrict__ conics,
                        const float* __restrict__ v_xy, int ld_xy, const float* __restrict__ v_conic, int ld_conic,
                        float* __restrict__ v_cov2d, float* __restrict__ v_mean2d, float* __restrict__ v_scale,
-                       float* __restrict__ v_rot) {
+                       float* __restrict__ v_rot, float offdiag) {
     const int i = blockIdx.x * kProjThreads + threadIdx.x;
     if (i >= n) return;
     float3 vc = make_float3(0.f, 0.f, 0.f);
@@ -131,10 +131,10 @@ k_project_scalerot_bwd(int n, const float* __restrict__ scales, const float* __r
         const float a10 = -c * sxx * c - sn * syy * sn;
         const float a11 = c * sxx * sn - sn * syy * c;
         const float t00 = 2.f * a00, t01 = a01 + a10, t11 = 2.f * a11;
-        // backward2d.cu:103-105 (factor 2 on G_12)
-        vs.x = vc.x * gx00 + 2.f * vc.y * gx01 + vc.z * gx11;
-        vs.y = vc.x * gy00 + 2.f * vc.y * gy01 + vc.z * gy11;
-        vr = vc.x * t00 + 2.f * vc.y * t01 + vc.z * t11;
+        // backward2d.cu:103-105: offdiag = 2 (factor 2 on G_12); 1 = analytic gradient
+        vs.x = vc.x * gx00 + offdiag * vc.y * gx01 + vc.z * gx11;
+        vs.y = vc.x * gy00 + offdiag * vc.y * gy01 + vc.z * gy11;
+        vr = vc.x * t00 + offdiag * vc.y * t01 + vc.z * t11;
         const float* xp = v_xy + (size_t)i * ld_xy;
         vm = make_float2(xp[0] * half_w, xp[1] * half_h);
     }
@@ -192,18 +192,48 @@ int gs2d_project_scalerot_fwd(int n, const float* means2d, const float* scales, 
     return GS2D_OK;
 }
 
-int gs2d_project_chol_bwd(int n, const float* L, int img_h, int img_w, const int32_t* radii, const float* conics,
-                          const float* v_xy, int ld_v_xy, const float* v_conic, int ld_v_conic, float* v_cov2d,
-                          float* v_mean2d, float* v_L, gs2d_stream_t stream) {
+static int project_chol_bwd(int n, const float* L, int img_h, int img_w, const int32_t* radii, const float* conics,
+                            const float* v_xy, int ld_v_xy, const float* v_conic, int ld_v_conic, float* v_cov2d,
+                            float* v_mean2d, float* v_L, float offdiag, gs2d_stream_t stream) {
     GS2D_REQUIRE(n >= 0 && ld_v_xy >= 2 && ld_v_conic >= 3, "project_chol_bwd: bad sizes");
     if (n == 0) return GS2D_OK;
     {
         ProfScope ps_(GS2D_STAGE_PROJECT_BWD, (cudaStream_t)stream);
         k_project_chol_bwd<<<div_up(n, kProjThreads), kProjThreads, 0, (cudaStream_t)stream>>>(
         n, L, 0.5f * (float)(unsigned)img_w, 0.5f * (float)(unsigned)img_h, radii, conics, v_xy, ld_v_xy, v_conic,
-        ld_v_conic, v_cov2d, v_mean2d, v_L);
+        ld_v_conic, v_cov2d, v_mean2d, v_L, offdiag);
     }
     GS2D_CHECK_LAUNCH("project_chol_bwd");
+    return GS2D_OK;
+}
+
+int gs2d_project_chol_bwd(int n, const float* L, int img_h, int img_w, const int32_t* radii, const float* conics,
+                          const float* v_xy, int ld_v_xy, const float* v_conic, int ld_v_conic, float* v_cov2d,
+                          float* v_mean2d, float* v_L, gs2d_stream_t stream) {
+    return project_chol_bwd(n, L, img_h, img_w, radii, conics, v_xy, ld_v_xy, v_conic, ld_v_conic, v_cov2d, v_mean2d,
+                            v_L, 2.f, stream);
+}
+
+int gs2d_project_chol_bwd_analytic(int n, const float* L, int img_h, int img_w, const int32_t* radii,
+                                   const float* conics, const float* v_xy, int ld_v_xy, const float* v_conic,
+                                   int ld_v_conic, float* v_cov2d, float* v_mean2d, float* v_L, gs2d_stream_t stream) {
+    return project_chol_bwd(n, L, img_h, img_w, radii, conics, v_xy, ld_v_xy, v_conic, ld_v_conic, v_cov2d, v_mean2d,
+                            v_L, 1.f, stream);
+}
+
+static int project_scalerot_bwd(int n, const float* scales, const float* rot, int img_h, int img_w,
+                                const int32_t* radii, const float* conics, const float* v_xy, int ld_v_xy,
+                                const float* v_conic, int ld_v_conic, float* v_cov2d, float* v_mean2d, float* v_scale,
+                                float* v_rot, float offdiag, gs2d_stream_t stream) {
+    GS2D_REQUIRE(n >= 0 && ld_v_xy >= 2 && ld_v_conic >= 3, "project_scalerot_bwd: bad sizes");
+    if (n == 0) return GS2D_OK;
+    {
+        ProfScope ps_(GS2D_STAGE_PROJECT_BWD, (cudaStream_t)stream);
+        k_project_scalerot_bwd<<<div_up(n, kProjThreads), kProjThreads, 0, (cudaStream_t)stream>>>(
+        n, scales, rot, 0.5f * (float)(unsigned)img_w, 0.5f * (float)(unsigned)img_h, radii, conics, v_xy, ld_v_xy,
+        v_conic, ld_v_conic, v_cov2d, v_mean2d, v_scale, v_rot, offdiag);
+    }
+    GS2D_CHECK_LAUNCH("project_scalerot_bwd");
     return GS2D_OK;
 }
 
@@ -211,16 +241,16 @@ int gs2d_project_scalerot_bwd(int n, const float* scales, const float* rot, int 
                               const int32_t* radii, const float* conics, const float* v_xy, int ld_v_xy,
                               const float* v_conic, int ld_v_conic, float* v_cov2d, float* v_mean2d, float* v_scale,
                               float* v_rot, gs2d_stream_t stream) {
-    GS2D_REQUIRE(n >= 0 && ld_v_xy >= 2 && ld_v_conic >= 3, "project_scalerot_bwd: bad sizes");
-    if (n == 0) return GS2D_OK;
-    {
-        ProfScope ps_(GS2D_STAGE_PROJECT_BWD, (cudaStream_t)stream);
-        k_project_scalerot_bwd<<<div_up(n, kProjThreads), kProjThreads, 0, (cudaStream_t)stream>>>(
-        n, scales, rot, 0.5f * (float)(unsigned)img_w, 0.5f * (float)(unsigned)img_h, radii, conics, v_xy, ld_v_xy,
-        v_conic, ld_v_conic, v_cov2d, v_mean2d, v_scale, v_rot);
-    }
-    GS2D_CHECK_LAUNCH("project_scalerot_bwd");
-    return GS2D_OK;
+    return project_scalerot_bwd(n, scales, rot, img_h, img_w, radii, conics, v_xy, ld_v_xy, v_conic, ld_v_conic,
+                                v_cov2d, v_mean2d, v_scale, v_rot, 2.f, stream);
+}
+
+int gs2d_project_scalerot_bwd_analytic(int n, const float* scales, const float* rot, int img_h, int img_w,
+                                       const int32_t* radii, const float* conics, const float* v_xy, int ld_v_xy,
+                                       const float* v_conic, int ld_v_conic, float* v_cov2d, float* v_mean2d,
+                                       float* v_scale, float* v_rot, gs2d_stream_t stream) {
+    return project_scalerot_bwd(n, scales, rot, img_h, img_w, radii, conics, v_xy, ld_v_xy, v_conic, ld_v_conic,
+                                v_cov2d, v_mean2d, v_scale, v_rot, 1.f, stream);
 }
 
 int gs2d_cov2d_bounds(int n, const float* cov2d, float* conics, float* radii, gs2d_stream_t stream) {

@@ -178,6 +178,193 @@ k_raster_bwd(const int32_t* __restrict__ n_dev, int n_static, int W, int tx, con
     }
 }
 
+
+// ------------------------------------------------------------------------------------------
+// N-channel / untruncated variant (no bound counterpart in the reference: its
+// nd_rasterize_forward_sum forward.cu:630-710 and nd_rasterize_backward_sum_kernel
+// backward.cu:864-978 exist but are never launched).
+//
+// Same tile / record layout as above, but (1) the colours of a batch are staged by Gaussian id
+// into shared memory as [record][channel] rows next to the geometry records, (2) a tile is
+// rendered in batches of 256 records up to `max_tile` (INT_MAX = every Gaussian of the tile, as
+// the reference's N-channel kernel does; 256 = the 3-channel kernel's truncation),
+// (3) colour gradients go to their own [n][C] tensor.  The pixel test and the accumulation order
+// are the 3-channel kernel's (the reference's N-channel SASS has the identical sigma / EX2 /
+// FFMA sequence), so with C = 3 and max_tile = 256 the image is bit-identical to k_raster_fwd.
+// final_idx keeps the 3-channel meaning (last sorted index that passed, 0 when none).
+// ------------------------------------------------------------------------------------------
+template <int CMAX>
+__global__ void __launch_bounds__(GS2D_TILE_PIX)
+k_raster_nd_fwd(int W, int H, int tx, int C, int max_tile, const int32_t* __restrict__ tile_bins,
+                const float4* __restrict__ packed, const float* __restrict__ colors, float* __restrict__ out_img,
+                int32_t* __restrict__ final_idx) {
+    extern __shared__ float4 nd_smem[];
+    float4* sq = nd_smem;                                                    // [256][3]
+    float* scol = reinterpret_cast<float*>(nd_smem + GS2D_MAX_PER_TILE * 3);   // [256][C]
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int t = blockIdx.y * tx + blockIdx.x;
+    const int2 range = reinterpret_cast<const int2*>(tile_bins)[t];
+    const int lo = range.x;
+    const int cnt = max(0, min(range.y - range.x, max_tile));
+
+    const int lx = tid & 15, ly = tid >> 4;
+    const int px_i = blockIdx.x * GS2D_TILE + lx, py_i = blockIdx.y * GS2D_TILE + ly;
+    const bool inside = px_i < W && py_i < H;
+    const float px = (float)px_i, py = (float)py_i;
+    const int row_lo = 2 * warp, row_hi = 2 * warp + 1;
+
+    float acc[CMAX];
+#pragma unroll
+    for (int c = 0; c < CMAX; ++c) acc[c] = 0.f;
+    int cur_idx = 0;
+    for (int base = 0; base < cnt; base += GS2D_MAX_PER_TILE) {
+        const int nb = min(GS2D_MAX_PER_TILE, cnt - base);
+        if (base) __syncthreads();   // everyone is done with the previous batch
+        const float4* src = packed + 3 * (size_t)(lo + base);
+        for (int i = tid; i < nb * 3; i += GS2D_TILE_PIX) cp_async16(&sq[i], src + i);
+        cp_async_wait_all();
+        __syncthreads();
+        for (int i = tid; i < nb * C; i += GS2D_TILE_PIX) {
+            const int k = i / C;
+            const int g = __float_as_int(sq[3 * k + 1].w);
+            scol[i] = colors[(size_t)g * C + (i - k * C)];
+        }
+        __syncthreads();
+        for (int c0 = 0; c0 < nb; c0 += 32) {
+            const int k_lane = c0 + lane;
+            bool touch = false;
+            if (k_lane < nb) {
+                const uint32_t rect = __float_as_uint(sq[3 * k_lane + 1].z);
+                const int y0 = (rect >> 16) & 255, y1 = rect >> 24;
+                touch = (y1 >= row_lo) && (y0 <= row_hi);
+            }
+            unsigned m = __ballot_sync(0xffffffffu, touch);
+            while (m) {
+                const int k = c0 + __ffs(m) - 1;
+                m &= m - 1;
+                const float4 q0 = sq[3 * k];
+                const float4 q1 = sq[3 * k + 1];
+                const float dx = subf(q0.x, px), dy = subf(q0.y, py);
+                const float sigma = gauss_sigma(dx, dy, q0.z, q0.w, q1.x);
+                const float alpha = minf(mulf(q1.y, gauss_vis(sigma)), 1.f);
+                if (inside && gauss_pass(sigma, alpha)) {
+                    const float* col = scol + k * C;
+#pragma unroll
+                    for (int c = 0; c < CMAX; ++c)
+                        if (c < C) acc[c] = fmaf_(alpha, col[c], acc[c]);
+                    cur_idx = lo + base + k;
+                }
+            }
+        }
+    }
+    if (inside) {
+        const size_t p = (size_t)py_i * W + px_i;
+#pragma unroll
+        for (int c = 0; c < CMAX; ++c)
+            if (c < C) out_img[p * C + c] = acc[c];
+        if (final_idx) final_idx[p] = cur_idx;
+    }
+}
+
+// one warp per sorted (tile, Gaussian) pair, as k_raster_bwd; the C colour sums are reduced in
+// groups of eight with the same transposed butterfly.
+template <int CMAX>
+__global__ void __launch_bounds__(kBwdThreads)
+k_raster_nd_bwd(const int32_t* __restrict__ n_dev, int n_static, int W, int tx, int C, int max_tile,
+                const int32_t* __restrict__ tile_bins, const float4* __restrict__ packed,
+                const float* __restrict__ colors, const int32_t* __restrict__ final_idx,
+                const float* __restrict__ v_out, float* __restrict__ grads, float* __restrict__ v_colors) {
+    const int n = n_dev ? *n_dev : n_static;
+    const int lane = threadIdx.x & 31;
+    const int i = blockIdx.x * (kBwdThreads / 32) + (threadIdx.x >> 5);
+    if (i >= n) return;
+    const float4 q1 = packed[3 * (size_t)i + 1];
+    const uint32_t rect = __float_as_uint(q1.z);
+    const int rx0 = rect & 255, rx1 = (rect >> 8) & 255, ry0 = (rect >> 16) & 255, ry1 = rect >> 24;
+    if (ry1 < ry0) return;
+    const int t = (int)__float_as_uint(packed[3 * (size_t)i + 2].w);
+    if (i - tile_bins[2 * t] >= max_tile) return;
+    const float4 q0 = packed[3 * (size_t)i];
+    const float gx = q0.x, gy = q0.y, cx = q0.z, cy = q0.w, cz = q1.x, opac = q1.y;
+    const int g = __float_as_int(q1.w);
+    float col[CMAX], vcol[CMAX];
+#pragma unroll
+    for (int c = 0; c < CMAX; ++c) {
+        col[c] = c < C ? colors[(size_t)g * C + c] : 0.f;
+        vcol[c] = 0.f;
+    }
+    const int ox = (t % tx) * GS2D_TILE, oy = (t / tx) * GS2D_TILE;
+    const int w = rx1 - rx0 + 1, area = w * (ry1 - ry0 + 1);
+    const float inv_w = 1.f / (float)w;
+
+    float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};   // v_xy 2 | v_conic 3 | v_opacity | - | -
+    for (int p = lane; p < area; p += 32) {
+        const int ry = (int)(((float)p + 0.5f) * inv_w);
+        const int px_i = ox + rx0 + (p - ry * w), py_i = oy + ry0 + ry;
+        const size_t pid = (size_t)py_i * W + px_i;
+        if (i > final_idx[pid]) continue;
+        const float dx = subf(gx, (float)px_i), dy = subf(gy, (float)py_i);
+        const float sigma = gauss_sigma(dx, dy, cx, cy, cz);
+        const float vis = gauss_vis(sigma);
+        const float alpha = minf(mulf(opac, vis), 1.f);
+        if (!gauss_pass(sigma, alpha)) continue;
+        const float* vo = v_out + pid * C;
+        float v_alpha = 0.f;
+#pragma unroll
+        for (int c = 0; c < CMAX; ++c) {
+            if (c < C) {
+                const float v = vo[c];
+                v_alpha += col[c] * v;
+                vcol[c] += alpha * v;
+            }
+        }
+        const float v_sigma = -opac * vis * v_alpha;
+        acc[0] += v_sigma * (cx * dx + cy * dy);
+        acc[1] += v_sigma * (cy * dx + cz * dy);
+        const float hs = 0.5f * v_sigma;
+        acc[2] += hs * dx * dx;
+        acc[3] += hs * dx * dy;
+        acc[4] += hs * dy * dy;
+        acc[5] += vis * v_alpha;
+    }
+    const float tot = warp_reduce8_transposed(acc, lane);
+    float* row = grads + (size_t)g * 12;
+    if ((lane & 3) == 0 && tot != 0.f) {
+        const int j = lane >> 2;
+        if (j < 5) atomicAdd(row + j, tot);
+        else if (j == 5) atomicAdd(row + 8, tot);
+    }
+#pragma unroll
+    for (int c8 = 0; c8 < CMAX; c8 += 8) {
+        if (c8 < C) {
+            float part[8];
+#pragma unroll
+            for (int k = 0; k < 8; ++k) part[k] = c8 + k < CMAX ? vcol[c8 + k] : 0.f;
+            const float ct = warp_reduce8_transposed(part, lane);
+            const int c = c8 + (lane >> 2);
+            if ((lane & 3) == 0 && c < C && ct != 0.f) atomicAdd(v_colors + (size_t)g * C + c, ct);
+        }
+    }
+}
+
+constexpr int kMaxChannels = 32;
+static size_t nd_smem_bytes(int C) { return (size_t)GS2D_MAX_PER_TILE * (3 * sizeof(float4) + (size_t)C * sizeof(float)); }
+
+template <int CMAX>
+static cudaError_t launch_nd_fwd(dim3 grid, int W, int H, int tx, int C, int max_tile, const int32_t* tile_bins,
+                                 const float4* packed, const float* colors, float* out_img, int32_t* final_idx,
+                                 cudaStream_t s) {
+    const size_t smem = nd_smem_bytes(C);
+    if (smem > 48 * 1024) {
+        const cudaError_t e = cudaFuncSetAttribute(k_raster_nd_fwd<CMAX>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                                   (int)nd_smem_bytes(CMAX));
+        if (e != cudaSuccess) return e;
+    }
+    k_raster_nd_fwd<CMAX><<<grid, GS2D_TILE_PIX, smem, s>>>(W, H, tx, C, max_tile, tile_bins, packed, colors, out_img,
+                                                           final_idx);
+    return cudaSuccess;
+}
+
 static size_t align256(size_t v) { return (v + 255) / 256 * 256; }
 
 }  // namespace gs2d
@@ -285,6 +472,75 @@ int gs2d_rasterize_sum_bwd_binned(int n, int num_intersects, const int32_t* ids_
         nullptr, num_intersects, img_w, tx, tile_bins, (const float4*)scratch, final_idx, v_out, grads);
     }
     GS2D_CHECK_LAUNCH("raster_bwd_binned");
+    return GS2D_OK;
+}
+
+int gs2d_rasterize_sum_nd_fwd(int n, int channels, const float* xys, const float* depths, const int32_t* radii,
+                              const float* conics, const int32_t* num_tiles_hit, const float* colors,
+                              const float* opacities, int img_h, int img_w, int cap, int max_per_tile, void* state,
+                              size_t state_bytes, float* out_img, int32_t* final_idx, int32_t* status_host,
+                              gs2d_event_t scan_done, gs2d_stream_t stream) {
+    GS2D_REQUIRE(n >= 0 && img_h > 0 && img_w > 0 && cap > 0 && max_per_tile >= 0, "rasterize_sum_nd_fwd: bad sizes");
+    GS2D_REQUIRE(channels >= 1 && channels <= kMaxChannels, "rasterize_sum_nd_fwd: 1..32 channels are supported");
+    const int tx = div_up(img_w, GS2D_TILE), ty = div_up(img_h, GS2D_TILE);
+    StateOffsets so;
+    int rc = compute_state_offsets(n, cap, tx, ty, &so);
+    if (rc != GS2D_OK) return rc;
+    GS2D_REQUIRE(state_bytes >= so.pub.total_bytes, "rasterize_sum_nd_fwd: state buffer too small");
+    GS2D_REQUIRE(((uintptr_t)state & 255) == 0, "rasterize_sum_nd_fwd: state buffer must be 256-byte aligned");
+    cudaStream_t s = (cudaStream_t)stream;
+    char* st = (char*)state;
+    rc = launch_bin_and_pack(n, xys, depths, radii, num_tiles_hit, conics, nullptr, opacities, img_h, img_w, cap, so,
+                             st, status_host, (cudaEvent_t)scan_done, s);
+    if (rc != GS2D_OK) return rc;
+    const int max_tile = max_per_tile > 0 ? max_per_tile : 0x7fffffff;
+    const int32_t* bins = (const int32_t*)(st + so.pub.off_tile_bins);
+    const float4* packed = (const float4*)(st + so.pub.off_packed);
+    const dim3 grid(tx, ty);
+    {
+        ProfScope ps_(GS2D_STAGE_RASTER_FWD, s);
+        cudaError_t e;
+        if (channels <= 4) e = launch_nd_fwd<4>(grid, img_w, img_h, tx, channels, max_tile, bins, packed, colors, out_img, final_idx, s);
+        else if (channels <= 8) e = launch_nd_fwd<8>(grid, img_w, img_h, tx, channels, max_tile, bins, packed, colors, out_img, final_idx, s);
+        else if (channels <= 16) e = launch_nd_fwd<16>(grid, img_w, img_h, tx, channels, max_tile, bins, packed, colors, out_img, final_idx, s);
+        else e = launch_nd_fwd<32>(grid, img_w, img_h, tx, channels, max_tile, bins, packed, colors, out_img, final_idx, s);
+        GS2D_CHECK_CUDA(e);
+    }
+    GS2D_CHECK_LAUNCH("raster_nd_fwd");
+    return GS2D_OK;
+}
+
+int gs2d_rasterize_sum_nd_bwd(int n, int channels, int img_h, int img_w, int cap, int max_per_tile, const void* state,
+                              size_t state_bytes, const float* colors, const int32_t* final_idx, const float* v_out,
+                              float* grads, float* v_colors, gs2d_stream_t stream) {
+    GS2D_REQUIRE(n >= 0 && img_h > 0 && img_w > 0 && cap > 0 && max_per_tile >= 0, "rasterize_sum_nd_bwd: bad sizes");
+    GS2D_REQUIRE(channels >= 1 && channels <= kMaxChannels, "rasterize_sum_nd_bwd: 1..32 channels are supported");
+    const int tx = div_up(img_w, GS2D_TILE), ty = div_up(img_h, GS2D_TILE);
+    StateOffsets so;
+    const int rc = compute_state_offsets(n, cap, tx, ty, &so);
+    if (rc != GS2D_OK) return rc;
+    GS2D_REQUIRE(state_bytes >= so.pub.total_bytes, "rasterize_sum_nd_bwd: state buffer too small");
+    cudaStream_t s = (cudaStream_t)stream;
+    const char* st = (const char*)state;
+    if (n == 0) return GS2D_OK;
+    {
+        ProfScope ps_(GS2D_STAGE_MEMSET, s);
+        GS2D_CHECK_CUDA(cudaMemsetAsync(grads, 0, (size_t)n * 12 * sizeof(float), s));
+        GS2D_CHECK_CUDA(cudaMemsetAsync(v_colors, 0, (size_t)n * channels * sizeof(float), s));
+    }
+    const int max_tile = max_per_tile > 0 ? max_per_tile : 0x7fffffff;
+    const int32_t* nd = (const int32_t*)(st + so.pub.off_status) + 3;
+    const int32_t* bins = (const int32_t*)(st + so.pub.off_tile_bins);
+    const float4* packed = (const float4*)(st + so.pub.off_packed);
+    const int blocks = div_up(cap, kBwdThreads / 32);
+    {
+        ProfScope ps_(GS2D_STAGE_RASTER_BWD, s);
+        if (channels <= 4) k_raster_nd_bwd<4><<<blocks, kBwdThreads, 0, s>>>(nd, 0, img_w, tx, channels, max_tile, bins, packed, colors, final_idx, v_out, grads, v_colors);
+        else if (channels <= 8) k_raster_nd_bwd<8><<<blocks, kBwdThreads, 0, s>>>(nd, 0, img_w, tx, channels, max_tile, bins, packed, colors, final_idx, v_out, grads, v_colors);
+        else if (channels <= 16) k_raster_nd_bwd<16><<<blocks, kBwdThreads, 0, s>>>(nd, 0, img_w, tx, channels, max_tile, bins, packed, colors, final_idx, v_out, grads, v_colors);
+        else k_raster_nd_bwd<32><<<blocks, kBwdThreads, 0, s>>>(nd, 0, img_w, tx, channels, max_tile, bins, packed, colors, final_idx, v_out, grads, v_colors);
+    }
+    GS2D_CHECK_LAUNCH("raster_nd_bwd");
     return GS2D_OK;
 }
 

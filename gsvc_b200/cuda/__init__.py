@@ -114,7 +114,7 @@ def _rows(t: torch.Tensor, width: int, name: str):
 
 # --- bindings.cu:902-949 -------------------------------------------------------------------
 def project_gaussians_2d_backward(num_points, means2d, L_elements, img_height, img_width, radii, conics, v_xy,
-                                  v_depth, v_conic):
+                                  v_depth, v_conic, analytic: bool = False):
     _chk(L_elements, "L_elements", _f32)
     _chk(radii, "radii", _i32)
     _chk(conics, "conics", _f32)
@@ -125,7 +125,8 @@ def project_gaussians_2d_backward(num_points, means2d, L_elements, img_height, i
     v_mean2d = torch.empty((num_points, 2), dtype=_f32, device=dev)
     v_L = torch.empty((num_points, 3), dtype=_f32, device=dev)
     with _guard(dev):
-        _lib.check(_lib.load().gs2d_project_chol_bwd(
+        fn = _lib.load().gs2d_project_chol_bwd_analytic if analytic else _lib.load().gs2d_project_chol_bwd
+        _lib.check(fn(
             num_points, _ptr(L_elements), int(img_height), int(img_width), _ptr(radii), _ptr(conics), _ptr(v_xy),
             ld_xy, _ptr(v_conic), ld_conic, _ptr(v_cov2d), _ptr(v_mean2d), _ptr(v_L), _stream(dev)),
             "project_chol_bwd")
@@ -134,7 +135,7 @@ def project_gaussians_2d_backward(num_points, means2d, L_elements, img_height, i
 
 # --- bindings.cu:951-1004 ------------------------------------------------------------------
 def project_gaussians_2d_scale_rot_backward(num_points, means2d, scales2d, rotation, img_height, img_width, radii,
-                                            conics, v_xy, v_depth, v_conic):
+                                            conics, v_xy, v_depth, v_conic, analytic: bool = False):
     _chk(scales2d, "scales2d", _f32)
     _chk(rotation, "rotation", _f32)
     _chk(radii, "radii", _i32)
@@ -147,7 +148,9 @@ def project_gaussians_2d_scale_rot_backward(num_points, means2d, scales2d, rotat
     v_scale = torch.empty((num_points, 2), dtype=_f32, device=dev)
     v_rot = torch.empty((num_points, 1), dtype=_f32, device=dev)
     with _guard(dev):
-        _lib.check(_lib.load().gs2d_project_scalerot_bwd(
+        fn = (_lib.load().gs2d_project_scalerot_bwd_analytic if analytic
+              else _lib.load().gs2d_project_scalerot_bwd)
+        _lib.check(fn(
             num_points, _ptr(scales2d), _ptr(rotation), int(img_height), int(img_width), _ptr(radii), _ptr(conics),
             _ptr(v_xy), ld_xy, _ptr(v_conic), ld_conic, _ptr(v_cov2d), _ptr(v_mean2d), _ptr(v_scale), _ptr(v_rot),
             _stream(dev)), "project_scalerot_bwd")

@@ -162,17 +162,27 @@ class FusedFrameFit(torch.nn.Module):
     the raw uint8 I420 frame [H*3/2,W] of the .yuv file (decoded inside the tile kernel exactly as
     the reference's cv2 loader would)."""
 
-    path_name = "fused C-ABI fit step (scatter-pack, tile kernel fwd+L2+bwd, projection-bwd+Adan+next count/scan): 3 kernels/iter"
+    @property
+    def path_name(self) -> str:
+        if self.slots:
+            return ("fused C-ABI fit step on tile slots: tile kernel (fwd + clamp/L2 + bwd) and update kernel "
+                    "(projection-bwd + Adan + the next step's projection and records), PDL: 2 kernels/iter")
+        return ("fused C-ABI fit step on tile ranges: scatter-pack, tile kernel (fwd + clamp/L2 + bwd), update kernel "
+                "(projection-bwd + Adan + next count/scan): 3 kernels/iter")
 
     def __init__(self, H: int, W: int, num_points: int, device, lr: float = 1e-3, seed: int = 1,
                  init: dict | None = None, betas=(0.98, 0.92, 0.99), eps: float = 1e-8, weight_decay: float = 0.0,
                  cap: int | None = None, lr_step_size: int = 20000, lr_gamma: float = 0.5, isdensity: bool = False,
                  isremoval: bool = False, removal_rate: float = 0.1, max_num_points: int | None = None,
-                 densification_interval: int = 100, plan=None, slots: bool = True):
+                 densification_interval: int = 100, plan=None, slots: bool = True, analytic_grad: bool | None = None):
         """slots: fixed 256-record slots per tile instead of tile ranges (include/gs2d.h,
         gs2d_fit_options.slots): two kernels per iteration instead of three.  The first tile that
-        would need a 257th record switches the model to ranges for good (same results, see _recover)."""
+        would need a 257th record switches the model to ranges for good (same results, see _recover).
+        analytic_grad: the projection backward's analytic gradient instead of the reference's formula
+        (SURVEY Q12 / 8f.4); None = gsvc_b200.options.analytic_projection_grad (default off)."""
         super().__init__()
+        from .options import options as _options
+        self.analytic_grad = bool(_options.analytic_projection_grad if analytic_grad is None else analytic_grad)
         import ctypes
         from . import _lib
         from . import cuda as _C
@@ -268,6 +278,7 @@ class FusedFrameFit(torch.nn.Module):
             o.rgb_w_grad_out = None if w_grad_out is None else w_grad_out.data_ptr()
         o.adan_step, o.adan_fresh, o.skip_update = int(adan_step), int(fresh), int(skip)
         o.slots = int(self.slots)
+        o.analytic_grad = int(self.analytic_grad)
         return o
 
     def _issue(self, gt, fmt, out_img=None, grads_out=None, ids_out=None, w_grad_out=None, stream=None):

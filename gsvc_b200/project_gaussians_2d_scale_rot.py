@@ -8,6 +8,7 @@ from torch import Tensor
 from torch.autograd import Function
 
 from . import cuda as _C
+from .options import options
 
 
 def project_gaussians_2d_scale_rot(means2d: Tensor, scales2d: Tensor, rotation: Tensor, img_height: int,
@@ -32,6 +33,7 @@ class _ProjectGaussians2dScaleRot(Function):
         ctx.img_height = img_height
         ctx.img_width = img_width
         ctx.num_points = num_points
+        ctx.analytic = bool(options.analytic_projection_grad)   # SURVEY 8f.4; default: reference formula
         ctx.save_for_backward(means2d, scales2d, rotation, radii, conics)
         ctx.mark_non_differentiable(radii, num_tiles_hit)
         return xys, depths, radii, conics, num_tiles_hit
@@ -41,5 +43,5 @@ class _ProjectGaussians2dScaleRot(Function):
         means2d, scales2d, rotation, radii, conics = ctx.saved_tensors
         _v_cov2d, v_mean2d, v_scale, v_rot = _C.project_gaussians_2d_scale_rot_backward(
             ctx.num_points, means2d, scales2d, rotation, ctx.img_height, ctx.img_width, radii, conics, v_xys,
-            v_depths, v_conics)
+            v_depths, v_conics, analytic=ctx.analytic)
         return v_mean2d, v_scale, v_rot, None, None, None, None

@@ -18,8 +18,10 @@ from torch.autograd import Function
 
 from . import _lib
 from . import cuda as _C
+from .options import options
 
 _RING = 64
+GS2D_MAX_PER_TILE = 256   # forward.cu:566-614
 _CAP_QUANTUM = 16384
 
 
@@ -117,9 +119,15 @@ class _RasterizeGaussiansSum(Function):
         if BLOCK_H != 16 or BLOCK_W != 16:
             # the reference's binning and shared-memory batch are compile-time 16x16
             raise ValueError("rasterize_gaussians_sum supports only BLOCK_H = BLOCK_W = 16")
-        if colors.shape[-1] != 3:
+        channels = int(colors.shape[-1])
+        if channels != 3 and not options.nd_channels:
             # the reference dispatches other channel counts to an unbound function
-            raise NotImplementedError("rasterize_gaussians_sum supports only 3 colour channels")
+            raise NotImplementedError("rasterize_gaussians_sum supports only 3 colour channels "
+                                      "(gsvc_b200.options.nd_channels = True enables 1..32)")
+        # SURVEY 8f.4 options; the defaults select the reference-exact 3-channel kernels.  The
+        # reference's N-channel kernel has no per-tile limit (forward.cu:664), so neither has ours.
+        max_tile = int(options.max_per_tile) if channels == 3 else 0
+        nd = channels != 3 or max_tile != GS2D_MAX_PER_TILE
         dev = xys.device
         if not xys.is_cuda:
             raise RuntimeError("rasterize_gaussians_sum needs CUDA tensors (there is no CPU path)")
@@ -144,18 +152,26 @@ class _RasterizeGaussiansSum(Function):
             while True:
                 lay = dctx.layout(n, cap, tx, ty)
                 state = torch.empty((lay.total_bytes,), dtype=torch.uint8, device=dev)
-                out_img = torch.empty((H, W, 3), dtype=torch.float32, device=dev)
+                out_img = torch.empty((H, W, channels), dtype=torch.float32, device=dev)
                 final_idx = torch.empty((H, W), dtype=torch.int32, device=dev) if need_grad else None
                 slot = dctx.slot
                 dctx.slot = (slot + 1) % _RING
                 ev = dctx.events[slot]
                 mail = dctx.mail[slot]
-                _lib.check(lib.gs2d_rasterize_sum_fwd(
-                    n, xys.data_ptr(), None if zero_depth else depths.data_ptr(), radii.data_ptr(),
-                    conics.data_ptr(), num_tiles_hit.data_ptr(), colors.data_ptr(), opacity.data_ptr(), H, W, cap,
-                    state.data_ptr(), lay.total_bytes, out_img.data_ptr(),
-                    None if final_idx is None else final_idx.data_ptr(), mail.data_ptr(), ev.cuda_event, stream),
-                    "rasterize_sum_fwd")
+                if nd:
+                    _lib.check(lib.gs2d_rasterize_sum_nd_fwd(
+                        n, channels, xys.data_ptr(), None if zero_depth else depths.data_ptr(), radii.data_ptr(),
+                        conics.data_ptr(), num_tiles_hit.data_ptr(), colors.data_ptr(), opacity.data_ptr(), H, W,
+                        cap, max_tile, state.data_ptr(), lay.total_bytes, out_img.data_ptr(),
+                        None if final_idx is None else final_idx.data_ptr(), mail.data_ptr(), ev.cuda_event,
+                        stream), "rasterize_sum_nd_fwd")
+                else:
+                    _lib.check(lib.gs2d_rasterize_sum_fwd(
+                        n, xys.data_ptr(), None if zero_depth else depths.data_ptr(), radii.data_ptr(),
+                        conics.data_ptr(), num_tiles_hit.data_ptr(), colors.data_ptr(), opacity.data_ptr(), H, W,
+                        cap, state.data_ptr(), lay.total_bytes, out_img.data_ptr(),
+                        None if final_idx is None else final_idx.data_ptr(), mail.data_ptr(), ev.cuda_event,
+                        stream), "rasterize_sum_fwd")
                 ev.synchronize()   # waits for the scan stage only; the rest is already queued
                 m = dctx.mail_np[slot]
                 num_intersects, overflow, depth_or = int(m[0]), int(m[1]), int(m[2])
@@ -166,6 +182,9 @@ class _RasterizeGaussiansSum(Function):
                 if num_intersects * 3 > cap * 2 or (H, W) not in dctx.cap:
                     dctx.cap[(H, W)] = max(cap, _round_cap(2 * num_intersects))
                 if depth_or != 0:
+                    if nd:
+                        raise NotImplementedError("N-channel / untruncated rasterisation needs zero depths "
+                                                  "(both projections emit zeros)")
                     general = True   # non-zero depths: keys need the depth bits (64-bit path)
                 break
 
@@ -174,6 +193,7 @@ class _RasterizeGaussiansSum(Function):
         ctx.num_intersects = num_intersects
         ctx.num_points = n
         ctx.general = bool(general)
+        ctx.nd, ctx.channels, ctx.max_tile = nd, channels, max_tile
 
         if num_intersects < 1:
             # rasterize_sum.py:121-129
@@ -220,11 +240,20 @@ class _RasterizeGaussiansSum(Function):
                 v_out_img = v_out_img.float()
             grads = torch.empty((n, 12), dtype=torch.float32, device=dev)
             with _C._guard(dev):
-                _lib.check(_lib.load().gs2d_rasterize_sum_bwd(
-                    n, ctx.img_height, ctx.img_width, ctx.cap, state.data_ptr(), ctx.state_bytes,
-                    final_idx.data_ptr(), v_out_img.data_ptr(), grads.data_ptr(),
-                    torch.cuda.current_stream(dev).cuda_stream), "rasterize_sum_bwd")
-            v_xy, v_conic, v_colors, v_opacity = grads[:, 0:2], grads[:, 2:5], grads[:, 5:8], grads[:, 8:9]
+                if ctx.nd:
+                    v_colors = torch.empty((n, ctx.channels), dtype=torch.float32, device=dev)
+                    _lib.check(_lib.load().gs2d_rasterize_sum_nd_bwd(
+                        n, ctx.channels, ctx.img_height, ctx.img_width, ctx.cap, ctx.max_tile, state.data_ptr(),
+                        ctx.state_bytes, colors.data_ptr(), final_idx.data_ptr(), v_out_img.data_ptr(),
+                        grads.data_ptr(), v_colors.data_ptr(), torch.cuda.current_stream(dev).cuda_stream),
+                        "rasterize_sum_nd_bwd")
+                else:
+                    _lib.check(_lib.load().gs2d_rasterize_sum_bwd(
+                        n, ctx.img_height, ctx.img_width, ctx.cap, state.data_ptr(), ctx.state_bytes,
+                        final_idx.data_ptr(), v_out_img.data_ptr(), grads.data_ptr(),
+                        torch.cuda.current_stream(dev).cuda_stream), "rasterize_sum_bwd")
+                    v_colors = grads[:, 5:8]
+            v_xy, v_conic, v_opacity = grads[:, 0:2], grads[:, 2:5], grads[:, 8:9]
         return (v_xy, None, None, v_conic, None, v_colors, v_opacity, None, None, None, None, None, None, None)
 
 

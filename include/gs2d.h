@@ -79,6 +79,20 @@ int gs2d_project_scalerot_bwd(int n, const float* scales2d, const float* rotatio
                               const int32_t* radii, const float* conics, const float* v_xy, int ld_v_xy,
                               const float* v_conic, int ld_v_conic, float* v_cov2d, float* v_mean2d, float* v_scale,
                               float* v_rot, gs2d_stream_t stream);
+/* SURVEY 8f.4 option, no reference counterpart: the same two backwards with the ANALYTIC gradient of
+ * the forward.  The reference counts the off-diagonal covariance term twice (v_cov2d.y is already
+ * the total derivative w.r.t. the shared off-diagonal, helpers.cuh:80, and backward2d.cu:39-40 /
+ * :103-105 multiply it by 2 again); these use the factor 1, which is what autograd of
+ * the forward chain gives (tests/test_gpu_extensions.py checks them against fp64 autograd).
+ * Everything else -- arguments, outputs, radii <= 0 handling -- is identical. */
+int gs2d_project_chol_bwd_analytic(int n, const float* L_elements, int img_h, int img_w, const int32_t* radii,
+                                   const float* conics, const float* v_xy, int ld_v_xy, const float* v_conic,
+                                   int ld_v_conic, float* v_cov2d, float* v_mean2d, float* v_L_elements,
+                                   gs2d_stream_t stream);
+int gs2d_project_scalerot_bwd_analytic(int n, const float* scales2d, const float* rotation, int img_h, int img_w,
+                                       const int32_t* radii, const float* conics, const float* v_xy, int ld_v_xy,
+                                       const float* v_conic, int ld_v_conic, float* v_cov2d, float* v_mean2d,
+                                       float* v_scale, float* v_rot, gs2d_stream_t stream);
 /* replaces compute_cov2d_bounds_tensor, bindings.cu:41-61 (helpers.cuh:45-68); radii is fp32 [n] */
 int gs2d_cov2d_bounds(int n, const float* cov2d, float* conics, float* radii, gs2d_stream_t stream);
 
@@ -163,6 +177,30 @@ int gs2d_rasterize_sum_bwd_binned(int n, int num_intersects, const int32_t* gaus
                                   const float* colors, const float* opacities, int img_h, int img_w,
                                   const int32_t* final_idx, const float* v_out, float* grads, void* scratch,
                                   size_t scratch_bytes, gs2d_stream_t stream);
+
+/* N-channel and / or untruncated accumulated-sum rasteriser.  The reference's Python
+ * dispatches colours with channels != 3 to nd_rasterize_sum_forward / _backward (rasterize_sum.py:
+ * 147-150, 218-221), which its extension never binds although the kernels exist
+ * (nd_rasterize_forward_sum forward.cu:630-710, nd_rasterize_backward_sum_kernel backward.cu:864-978);
+ * and its 3-channel kernel renders only the first 256 Gaussians of a tile.  These two
+ * entry points close both gaps; arguments as gs2d_rasterize_sum_fwd / _bwd plus
+ *   channels      1..32; colors is [n][channels], out_img / v_out are [H][W][channels]
+ *   max_per_tile  256: the reference's 3-channel truncation; 0: every Gaussian of a tile is rendered
+ *                 (what the reference's N-channel kernel does), in batches of 256
+ *   v_colors      [n][channels] colour gradients (zero-filled here); `grads` rows keep v_xy(2)
+ *                 v_conic(3) . . . v_opacity(1), their colour slots stay zero.
+ * Same pixel test and accumulation order as the 3-channel kernels: channels = 3 with max_per_tile =
+ * 256 is bit-identical to gs2d_rasterize_sum_fwd.  final_idx keeps the 3-channel meaning.
+ * The backward gives every rendered Gaussian its gradient (the reference's unlaunched N-channel
+ * backward starts one entry below final_index and so skips each tile's last Gaussian). */
+int gs2d_rasterize_sum_nd_fwd(int n, int channels, const float* xys, const float* depths, const int32_t* radii,
+                              const float* conics, const int32_t* num_tiles_hit, const float* colors,
+                              const float* opacities, int img_h, int img_w, int cap, int max_per_tile, void* state,
+                              size_t state_bytes, float* out_img, int32_t* final_idx, int32_t* status_host,
+                              gs2d_event_t scan_done, gs2d_stream_t stream);
+int gs2d_rasterize_sum_nd_bwd(int n, int channels, int img_h, int img_w, int cap, int max_per_tile, const void* state,
+                              size_t state_bytes, const float* colors, const int32_t* final_idx, const float* v_out,
+                              float* grads, float* v_colors, gs2d_stream_t stream);
 
 /* ---- fused fit iteration and render (callers either side of the path) ----
  * One frame model = raw parameters exactly as the reference's GaussianVideo_frame holds them
@@ -337,6 +375,9 @@ typedef struct {
     int adan_fresh;
     int skip_update;
     int slots;
+    int analytic_grad;   /* != 0: the projection backward uses the analytic gradient of the forward instead
+                          * of the reference's formula (see
+                          * gs2d_project_chol_bwd_analytic).  Off = parity with the reference. */
 } gs2d_fit_options;
 int gs2d_fit_step_band(int n, int cap, int img_h, int img_w, float* xyz_raw, float* chol_raw, float* features,
                        float* adan_state, const void* target, int target_format, void* work, size_t work_bytes,

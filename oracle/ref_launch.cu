@@ -163,4 +163,42 @@ int ref_rasterize_sum_backward(int n, int H, int W, const int *gaussian_ids_sort
     return (int)cudaGetLastError();
 }
 
+/* The reference's N-channel sum kernels (forward.cu:630-710, backward.cu:864-978).  The reference
+ * has NO host code for them (its rasterize_sum.py:147-150, 218-221 names functions that ext.cpp
+ * never binds); they are launched here the way bindings.cu launches their
+ * alpha-compositing siblings (nd_rasterize_forward_tensor bindings.cu:475-549): one 16x16 block per
+ * tile, zero-initialised outputs (the forward accumulates into out_img with +=). */
+int ref_nd_rasterize_sum_forward(int H, int W, int channels, const int *gaussian_ids_sorted, const int *tile_bins,
+                                 const float *xys, const float *conics, const float *colors, const float *opacities,
+                                 const float *background, float *out_img, float *final_Ts, int *final_idx,
+                                 cudaStream_t s) {
+    dim3 tb((W + 15) / 16, (H + 15) / 16, 1), block(16, 16, 1), img(W, H, 1);
+    cudaMemsetAsync(out_img, 0, sizeof(float) * channels * H * W, s);
+    cudaMemsetAsync(final_Ts, 0, sizeof(float) * H * W, s);
+    cudaMemsetAsync(final_idx, 0, sizeof(int) * H * W, s);
+    nd_rasterize_forward_sum<<<tb, block, 0, s>>>(tb, img, (unsigned)channels, gaussian_ids_sorted,
+                                                  (const int2 *)tile_bins, (const float2 *)xys,
+                                                  (const float3 *)conics, colors, opacities, final_Ts, final_idx,
+                                                  out_img, background);
+    return (int)cudaGetLastError();
+}
+
+/* workspace: channels * H * W floats (needed by the kernel when channels > MAX_REGISTER_CHANNELS = 3) */
+int ref_nd_rasterize_sum_backward(int n, int H, int W, int channels, const int *gaussian_ids_sorted,
+                                  const int *tile_bins, const float *xys, const float *conics, const float *colors,
+                                  const float *opacities, const float *background, const float *final_Ts,
+                                  const int *final_idx, const float *v_output, const float *v_output_alpha,
+                                  float *v_xy, float *v_conic, float *v_colors, float *v_opacity, float *workspace,
+                                  cudaStream_t s) {
+    dim3 tb((W + 15) / 16, (H + 15) / 16, 1), block(16, 16, 1), img(W, H, 1);
+    cudaMemsetAsync(v_xy, 0, sizeof(float) * 2 * n, s); cudaMemsetAsync(v_conic, 0, sizeof(float) * 3 * n, s);
+    cudaMemsetAsync(v_colors, 0, sizeof(float) * channels * n, s); cudaMemsetAsync(v_opacity, 0, sizeof(float) * n, s);
+    cudaMemsetAsync(workspace, 0, sizeof(float) * channels * H * W, s);
+    nd_rasterize_backward_sum_kernel<<<tb, block, 0, s>>>(
+        tb, img, (unsigned)channels, gaussian_ids_sorted, (const int2 *)tile_bins, (const float2 *)xys,
+        (const float3 *)conics, colors, opacities, background, final_Ts, final_idx, v_output, v_output_alpha,
+        (float2 *)v_xy, (float3 *)v_conic, v_colors, v_opacity, workspace);
+    return (int)cudaGetLastError();
+}
+
 } /* extern "C" */

@@ -147,6 +147,40 @@ def rasterize_sum_backward(H, W, ids_sorted, tile_bins, xys, conics, colors, opa
     return v_xy, v_conic, v_col, v_op
 
 
+def nd_rasterize_sum_forward(H, W, ids_sorted, tile_bins, xys, conics, colors, opac):
+    """the reference's unbound N-channel forward (forward.cu:630-710); colors [n, C]"""
+    dev = xys.device
+    C = colors.shape[1]
+    background = torch.ones(C, dtype=f32, device=dev)
+    out = torch.empty((H, W, C), dtype=f32, device=dev)
+    Ts = torch.empty((H, W), dtype=f32, device=dev)
+    fidx = torch.empty((H, W), dtype=i32, device=dev)
+    _ck(lib().ref_nd_rasterize_sum_forward(H, W, C, _p(ids_sorted), _p(tile_bins), _p(xys), _p(conics),
+                                           _p(colors.contiguous()), _p(opac), _p(background), _p(out), _p(Ts),
+                                           _p(fidx), _s()), "nd_raster_fwd")
+    return out, Ts, fidx
+
+
+def nd_rasterize_sum_backward(H, W, ids_sorted, tile_bins, xys, conics, colors, opac, final_Ts, final_idx, v_out):
+    """the reference's unbound N-channel backward (backward.cu:864-978).  It walks sorted indices
+    final_idx - 1 down to the tile's first, so pass final_idx = (one past the last index that is to
+    receive a gradient)."""
+    dev = xys.device
+    n, C = xys.shape[0], colors.shape[1]
+    background = torch.ones(C, dtype=f32, device=dev)
+    v_alpha = torch.zeros((H, W), dtype=f32, device=dev)
+    v_xy = torch.empty((n, 2), dtype=f32, device=dev)
+    v_conic = torch.empty((n, 3), dtype=f32, device=dev)
+    v_col = torch.empty((n, C), dtype=f32, device=dev)
+    v_op = torch.empty((n, 1), dtype=f32, device=dev)
+    ws = torch.empty((H, W, C), dtype=f32, device=dev)
+    _ck(lib().ref_nd_rasterize_sum_backward(n, H, W, C, _p(ids_sorted), _p(tile_bins), _p(xys), _p(conics),
+                                            _p(colors.contiguous()), _p(opac), _p(background), _p(final_Ts),
+                                            _p(final_idx.contiguous()), _p(v_out.contiguous()), _p(v_alpha), _p(v_xy),
+                                            _p(v_conic), _p(v_col), _p(v_op), _p(ws), _s()), "nd_raster_bwd")
+    return v_xy, v_conic, v_col, v_op
+
+
 def bin_and_sort(n, xys, depths, radii, nth, tile_bounds, stable=True):
     """utils.py:99-167 of the reference around its kernels.  tile_bins gets max(I, tiles) rows so
     the reference kernel stays in bounds."""
