@@ -380,7 +380,13 @@ k_fit_reset_slots(int tiles, int32_t* tile_fill, int32_t* status) {
 // K3: the tile kernel
 // ------------------------------------------------------------------------------------------
 constexpr int kIdChunk = 1024;
-constexpr int kTileThreads = 64;   // two warps per 16x16 tile, four pixels per thread
+#ifndef GS2D_TILE_THREADS
+#define GS2D_TILE_THREADS 64
+#endif
+constexpr int kTileThreads = GS2D_TILE_THREADS;            // warps per 16x16 tile x 32
+constexpr int kPix = GS2D_TILE_PIX / kTileThreads;          // pixels per thread (one column, rows 2 apart)
+constexpr int kWarpRows = 2 * kPix;                         // tile rows owned by one warp
+static_assert(kTileThreads == 32 || kTileThreads == 64, "one or two warps per tile");
 #ifndef GS2D_BWD_ROWS
 #define GS2D_BWD_ROWS 2
 #endif
@@ -504,18 +510,18 @@ k_fit_tiles(int W, int H, int tx, int row0, const int32_t* __restrict__ tile_off
             sv[GS2D_TILE_PIX + j * kTileThreads + tid] = make_float4(0.f, 0.f, 0.f, 0.f);
     }
 
-    const int lx = lane & 15, ly0 = 8 * warp + (lane >> 4);   // pixel j: (lx, ly0 + 2j)
+    const int lx = lane & 15, ly0 = kWarpRows * warp + (lane >> 4);   // pixel j: (lx, ly0 + 2j)
     const int ox = blockIdx.x * GS2D_TILE, oy = tile_y * GS2D_TILE;
     const int px_i = ox + lx;
     const bool in_x = px_i < W;
-    uint32_t tgt_u8[4] = {0u, 0u, 0u, 0u};
-    uint8_t raw_y[4] = {0, 0, 0, 0}, raw_u[4] = {0, 0, 0, 0}, raw_v[4] = {0, 0, 0, 0};   // I420: decoded where the target is used
-    float3 tgt[4];
+    uint32_t tgt_u8[kPix] = {};
+    uint8_t raw_y[kPix] = {}, raw_u[kPix] = {}, raw_v[kPix] = {};   // I420: decoded where the target is used
+    float3 tgt[kPix];
 #pragma unroll
-    for (int j = 0; j < 4; ++j) tgt[j] = make_float3(0.f, 0.f, 0.f);
+    for (int j = 0; j < kPix; ++j) tgt[j] = make_float3(0.f, 0.f, 0.f);
     if (MODE == 0 && in_x) {   // issued before the batch arrives: independent loads
 #pragma unroll
-        for (int j = 0; j < 4; ++j) {
+        for (int j = 0; j < kPix; ++j) {
             const int py_i = oy + ly0 + 2 * j;
             if (py_i < H) {
                 const size_t pid = (size_t)py_i * W + px_i;
@@ -571,25 +577,27 @@ k_fit_tiles(int W, int H, int tx, int row0, const int32_t* __restrict__ tile_off
 
     // ---- forward (forward.cu:590-612) --------------------------------------------------------
     const float px = (float)px_i;
-    float py[4];
-    bool inside[4];
+    float py[kPix];
+    bool inside[kPix];
 #pragma unroll
-    for (int j = 0; j < 4; ++j) {
+    for (int j = 0; j < kPix; ++j) {
         py[j] = (float)(oy + ly0 + 2 * j);
         inside[j] = in_x && (oy + ly0 + 2 * j) < H;
     }
-    const int wrow_lo = 8 * warp, wrow_hi = 8 * warp + 7;
-    float3 pix[4];
-    int cur_idx[4] = {0, 0, 0, 0};
+    const int wrow_lo = kWarpRows * warp, wrow_hi = kWarpRows * warp + kWarpRows - 1;
+    float3 pix[kPix];
+    int cur_idx[kPix] = {};
     // Pixels (0,1) and (2,3) of a lane ride in the two lanes of FFMA2 / FMUL2 / FADD2 (sm_100a):
     // the same single-rounding operations per pixel as the scalar form (bit-identical results),
     // half the issue slots for the arithmetic (measured: fit +2.9 %, trained-like +4.2 %, render
     // +3.7..7 %; the same packing of the backward's row pairs cost 31 registers and was 8 % slower).
     // A pixel that fails the test accumulates alpha = 0.
-    const f32x2 py2[2] = {pk2(py[0], py[1]), pk2(py[2], py[3])};
-    f32x2 pr[2], pg[2], pb[2];
+    f32x2 py2[kPix / 2], pr[kPix / 2], pg[kPix / 2], pb[kPix / 2];
 #pragma unroll
-    for (int P = 0; P < 2; ++P) pr[P] = pg[P] = pb[P] = pk2(0.f, 0.f);
+    for (int P = 0; P < kPix / 2; ++P) {
+        py2[P] = pk2(py[2 * P], py[2 * P + 1]);
+        pr[P] = pg[P] = pb[P] = pk2(0.f, 0.f);
+    }
     for (int c = 0; c < nb; c += 32) {
         const int r_lane = c + lane;
         bool touch = false;
@@ -610,7 +618,7 @@ k_fit_tiles(int W, int H, int tx, int row0, const int32_t* __restrict__ tile_off
             const float dx = subf(q0.x, px);
             const float t1 = mulf(q0.z, dx), t3 = mulf(q0.w, dx);
 #pragma unroll
-            for (int P = 0; P < 2; ++P) {
+            for (int P = 0; P < kPix / 2; ++P) {
                 if (y1 < 4 * P || y0 > 4 * P + 3) continue;   // warp-uniform: rows 4P..4P+3 outside the rectangle
                 const f32x2 dy = sub2(bc2(q0.y), py2[P]);
                 // reference expression 0.5*(cx*dx*dx + cz*dy*dy) + cy*dx*dy as its build contracts it
@@ -633,13 +641,13 @@ k_fit_tiles(int W, int H, int tx, int row0, const int32_t* __restrict__ tile_off
         }
     }
 #pragma unroll
-    for (int P = 0; P < 2; ++P) {
+    for (int P = 0; P < kPix / 2; ++P) {
         pix[2 * P] = make_float3(lo2(pr[P]), lo2(pg[P]), lo2(pb[P]));
         pix[2 * P + 1] = make_float3(hi2(pr[P]), hi2(pg[P]), hi2(pb[P]));
     }
     if (out_img || final_idx) {
 #pragma unroll
-        for (int j = 0; j < 4; ++j) {
+        for (int j = 0; j < kPix; ++j) {
             if (!inside[j]) continue;
             const size_t pid = (size_t)(oy + ly0 + 2 * j) * W + px_i;
             if (out_img) {
@@ -660,7 +668,7 @@ k_fit_tiles(int W, int H, int tx, int row0, const int32_t* __restrict__ tile_off
     // ---- clamp + L2 loss and its gradient w.r.t. the unclamped sum --------------------------
     float l = 0.f;
 #pragma unroll
-    for (int j = 0; j < 4; ++j) {
+    for (int j = 0; j < kPix; ++j) {
         float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
         if (GT == 2) tgt_u8[j] = yuv_to_rgb_packed(raw_y[j], raw_u[j], raw_v[j]);
         if (GT != 0) tgt[j] = make_float3(u8_over_255(tgt_u8[j] & 255u), u8_over_255((tgt_u8[j] >> 8) & 255u),
@@ -683,7 +691,9 @@ k_fit_tiles(int W, int H, int tx, int row0, const int32_t* __restrict__ tile_off
     if (lane == 0) sred[warp] = l;
     __syncthreads();
     if (tid == 0) {
-        const float s = sred[0] + sred[1];
+        float s = sred[0];
+#pragma unroll
+        for (int w = 1; w < kTileThreads / 32; ++w) s += sred[w];
         if (s != 0.f) {
             atomicAdd(loss_acc, (double)s);
             // spatial mode: the loss rides in the pad of gradient row 0 so that one all-reduce of the
@@ -723,12 +733,14 @@ k_fit_tiles(int W, int H, int tx, int row0, const int32_t* __restrict__ tile_off
             const int lxs = min(lxp, GS2D_TILE - 1);                   // a readable column for lanes outside the rectangle
             const float dx = subf(gx, (float)(ox + lxp));
             const float t1 = mulf(cx, dx), t3 = mulf(cy, dx);
-            // Straight-line inner loop: a lane outside its pair's rectangle (column beyond rx1, row
-            // beyond ry1) or a pixel that fails the reference's test contributes vis = alpha = 0.
+            // Straight-line inner loop: a pixel that fails the reference's test contributes vis = alpha
+            // = 0, and so does a lane whose column lies outside its pair's rectangle (col_ok).  Rows are
+            // not masked: the four pairs of a pass walk max_h rows, and a row past a pair's own ry1 is
+            // either inside the tile, where the rectangle guarantees that the test fails
+            // (gs2d_math.cuh:pair_rect), or past the tile, where v_out reads the zero rows.
             // Per pixel only the moments of v_sigma over dy are accumulated (dx is the lane's
             // constant): S0 = sum v_sigma, S1 = sum v_sigma*dy, S2 = sum v_sigma*dy^2; v_xy and
             // v_conic (backward.cu:828-832) are linear in them and folded in after the column.
-            const float fy_last = col_ok ? (float)(oy + ry1) : -1.f;   // last row this lane really owns
             float S0 = 0.f, S1 = 0.f, S2 = 0.f, cr = 0.f, cg = 0.f, cbl = 0.f;
             float fy = (float)(oy + ry0);                              // row coordinate as a float (exact)
             const float4* svc = sv + ry0 * GS2D_TILE + lxs;
@@ -743,7 +755,7 @@ k_fit_tiles(int W, int H, int tx, int row0, const int32_t* __restrict__ tile_off
                     const float sg = fmaf_(dy, t3, mulf(q, 0.5f));
                     const float vis = gauss_vis(sg);
                     const float al = minf(mulf(opac, vis), 1.f);
-                    const bool ok = (fyu <= fy_last) && gauss_pass(sg, al);
+                    const bool ok = col_ok && gauss_pass(sg, al);
                     const float visk = ok ? vis : 0.f, alk = ok ? al : 0.f;
                     const float4 vo = svc[(ry + u) * GS2D_TILE];          // rows past the tile read the zero rows
                     const float v_alpha = q2.x * vo.x + q2.y * vo.y + q2.z * vo.z;   // backward.cu:821-825
@@ -807,7 +819,8 @@ __device__ __forceinline__ float adan_one(float p, float g, float& m, float& nn,
     nn = nn * h.b3 + (1.f - h.b3) * u * u;
     const float denom = sqrtf(nn) * h.inv_bc3_sqrt + h.eps;
     prev = g;
-    return (p - h.step_size * (m / denom) - h.step_size_diff * (d / denom)) / h.decay_div;
+    const float q = p - h.step_size * (m / denom) - h.step_size_diff * (d / denom);
+    return h.decay_div == 1.f ? q : q / h.decay_div;   // x / 1 == x: no weight decay (the reference's setting), no division
 }
 
 __global__ void __launch_bounds__(kFitThreads)
