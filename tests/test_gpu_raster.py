@@ -48,6 +48,7 @@ CASES = [
     pytest.param(1080, 1920, 50_000, False, id="C2-1080p-50k"),
     pytest.param(1080, 1920, 50_000, True, id="1080p-50k-trained-like"),
     pytest.param(130, 250, 3_000, True, id="ragged-130x250"),
+    pytest.param(2160, 3840, 200_000, False, id="C5-4K-200k"),
 ]
 
 
