@@ -117,9 +117,10 @@ def algorithmic_bytes(stage: str, n: int, I: int, hw: int, tiles: int) -> float:
     }[stage]
 
 
-def ncu_traffic(stage: str):
-    """dram__bytes_read.sum + dram__bytes_write.sum per launch of the stage's kernel from the committed
-    `ncu --set full` capture (profiles/r1_fit_kernels_ncu.json; taken at ~124k intersections), or None"""
+def ncu_capture(stage: str, key: str = "dram_traffic_bytes"):
+    """one number per launch of the stage's kernel from the committed `ncu --set full` capture
+    (profiles/r1_fit_kernels_ncu.json; taken with this same bench command), or None.  Default:
+    dram__bytes_read.sum + dram__bytes_write.sum"""
     kern = {"fit_tiles": "k_fit_tiles", "adan": "k_fit_update", "edges_pack": "k_fit_scatter"}.get(stage)
     try:
         recs = json.load(open(os.path.join(ROOT, "profiles", "r1_fit_kernels_ncu.json")))
@@ -127,7 +128,7 @@ def ncu_traffic(stage: str):
         return None
     for r in recs:
         if kern and kern in r.get("kernel", ""):
-            return r.get("dram_traffic_bytes")
+            return r.get(key)
     return None
 
 
@@ -398,9 +399,17 @@ def main_gpu(args, rank: int, world: int, local_rank: int):
             alg = algorithmic_bytes(top, NPTS, I or 124_000, H * W, tiles)
             dur_s = kern[top]["ms_per_step"] / n_l * 1e-3
             line["roofline"] = {"kernel": top, "bound": "hbm", "achieved": alg / dur_s / 1e9, "peak": peak,
-                                "unit": "GB/s", "frac": alg / dur_s / 1e9 / peak, "traffic": ncu_traffic(top),
+                                "unit": "GB/s", "frac": alg / dur_s / 1e9 / peak, "traffic": ncu_capture(top),
                                 "algorithmic_bytes": alg, "avg_launch_us": dur_s * 1e6,
                                 "peak_source": "MEASURED_PEAKS.json hbm_gbs (measured)" if peaks else "fallback 6650"}
+            # what actually bounds this kernel: warp instructions issued per second
+            # against 4 schedulers x SMs x clock -- instruction count from the committed ncu capture, time live
+            inst = ncu_capture(top, "smsp__inst_executed.sum")
+            if inst and clocks and clocks.get("sm_mhz"):
+                sms = torch.cuda.get_device_properties(dev).multi_processor_count
+                issue_peak = 4.0 * sms * clocks["sm_mhz"] * 1e6
+                line["roofline"]["issue"] = {"warp_instructions": inst, "achieved_ginst_s": inst / dur_s / 1e9,
+                                             "peak_ginst_s": issue_peak / 1e9, "frac": inst / dur_s / issue_peak}
         if world == 1 and mine and not args.no_cpu:
             r = run_cpu(args.cpu_steps, 1)
             line["cpu_baseline"] = {k: r[k] for k in ("value", "unit", "cores", "kind", "sample")}

@@ -316,8 +316,11 @@ __device__ __forceinline__ int scatter_records(const Proj2d& p, int i, float o, 
                 if (ok) {
                     const uint32_t rect = pair_rect(p.cx, p.cy, o, p.conic.x, p.conic.y, p.conic.z, xr * GS2D_TILE,
                                                     yr * GS2D_TILE, W, H);
-                    packed[3 * at + 0] = make_float4(p.cx, p.cy, p.conic.x, p.conic.y);
-                    packed[3 * at + 1] = make_float4(p.conic.z, o, __uint_as_float(rect), __int_as_float(i));
+                    // the diagonal conic terms are stored HALVED: sigma = 0.5*(cx dx^2 + cz dy^2) + cy dx dy is
+                    // then fma(dy, cy*dx, fma(dx, (cx/2)*dx, ((cz/2)*dy)*dy)) with no separate multiply by 0.5 per
+                    // pixel; halving is exact, so every rounding is the reference's
+                    packed[3 * at + 0] = make_float4(p.cx, p.cy, 0.5f * p.conic.x, p.conic.y);
+                    packed[3 * at + 1] = make_float4(0.5f * p.conic.z, o, __uint_as_float(rect), __int_as_float(i));
                     packed[3 * at + 2] = make_float4(r, g, b, __uint_as_float((uint32_t)t));
                 }
                 if (++xr == p.x1) { xr = p.x0; ++yr; }
@@ -390,6 +393,11 @@ static_assert(kTileThreads == 32 || kTileThreads == 64, "one or two warps per ti
 #ifndef GS2D_BWD_ROWS
 #define GS2D_BWD_ROWS 2
 #endif
+#ifndef GS2D_BWD_UNROLL
+#define GS2D_BWD_UNROLL 1   // trips unrolled by the compiler.  Measured (fit_tiles, C2 / trained-like): 1 -> 58.9 / 158.8 us at 70
+                            // registers, 2 -> 59.7 / 160.2 at 80, left to the compiler (4) -> 65.2 / 166.3 at 103
+#endif
+constexpr int kBwdUnroll = GS2D_BWD_UNROLL;
 constexpr int kBwdRows = GS2D_BWD_ROWS;   // rows of a pair's rectangle a lane evaluates per loop trip
 
 // Stage the tile's batch into shared memory in ascending Gaussian-id order (the scatter wrote
@@ -610,20 +618,21 @@ k_fit_tiles(int W, int H, int tx, int row0, const int32_t* __restrict__ tile_off
         while (m) {
             const int k = c + __ffs(m) - 1;
             m &= m - 1;
-            const float4 q0 = sq[3 * k];       // x, y, conic.x, conic.y
-            const float4 q1 = sq[3 * k + 1];   // conic.z, opacity, rect, id
+            const float4 q0 = sq[3 * k];       // x, y, conic.x / 2, conic.y
+            const float4 q1 = sq[3 * k + 1];   // conic.z / 2, opacity, rect, id
             const float4 q2 = sq[3 * k + 2];   // r, g, b, tile
             const uint32_t rect = __float_as_uint(q1.z);
             const int y0 = (int)((rect >> 16) & 255) - wrow_lo, y1 = (int)(rect >> 24) - wrow_lo;   // warp-local rows
             const float dx = subf(q0.x, px);
-            const float t1 = mulf(q0.z, dx), t3 = mulf(q0.w, dx);
+            const float t1 = mulf(q0.z, dx), t3 = mulf(q0.w, dx);   // t1 = (cx * dx) / 2
 #pragma unroll
             for (int P = 0; P < kPix / 2; ++P) {
                 if (y1 < 4 * P || y0 > 4 * P + 3) continue;   // warp-uniform: rows 4P..4P+3 outside the rectangle
                 const f32x2 dy = sub2(bc2(q0.y), py2[P]);
-                // reference expression 0.5*(cx*dx*dx + cz*dy*dy) + cy*dx*dy as its build contracts it
+                // reference expression 0.5*(cx*dx*dx + cz*dy*dy) + cy*dx*dy as its build contracts it:
+                // fma(dy, cy*dx, 0.5 * fma(dx, cx*dx, (cz*dy)*dy)), the exact factor 0.5 carried by the record
                 const f32x2 q = fma2(bc2(dx), bc2(t1), mul2(mul2(bc2(q1.x), dy), dy));
-                const f32x2 sg = fma2(dy, bc2(t3), mul2(q, bc2(0.5f)));
+                const f32x2 sg = fma2(dy, bc2(t3), q);
                 const f32x2 e = mul2(sg, bc2(-1.4426950216293334961f));
                 const f32x2 al = mul2(bc2(q1.y), pk2(ex2_approx(lo2(e)), ex2_approx(hi2(e))));
                 const float a0 = minf(lo2(al), 1.f), a1 = minf(hi2(al), 1.f);
@@ -721,7 +730,8 @@ k_fit_tiles(int W, int H, int tx, int row0, const int32_t* __restrict__ tile_off
         max_iters = max(max_iters, __shfl_xor_sync(0xffffffffu, max_iters, 16));
         if (max_iters == 0) continue;   // no pixel of this tile can pass for any of the four
         const float4 q0 = sq[3 * k], q2 = sq[3 * k + 2];
-        const float gx = q0.x, gy = q0.y, cx = q0.z, cy = q0.w, cz = q1.x, opac = q1.y;
+        const float gx = q0.x, gy = q0.y, cxh = q0.z, cy = q0.w, czh = q1.x, opac = q1.y;   // cxh, czh: conic.x / 2, conic.z / 2
+        const float cx = 2.f * cxh, cz = 2.f * czh;
         float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
         for (int cb0 = 0; cb0 < 2; ++cb0) {
             int max_h = (cb0 < ncol) ? h : 0;
@@ -732,7 +742,7 @@ k_fit_tiles(int W, int H, int tx, int row0, const int32_t* __restrict__ tile_off
             const bool col_ok = (cb0 < ncol) && lxp <= rx1;
             const int lxs = min(lxp, GS2D_TILE - 1);                   // a readable column for lanes outside the rectangle
             const float dx = subf(gx, (float)(ox + lxp));
-            const float t1 = mulf(cx, dx), t3 = mulf(cy, dx);
+            const float t1 = mulf(cxh, dx), t3 = mulf(cy, dx);
             // Straight-line inner loop: a pixel that fails the reference's test contributes vis = alpha
             // = 0, and so does a lane whose column lies outside its pair's rectangle (col_ok).  Rows are
             // not masked: the four pairs of a pass walk max_h rows, and a row past a pair's own ry1 is
@@ -742,24 +752,26 @@ k_fit_tiles(int W, int H, int tx, int row0, const int32_t* __restrict__ tile_off
             // constant): S0 = sum v_sigma, S1 = sum v_sigma*dy, S2 = sum v_sigma*dy^2; v_xy and
             // v_conic (backward.cu:828-832) are linear in them and folded in after the column.
             float S0 = 0.f, S1 = 0.f, S2 = 0.f, cr = 0.f, cg = 0.f, cbl = 0.f;
-            float fy = (float)(oy + ry0);                              // row coordinate as a float (exact)
+            // dy of the trip's first row; gy - row is exact in fp32 (the result is a multiple of ulp(gy) far
+            // below 2^24 ulps), so stepping it by whole rows gives the bits of subf(gy, row) every time
+            float dy0 = subf(gy, (float)(oy + ry0));
             const float4* svc = sv + ry0 * GS2D_TILE + lxs;
             // kBwdRows rows per trip: that many independent sigma / ex2 chains in flight per lane
             // (the loop is latency-bound, not issue-bound: profiles/r1 notes)
+#pragma unroll kBwdUnroll
             for (int ry = 0; ry < max_h; ry += kBwdRows) {
 #pragma unroll
                 for (int u = 0; u < kBwdRows; ++u) {
-                    const float fyu = fy + (float)u;
-                    const float dy = subf(gy, fyu);
-                    const float q = fmaf_(dx, t1, mulf(mulf(cz, dy), dy));
-                    const float sg = fmaf_(dy, t3, mulf(q, 0.5f));
+                    const float dy = dy0 - (float)u;
+                    const float sg = fmaf_(dy, t3, fmaf_(dx, t1, mulf(mulf(czh, dy), dy)));
                     const float vis = gauss_vis(sg);
-                    const float al = minf(mulf(opac, vis), 1.f);
+                    const float oa = mulf(opac, vis);                                 // alpha before the clamp at 1
+                    const float al = minf(oa, 1.f);
                     const bool ok = col_ok && gauss_pass(sg, al);
-                    const float visk = ok ? vis : 0.f, alk = ok ? al : 0.f;
+                    const float oak = ok ? oa : 0.f, alk = ok ? al : 0.f;
                     const float4 vo = svc[(ry + u) * GS2D_TILE];          // rows past the tile read the zero rows
                     const float v_alpha = q2.x * vo.x + q2.y * vo.y + q2.z * vo.z;   // backward.cu:821-825
-                    const float v_sigma = -opac * visk * v_alpha;                     // :827
+                    const float v_sigma = -oak * v_alpha;                             // :827  (-opac * vis * v_alpha)
                     const float t = v_sigma * dy;
                     S0 += v_sigma;
                     S1 += t;
@@ -768,7 +780,7 @@ k_fit_tiles(int W, int H, int tx, int row0, const int32_t* __restrict__ tile_off
                     cg = fmaf(alk, vo.y, cg);
                     cbl = fmaf(alk, vo.z, cbl);
                 }
-                fy += (float)kBwdRows;
+                dy0 -= (float)kBwdRows;
             }
             acc[0] += cx * dx * S0 + cy * S1;                                         // v_xy     :831-832
             acc[1] += cy * dx * S0 + cz * S1;
