@@ -60,7 +60,8 @@ class FitOptions(Structure):
     """mirror of gs2d_fit_options (include/gs2d.h)"""
 
     _fields_ = [("rgb_w", c_void_p), ("adan_state_w", c_void_p), ("rgb_w_grad_out", c_void_p), ("adan_step", c_int),
-                ("adan_fresh", c_int), ("skip_update", c_int), ("slots", c_int), ("analytic_grad", c_int)]
+                ("adan_fresh", c_int), ("skip_update", c_int), ("slots", c_int), ("all_per_tile", c_int),
+                ("analytic_grad", c_int)]
 
 
 class QuantizedFrame(Structure):

@@ -407,8 +407,11 @@ constexpr int kBwdRows = GS2D_BWD_ROWS;   // rows of a pair's rectangle a lane e
 // in flight while the ids land).  cnt > 256 (rare; the reference then renders only the 256
 // lowest ids): ranks are computed against all cnt ids in chunks and the 256
 // lowest-ranked records are kept.
+// publish (every Gaussian of a fuller tile is to be rendered, in batches of 256): the rank of each
+// record is also stored into the record's spare word (q2.w, the tile id, which the fit kernels never
+// read), so that the later batches are staged by stage_tile_window without ranking again.
 __device__ __forceinline__ int stage_tile_sorted(const float4* __restrict__ src, int cnt, float4* sq, int* sid,
-                                                 int tid) {
+                                                 int tid, bool publish = false) {
     const int nb = min(cnt, GS2D_MAX_PER_TILE);
     if (cnt <= GS2D_MAX_PER_TILE) {
         float4 r0, r1, r2;
@@ -452,10 +455,30 @@ __device__ __forceinline__ int stage_tile_sorted(const float4* __restrict__ src,
                 sq[3 * rank + 1] = __ldg(&src[3 * (size_t)j + 1]);
                 sq[3 * rank + 2] = __ldg(&src[3 * (size_t)j + 2]);
             }
+            if (publish && j < cnt)
+                reinterpret_cast<int*>(const_cast<float4*>(src) + 3 * (size_t)j + 2)[3] = rank;
         }
         __syncthreads();
     }
     return nb;
+}
+
+// Batch `base / 256` of a tile whose ranks stage_tile_sorted published: the records with rank in
+// [base, base + 256), at their place.  The caller has made sure nobody still reads sq.  Ranks are
+// read past L1 (another thread of the CTA wrote them, before a barrier); no scratch is used, so this
+// also runs while sv holds v_out.
+__device__ __forceinline__ int stage_tile_window(const float4* __restrict__ src, int cnt, int base, float4* sq,
+                                                 int tid) {
+    for (int j = tid; j < cnt; j += kTileThreads) {
+        const int rank = __ldcg(reinterpret_cast<const int*>(src + 3 * (size_t)j + 2) + 3) - base;
+        if (rank >= 0 && rank < GS2D_MAX_PER_TILE) {
+            sq[3 * rank + 0] = __ldg(&src[3 * (size_t)j + 0]);
+            sq[3 * rank + 1] = __ldg(&src[3 * (size_t)j + 1]);
+            sq[3 * rank + 2] = __ldg(&src[3 * (size_t)j + 2]);
+        }
+    }
+    __syncthreads();
+    return min(cnt - base, GS2D_MAX_PER_TILE);
 }
 
 // Sum 8 per-lane values over each group of 8 consecutive lanes with 7 shuffles: lane l of a
@@ -495,13 +518,18 @@ __device__ __forceinline__ float group8_reduce8_t(float (&v)[8], int lane) {
 #ifndef GS2D_TILE_MIN_BLOCKS
 #define GS2D_TILE_MIN_BLOCKS 1
 #endif
-template <int MODE, int GT>
+constexpr int kTileLossInGrads = 1;   // flags: spatial mode, the tile's loss also rides in the gradient buffer
+constexpr int kTileAllPerTile = 2;    //        every Gaussian of a tile is rendered, in batches of 256 (ranges only)
+// ALL: the instantiation that walks a fuller tile in batches (kTileAllPerTile); a run-time switch in the one
+// kernel cost the common case 42 registers and 12 % (58.9 -> 66.2 us), so it is a kernel of its own.
+template <int MODE, int GT, bool ALL = false>
 __global__ void __launch_bounds__(kTileThreads, GS2D_TILE_MIN_BLOCKS)
 k_fit_tiles(int W, int H, int tx, int row0, const int32_t* __restrict__ tile_off, int32_t* tile_fill,
             const float4* __restrict__ packed, const void* __restrict__ gt, float grad_scale,
             float* __restrict__ grads, double* loss_acc, int32_t* __restrict__ status,
             float* __restrict__ out_img, int out_chw, int out_clamp, int32_t* __restrict__ final_idx,
-            int32_t* __restrict__ ids_sorted_dbg, int step, int loss_in_grads) {
+            int32_t* __restrict__ ids_sorted_dbg, int step, int flags) {
+    const int loss_in_grads = flags & kTileLossInGrads;
     __shared__ float4 sq[GS2D_MAX_PER_TILE * 3];
     // v_out of the tile (rows 0..15; before that, the id chunk of the staging) + 16 rows of zeros:
     // the backward's row walk may run past the tile for lanes whose pair has a shorter rectangle
@@ -569,7 +597,11 @@ k_fit_tiles(int W, int H, int tx, int row0, const int32_t* __restrict__ tile_off
     if (of != 0) return;
     // (tile_fill[t] is re-zeroed after the staging's barrier: a store to the address of the load in
     // flight would park this warp on it)
-    const int nb = stage_tile_sorted(packed + 3 * (size_t)lo, cnt, sq, sid, tid);
+    // more than 256 and all of them wanted (the reference renders the first 256, Q1): the
+    // forward walks the batches in rank order, the backward walks them again; one batch otherwise
+    const bool all = ALL && cnt > GS2D_MAX_PER_TILE;
+    const int nbat = all ? (cnt + GS2D_MAX_PER_TILE - 1) / GS2D_MAX_PER_TILE : 1;
+    int nb = stage_tile_sorted(packed + 3 * (size_t)lo, cnt, sq, sid, tid, all);
     if (tid == 0) {                   // every thread is past a barrier that it reached knowing cnt
         tile_fill[t] = 0;             // ready for the next iteration's scatter
         if (!tile_off && MODE == 0) {
@@ -578,10 +610,8 @@ k_fit_tiles(int W, int H, int tx, int row0, const int32_t* __restrict__ tile_off
                 status[kStSlotIsect + ((step + 1) & 1)] = 0;
         }
     }
-    if (ids_sorted_dbg) {   // parity tests: the order the batch is rendered in
-        for (int r = tid; r < nb; r += kTileThreads) ids_sorted_dbg[lo + r] = __float_as_int(sq[3 * r + 1].w);
+    if (ids_sorted_dbg && !all)   // parity tests: the order the batch is rendered in
         for (int r = nb + tid; r < cnt; r += kTileThreads) ids_sorted_dbg[lo + r] = -1;
-    }
 
     // ---- forward (forward.cu:590-612) --------------------------------------------------------
     const float px = (float)px_i;
@@ -606,6 +636,14 @@ k_fit_tiles(int W, int H, int tx, int row0, const int32_t* __restrict__ tile_off
         py2[P] = pk2(py[2 * P], py[2 * P + 1]);
         pr[P] = pg[P] = pb[P] = pk2(0.f, 0.f);
     }
+    for (int bat = 0; bat < nbat; ++bat) {
+    if (bat) {
+        __syncthreads();   // everyone is done with the previous batch
+        nb = stage_tile_window(packed + 3 * (size_t)lo, cnt, bat * GS2D_MAX_PER_TILE, sq, tid);
+    }
+    const int lob = lo + bat * GS2D_MAX_PER_TILE;   // sorted index of the batch's first record
+    if (ids_sorted_dbg)
+        for (int r = tid; r < nb; r += kTileThreads) ids_sorted_dbg[lob + r] = __float_as_int(sq[3 * r + 1].w);
     for (int c = 0; c < nb; c += 32) {
         const int r_lane = c + lane;
         bool touch = false;
@@ -643,12 +681,13 @@ k_fit_tiles(int W, int H, int tx, int row0, const int32_t* __restrict__ tile_off
                 pg[P] = fma2(ak, bc2(q2.y), pg[P]);
                 pb[P] = fma2(ak, bc2(q2.z), pb[P]);
                 if (MODE == 1) {
-                    if (ok0) cur_idx[2 * P] = lo + k;
-                    if (ok1) cur_idx[2 * P + 1] = lo + k;
+                    if (ok0) cur_idx[2 * P] = lob + k;
+                    if (ok1) cur_idx[2 * P + 1] = lob + k;
                 }
             }
         }
     }
+    }   // batches
 #pragma unroll
     for (int P = 0; P < kPix / 2; ++P) {
         pix[2 * P] = make_float3(lo2(pr[P]), lo2(pg[P]), lo2(pb[P]));
@@ -717,6 +756,11 @@ k_fit_tiles(int W, int H, int tx, int row0, const int32_t* __restrict__ tile_off
     // transposed reduction leaves the total of value l in lane l of the group, and one reduction
     // instruction per pass adds the four pairs' 8 consecutive floats to their gradient rows.
     const int sub = lane >> 3, l8 = lane & 7;
+    for (int bat = nbat - 1; bat >= 0; --bat) {   // the forward left the last batch staged
+    if (bat != nbat - 1) {
+        __syncthreads();
+        nb = stage_tile_window(packed + 3 * (size_t)lo, cnt, bat * GS2D_MAX_PER_TILE, sq, tid);
+    }
     for (int r0 = warp * 4; r0 < nb; r0 += (kTileThreads / 32) * 4) {
         const int k = min(r0 + sub, nb - 1);
         const float4 q1 = sq[3 * k + 1];
@@ -793,6 +837,7 @@ k_fit_tiles(int W, int H, int tx, int row0, const int32_t* __restrict__ tile_off
         float* row = grads + (size_t)__float_as_int(q1.w) * 12;
         if (live && tot != 0.f) atomicAdd(row + l8, tot);   // 4 pairs x 8 consecutive floats
     }
+    }   // batches
 }
 
 // ------------------------------------------------------------------------------------------
@@ -1262,7 +1307,7 @@ int gs2d_fit_step_band(int n, int cap, int img_h, int img_w, float* xyz_raw, flo
     }
     const bool sharded = rt.R > 0;
     float* rgb_w = nullptr; float* adan_w = nullptr; float* rgb_w_grad_out = nullptr;
-    int adan_step = step, adan_fresh = step == 1, skip_update = 0, slots = 0, analytic = 0;
+    int adan_step = step, adan_fresh = step == 1, skip_update = 0, slots = 0, analytic = 0, all_per_tile = 0;
     if (options) {
         slots = options->slots != 0;
         GS2D_REQUIRE(!slots || (long long)cap >= (long long)L.tiles * GS2D_MAX_PER_TILE,
@@ -1274,6 +1319,8 @@ int gs2d_fit_step_band(int n, int cap, int img_h, int img_w, float* xyz_raw, flo
         if (options->adan_step > 0) { adan_step = options->adan_step; adan_fresh = options->adan_fresh != 0; }
         skip_update = options->skip_update != 0;
         analytic = options->analytic_grad != 0;
+        all_per_tile = options->all_per_tile != 0;
+        GS2D_REQUIRE(!(all_per_tile && slots), "fit_step: all_per_tile needs tile ranges (a slot holds 256 records)");
     }
     GS2D_REQUIRE(!sharded || (slots && rgb_w == nullptr && !skip_update),
                  "fit_step: a sharded update needs tile slots (and has no prune / add control)");
@@ -1304,23 +1351,27 @@ int gs2d_fit_step_band(int n, int cap, int img_h, int img_w, float* xyz_raw, flo
         }
         const int32_t* tile_off_arg = slots ? nullptr : (const int32_t*)(w + L.off_tile_off);
         const float grad_scale = (float)(2.0 / (3.0 * (double)img_h * (double)img_w));   // the WHOLE frame's mean
+        const int tile_flags = (banded ? kTileLossInGrads : 0) | (all_per_tile ? kTileAllPerTile : 0);
         ProfScope ps_(GS2D_STAGE_FIT_TILES, s);
         const dim3 grid(tx, row1 - row0);
         if (target_format == GS2D_TARGET_F32_CHW)
-            GS2D_CHECK_CUDA(launch_pdl(k_fit_tiles<0, 0>, grid, dim3(kTileThreads), s,
+            GS2D_CHECK_CUDA(launch_pdl(all_per_tile ? k_fit_tiles<0, 0, true> : k_fit_tiles<0, 0, false>, grid,
+                dim3(kTileThreads), s,
                 img_w, img_h, tx, row0, tile_off_arg, (int32_t*)(w + L.off_tile_count),
                 (const float4*)(w + L.off_packed), target, grad_scale, grads, loss + (step % GS2D_FIT_LOSS_SLOTS),
-                status, out_img, 1, 1, (int32_t*)nullptr, ids_sorted_out, step, banded ? 1 : 0));
+                status, out_img, 1, 1, (int32_t*)nullptr, ids_sorted_out, step, tile_flags));
         else if (target_format == GS2D_TARGET_U8_HWC)
-            GS2D_CHECK_CUDA(launch_pdl(k_fit_tiles<0, 1>, grid, dim3(kTileThreads), s,
+            GS2D_CHECK_CUDA(launch_pdl(all_per_tile ? k_fit_tiles<0, 1, true> : k_fit_tiles<0, 1, false>, grid,
+                dim3(kTileThreads), s,
                 img_w, img_h, tx, row0, tile_off_arg, (int32_t*)(w + L.off_tile_count),
                 (const float4*)(w + L.off_packed), target, grad_scale, grads, loss + (step % GS2D_FIT_LOSS_SLOTS),
-                status, out_img, 1, 1, (int32_t*)nullptr, ids_sorted_out, step, banded ? 1 : 0));
+                status, out_img, 1, 1, (int32_t*)nullptr, ids_sorted_out, step, tile_flags));
         else
-            GS2D_CHECK_CUDA(launch_pdl(k_fit_tiles<0, 2>, grid, dim3(kTileThreads), s,
+            GS2D_CHECK_CUDA(launch_pdl(all_per_tile ? k_fit_tiles<0, 2, true> : k_fit_tiles<0, 2, false>, grid,
+                dim3(kTileThreads), s,
                 img_w, img_h, tx, row0, tile_off_arg, (int32_t*)(w + L.off_tile_count),
                 (const float4*)(w + L.off_packed), target, grad_scale, grads, loss + (step % GS2D_FIT_LOSS_SLOTS),
-                status, out_img, 1, 1, (int32_t*)nullptr, ids_sorted_out, step, banded ? 1 : 0));
+                status, out_img, 1, 1, (int32_t*)nullptr, ids_sorted_out, step, tile_flags));
         GS2D_CHECK_LAUNCH("fit_tiles");
     }
     const bool own_barrier = exchange && exchange->barrier_pads &&
@@ -1448,14 +1499,17 @@ int gs2d_render_chol(int n, int cap, int img_h, int img_w, const float* means_or
     cudaStream_t s = (cudaStream_t)stream;
     char* w = (char*)work;
     const int tx = div_up(img_w, GS2D_TILE), ty = div_up(img_h, GS2D_TILE);
-    rc = launch_bin(n, means_or_xyz_raw, chol, colors, opacities, nullptr, activate, img_h, img_w, 0, ty, cap, 0, L, w, s);
+    const int tile_flags = (activate & GS2D_RENDER_ALL_PER_TILE) ? kTileAllPerTile : 0;
+    rc = launch_bin(n, means_or_xyz_raw, chol, colors, opacities, nullptr, (activate & GS2D_RENDER_ACTIVATE) ? 1 : 0, img_h,
+                    img_w, 0, ty, cap, 0, L, w, s);
     if (rc != GS2D_OK) return rc;
     {
         ProfScope ps_(GS2D_STAGE_RASTER_FWD, s);
-        k_fit_tiles<1, 0><<<dim3(tx, ty), kTileThreads, 0, s>>>(
+        auto kern = tile_flags ? k_fit_tiles<1, 0, true> : k_fit_tiles<1, 0, false>;
+        kern<<<dim3(tx, ty), kTileThreads, 0, s>>>(
             img_w, img_h, tx, 0, (const int32_t*)(w + L.off_tile_off), (int32_t*)(w + L.off_tile_count),
             (const float4*)(w + L.off_packed), nullptr, 0.f, nullptr, nullptr, (int32_t*)(w + L.off_status),
-            out_img, out_chw, out_clamp, final_idx, ids_sorted_out, 0, 0);
+            out_img, out_chw, out_clamp, final_idx, ids_sorted_out, 0, tile_flags);
         GS2D_CHECK_LAUNCH("render_tiles");
     }
     return GS2D_OK;

@@ -174,15 +174,23 @@ class FusedFrameFit(torch.nn.Module):
                  init: dict | None = None, betas=(0.98, 0.92, 0.99), eps: float = 1e-8, weight_decay: float = 0.0,
                  cap: int | None = None, lr_step_size: int = 20000, lr_gamma: float = 0.5, isdensity: bool = False,
                  isremoval: bool = False, removal_rate: float = 0.1, max_num_points: int | None = None,
-                 densification_interval: int = 100, plan=None, slots: bool = True, analytic_grad: bool | None = None):
+                 densification_interval: int = 100, plan=None, slots: bool = True, analytic_grad: bool | None = None,
+                 max_per_tile: int | None = None):
         """slots: fixed 256-record slots per tile instead of tile ranges (include/gs2d.h,
         gs2d_fit_options.slots): two kernels per iteration instead of three.  The first tile that
         would need a 257th record switches the model to ranges for good (same results, see _recover).
         analytic_grad: the projection backward's analytic gradient instead of the reference's formula
-        (SURVEY Q12 / 8f.4); None = gsvc_b200.options.analytic_projection_grad (default off)."""
+        (SURVEY Q12 / 8f.4); None = gsvc_b200.options.analytic_projection_grad (default off).
+        max_per_tile: 256 = the reference renders (and fits) only the first 256 Gaussians of a tile
+        (SURVEY Q1); 0 = all of them, in batches of 256 (a tile that fills its 256 slots moves the model to
+        tile ranges, where that applies); None = gsvc_b200.options.max_per_tile (default 256)."""
         super().__init__()
         from .options import options as _options
         self.analytic_grad = bool(_options.analytic_projection_grad if analytic_grad is None else analytic_grad)
+        mpt = int(_options.max_per_tile if max_per_tile is None else max_per_tile)
+        if mpt not in (0, 256):
+            raise ValueError("max_per_tile must be 256 (the reference) or 0 (no limit)")
+        self.all_per_tile = mpt == 0
         import ctypes
         from . import _lib
         from . import cuda as _C
@@ -279,6 +287,7 @@ class FusedFrameFit(torch.nn.Module):
         o.adan_step, o.adan_fresh, o.skip_update = int(adan_step), int(fresh), int(skip)
         o.slots = int(self.slots)
         o.analytic_grad = int(self.analytic_grad)
+        o.all_per_tile = int(self.all_per_tile and not self.slots)   # slots hold 256: a fuller tile moves the model to ranges
         return o
 
     def _issue(self, gt, fmt, out_img=None, grads_out=None, ids_out=None, w_grad_out=None, stream=None):
@@ -553,7 +562,8 @@ class FusedFrameFit(torch.nn.Module):
         with self._C._guard(self.device):
             self._lib.check(self._lib.load().gs2d_render_chol(
                 self.n, self.cap, self.H, self.W, self._xyz.data_ptr(), self._cholesky.data_ptr(),
-                colors.data_ptr(), None, 1, self._render_work.data_ptr(), self._render_work.numel(),
+                colors.data_ptr(), None, 1 | (4 if self.all_per_tile else 0), self._render_work.data_ptr(),
+                self._render_work.numel(),
                 out.data_ptr(), 1, 1, None, None, torch.cuda.current_stream(self.device).cuda_stream), "render_chol")
         return out
 

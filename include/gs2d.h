@@ -375,6 +375,9 @@ typedef struct {
     int adan_fresh;
     int skip_update;
     int slots;
+    int all_per_tile;    /* != 0: every Gaussian of a tile is rendered and gets its gradient, in batches of 256,
+                          * where the reference stops after the first 256 (forward.cu:566-614, SURVEY Q1 /
+                          * 8f.4).  Needs slots == 0 (tile ranges).  Off = parity with the reference. */
     int analytic_grad;   /* != 0: the projection backward uses the analytic gradient of the forward instead
                           * of the reference's formula (see
                           * gs2d_project_chol_bwd_analytic).  Off = parity with the reference. */
@@ -449,11 +452,14 @@ int gs2d_frame_pipe_release(gs2d_frame_pipe* pipe, int slot, gs2d_stream_t strea
  * (oracle/yuv.py states it; bit-exact against cv2 over all 2^24 triples).  H and W even. */
 int gs2d_i420_to_rgb(int img_h, int img_w, const uint8_t* yuv, uint8_t* rgb, gs2d_stream_t stream);
 /* Render-only (decode): project_gaussians_2d + rasterize_gaussians_sum forward of the reference
- * (GaussianSplats_Represent.py:83-90) as three kernels, sync-free.  activate != 0: inputs are
- * the raw parameters (tanh / bound applied here); else means2d / L_elements as the projection
- * API takes them.  opacities may be NULL (= 1).  out_img fp32: planar [3][H][W] when out_chw,
+ * (GaussianSplats_Represent.py:83-90) as three kernels, sync-free.  activate is a bit set:
+ * GS2D_RENDER_ACTIVATE (1; any odd value): inputs are the raw parameters (tanh / bound applied here),
+ * else means2d / L_elements as the projection API takes them; GS2D_RENDER_ALL_PER_TILE (4): every
+ * Gaussian of a tile is rendered, not only the first 256 (see gs2d_fit_options.all_per_tile).  opacities may be NULL (= 1).  out_img fp32: planar [3][H][W] when out_chw,
  * else [H][W][3]; clamped to [0,1] when out_clamp.  final_idx [H][W] and ids_sorted_out may be
  * NULL.  work as above (gs2d_fit_init first; the Adan pointer may be NULL there). */
+#define GS2D_RENDER_ACTIVATE 1
+#define GS2D_RENDER_ALL_PER_TILE 4
 int gs2d_render_chol(int n, int cap, int img_h, int img_w, const float* means_or_xyz_raw, const float* chol,
                      const float* colors, const float* opacities, int activate, void* work, size_t work_bytes,
                      float* out_img, int out_chw, int out_clamp, int32_t* final_idx, int32_t* ids_sorted_out,

@@ -303,3 +303,56 @@ def test_fused_fit_step_with_analytic_gradient():
     # same raster gradients (up to the order of the atomics), different Cholesky formula for l11 / l21 only
     assert _rel(r[:, 0:2], a[:, 0:2]) <= 1e-4 and _rel(r[:, 4], a[:, 4]) <= 1e-4 and _rel(r[:, 5:8], a[:, 5:8]) <= 1e-4
     assert _rel(r[:, 2:4], a[:, 2:4]) > 1e-2
+
+
+def test_fused_fit_step_renders_every_gaussian_of_a_tile_on_request():
+    """FusedFrameFit(max_per_tile=0): tiles with more than 256 Gaussians are rendered and fitted in
+    batches of 256.  Checker: the drop-in operators with options.max_per_tile = 0, themselves pinned
+    against the reference's N-channel kernels above.  Ids come out in the reference's sorted order
+    for the whole tile range (nothing is dropped), the render equals the operators' image, and the
+    default (256) differs visibly on this fixture."""
+    import gsvc_b200 as G
+    from gsvc_b200.fit import FusedFrameFit
+    H, W, n = 96, 128, 6_000
+    g = synth.gaussians(n, seed=11, trained_like=True)
+    gt = synth.target_frame(H, W, seed=11).to(cuda)
+    tb = ((W + 15) // 16, (H + 15) // 16, 1)
+
+    xyz = g["_xyz"].to(cuda).requires_grad_(True)
+    chol = g["_cholesky"].to(cuda).requires_grad_(True)
+    feat = g["_features_dc"].to(cuda).requires_grad_(True)
+    with G.options.override(max_per_tile=0):
+        p = G.project_gaussians_2d(torch.tanh(xyz), chol + torch.tensor([0.5, 0.0, 0.5], device=cuda), H, W, tb)
+        out = G.rasterize_gaussians_sum(*p, feat, torch.ones(n, 1, device=cuda), H, W, 16, 16)
+        loss = torch.nn.functional.mse_loss(out.clamp(0, 1).permute(2, 0, 1).unsqueeze(0), gt)
+        loss.backward()
+    r = ref_gpu.bin_and_sort(n, *(t.detach() for t in (p[0], p[1], p[2], p[4])), tb)
+    cnt = r["tile_bins"][: tb[0] * tb[1], 1] - r["tile_bins"][: tb[0] * tb[1], 0]
+    assert cnt.max().item() > 256 + 64
+
+    fit = FusedFrameFit(H, W, n, cuda, init=g, slots=False, max_per_tile=0)
+    img0 = fit.forward()
+    assert (img0[0].permute(1, 2, 0) - out.detach().clamp(0, 1)).abs().max().item() <= 1e-5
+    grads = torch.empty((n, 8), device=cuda)
+    ids = torch.full((fit.cap,), -7, dtype=torch.int32, device=cuda)
+    fit.train_iters(gt, 1, grads_out=grads, ids_out=ids)
+    assert fit.status()[1] == 0
+    I = r["num_intersects"]
+    assert torch.equal(ids[:I], r["gaussian_ids_sorted"])
+    assert abs(fit.loss() - loss.item()) <= 1e-5 * loss.item()
+    assert _rel(grads[:, 0:2], xyz.grad) <= 2e-4
+    assert _rel(grads[:, 2:5], chol.grad) <= 2e-4
+    assert _rel(grads[:, 5:8], feat.grad) <= 2e-4
+
+    # a model on tile slots moves to ranges at the first fuller tile and then renders all of it too
+    fit_s = FusedFrameFit(H, W, n, cuda, init=g, slots=True, max_per_tile=0)
+    fit_s.train_iters(gt, 1)
+    with pytest.raises(RuntimeError):
+        fit_s.loss()
+    assert fit_s.slots is False
+    fit_s.train_iters(gt, 1)
+    assert abs(fit_s.loss() - loss.item()) <= 1e-5 * loss.item()
+
+    ref256 = FusedFrameFit(H, W, n, cuda, init=g, slots=False)
+    ref256.train_iters(gt, 1)
+    assert abs(ref256.loss() - loss.item()) > 1e-3 * loss.item()
