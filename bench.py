@@ -491,7 +491,8 @@ def main_gop(args, rank: int, world: int, local_rank: int):
     a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     wall0 = time.perf_counter()
     a.record()
-    out = gop.fit_sequence(get, F, keyframes, make, args.gop_iters_key, args.gop_iters_pred, group=gather_group)
+    out = gop.fit_sequence(get, F, keyframes, make, args.gop_iters_key, args.gop_iters_pred, group=gather_group,
+                           chains=args.gop_chains)
     b.record()
     torch.cuda.synchronize(dev)
     if world > 1:
@@ -516,7 +517,8 @@ def main_gop(args, rank: int, world: int, local_rank: int):
                                    f"predicted frames {args.gop_iters_pred} iters with random add + prune",
                        "H": H, "W": W, "gaussians": NPTS, "gops": len(gops),
                        "gops_per_rank": [len(x) for x in gop.assign_gops(gops, world, cost=cost)],
-                       "parallelism": f"{len(gops)} key-frame-delimited GOPs over {world} GPU(s), no data-path collective"},
+                       "parallelism": f"{len(gops)} key-frame-delimited GOPs over {world} GPU(s), no data-path collective; "
+                                      f"up to {args.gop_chains} concurrent chain(s) per GPU"},
             "clocks": clocks, "gpu_launches": launches, "fit_iterations": iters,
             "fit_iters_per_s": iters / (ms * 1e-3), "wall_s_timed_region": wall,
             "psnr_mean": sum(psnrs) / len(psnrs), "psnr_min": min(psnrs),
@@ -536,6 +538,8 @@ def main():
                     help="fit: the headline line (C2 + C3 render); gop: BASELINE config 4 (sequence, GOP sharding)")
     ap.add_argument("--gop-frames", type=int, default=120)
     ap.add_argument("--gop-cut", type=int, default=30, help="scene cut (key frame) every this many frames")
+    ap.add_argument("--gop-chains", type=int, default=4,
+                    help="GOPs a rank fits concurrently (own stream + host thread each); 1 = one after the other")
     ap.add_argument("--gop-detect", action="store_true",
                     help="run the key-frame detection pre-pass first and shard by the key frames it finds")
     ap.add_argument("--gop-iters-key", type=int, default=4100,

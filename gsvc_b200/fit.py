@@ -218,6 +218,7 @@ class FusedFrameFit(torch.nn.Module):
         else:
             self.rgb_W = None
         self.clock = OptimizerClock()
+        self.rng = None   # torch.Generator for the random add (None = torch's global CPU generator)
         self._opts = _lib.FitOptions()
         self._cdll = _lib.load()
         self._tile_rows = (self.H + 15) // 16
@@ -361,7 +362,9 @@ class FusedFrameFit(torch.nn.Module):
         else:
             # same draws, in the same order, from the global CPU generator as the reference
             c = act.count
-            add = [torch.atanh(2 * (torch.rand(c, 2) - 0.5)), torch.rand(c, 3), torch.rand(c, 3), 0.01 * torch.ones(c, 1)]
+            g = self.rng   # None: the global CPU generator, as the reference; gop.fit_gop hands every frame its own
+            add = [torch.atanh(2 * (torch.rand(c, 2, generator=g) - 0.5)), torch.rand(c, 3, generator=g),
+                   torch.rand(c, 3, generator=g), 0.01 * torch.ones(c, 1)]
             old = [self._xyz, self._cholesky, self._features_dc, self.rgb_W]
             cat = [torch.cat((o, a.to(dev)), dim=0) for o, a in zip(old, add)]
             new = [cat[3], cat[0], cat[1], cat[2]]

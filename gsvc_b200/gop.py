@@ -57,9 +57,14 @@ def fit_gop(get_frame: Callable[[int], torch.Tensor], gop: Gop, make_fitter: Cal
     for f in range(gop[0], gop[1]):
         if seed is not None:
             # every frame draws (fresh Gaussians, the random add) from its own stream, so the result
-            # of a frame does not depend on which rank fitted which other frames before it
+            # of a frame does not depend on which rank (or which of a rank's concurrent chains) fitted
+            # which other frames before it
             torch.manual_seed(int(seed) * 100003 + f)
         fit = make_fitter(prev)
+        if seed is not None and hasattr(fit, "rng"):
+            # the same stream as a private generator (same engine, same seed => same draws): two chains
+            # of one process cannot then interleave their draws from the global generator
+            fit.rng = torch.Generator().manual_seed(int(seed) * 100003 + f)
         iters = iters_key if prev is None else iters_pred
         gt = get_frame(f)
         fit.train_iters(gt, iters)
@@ -76,9 +81,14 @@ def fit_gop(get_frame: Callable[[int], torch.Tensor], gop: Gop, make_fitter: Cal
 
 def fit_sequence(get_frame: Callable[[int], torch.Tensor], num_frames: int, keyframes: Sequence[int],
                  make_fitter: Callable[[Optional[dict]], object], iters_key: int, iters_pred: int,
-                 group=None, seed: Optional[int] = 1) -> Optional[Dict[int, dict]]:
+                 group=None, seed: Optional[int] = 1, chains: int = 1) -> Optional[Dict[int, dict]]:
     """Every rank fits its share of the GOPs; rank 0 returns {frame: result} for the whole
-    sequence (other ranks return None).  Works without torch.distributed (one process)."""
+    sequence (other ranks return None).  Works without torch.distributed (one process).
+
+    chains > 1: a rank with several GOPs fits up to that many of them CONCURRENTLY, each chain on a
+    CUDA stream of its own fed by a host thread of its own.  A fit iteration is two dependent kernels
+    and the second (the per-Gaussian update) leaves most of the GPU idle; a second independent chain
+    fills it.  Results do not depend on `chains` (every frame has its own random stream)."""
     distributed = dist.is_available() and dist.is_initialized()
     world = dist.get_world_size(group) if distributed else 1
     rank = dist.get_rank(group) if distributed else 0
@@ -86,8 +96,13 @@ def fit_sequence(get_frame: Callable[[int], torch.Tensor], num_frames: int, keyf
     # a keyframe costs iters_key, a predicted frame iters_pred
     mine = assign_gops(gops, world, cost=lambda g: iters_key + (g[1] - g[0] - 1) * iters_pred)[rank]
     local: Dict[int, dict] = {}
-    for g in mine:
-        local.update(fit_gop(get_frame, g, make_fitter, iters_key, iters_pred, seed=seed))
+    cost = lambda g: iters_key + (g[1] - g[0] - 1) * iters_pred
+    lanes = [l for l in assign_gops(mine, max(1, min(int(chains), len(mine))), cost=cost) if l] if mine else []
+    if len(lanes) <= 1 or not torch.cuda.is_available():
+        for g in mine:
+            local.update(fit_gop(get_frame, g, make_fitter, iters_key, iters_pred, seed=seed))
+    else:
+        local.update(_fit_lanes(get_frame, lanes, make_fitter, iters_key, iters_pred, seed))
     if not distributed:
         return local
     gathered = [None] * world if rank == 0 else None
@@ -99,6 +114,41 @@ def fit_sequence(get_frame: Callable[[int], torch.Tensor], num_frames: int, keyf
         merged.update(part)
     assert sorted(merged) == list(range(num_frames)), "GOP sharding lost or duplicated frames"
     return merged
+
+
+def _fit_lanes(get_frame, lanes, make_fitter, iters_key, iters_pred, seed) -> Dict[int, dict]:
+    """one host thread + one CUDA stream per lane (a list of GOPs fitted in order); the caller's
+    stream waits for all of them, so events recorded around fit_sequence span the whole work"""
+    import threading
+    dev = torch.cuda.current_device()
+    main = torch.cuda.current_stream(dev)
+    streams = [torch.cuda.Stream(dev) for _ in lanes]
+    results: List[Dict[int, dict]] = [dict() for _ in lanes]
+    errors: List[BaseException] = []
+
+    def work(i: int):
+        try:
+            torch.cuda.set_device(dev)
+            streams[i].wait_stream(main)
+            with torch.cuda.stream(streams[i]):
+                for g in lanes[i]:
+                    results[i].update(fit_gop(get_frame, g, make_fitter, iters_key, iters_pred, seed=seed))
+        except BaseException as e:   # noqa: BLE001 -- re-raised on the caller's thread
+            errors.append(e)
+
+    threads = [threading.Thread(target=work, args=(i,), name=f"gop-lane-{i}") for i in range(len(lanes))]
+    for t in threads:
+        t.start()
+    for t in threads:
+        t.join()
+    for s in streams:
+        main.wait_stream(s)
+    if errors:
+        raise errors[0]
+    out: Dict[int, dict] = {}
+    for r in results:
+        out.update(r)
+    return out
 
 
 def synthetic_sequence(H: int, W: int, num_frames: int = 120, cut_every: int = 30, shift_px: float = 2.0,

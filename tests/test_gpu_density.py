@@ -193,3 +193,24 @@ def test_keyframe_prepass_finds_the_scene_cuts():
     assert gop.keyframes_from_scores(scores) == cuts == [0, 4, 8]
     at_cuts = min(scores[4], scores[8])
     assert at_cuts > 3 * max(s for i, s in enumerate(scores) if i not in (0, 4, 8))
+
+
+def test_concurrent_gop_chains_give_the_sequential_result():
+    """gop.fit_sequence(chains=2): two GOPs of one rank fitted at the same time, each on its own
+    stream and host thread.  Every frame has its own random stream, so the prune / add schedule, the
+    Gaussian counts and the fitted frames equal the one-after-the-other run (up to the order of the
+    gradient atomics)."""
+    from gsvc_b200 import gop
+    H, W, F, n = 96, 128, 6, 1500
+    frame, cuts = gop.synthetic_sequence(H, W, F, cut_every=3, seed=2)
+    frames = [frame(f).to(cuda) for f in range(F)]
+    make = gop.reference_fitters(H, W, n, cuda, densification_interval=20)
+    run = lambda chains: gop.fit_sequence(lambda f: frames[f], F, cuts, make, iters_key=260, iters_pred=120,
+                                          chains=chains)
+    a, b = run(1), run(2)
+    assert sorted(a) == sorted(b) == list(range(F))
+    for f in range(F):
+        assert a[f]["num_points"] == b[f]["num_points"] and a[f]["iters"] == b[f]["iters"]
+        assert abs(a[f]["psnr"] - b[f]["psnr"]) <= 0.05, (f, a[f]["psnr"], b[f]["psnr"])
+    # the frames really went through the prune / add control
+    assert any(a[f]["num_points"] != n for f in range(F))
