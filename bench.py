@@ -155,6 +155,11 @@ def make_cpu_fit(seed=1):
 
 
 def run_cpu(steps: int, warmup: int) -> dict:
+    from oracle import oracle as _O
+    try:   # every host core this process may run on (torchrun exports OMP_NUM_THREADS=1 to its ranks)
+        _O.set_num_threads(len(os.sched_getaffinity(0)))
+    except (AttributeError, OSError):
+        pass
     fit = make_cpu_fit()
     for _ in range(warmup):
         fit.step()

@@ -416,3 +416,13 @@ int gs2d_oracle_num_threads(void) {
     return 1;
 #endif
 }
+
+/* bench.py's CPU arm: use this many OpenMP threads from now on (torchrun exports OMP_NUM_THREADS=1
+ * to every rank, which would otherwise leave the timed CPU baseline on one core) */
+void gs2d_oracle_set_num_threads(int n) {
+#ifdef _OPENMP
+    if (n > 0) omp_set_num_threads(n);
+#else
+    (void)n;
+#endif
+}

@@ -54,6 +54,10 @@ def num_threads() -> int:
     return int(lib().gs2d_oracle_num_threads())
 
 
+def set_num_threads(n: int) -> None:
+    lib().gs2d_oracle_set_num_threads(int(n))
+
+
 def tile_bounds_of(H: int, W: int):
     return ((W + 15) // 16, (H + 15) // 16, 1)
 
