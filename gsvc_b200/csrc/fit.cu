@@ -241,6 +241,7 @@ k_fit_count(int n, const float* __restrict__ xyz_raw, const float* __restrict__ 
     __shared__ int sh[8];
     __shared__ int s_last;
     const int i = blockIdx.x * kFitThreads + threadIdx.x;
+    pdl_release();   // render chain: the scatter kernel's projection may run under this kernel (it waits before it reads the scan)
     if (i < n) {
         Proj2d p; float2 m; float3 L;
         fit_project(i, xyz_raw, chol_raw, activate, half_w, half_h, tx, ty, p, m, L, qc);
@@ -354,14 +355,22 @@ k_fit_scatter(int n, const float* __restrict__ xyz_raw, const float* __restrict_
     __shared__ int sh[8];
     // not an early return: in slot mode another block may raise the flag while this one runs, and
     // every thread must reach the block sum below
-    const bool dead = status[kStOverflow] != 0;
     const int i = blockIdx.x * kFitThreads + threadIdx.x;
     int claimed = 0;
-    if (i < n && !dead) {
-        Proj2d p; float2 m; float3 L;
+    // the projection depends on the parameters alone: launched programmatically after the count kernel
+    // (render chain) it runs under that kernel; everything the count / scan wrote is read after the wait
+    Proj2d p; float2 m; float3 L;
+    float o = 1.f;
+    float3 col = make_float3(0.f, 0.f, 0.f);
+    if (i < n) {
         fit_project(i, xyz_raw, chol_raw, activate, half_w, half_h, tx, ty, p, m, L, qc);
-        const float o = opac ? opac[i] : 1.f;
-        const float3 col = fit_colour(i, feat, rgb_w, activate, qc);
+        o = opac ? opac[i] : 1.f;
+        col = fit_colour(i, feat, rgb_w, activate, qc);
+    }
+    pdl_wait();
+    pdl_release();
+    const bool dead = status[kStOverflow] != 0;
+    if (i < n && !dead) {
         const float r = col.x, g = col.y, b = col.z;
         if (slots)
             claimed = scatter_records<true>(p, i, o, r, g, b, tx, row0, row1, W, H, nullptr, tile_fill, packed, status, step, rt);
@@ -1222,7 +1231,7 @@ int gs2d_fit_init(int n, int cap, int img_h, int img_w, void* work, size_t work_
 static int launch_bin(int n, const float* xyz, const float* chol, const float* feat, const float* opac,
                       const float* rgb_w, int activate,
                       int img_h, int img_w, int row0, int row1, int cap, int step, const gs2d_fit_layout& L, char* w,
-                      cudaStream_t s, bool precounted = false, const QuantConst& qc = QuantConst()) {
+                      cudaStream_t s, bool precounted = false, const QuantConst& qc = QuantConst(), bool pdl = false) {
     const int tx = div_up(img_w, GS2D_TILE), ty = div_up(img_h, GS2D_TILE);
     const float half_w = 0.5f * (float)(unsigned)img_w, half_h = 0.5f * (float)(unsigned)img_h;
     int32_t* status = (int32_t*)(w + L.off_status);
@@ -1237,9 +1246,14 @@ static int launch_bin(int n, const float* xyz, const float* chol, const float* f
     }
     {
         ProfScope ps_(GS2D_STAGE_EDGES_PACK, s);
-        k_fit_scatter<<<blocks, kFitThreads, 0, s>>>(n, xyz, chol, feat, opac, rgb_w, activate, half_w, half_h, tx, ty,
-                                                     row0, row1, img_w, img_h, tile_off, tile_count, status,
-                                                     (float4*)(w + L.off_packed), 0, step, qc, Route());
+        if (pdl && !precounted)   // render chain: count -> scatter -> tiles, each under its predecessor's tail
+            GS2D_CHECK_CUDA(launch_pdl(k_fit_scatter, dim3(blocks), dim3(kFitThreads), s, n, xyz, chol, feat, opac, rgb_w,
+                                       activate, half_w, half_h, tx, ty, row0, row1, img_w, img_h, (const int32_t*)tile_off,
+                                       tile_count, status, (float4*)(w + L.off_packed), 0, step, qc, Route()));
+        else
+            k_fit_scatter<<<blocks, kFitThreads, 0, s>>>(n, xyz, chol, feat, opac, rgb_w, activate, half_w, half_h, tx, ty,
+                                                         row0, row1, img_w, img_h, tile_off, tile_count, status,
+                                                         (float4*)(w + L.off_packed), 0, step, qc, Route());
         GS2D_CHECK_LAUNCH("fit_scatter");
     }
     return GS2D_OK;
@@ -1447,14 +1461,14 @@ int gs2d_render_quantized(int n, int cap, int img_h, int img_w, const gs2d_quant
     char* w = (char*)work;
     const int tx = div_up(img_w, GS2D_TILE), ty = div_up(img_h, GS2D_TILE);
     rc = launch_bin(n, (const float*)q->xyz_half, (const float*)q->chol_code, (const float*)q->color_index, nullptr,
-                    nullptr, 2, img_h, img_w, 0, ty, cap, 0, L, w, s, false, qc);
+                    nullptr, 2, img_h, img_w, 0, ty, cap, 0, L, w, s, false, qc, true);
     if (rc != GS2D_OK) return rc;
     {
         ProfScope ps_(GS2D_STAGE_RASTER_FWD, s);
-        k_fit_tiles<1, 0><<<dim3(tx, ty), kTileThreads, 0, s>>>(
+        GS2D_CHECK_CUDA(launch_pdl(k_fit_tiles<1, 0, false>, dim3(tx, ty), dim3(kTileThreads), s,
             img_w, img_h, tx, 0, (const int32_t*)(w + L.off_tile_off), (int32_t*)(w + L.off_tile_count),
-            (const float4*)(w + L.off_packed), nullptr, 0.f, nullptr, nullptr, (int32_t*)(w + L.off_status),
-            out_img, out_chw, out_clamp, final_idx, ids_sorted_out, 0, 0);
+            (const float4*)(w + L.off_packed), (const void*)nullptr, 0.f, (float*)nullptr, (double*)nullptr,
+            (int32_t*)(w + L.off_status), out_img, out_chw, out_clamp, final_idx, ids_sorted_out, 0, 0));
         GS2D_CHECK_LAUNCH("render_tiles");
     }
     return GS2D_OK;
@@ -1501,15 +1515,15 @@ int gs2d_render_chol(int n, int cap, int img_h, int img_w, const float* means_or
     const int tx = div_up(img_w, GS2D_TILE), ty = div_up(img_h, GS2D_TILE);
     const int tile_flags = (activate & GS2D_RENDER_ALL_PER_TILE) ? kTileAllPerTile : 0;
     rc = launch_bin(n, means_or_xyz_raw, chol, colors, opacities, nullptr, (activate & GS2D_RENDER_ACTIVATE) ? 1 : 0, img_h,
-                    img_w, 0, ty, cap, 0, L, w, s);
+                    img_w, 0, ty, cap, 0, L, w, s, false, QuantConst(), true);
     if (rc != GS2D_OK) return rc;
     {
         ProfScope ps_(GS2D_STAGE_RASTER_FWD, s);
-        auto kern = tile_flags ? k_fit_tiles<1, 0, true> : k_fit_tiles<1, 0, false>;
-        kern<<<dim3(tx, ty), kTileThreads, 0, s>>>(
+        GS2D_CHECK_CUDA(launch_pdl(tile_flags ? k_fit_tiles<1, 0, true> : k_fit_tiles<1, 0, false>, dim3(tx, ty),
+            dim3(kTileThreads), s,
             img_w, img_h, tx, 0, (const int32_t*)(w + L.off_tile_off), (int32_t*)(w + L.off_tile_count),
-            (const float4*)(w + L.off_packed), nullptr, 0.f, nullptr, nullptr, (int32_t*)(w + L.off_status),
-            out_img, out_chw, out_clamp, final_idx, ids_sorted_out, 0, tile_flags);
+            (const float4*)(w + L.off_packed), (const void*)nullptr, 0.f, (float*)nullptr, (double*)nullptr,
+            (int32_t*)(w + L.off_status), out_img, out_chw, out_clamp, final_idx, ids_sorted_out, 0, tile_flags));
         GS2D_CHECK_LAUNCH("render_tiles");
     }
     return GS2D_OK;
