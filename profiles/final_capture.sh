@@ -2,7 +2,7 @@
 # One-GPU evidence run (under gpurun): tests, smoke, the bench line, then -- each only after its own command
 # exited 0 without ncu -- the ncu launch list of the same bench command and one `--set full` capture of the
 # two fit kernels.  Outputs land in gpurun_out/ (copied to profiles/ by hand).
-T=${1:-r1_f}
+T=${1:-r1_g}
 python -m pytest tests -m gpu -q 2>&1 | tail -2
 python __graft_entry__.py smoke 2>&1 | tail -2
 python bench.py > gpurun_out/${T}_bench.json 2> gpurun_out/${T}_bench.err || exit 1
