@@ -68,6 +68,40 @@ def test_fit_sequence_single_process():
         assert r["iters"] == (100 if f in kf else 10)
 
 
+def test_chains_split_is_a_partition_and_cpu_falls_back_to_one_chain():
+    """fit_sequence(chains=k): a rank's GOPs are split into k lanes by the same longest-first rule;
+    without CUDA the lanes run one after the other -- same result either way"""
+    kf = [0, 4, 7, 9]
+    a = gop.fit_sequence(lambda f: torch.full((3, 2, 2), float(f)), 12, kf, _FakeFit, 100, 10, chains=1)
+    b = gop.fit_sequence(lambda f: torch.full((3, 2, 2), float(f)), 12, kf, _FakeFit, 100, 10, chains=3)
+    assert sorted(a) == sorted(b) == list(range(12))
+    for f in a:
+        assert torch.equal(a[f]["state"]["_xyz"], b[f]["state"]["_xyz"]) and a[f]["iters"] == b[f]["iters"]
+    gops = gop.gops_from_keyframes(kf, 12)
+    lanes = gop.assign_gops(gops, 3)
+    assert sorted(g for lane in lanes for g in lane) == sorted(gops) and all(lane == sorted(lane) for lane in lanes)
+
+
+def test_options_defaults_are_the_reference_and_override_restores():
+    import gsvc_b200 as G
+    o = G.options
+    assert (o.analytic_projection_grad, o.max_per_tile, o.nd_channels) == (False, 256, False)
+    with o.override(max_per_tile=0, nd_channels=True):
+        assert o.max_per_tile == 0 and o.nd_channels is True
+        with o.override(analytic_projection_grad=True):
+            assert o.analytic_projection_grad is True
+        assert o.analytic_projection_grad is False
+    assert (o.analytic_projection_grad, o.max_per_tile, o.nd_channels) == (False, 256, False)
+    try:
+        with o.override(no_such_option=1):
+            pass
+    except AttributeError:
+        pass
+    else:
+        raise AssertionError("unknown option accepted")
+    assert not hasattr(o, "no_such_option")
+
+
 def _free_port():
     with socket.socket() as s:
         s.bind(("127.0.0.1", 0))
