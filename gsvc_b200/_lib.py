@@ -102,6 +102,11 @@ _SIGNATURES = {
     "gs2d_rasterize_sum_fwd_binned": (c_int, [c_int, c_int, _P, _P, _P, _P, _P, _P, c_int, c_int, _P, _P, _P, _P, c_size_t, _P]),
     "gs2d_rasterize_sum_bwd": (c_int, [c_int, c_int, c_int, c_int, _P, c_size_t, _P, _P, _P, _P]),
     "gs2d_rasterize_sum_bwd_binned": (c_int, [c_int, c_int, _P, _P, _P, _P, _P, _P, c_int, c_int, _P, _P, _P, _P, c_size_t, _P]),
+    "gs2d_opstate_bytes": (c_size_t, [c_int, c_int, c_int]),
+    "gs2d_opstate_ranges": (c_int, [c_int, c_int, c_int, POINTER(c_size_t), POINTER(c_size_t), POINTER(c_size_t)]),
+    "gs2d_rasterize_sum_fwd_ranked": (c_int, [c_int, _P, _P, _P, _P, _P, _P, c_int, c_int, c_int, _P, c_size_t, _P, _P,
+                                              _P, c_int, _P]),
+    "gs2d_rasterize_sum_bwd_ranked": (c_int, [c_int, c_int, c_int, c_int, _P, c_size_t, _P, _P, _P, _P]),
     "gs2d_rasterize_sum_nd_fwd": (c_int, [c_int, c_int, _P, _P, _P, _P, _P, _P, _P, c_int, c_int, c_int, c_int, _P, c_size_t, _P, _P, _P, _P, _P]),
     "gs2d_rasterize_sum_nd_bwd": (c_int, [c_int, c_int, c_int, c_int, c_int, c_int, _P, c_size_t, _P, _P, _P, _P, _P, _P]),
     "gs2d_fit_layout_for": (c_int, [c_int, c_int, c_int, c_int, POINTER(FitLayout)]),
@@ -119,6 +124,8 @@ _SIGNATURES = {
     "gs2d_frame_pipe_push": (c_int, [_P, _P, POINTER(c_int)]),
     "gs2d_frame_pipe_acquire": (c_int, [_P, c_int, _P, POINTER(c_void_p)]),
     "gs2d_frame_pipe_release": (c_int, [_P, c_int, _P]),
+    "gs2d_adan_step": (c_int, [c_int, _P, _P, _P, _P, _P, _P, _P, c_float, c_float, c_float, c_float, c_float, c_float,
+                               c_int, c_int, _P]),
     "gs2d_prune_scratch_bytes": (c_size_t, [c_int]),
     "gs2d_prune_lowest": (c_int, [c_int, c_int, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, c_size_t, _P]),
     "gs2d_render_chol": (c_int, [c_int, c_int, c_int, c_int, _P, _P, _P, _P, c_int, _P, c_size_t, _P, c_int, c_int,

@@ -2,10 +2,17 @@
 
 The reference's fit loop constructs `Adan(params, lr=...)` from its own optimizer.py
 (optimizer.py:65-74 of the reference: betas (0.98, 0.92, 0.99), eps 1e-8, weight_decay 0,
-no_prox False, bias-corrected, previous gradient := first gradient at step 1).  This is an
-independent implementation of the published update with those defaults; `step()` on CUDA
-parameters runs one multi-tensor kernel of libgs2d.so (gs2d_adan_step) when `fused=True`,
-else a handful of torch._foreach ops (works on CPU tensors too: used by the CPU baseline).
+max_grad_norm 0, no_prox False, bias-corrected, previous gradient := first gradient at step 1).
+This is an independent implementation of the published update for THAT configuration; the
+constructor takes the reference's keyword arguments so it can stand in for it, and refuses the
+non-default settings it does not implement (gradient clipping, no_prox) instead of ignoring them.
+
+`step()` runs one multi-tensor kernel of libgs2d.so (`gs2d_adan_step`, include/gs2d.h) when every
+parameter is a contiguous fp32 CUDA tensor (`fused=None`, the default, decides per step;
+`fused=True` insists, `fused=False` never) -- the reference's multi-tensor path is ~20
+torch._foreach launches per step (optimizer.py:296-362) and it anticipates an external fused
+kernel itself (:365-395).  Otherwise a handful of torch._foreach ops (CPU tensors too: the CPU
+tests and trajectories use that path).
 
 Per element, with g the gradient and g' the previous one (g' = g at the first step):
     m <- b1 m + (1-b1) g
@@ -17,16 +24,45 @@ Per element, with g the gradient and g' the previous one (g' = g at the first st
 """
 from __future__ import annotations
 
+import ctypes
 import math
+from typing import Optional
 
 import torch
 
 
 class Adan(torch.optim.Optimizer):
-    def __init__(self, params, lr=1e-3, betas=(0.98, 0.92, 0.99), eps=1e-8, weight_decay=0.0):
+    def __init__(self, params, lr=1e-3, betas=(0.98, 0.92, 0.99), eps=1e-8, weight_decay=0.0, max_grad_norm=0.0,
+                 no_prox=False, foreach: bool = True, fused: Optional[bool] = None):
         if lr < 0 or eps < 0 or not all(0.0 <= b < 1.0 for b in betas):
             raise ValueError("Adan: invalid hyper-parameters")
+        if max_grad_norm != 0.0:
+            raise NotImplementedError("Adan: max_grad_norm (gradient clipping, optimizer.py:148-163) is not implemented; "
+                                      "the reference's fit loop leaves it at 0")
+        if no_prox:
+            raise NotImplementedError("Adan: no_prox=True (optimizer.py:351-357) is not implemented; the reference's "
+                                      "fit loop leaves it False")
+        self.fused = fused
+        del foreach   # accepted for constructor compatibility: both paths here are multi-tensor
         super().__init__(params, dict(lr=lr, betas=betas, eps=eps, weight_decay=weight_decay))
+
+    @staticmethod
+    def _fusable(ps, gs) -> bool:
+        return all(p.is_cuda and p.dtype == torch.float32 and p.is_contiguous() and g.is_cuda
+                   and g.dtype == torch.float32 and p.device == ps[0].device for p, g in zip(ps, gs))
+
+    def _step_fused(self, ps, gs, ms, ns, ds, prevs, lr, b1, b2, b3, eps, wd, t, first):
+        from . import _lib
+        from . import cuda as _C
+        gs = [g if g.is_contiguous() else g.contiguous() for g in gs]
+        k = len(ps)
+        table = lambda ts: (ctypes.c_void_p * k)(*[x.data_ptr() for x in ts])
+        counts = (ctypes.c_int * k)(*[p.numel() for p in ps])
+        dev = ps[0].device
+        with _C._guard(dev):
+            _lib.check(_lib.load().gs2d_adan_step(k, table(ps), table(gs), table(ms), table(ns), table(ds), table(prevs),
+                                                  counts, lr, b1, b2, b3, eps, wd, t, 1 if first else 0,
+                                                  torch.cuda.current_stream(dev).cuda_stream), "adan_step")
 
     @torch.no_grad()
     def step(self, closure=None):
@@ -40,20 +76,37 @@ class Adan(torch.optim.Optimizer):
             bc1, bc2, bc3s = 1.0 - b1 ** t, 1.0 - b2 ** t, math.sqrt(1.0 - b3 ** t)
             lr, eps, wd = group["lr"], group["eps"], group["weight_decay"]
             ps, gs, ms, ns, ds, prevs = [], [], [], [], [], []
+            fresh = []
             for p in group["params"]:
                 if p.grad is None:
                     continue
                 st = self.state[p]
                 if not st:
-                    st["m"] = torch.zeros_like(p)
-                    st["n"] = torch.zeros_like(p)
-                    st["d"] = torch.zeros_like(p)
-                if "prev" not in st or t == 1:
-                    st["prev"] = p.grad.clone()
+                    st["m"] = torch.zeros_like(p, memory_format=torch.contiguous_format)
+                    st["n"] = torch.zeros_like(p, memory_format=torch.contiguous_format)
+                    st["d"] = torch.zeros_like(p, memory_format=torch.contiguous_format)
+                new_prev = "prev" not in st or t == 1
+                fresh.append(new_prev)
                 ps.append(p); gs.append(p.grad); ms.append(st["m"]); ns.append(st["n"]); ds.append(st["d"])
-                prevs.append(st["prev"])
+                prevs.append(st.get("prev"))
             if not ps:
                 continue
+            fused = self.fused
+            if fused is None or fused:
+                ok = self._fusable(ps, gs) and (all(fresh) or not any(fresh))
+                if fused and not ok:
+                    raise RuntimeError("Adan(fused=True) needs contiguous fp32 CUDA parameters on one device")
+                fused = ok
+            if fused:
+                first = all(fresh)
+                if first:   # the kernel writes prev := g; it only needs somewhere to put it
+                    for i, p in enumerate(ps):
+                        prevs[i] = self.state[p]["prev"] = torch.empty_like(p, memory_format=torch.contiguous_format)
+                self._step_fused(ps, gs, ms, ns, ds, prevs, lr, b1, b2, b3, eps, wd, t, first)
+                continue
+            for i, p in enumerate(ps):
+                if fresh[i]:
+                    prevs[i] = self.state[p]["prev"] = p.grad.clone()
             diff = torch._foreach_sub(gs, prevs)
             torch._foreach_mul_(ms, b1)
             torch._foreach_add_(ms, gs, alpha=1 - b1)

@@ -15,7 +15,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIBDIR = os.path.join(HERE, "lib")
 LIB = os.path.join(LIBDIR, "libgs2d.so")
-SOURCES = ["capi.cu", "project.cu", "binning.cu", "raster.cu", "fit.cu", "density.cu", "pipe.cu"]
+SOURCES = ["capi.cu", "project.cu", "binning.cu", "raster.cu", "fit.cu", "density.cu", "pipe.cu", "adan.cu"]
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
     "-Xcompiler", "-fPIC", "-Xcompiler", "-O2", "--expt-relaxed-constexpr",

@@ -26,6 +26,7 @@
 
 #include "gs2d_internal.h"
 #include "gs2d_math.cuh"
+#include "gs2d_stage.cuh"
 
 namespace gs2d {
 
@@ -94,14 +95,40 @@ __device__ __forceinline__ uint32_t yuv_to_rgb_packed(int y, int u, int v) {
 //      8-entry codebooks (VectorQuantizer.decompress, quantize.py:146-150: 0 + e0[i0] + e1[i1]).
 //      The pointers then hold uint16 [n][2], uint8 [n][3] and uint8 [n][2]: 9 bytes per Gaussian
 //      instead of 32, decoded in registers -- no fp32 copy of the frame's Gaussians ever exists.
+//   3  the OUTPUTS of the projection operator (operator path: rasterize_gaussians_sum is handed
+//      xys / radii / conics by its caller): nothing is projected again, the tile bbox comes from
+//      (xys, radii) exactly as the reference's map_gaussian_to_intersects recomputes it
+//      (forward.cu:113-123).  The pointers then hold xys [n][2], conics [n][3], colours [n][3] and
+//      `radii` int32 [n].
 struct QuantConst {
     float scale[3], beta[3];
     const float* codebooks;   // [2][8][3]
+    const int32_t* radii;     // activate == 3 only
+    int32_t* mail_host;       // operator path: pinned int32[8] the scan reports into (may be NULL)
+    int mail_seq;
 };
 
 __device__ __forceinline__ void fit_project(int i, const float* __restrict__ xyz_raw, const float* __restrict__ chol_raw,
                                             int activate, float half_w, float half_h, int tx, int ty, Proj2d& p,
                                             float2& means, float3& L, const QuantConst& qc) {
+    if (activate == 3) {
+        const float2 c = reinterpret_cast<const float2*>(xyz_raw)[i];
+        const int rad = qc.radii[i];
+        means = c;
+        L = make_float3(0.f, 0.f, 0.f);
+        p.cx = c.x; p.cy = c.y;
+        p.conic = make_float3(chol_raw[3 * i], chol_raw[3 * i + 1], chol_raw[3 * i + 2]);
+        p.radius = (float)rad;
+        p.x0 = p.y0 = p.x1 = p.y1 = 0;
+        p.nth = 0;
+        p.ok = rad > 0;                   // forward.cu:111: radii <= 0 emits nothing
+        if (p.ok) {
+            tile_bbox(p.cx, p.cy, p.radius, tx, ty, p.x0, p.y0, p.x1, p.y1);
+            const int area = (p.x1 - p.x0) * (p.y1 - p.y0);
+            p.nth = area > 0 ? area : 0;
+        }
+        return;
+    }
     if (activate == 2) {
         const uint32_t hx = reinterpret_cast<const uint32_t*>(xyz_raw)[i];          // two fp16
         const uint8_t* c = reinterpret_cast<const uint8_t*>(chol_raw) + 3 * (size_t)i;
@@ -150,7 +177,7 @@ __device__ __forceinline__ void count_tiles(const Proj2d& p, int tx, int row0, i
 // the per-tile counts into tile ranges.  sh: 8 ints, s_last: 1 int of shared memory.
 __device__ __forceinline__ void scan_tiles_by_last_block(int tx, int ty, int cap, int step, int32_t* tile_count,
                                                          int32_t* __restrict__ tile_off, int32_t* status, int* sh,
-                                                         int* s_last) {
+                                                         int* s_last, int32_t* mail_host = nullptr, int mail_seq = 0) {
     __threadfence();
     __syncthreads();
     if (threadIdx.x == 0) *s_last = (atomicAdd(&status[kStTicket], 1) == (int)gridDim.x - 1);
@@ -231,6 +258,15 @@ __device__ __forceinline__ void scan_tiles_by_last_block(int tx, int ty, int cap
         status[kStMaxPerTile] = mx;
         status[kStTicket] = 0;
         if (carry > cap && status[kStOverflow] == 0) status[kStOverflow] = step > 0 ? step : 1;
+        if (mail_host) {
+            // operator path: the host learns the intersection count (capacity hint of later calls,
+            // overflow check) from pinned memory whenever it next looks -- nothing waits for it
+            mail_host[0] = carry;
+            mail_host[1] = carry > cap ? 1 : 0;
+            mail_host[2] = mx;
+            __threadfence_system();
+            mail_host[4] = mail_seq;      // written last: the record is complete once it shows
+        }
     }
 }
 
@@ -247,7 +283,7 @@ k_fit_count(int n, const float* __restrict__ xyz_raw, const float* __restrict__ 
         fit_project(i, xyz_raw, chol_raw, activate, half_w, half_h, tx, ty, p, m, L, qc);
         count_tiles(p, tx, row0, row1, tile_count);
     }
-    scan_tiles_by_last_block(tx, ty, cap, step, tile_count, tile_off, status, sh, &s_last);
+    scan_tiles_by_last_block(tx, ty, cap, step, tile_count, tile_off, status, sh, &s_last, qc.mail_host, qc.mail_seq);
 }
 
 // ------------------------------------------------------------------------------------------
@@ -391,7 +427,6 @@ k_fit_reset_slots(int tiles, int32_t* tile_fill, int32_t* status) {
 // ------------------------------------------------------------------------------------------
 // K3: the tile kernel
 // ------------------------------------------------------------------------------------------
-constexpr int kIdChunk = 1024;
 #ifndef GS2D_TILE_THREADS
 #define GS2D_TILE_THREADS 64
 #endif
@@ -408,110 +443,21 @@ static_assert(kTileThreads == 32 || kTileThreads == 64, "one or two warps per ti
 #endif
 constexpr int kBwdUnroll = GS2D_BWD_UNROLL;
 constexpr int kBwdRows = GS2D_BWD_ROWS;   // rows of a pair's rectangle a lane evaluates per loop trip
-
-// Stage the tile's batch into shared memory in ascending Gaussian-id order (the scatter wrote
-// the range in arbitrary order; ascending id is the order of the reference's stable sort on
-// tile id).  cnt <= 256: ids go to shared memory, every thread ranks its records'
-// ids against them and stores each record at its rank (the first record per thread is already
-// in flight while the ids land).  cnt > 256 (rare; the reference then renders only the 256
-// lowest ids): ranks are computed against all cnt ids in chunks and the 256
-// lowest-ranked records are kept.
-// publish (every Gaussian of a fuller tile is to be rendered, in batches of 256): the rank of each
-// record is also stored into the record's spare word (q2.w, the tile id, which the fit kernels never
-// read), so that the later batches are staged by stage_tile_window without ranking again.
-__device__ __forceinline__ int stage_tile_sorted(const float4* __restrict__ src, int cnt, float4* sq, int* sid,
-                                                 int tid, bool publish = false) {
-    const int nb = min(cnt, GS2D_MAX_PER_TILE);
-    if (cnt <= GS2D_MAX_PER_TILE) {
-        float4 r0, r1, r2;
-        if (tid < cnt) {
-            r0 = __ldg(&src[3 * (size_t)tid + 0]);
-            r1 = __ldg(&src[3 * (size_t)tid + 1]);
-            r2 = __ldg(&src[3 * (size_t)tid + 2]);
-            sid[tid] = __float_as_int(r1.w);
-        }
-        for (int j = tid + kTileThreads; j < cnt; j += kTileThreads)
-            sid[j] = __float_as_int(__ldg(&src[3 * (size_t)j + 1]).w);
-        __syncthreads();
-        for (int j = tid; j < cnt; j += kTileThreads) {
-            const int my = sid[j];
-            int rank = 0;
-            for (int i = 0; i < cnt; ++i) rank += (sid[i] < my) ? 1 : 0;
-            if (j != tid) {
-                r0 = __ldg(&src[3 * (size_t)j + 0]);
-                r1 = __ldg(&src[3 * (size_t)j + 1]);
-                r2 = __ldg(&src[3 * (size_t)j + 2]);
-            }
-            sq[3 * rank + 0] = r0;
-            sq[3 * rank + 1] = r1;
-            sq[3 * rank + 2] = r2;
-        }
-        __syncthreads();
-    } else {
-        for (int r0 = 0; r0 < cnt; r0 += kTileThreads) {
-            const int j = r0 + tid;
-            const int my = j < cnt ? __float_as_int(__ldg(&src[3 * (size_t)j + 1]).w) : 0x7fffffff;
-            int rank = 0;
-            for (int c0 = 0; c0 < cnt; c0 += kIdChunk) {
-                const int m = min(kIdChunk, cnt - c0);
-                __syncthreads();
-                for (int k = tid; k < m; k += kTileThreads) sid[k] = __float_as_int(__ldg(&src[3 * (size_t)(c0 + k) + 1]).w);
-                __syncthreads();
-                for (int k = 0; k < m; ++k) rank += (sid[k] < my) ? 1 : 0;
-            }
-            if (j < cnt && rank < GS2D_MAX_PER_TILE) {
-                sq[3 * rank + 0] = __ldg(&src[3 * (size_t)j + 0]);
-                sq[3 * rank + 1] = __ldg(&src[3 * (size_t)j + 1]);
-                sq[3 * rank + 2] = __ldg(&src[3 * (size_t)j + 2]);
-            }
-            if (publish && j < cnt)
-                reinterpret_cast<int*>(const_cast<float4*>(src) + 3 * (size_t)j + 2)[3] = rank;
-        }
-        __syncthreads();
-    }
-    return nb;
-}
-
-// Batch `base / 256` of a tile whose ranks stage_tile_sorted published: the records with rank in
-// [base, base + 256), at their place.  The caller has made sure nobody still reads sq.  Ranks are
-// read past L1 (another thread of the CTA wrote them, before a barrier); no scratch is used, so this
-// also runs while sv holds v_out.
-__device__ __forceinline__ int stage_tile_window(const float4* __restrict__ src, int cnt, int base, float4* sq,
-                                                 int tid) {
-    for (int j = tid; j < cnt; j += kTileThreads) {
-        const int rank = __ldcg(reinterpret_cast<const int*>(src + 3 * (size_t)j + 2) + 3) - base;
-        if (rank >= 0 && rank < GS2D_MAX_PER_TILE) {
-            sq[3 * rank + 0] = __ldg(&src[3 * (size_t)j + 0]);
-            sq[3 * rank + 1] = __ldg(&src[3 * (size_t)j + 1]);
-            sq[3 * rank + 2] = __ldg(&src[3 * (size_t)j + 2]);
-        }
-    }
-    __syncthreads();
-    return min(cnt - base, GS2D_MAX_PER_TILE);
-}
-
-// Sum 8 per-lane values over each group of 8 consecutive lanes with 7 shuffles: lane l of a
-// group ends up with the group's total of v[l].
-__device__ __forceinline__ float group8_reduce8_t(float (&v)[8], int lane) {
-    const bool b2 = lane & 4, b1 = lane & 2, b0 = lane & 1;
-    float w[4];
-#pragma unroll
-    for (int k = 0; k < 4; ++k) {
-        const float send = b2 ? v[k] : v[4 + k];
-        const float keep = b2 ? v[4 + k] : v[k];
-        w[k] = keep + __shfl_xor_sync(0xffffffffu, send, 4);
-    }
-    float u[2];
-#pragma unroll
-    for (int k = 0; k < 2; ++k) {
-        const float send = b1 ? w[k] : w[2 + k];
-        const float keep = b1 ? w[2 + k] : w[k];
-        u[k] = keep + __shfl_xor_sync(0xffffffffu, send, 2);
-    }
-    const float send = b0 ? u[0] : u[1];
-    const float keep = b0 ? u[1] : u[0];
-    return keep + __shfl_xor_sync(0xffffffffu, send, 1);
-}
+#ifndef GS2D_WARP_STAGE
+#define GS2D_WARP_STAGE 1   // tiles of at most 32 records (the common case: mean 15, max 31 at 1080p / 50k) are staged and
+                            // ranked by each warp for itself -- registers + shuffles, no block barrier (stage_tile_warp)
+#endif
+#ifndef GS2D_TILE_PERSIST
+#define GS2D_TILE_PERSIST 0   // experiment: see k_fit_tiles
+#endif
+#ifndef GS2D_TILE_PERSIST_OCC
+#define GS2D_TILE_PERSIST_OCC 10   // resident CTAs per SM the persistent grid is sized for
+#endif
+#ifndef GS2D_SQ_RECORDS
+#define GS2D_SQ_RECORDS GS2D_MAX_PER_TILE   // experiments only: a smaller batch buffer (tiles beyond it are then truncated)
+#endif
+constexpr int kWarpStage = GS2D_WARP_STAGE;
+constexpr int kSqRecords = GS2D_SQ_RECORDS > 32 * (kTileThreads / 32) ? GS2D_SQ_RECORDS : 32 * (kTileThreads / 32);
 
 // MODE 0: fit (loss + backward, no image written unless out_img != NULL)
 // MODE 1: render only (image [+ final_idx] written, no target, no backward)
@@ -539,7 +485,7 @@ k_fit_tiles(int W, int H, int tx, int row0, const int32_t* __restrict__ tile_off
             float* __restrict__ out_img, int out_chw, int out_clamp, int32_t* __restrict__ final_idx,
             int32_t* __restrict__ ids_sorted_dbg, int step, int flags) {
     const int loss_in_grads = flags & kTileLossInGrads;
-    __shared__ float4 sq[GS2D_MAX_PER_TILE * 3];
+    __shared__ float4 sq_all[kSqRecords * 3];
     // v_out of the tile (rows 0..15; before that, the id chunk of the staging) + 16 rows of zeros:
     // the backward's row walk may run past the tile for lanes whose pair has a shorter rectangle
     __shared__ float4 sv[2 * GS2D_TILE_PIX];
@@ -547,8 +493,19 @@ k_fit_tiles(int W, int H, int tx, int row0, const int32_t* __restrict__ tile_off
     int* sid = reinterpret_cast<int*>(sv);
     static_assert(sizeof(float4) * GS2D_TILE_PIX >= sizeof(int) * kIdChunk, "id chunk must fit in sv");
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int tile_y = (int)blockIdx.y + row0;
-    const int t = tile_y * tx + blockIdx.x;
+#if GS2D_TILE_PERSIST
+    // experiment: resident CTAs walk the tiles with a grid stride (flags >> 8 = tile rows of the band)
+    const int n_tiles = tx * (flags >> 8);
+    for (int tt = blockIdx.x; tt < n_tiles; tt += gridDim.x) {
+    const int bx = tt % tx, by = tt / tx;
+    if (tt != (int)blockIdx.x) __syncthreads();   // the previous tile's sv is dead
+#define GS2D_TILE_DONE continue
+#else
+    const int bx = blockIdx.x, by = blockIdx.y;
+#define GS2D_TILE_DONE return
+#endif
+    const int tile_y = by + row0;
+    const int t = tile_y * tx + bx;
     if (MODE == 0) {
 #pragma unroll
         for (int j = 0; j < GS2D_TILE_PIX / kTileThreads; ++j)
@@ -556,7 +513,7 @@ k_fit_tiles(int W, int H, int tx, int row0, const int32_t* __restrict__ tile_off
     }
 
     const int lx = lane & 15, ly0 = kWarpRows * warp + (lane >> 4);   // pixel j: (lx, ly0 + 2j)
-    const int ox = blockIdx.x * GS2D_TILE, oy = tile_y * GS2D_TILE;
+    const int ox = bx * GS2D_TILE, oy = tile_y * GS2D_TILE;
     const int px_i = ox + lx;
     const bool in_x = px_i < W;
     uint32_t tgt_u8[kPix] = {};
@@ -600,24 +557,63 @@ k_fit_tiles(int W, int H, int tx, int row0, const int32_t* __restrict__ tile_off
     // records speculatively as well -- their address does not depend on the count -- was measured:
     // no gain, and 25 MB per step of never-written slots pulled from DRAM.)
     const bool slot = tile_off == nullptr;
+    // slot mode: a tile's records start at a fixed address, so the first 32 can be requested together
+    // with the flag and the count -- one round trip to L2 instead of two.  (Requesting 64 per warp
+    // was measured in round 1: no gain, 25 MB per step of never-written slots pulled from DRAM.)
+    float4 w0 = make_float4(0.f, 0.f, 0.f, 0.f), w1 = w0, w2 = w0;
+    if (kWarpStage && slot) {
+        const float4* rec = packed + 3 * ((size_t)t * kSlotStride + lane);
+        w0 = __ldg(rec); w1 = __ldg(rec + 1); w2 = __ldg(rec + 2);
+    }
     const int of = status[kStOverflow];
     const int lo = slot ? t * kSlotStride : tile_off[t];
     const int cnt = slot ? tile_fill[t] : tile_off[t + 1] - lo;
-    if (of != 0) return;
-    // (tile_fill[t] is re-zeroed after the staging's barrier: a store to the address of the load in
-    // flight would park this warp on it)
+    if (of != 0) {
+        // the workspace overflowed: the step is a no-op.  A render must not hand back stale memory as
+        // an image: it is filled with NaN (the operator path reports the overflow lazily)
+        if (MODE == 1 && out_img && in_x) {
+            const float nanv = __int_as_float(0x7fc00000);
+#pragma unroll
+            for (int j = 0; j < kPix; ++j) {
+                const int py_i = oy + ly0 + 2 * j;
+                if (py_i >= H) continue;
+                const size_t pid = (size_t)py_i * W + px_i;
+                if (out_chw) {
+                    const size_t plane = (size_t)H * W;
+                    out_img[pid] = nanv; out_img[plane + pid] = nanv; out_img[2 * plane + pid] = nanv;
+                } else {
+                    out_img[3 * pid] = nanv; out_img[3 * pid + 1] = nanv; out_img[3 * pid + 2] = nanv;
+                }
+            }
+        }
+        return;
+    }
     // more than 256 and all of them wanted (the reference renders the first 256, Q1): the
     // forward walks the batches in rank order, the backward walks them again; one batch otherwise
     const bool all = ALL && cnt > GS2D_MAX_PER_TILE;
     const int nbat = all ? (cnt + GS2D_MAX_PER_TILE - 1) / GS2D_MAX_PER_TILE : 1;
-    int nb = stage_tile_sorted(packed + 3 * (size_t)lo, cnt, sq, sid, tid, all);
-    if (tid == 0) {                   // every thread is past a barrier that it reached knowing cnt
-        tile_fill[t] = 0;             // ready for the next iteration's scatter
-        if (!tile_off && MODE == 0) {
-            atomicMax(&status[kStSlotMax], cnt);   // result unused: a reduction the CTA never waits for
-            if (blockIdx.x == 0 && blockIdx.y == 0)                    // the update kernel counts the next step into it
-                status[kStSlotIsect + ((step + 1) & 1)] = 0;
+    const bool per_warp = kWarpStage && cnt <= 32;     // uniform over the CTA
+    float4* sq = sq_all + (per_warp ? warp * (32 * 3) : 0);
+    int nb;
+    if (per_warp) {
+        if (!slot && lane < cnt) {
+            const float4* rec = packed + 3 * ((size_t)lo + lane);
+            w0 = __ldg(rec); w1 = __ldg(rec + 1); w2 = __ldg(rec + 2);
         }
+        stage_tile_warp(w0, w1, w2, cnt, sq, lane);
+        nb = cnt;
+    } else {
+        const int cnt_s = kSqRecords < GS2D_MAX_PER_TILE ? min(cnt, kSqRecords) : cnt;   // (experiment builds truncate)
+        nb = stage_tile_sorted<kTileThreads>(packed + 3 * (size_t)lo, cnt_s, sq, sid, tid, all);
+    }
+    // tile_fill[t] goes back to zero for the next iteration's scatter once every thread of the CTA
+    // has read it: after the staging's barriers, or (per-warp staging has none) after the loss barrier
+    const bool reset_late = per_warp;
+    if (tid == 0 && !reset_late) tile_fill[t] = 0;
+    if (tid == 0 && !tile_off && MODE == 0) {
+        atomicMax(&status[kStSlotMax], cnt);   // result unused: a reduction the CTA never waits for
+        if (bx == 0 && by == 0)                                    // the update kernel counts the next step into it
+            status[kStSlotIsect + ((step + 1) & 1)] = 0;
     }
     if (ids_sorted_dbg && !all)   // parity tests: the order the batch is rendered in
         for (int r = nb + tid; r < cnt; r += kTileThreads) ids_sorted_dbg[lo + r] = -1;
@@ -648,7 +644,7 @@ k_fit_tiles(int W, int H, int tx, int row0, const int32_t* __restrict__ tile_off
     for (int bat = 0; bat < nbat; ++bat) {
     if (bat) {
         __syncthreads();   // everyone is done with the previous batch
-        nb = stage_tile_window(packed + 3 * (size_t)lo, cnt, bat * GS2D_MAX_PER_TILE, sq, tid);
+        nb = stage_tile_window<kTileThreads>(packed + 3 * (size_t)lo, cnt, bat * GS2D_MAX_PER_TILE, sq, tid);
     }
     const int lob = lo + bat * GS2D_MAX_PER_TILE;   // sorted index of the batch's first record
     if (ids_sorted_dbg)
@@ -703,12 +699,16 @@ k_fit_tiles(int W, int H, int tx, int row0, const int32_t* __restrict__ tile_off
         pix[2 * P + 1] = make_float3(hi2(pr[P]), hi2(pg[P]), hi2(pb[P]));
     }
     if (out_img || final_idx) {
+        // operator path (MODE 1, gt = background colour): with no intersection at all the reference
+        // returns ones(H, W, 3) * background instead of launching anything (rasterize_sum.py:121-129)
+        const float* bg = (MODE == 1 && gt != nullptr && status[kStNumIntersects] < 1) ? (const float*)gt : nullptr;
 #pragma unroll
         for (int j = 0; j < kPix; ++j) {
             if (!inside[j]) continue;
             const size_t pid = (size_t)(oy + ly0 + 2 * j) * W + px_i;
             if (out_img) {
                 float3 o = pix[j];
+                if (MODE == 1 && bg) o = make_float3(bg[0], bg[1], bg[2]);
                 if (out_clamp) o = make_float3(fminf(fmaxf(o.x, 0.f), 1.f), fminf(fmaxf(o.y, 0.f), 1.f), fminf(fmaxf(o.z, 0.f), 1.f));
                 if (out_chw) {
                     const size_t plane = (size_t)H * W;
@@ -720,7 +720,13 @@ k_fit_tiles(int W, int H, int tx, int row0, const int32_t* __restrict__ tile_off
             if (final_idx) final_idx[pid] = cur_idx[j];
         }
     }
-    if (MODE == 1) return;
+    if (MODE == 1) {
+        if (reset_late) {
+            __syncthreads();
+            if (tid == 0) tile_fill[t] = 0;
+        }
+        GS2D_TILE_DONE;
+    }
 
     // ---- clamp + L2 loss and its gradient w.r.t. the unclamped sum --------------------------
     float l = 0.f;
@@ -748,6 +754,7 @@ k_fit_tiles(int W, int H, int tx, int row0, const int32_t* __restrict__ tile_off
     if (lane == 0) sred[warp] = l;
     __syncthreads();
     if (tid == 0) {
+        if (reset_late) tile_fill[t] = 0;
         float s = sred[0];
 #pragma unroll
         for (int w = 1; w < kTileThreads / 32; ++w) s += sred[w];
@@ -768,7 +775,7 @@ k_fit_tiles(int W, int H, int tx, int row0, const int32_t* __restrict__ tile_off
     for (int bat = nbat - 1; bat >= 0; --bat) {   // the forward left the last batch staged
     if (bat != nbat - 1) {
         __syncthreads();
-        nb = stage_tile_window(packed + 3 * (size_t)lo, cnt, bat * GS2D_MAX_PER_TILE, sq, tid);
+        nb = stage_tile_window<kTileThreads>(packed + 3 * (size_t)lo, cnt, bat * GS2D_MAX_PER_TILE, sq, tid);
     }
     for (int r0 = warp * 4; r0 < nb; r0 += (kTileThreads / 32) * 4) {
         const int k = min(r0 + sub, nb - 1);
@@ -847,6 +854,10 @@ k_fit_tiles(int W, int H, int tx, int row0, const int32_t* __restrict__ tile_off
         if (live && tot != 0.f) atomicAdd(row + l8, tot);   // 4 pairs x 8 consecutive floats
     }
     }   // batches
+#if GS2D_TILE_PERSIST
+    }   // tiles
+#endif
+#undef GS2D_TILE_DONE
 }
 
 // ------------------------------------------------------------------------------------------
@@ -1185,6 +1196,25 @@ static cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, c
     return cudaLaunchKernelEx(&cfg, kernel, KArgs(std::forward<Args>(args))...);
 }
 
+// launch shape of the tile kernel: one CTA per tile of the band (the experiment build walks the tiles
+// with resident CTAs instead and gets the band's height through the flags)
+static inline dim3 tile_grid(int tx, int rows) {
+#if GS2D_TILE_PERSIST
+    const int want = 148 * GS2D_TILE_PERSIST_OCC;
+    return dim3(tx * rows < want ? tx * rows : want);
+#else
+    return dim3(tx, rows);
+#endif
+}
+static inline int tile_flags_for(int flags, int rows) {
+#if GS2D_TILE_PERSIST
+    return flags | (rows << 8);
+#else
+    (void)rows;
+    return flags;
+#endif
+}
+
 static int fit_layout(int n, int cap, int img_h, int img_w, gs2d_fit_layout* L) {
     if (n < 0 || cap < 1 || img_h < 1 || img_w < 1) {
         set_error("fit layout: bad sizes (n=%d cap=%d %dx%d)", n, cap, img_w, img_h);
@@ -1365,9 +1395,10 @@ int gs2d_fit_step_band(int n, int cap, int img_h, int img_w, float* xyz_raw, flo
         }
         const int32_t* tile_off_arg = slots ? nullptr : (const int32_t*)(w + L.off_tile_off);
         const float grad_scale = (float)(2.0 / (3.0 * (double)img_h * (double)img_w));   // the WHOLE frame's mean
-        const int tile_flags = (banded ? kTileLossInGrads : 0) | (all_per_tile ? kTileAllPerTile : 0);
+        const int tile_flags = tile_flags_for((banded ? kTileLossInGrads : 0) | (all_per_tile ? kTileAllPerTile : 0),
+                                              row1 - row0);
         ProfScope ps_(GS2D_STAGE_FIT_TILES, s);
-        const dim3 grid(tx, row1 - row0);
+        const dim3 grid = tile_grid(tx, row1 - row0);
         if (target_format == GS2D_TARGET_F32_CHW)
             GS2D_CHECK_CUDA(launch_pdl(all_per_tile ? k_fit_tiles<0, 0, true> : k_fit_tiles<0, 0, false>, grid,
                 dim3(kTileThreads), s,
@@ -1454,7 +1485,7 @@ int gs2d_render_quantized(int n, int cap, int img_h, int img_w, const gs2d_quant
     GS2D_REQUIRE(n > 0, "render_quantized: n must be positive");
     GS2D_REQUIRE(work != nullptr && work_bytes >= L.total_bytes, "render_quantized: workspace too small");
     GS2D_REQUIRE(out_img != nullptr, "render_quantized: null output");
-    QuantConst qc;
+    QuantConst qc = QuantConst();
     rc = quant_const(q, qc);
     if (rc != GS2D_OK) return rc;
     cudaStream_t s = (cudaStream_t)stream;
@@ -1465,10 +1496,11 @@ int gs2d_render_quantized(int n, int cap, int img_h, int img_w, const gs2d_quant
     if (rc != GS2D_OK) return rc;
     {
         ProfScope ps_(GS2D_STAGE_RASTER_FWD, s);
-        GS2D_CHECK_CUDA(launch_pdl(k_fit_tiles<1, 0, false>, dim3(tx, ty), dim3(kTileThreads), s,
+        GS2D_CHECK_CUDA(launch_pdl(k_fit_tiles<1, 0, false>, tile_grid(tx, ty), dim3(kTileThreads), s,
             img_w, img_h, tx, 0, (const int32_t*)(w + L.off_tile_off), (int32_t*)(w + L.off_tile_count),
             (const float4*)(w + L.off_packed), (const void*)nullptr, 0.f, (float*)nullptr, (double*)nullptr,
-            (int32_t*)(w + L.off_status), out_img, out_chw, out_clamp, final_idx, ids_sorted_out, 0, 0));
+            (int32_t*)(w + L.off_status), out_img, out_chw, out_clamp, final_idx, ids_sorted_out, 0,
+            tile_flags_for(0, ty)));
         GS2D_CHECK_LAUNCH("render_tiles");
     }
     return GS2D_OK;
@@ -1477,7 +1509,7 @@ int gs2d_render_quantized(int n, int cap, int img_h, int img_w, const gs2d_quant
 int gs2d_dequantize(int n, const gs2d_quantized_frame* q, float* xyz_raw, float* chol_raw, float* features,
                     gs2d_stream_t stream) {
     GS2D_REQUIRE(n > 0 && xyz_raw && chol_raw && features, "dequantize: bad arguments");
-    QuantConst qc;
+    QuantConst qc = QuantConst();
     const int rc = quant_const(q, qc);
     if (rc != GS2D_OK) return rc;
     cudaStream_t s = (cudaStream_t)stream;
@@ -1500,6 +1532,57 @@ int gs2d_i420_to_rgb(int img_h, int img_w, const uint8_t* yuv, uint8_t* rgb, gs2
     return GS2D_OK;
 }
 
+size_t gs2d_opstate_bytes(int cap, int img_h, int img_w) {
+    gs2d_fit_layout L;
+    if (fit_layout(1, cap, img_h, img_w, &L) != GS2D_OK) return 0;
+    return L.total_bytes;
+}
+
+int gs2d_rasterize_sum_fwd_ranked(int n, const float* xys, const int32_t* radii, const float* conics,
+                                  const float* colors, const float* opacities, const float* background, int img_h,
+                                  int img_w, int cap, void* state, size_t state_bytes, float* out_img,
+                                  int32_t* final_idx, int32_t* mail_host, int mail_seq, gs2d_stream_t stream) {
+    gs2d_fit_layout L;
+    int rc = fit_layout(1, cap, img_h, img_w, &L);
+    if (rc != GS2D_OK) return rc;
+    GS2D_REQUIRE(n > 0, "rasterize_sum_fwd_ranked: n must be positive");
+    GS2D_REQUIRE(state != nullptr && state_bytes >= L.total_bytes, "rasterize_sum_fwd_ranked: state buffer too small");
+    GS2D_REQUIRE(((uintptr_t)state & 255) == 0, "rasterize_sum_fwd_ranked: state buffer must be 256-byte aligned");
+    GS2D_REQUIRE(xys && radii && conics && colors && opacities && out_img, "rasterize_sum_fwd_ranked: null pointer");
+    cudaStream_t s = (cudaStream_t)stream;
+    char* w = (char*)state;
+    const int tx = div_up(img_w, GS2D_TILE), ty = div_up(img_h, GS2D_TILE);
+    {
+        ProfScope ps_(GS2D_STAGE_MEMSET, s);
+        GS2D_CHECK_CUDA(cudaMemsetAsync(w, 0, L.zero_bytes, s));
+    }
+    QuantConst qc = QuantConst();
+    qc.radii = radii;
+    qc.mail_host = mail_host;
+    qc.mail_seq = mail_seq;
+    rc = launch_bin(n, xys, conics, colors, opacities, nullptr, 3, img_h, img_w, 0, ty, cap, 0, L, w, s, false, qc, true);
+    if (rc != GS2D_OK) return rc;
+    {
+        ProfScope ps_(GS2D_STAGE_RASTER_FWD, s);
+        GS2D_CHECK_CUDA(launch_pdl(k_fit_tiles<1, 0, false>, tile_grid(tx, ty), dim3(kTileThreads), s,
+            img_w, img_h, tx, 0, (const int32_t*)(w + L.off_tile_off), (int32_t*)(w + L.off_tile_count),
+            (const float4*)(w + L.off_packed), (const void*)background, 0.f, (float*)nullptr, (double*)nullptr,
+            (int32_t*)(w + L.off_status), out_img, 0, 0, final_idx, (int32_t*)nullptr, 0, tile_flags_for(0, ty)));
+        GS2D_CHECK_LAUNCH("raster_fwd_ranked");
+    }
+    return GS2D_OK;
+}
+
+int gs2d_opstate_ranges(int cap, int img_h, int img_w, size_t* off_tile_off, size_t* off_packed, size_t* off_status) {
+    gs2d_fit_layout L;
+    const int rc = fit_layout(1, cap, img_h, img_w, &L);
+    if (rc != GS2D_OK) return rc;
+    if (off_tile_off) *off_tile_off = L.off_tile_off;
+    if (off_packed) *off_packed = L.off_packed;
+    if (off_status) *off_status = L.off_status;
+    return GS2D_OK;
+}
+
 int gs2d_render_chol(int n, int cap, int img_h, int img_w, const float* means_or_xyz_raw, const float* chol,
                      const float* colors, const float* opacities, int activate, void* work, size_t work_bytes,
                      float* out_img, int out_chw, int out_clamp, int32_t* final_idx, int32_t* ids_sorted_out,
@@ -1513,17 +1596,18 @@ int gs2d_render_chol(int n, int cap, int img_h, int img_w, const float* means_or
     cudaStream_t s = (cudaStream_t)stream;
     char* w = (char*)work;
     const int tx = div_up(img_w, GS2D_TILE), ty = div_up(img_h, GS2D_TILE);
-    const int tile_flags = (activate & GS2D_RENDER_ALL_PER_TILE) ? kTileAllPerTile : 0;
+    const int all_flag = (activate & GS2D_RENDER_ALL_PER_TILE) ? kTileAllPerTile : 0;
     rc = launch_bin(n, means_or_xyz_raw, chol, colors, opacities, nullptr, (activate & GS2D_RENDER_ACTIVATE) ? 1 : 0, img_h,
                     img_w, 0, ty, cap, 0, L, w, s, false, QuantConst(), true);
     if (rc != GS2D_OK) return rc;
     {
         ProfScope ps_(GS2D_STAGE_RASTER_FWD, s);
-        GS2D_CHECK_CUDA(launch_pdl(tile_flags ? k_fit_tiles<1, 0, true> : k_fit_tiles<1, 0, false>, dim3(tx, ty),
+        GS2D_CHECK_CUDA(launch_pdl(all_flag ? k_fit_tiles<1, 0, true> : k_fit_tiles<1, 0, false>, tile_grid(tx, ty),
             dim3(kTileThreads), s,
             img_w, img_h, tx, 0, (const int32_t*)(w + L.off_tile_off), (int32_t*)(w + L.off_tile_count),
             (const float4*)(w + L.off_packed), (const void*)nullptr, 0.f, (float*)nullptr, (double*)nullptr,
-            (int32_t*)(w + L.off_status), out_img, out_chw, out_clamp, final_idx, ids_sorted_out, 0, tile_flags));
+            (int32_t*)(w + L.off_status), out_img, out_chw, out_clamp, final_idx, ids_sorted_out, 0,
+            tile_flags_for(all_flag, ty)));
         GS2D_CHECK_LAUNCH("render_tiles");
     }
     return GS2D_OK;

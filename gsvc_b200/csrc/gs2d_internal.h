@@ -30,3 +30,9 @@ int launch_pack_binned(int num_intersects, const int32_t* ids_sorted, const int3
                        int img_w, float4* packed, cudaStream_t s);
 
 }  // namespace gs2d
+
+extern "C" {
+// fit.cu: layout of the operator path's per-call state (the fit workspace without gradient rows)
+size_t gs2d_opstate_bytes(int cap, int img_h, int img_w);
+int gs2d_opstate_ranges(int cap, int img_h, int img_w, size_t* off_tile_off, size_t* off_packed, size_t* off_status);
+}

@@ -19,6 +19,7 @@
 // 76 us at 1080p / 50k against 35 us now; the N-channel variant below still has that shape.)
 #include "gs2d_internal.h"
 #include "gs2d_math.cuh"
+#include "gs2d_stage.cuh"
 
 namespace gs2d {
 
@@ -157,20 +158,46 @@ __device__ __forceinline__ float group8_reduce8(float (&v)[8], int lane) {
 // for the opacities).  Rows past a pair's rectangle need no mask: inside the tile the rectangle
 // guarantees that the alpha test fails, past the tile the staged v_out rows are zero.
 constexpr int kBwdTileThreads = 64;
+// RANKED = false: records sorted in memory (onesweep path; tile_bins rows of (lo, hi), conics as given);
+// RANKED = true:  records as the count / scatter binning of fit.cu leaves them -- a tile's range is
+//                 [tile_off[t], tile_off[t+1]), in arbitrary order, conic diagonals stored halved --
+//                 and the batch is put into ascending-id order while it is staged (gs2d_stage.cuh),
+//                 the same order the forward (k_fit_tiles<1>) rendered and numbered final_idx in.
+template <bool RANKED>
 __global__ void __launch_bounds__(kBwdTileThreads)
 k_raster_bwd_tiles(int W, int H, int tx, const int32_t* __restrict__ tile_bins, const float4* __restrict__ packed,
                    const int32_t* __restrict__ final_idx, const float* __restrict__ v_out,
-                   float* __restrict__ grads) {
-    __shared__ float4 sq[GS2D_MAX_PER_TILE * 3];
+                   float* __restrict__ grads, const int32_t* __restrict__ status) {
+    __shared__ float4 sq_all[GS2D_MAX_PER_TILE * 3];
     __shared__ float4 sv[2 * GS2D_TILE_PIX];   // {v_out.rgb, final_idx} of rows 0..15, then 16 rows of zeros
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int t = blockIdx.y * tx + blockIdx.x;
-    const int2 range = reinterpret_cast<const int2*>(tile_bins)[t];
-    const int lo = range.x;
-    const int nb = max(0, min(range.y - range.x, GS2D_MAX_PER_TILE));
+    int lo, cnt;
+    if (RANKED) {
+        if (status[1] != 0) return;   // the forward overflowed its capacity: nothing was rendered
+        lo = tile_bins[t];
+        cnt = tile_bins[t + 1] - lo;
+    } else {
+        const int2 range = reinterpret_cast<const int2*>(tile_bins)[t];
+        lo = range.x;
+        cnt = range.y - range.x;
+    }
+    const int nb = max(0, min(cnt, GS2D_MAX_PER_TILE));
     if (nb == 0) return;
     const float4* src = packed + 3 * (size_t)lo;
-    for (int i = tid; i < nb * 3; i += kBwdTileThreads) cp_async16(&sq[i], src + i);
+    float4* sq = sq_all;
+    const bool per_warp = RANKED && cnt <= 32;
+    if (!RANKED) {
+        for (int i = tid; i < nb * 3; i += kBwdTileThreads) cp_async16(&sq[i], src + i);
+    } else if (per_warp) {
+        sq = sq_all + warp * (32 * 3);
+        float4 w0 = make_float4(0.f, 0.f, 0.f, 0.f), w1 = w0, w2 = w0;
+        if (lane < cnt) { w0 = __ldg(src + 3 * lane); w1 = __ldg(src + 3 * lane + 1); w2 = __ldg(src + 3 * lane + 2); }
+        stage_tile_warp(w0, w1, w2, cnt, sq, lane);
+    } else {
+        // ids go through the zero rows of sv (re-zeroed below, before anyone reads them as v_out)
+        stage_tile_sorted<kBwdTileThreads>(src, cnt, sq, reinterpret_cast<int*>(sv + GS2D_TILE_PIX), tid);
+    }
     const int ox = blockIdx.x * GS2D_TILE, oy = blockIdx.y * GS2D_TILE;
 #pragma unroll
     for (int j = 0; j < GS2D_TILE_PIX / kBwdTileThreads; ++j) {
@@ -185,7 +212,7 @@ k_raster_bwd_tiles(int W, int H, int tx, const int32_t* __restrict__ tile_bins, 
         sv[p] = v;
         sv[GS2D_TILE_PIX + p] = make_float4(0.f, 0.f, 0.f, __int_as_float(-1));
     }
-    cp_async_wait_all();
+    if (!RANKED) cp_async_wait_all();
     __syncthreads();
 
     const int sub = lane >> 3, l8 = lane & 7;
@@ -202,8 +229,10 @@ k_raster_bwd_tiles(int W, int H, int tx, const int32_t* __restrict__ tile_bins, 
         max_iters = max(max_iters, __shfl_xor_sync(0xffffffffu, max_iters, 16));
         if (max_iters == 0) continue;
         const float4 q0 = sq[3 * k], q2 = sq[3 * k + 2];
-        const float gx = q0.x, gy = q0.y, cx = q0.z, cy = q0.w, cz = q1.x, opac = q1.y;
-        const float cxh = 0.5f * cx, czh = 0.5f * cz;   // exact: sigma keeps the reference's roundings (fit.cu)
+        const float gx = q0.x, gy = q0.y, cy = q0.w, opac = q1.y;
+        // halving / doubling is exact: sigma keeps the reference's roundings either way (fit.cu)
+        const float cxh = RANKED ? q0.z : 0.5f * q0.z, czh = RANKED ? q1.x : 0.5f * q1.x;
+        const float cx = RANKED ? 2.f * q0.z : q0.z, cz = RANKED ? 2.f * q1.x : q1.x;
         const int gidx = lo + k;                        // sorted index of this pair (backward.cu:784-787)
         float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
         float acc_op = 0.f;
@@ -523,11 +552,37 @@ int gs2d_rasterize_sum_bwd(int n, int img_h, int img_w, int cap, const void* sta
     }
     {
         ProfScope ps_(GS2D_STAGE_RASTER_BWD, s);
-        k_raster_bwd_tiles<<<dim3(tx, ty), kBwdTileThreads, 0, s>>>(
+        k_raster_bwd_tiles<false><<<dim3(tx, ty), kBwdTileThreads, 0, s>>>(
         img_w, img_h, tx, (const int32_t*)(st + so.pub.off_tile_bins), (const float4*)(st + so.pub.off_packed),
-        final_idx, v_out, grads);
+        final_idx, v_out, grads, nullptr);
     }
     GS2D_CHECK_LAUNCH("raster_bwd");
+    return GS2D_OK;
+}
+
+int gs2d_rasterize_sum_bwd_ranked(int n, int img_h, int img_w, int cap, const void* state, size_t state_bytes,
+                                  const int32_t* final_idx, const float* v_out, float* grads, gs2d_stream_t stream) {
+    GS2D_REQUIRE(n > 0 && img_h > 0 && img_w > 0 && cap > 0, "rasterize_sum_bwd_ranked: bad sizes");
+    size_t off_tile_off = 0, off_packed = 0, off_status = 0;
+    const int rc = gs2d_opstate_ranges(cap, img_h, img_w, &off_tile_off, &off_packed, &off_status);
+    if (rc != GS2D_OK) return rc;
+    GS2D_REQUIRE(state != nullptr && state_bytes >= gs2d_opstate_bytes(cap, img_h, img_w),
+                 "rasterize_sum_bwd_ranked: state buffer too small");
+    GS2D_REQUIRE(final_idx && v_out && grads, "rasterize_sum_bwd_ranked: null pointer");
+    const int tx = div_up(img_w, GS2D_TILE), ty = div_up(img_h, GS2D_TILE);
+    cudaStream_t s = (cudaStream_t)stream;
+    const char* st = (const char*)state;
+    {
+        ProfScope ps_(GS2D_STAGE_MEMSET, s);
+        GS2D_CHECK_CUDA(cudaMemsetAsync(grads, 0, (size_t)n * 12 * sizeof(float), s));
+    }
+    {
+        ProfScope ps_(GS2D_STAGE_RASTER_BWD, s);
+        k_raster_bwd_tiles<true><<<dim3(tx, ty), kBwdTileThreads, 0, s>>>(
+            img_w, img_h, tx, (const int32_t*)(st + off_tile_off), (const float4*)(st + off_packed), final_idx, v_out,
+            grads, (const int32_t*)(st + off_status));
+    }
+    GS2D_CHECK_LAUNCH("raster_bwd_ranked");
     return GS2D_OK;
 }
 
@@ -550,8 +605,9 @@ int gs2d_rasterize_sum_bwd_binned(int n, int num_intersects, const int32_t* ids_
     if (rc != GS2D_OK) return rc;
     {
         ProfScope ps_(GS2D_STAGE_RASTER_BWD, s);
-        k_raster_bwd_tiles<<<dim3(tx, ty), kBwdTileThreads, 0, s>>>(img_w, img_h, tx, tile_bins, (const float4*)scratch,
-                                                                   final_idx, v_out, grads);
+        k_raster_bwd_tiles<false><<<dim3(tx, ty), kBwdTileThreads, 0, s>>>(img_w, img_h, tx, tile_bins,
+                                                                          (const float4*)scratch, final_idx, v_out,
+                                                                          grads, nullptr);
     }
     GS2D_CHECK_LAUNCH("raster_bwd_binned");
     return GS2D_OK;

@@ -142,6 +142,13 @@ class FrameFit(torch.nn.Module):
         return loss, psnr
 
 
+class GS2DOverflow(RuntimeError):
+    """A fused step found its workspace too small (more intersections than `cap`, or -- on tile slots --
+    a tile with more than 256 Gaussians): that step and every later one were no-ops.  By the time this is
+    raised the model has already rewound itself to the last step that really happened and regrown /
+    switched its workspace: re-issue the remaining iterations (FusedFrameFit.train_until does)."""
+
+
 class _NoAction:
     kind, count, rebuild, replaces_parameters = "none", 0, False, False
 
@@ -276,9 +283,11 @@ class FusedFrameFit(torch.nn.Module):
     def current_lr(self) -> float:
         # torch.optim.lr_scheduler.StepLR(step_size=20000, gamma=0.5), GaussianSplats_Represent.py:52;
         # the optimizer update_optimizer() builds (:93-97) has no scheduler: constant lr from then on
+        # iteration `it` (1-based, = step_index while it is being issued) runs optimizer.step() BEFORE the
+        # it-th scheduler.step() (GaussianSplats_Represent.py:203-206), i.e. at lr * gamma^((it-1) // step)
         if self.clock.lr_frozen:
             return self.lr
-        return self.lr * self.lr_gamma ** (self.step_index // self.lr_step_size)
+        return self.lr * self.lr_gamma ** (max(self.step_index - 1, 0) // self.lr_step_size)
 
     def _options(self, adan_step: int, fresh: bool, skip: bool, w_grad_out=None):
         o = self._opts
@@ -334,7 +343,7 @@ class FusedFrameFit(torch.nn.Module):
         _, _i, overflow, _m = self._read_report(prev)
         if overflow != 0:
             self.step_index = prev
-            raise RuntimeError(self._recover(overflow))
+            raise GS2DOverflow(self._recover(overflow))
 
     def _zero_optimizer_state(self):
         self.adan_state.zero_()
@@ -395,6 +404,28 @@ class FusedFrameFit(torch.nn.Module):
             for _ in range(int(iters)):
                 self._issue(gt, fmt, **dbg)
 
+    def train_until(self, gt_image: torch.Tensor, target_step: int, check_every: int = 0, max_recoveries: int = 8):
+        """Iterate until `target_step` iterations have REALLY happened, recovering from workspace
+        overflows on the way (GS2DOverflow: the model rewinds itself, regrows / switches its
+        workspace, and the lost iterations are issued again).  check_every: look at the device every
+        so many iterations (0: only at the end -- one host wait per call, like train_iters + loss).
+        Returns the loss of the last iteration."""
+        recoveries = 0
+        while True:
+            try:
+                while self.step_index < target_step:
+                    k = target_step - self.step_index
+                    if check_every > 0:
+                        k = min(k, check_every)
+                    self.train_iters(gt_image, k)
+                    if check_every > 0 and self.step_index < target_step:
+                        self.loss()
+                return self.loss()
+            except GS2DOverflow:
+                recoveries += 1
+                if recoveries > max_recoveries:
+                    raise
+
     def _read_report(self, step: int):
         """(loss_sum, num_intersects, overflow_step, max_per_tile) a step wrote into the pinned ring;
         the caller has already waited for that step"""
@@ -421,7 +452,7 @@ class FusedFrameFit(torch.nn.Module):
             torch.cuda.current_stream(self.device).synchronize()
         loss_sum, _i, overflow, _m = self._read_report(step)
         if overflow != 0:
-            raise RuntimeError(self._recover(overflow))
+            raise GS2DOverflow(self._recover(overflow))
         return loss_sum / (3.0 * self.H * self.W)
 
     def _recover(self, overflow_step: int) -> str:
@@ -464,6 +495,35 @@ class FusedFrameFit(torch.nn.Module):
                 if rec[5] != step:
                     raise RuntimeError(f"step {step} finished without reporting")
 
+    def _frame_pipe(self, frame_bytes: int, depth: int):
+        """the library's frame pipe (include/gs2d.h) and its ring of device slots, created once per
+        model and frame size (a copy stream + 2*depth events: ~0.1 ms that a short stream of frames
+        would otherwise pay on every call)"""
+        key = (int(frame_bytes), int(depth))
+        if getattr(self, "_pipe_key", None) != key:
+            self._drop_frame_pipe()
+            ct = self._ctypes
+            self._pipe_slots = torch.empty((depth, frame_bytes), dtype=torch.uint8, device=self.device)
+            pipe = ct.c_void_p()
+            with self._C._guard(self.device):
+                self._lib.check(self._cdll.gs2d_frame_pipe_create(self._pipe_slots.data_ptr(), frame_bytes, depth,
+                                                                  ct.byref(pipe)), "frame_pipe_create")
+            self._pipe, self._pipe_key = pipe, key
+        return self._pipe
+
+    def _drop_frame_pipe(self):
+        pipe = getattr(self, "_pipe", None)
+        if pipe is not None:
+            try:
+                torch.cuda.current_stream(self.device).synchronize()
+                self._cdll.gs2d_frame_pipe_destroy(pipe)
+            except Exception:   # noqa: BLE001 -- interpreter shutdown
+                pass
+        self._pipe, self._pipe_key, self._pipe_slots = None, None, None
+
+    def __del__(self):
+        self._drop_frame_pipe()
+
     def fit_stream(self, host_frames, prefetch: int = 2, lag: int = 1):
         """One iteration per frame of `host_frames` (an iterable of PINNED host targets of one
         format: raw I420 [H*3/2,W], uint8 RGB [H,W,3] or fp32 [1,3,H,W]); yields (loss, psnr) of
@@ -471,7 +531,11 @@ class FusedFrameFit(torch.nn.Module):
         the copy of frame i+1 runs on the pipe's stream under step i, and a step's loss arrives in
         pinned memory with the step itself.  lag: how many steps may be in flight when a result is
         handed back -- lag=1 (default) issues step i+1 before waiting for step i, so the host's
-        work on the next step hides under the device's; lag=0 is strictly synchronous."""
+        work on the next step hides under the device's; lag=0 is strictly synchronous.
+        A workspace overflow (GS2DOverflow: a tile beyond its 256 slots, more intersections than the
+        capacity) is absorbed: the model rewinds, and the frames of the steps that became no-ops --
+        still referenced here -- are issued again on the regrown / switched workspace, in order."""
+        import itertools
         dev = self.device
         ct, lib, check = self._ctypes, self._cdll, self._lib.check
         it = iter(host_frames)
@@ -483,12 +547,11 @@ class FusedFrameFit(torch.nn.Module):
         fmt = self._target(first)[1]
         frame_bytes = first.numel() * first.element_size()
         depth = max(2, min(int(prefetch), 8))
-        slots = torch.empty((depth, frame_bytes), dtype=torch.uint8, device=dev)
-        pipe = ct.c_void_p()
-        check(lib.gs2d_frame_pipe_create(slots.data_ptr(), frame_bytes, depth, ct.byref(pipe)), "frame_pipe_create")
+        pipe = self._frame_pipe(frame_bytes, depth)
         slot_out, ptr_out = ct.c_int(), ct.c_void_p()
         stream = torch.cuda.current_stream(dev).cuda_stream
         queued, inflight = [], []        # (slot, host frame) copied but not consumed; (step, host frame) issued
+        it = itertools.chain((first,), it)
 
         def push(frame):
             if frame.numel() * frame.element_size() != frame_bytes or not frame.is_pinned():
@@ -503,35 +566,50 @@ class FusedFrameFit(torch.nn.Module):
             loss = self.loss(step, wait=False)
             return loss, 10 * math.log10(1.0 / max(loss, 1e-20))
 
-        try:
+        def refill():
             with self._C._guard(dev):
-                push(first)
-                for _ in range(depth - 1):
+                while len(queued) < depth:
                     nxt = next(it, None)
                     if nxt is None:
                         break
                     push(nxt)
-            while queued:
-                slot, frame = queued.pop(0)
-                with self._C._guard(dev):
-                    rc = lib.gs2d_frame_pipe_acquire(pipe, slot, stream, ct.byref(ptr_out))
-                    if rc:
-                        check(rc, "frame_pipe_acquire")
-                    self._issue(ptr_out.value, fmt, stream=stream)
-                    rc = lib.gs2d_frame_pipe_release(pipe, slot, stream)
-                    if rc:
-                        check(rc, "frame_pipe_release")
-                    inflight.append((self.step_index, frame))   # the frame stays alive until its step reported
-                    nxt = next(it, None)
-                    if nxt is not None:                          # its copy overlaps the step just issued
-                        push(nxt)
-                while len(inflight) > lag:
-                    yield result(inflight.pop(0)[0])
-            while inflight:
-                yield result(inflight.pop(0)[0])
-        finally:
-            torch.cuda.current_stream(dev).synchronize()
-            lib.gs2d_frame_pipe_destroy(pipe)
+
+        recoveries = 0
+        refill()
+        while queued or inflight:
+            try:
+                if queued:
+                    slot, frame = queued.pop(0)
+                    with self._C._guard(dev):
+                        rc = lib.gs2d_frame_pipe_acquire(pipe, slot, stream, ct.byref(ptr_out))
+                        if rc:
+                            check(rc, "frame_pipe_acquire")
+                        self._issue(ptr_out.value, fmt, stream=stream)
+                        rc = lib.gs2d_frame_pipe_release(pipe, slot, stream)
+                        if rc:
+                            check(rc, "frame_pipe_release")
+                        inflight.append((self.step_index, frame))   # the frame stays alive until its step reported
+                        nxt = next(it, None)
+                        if nxt is not None:                          # its copy overlaps the step just issued
+                            push(nxt)
+                while len(inflight) > (lag if queued else 0):
+                    res = result(inflight[0][0])
+                    inflight.pop(0)
+                    yield res
+            except GS2DOverflow:
+                # loss() has rewound the model and re-made its workspace; the steps still in `inflight` were
+                # no-ops (the first of them is the one that overflowed): their frames, then the frames already
+                # copied but not consumed, go round again through a fresh pipe
+                recoveries += 1
+                if recoveries > 8:
+                    raise
+                redo = [fr for _st, fr in inflight] + [fr for _sl, fr in queued]
+                inflight.clear()
+                queued.clear()
+                self._drop_frame_pipe()
+                pipe = self._frame_pipe(frame_bytes, depth)
+                it = itertools.chain(redo, it)
+                refill()
 
     @property
     def last_num_intersects(self) -> int:

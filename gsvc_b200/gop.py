@@ -46,6 +46,16 @@ def assign_gops(gops: Sequence[Gop], world: int, cost: Optional[Callable[[Gop], 
     return out
 
 
+def _fit_all(fit, gt, iters: int) -> float:
+    """`iters` iterations that really happen: a fused fitter whose workspace overflows (a tile beyond
+    256 slots, more intersections than its capacity) rewinds and continues by itself
+    (FusedFrameFit.train_until); other fitters just iterate"""
+    if hasattr(fit, "train_until"):
+        return fit.train_until(gt, fit.step_index + iters)
+    fit.train_iters(gt, iters)
+    return fit.loss()
+
+
 def fit_gop(get_frame: Callable[[int], torch.Tensor], gop: Gop, make_fitter: Callable[[Optional[dict]], object],
             iters_key: int, iters_pred: int, on_frame: Optional[Callable[[int, object], None]] = None,
             seed: Optional[int] = None) -> Dict[int, dict]:
@@ -67,8 +77,7 @@ def fit_gop(get_frame: Callable[[int], torch.Tensor], gop: Gop, make_fitter: Cal
             fit.rng = torch.Generator().manual_seed(int(seed) * 100003 + f)
         iters = iters_key if prev is None else iters_pred
         gt = get_frame(f)
-        fit.train_iters(gt, iters)
-        loss = fit.loss()
+        loss = _fit_all(fit, gt, iters)
         # the reference hands on _xyz, _cholesky and the WEIGHTED colours (train_video_Represent.py:107-114)
         state = fit.frame_state() if hasattr(fit, "frame_state") else fit.state_dict()
         prev = {k: v.detach().clone() for k, v in state.items()}
@@ -238,9 +247,9 @@ def keyframe_scores(get_frame: Callable[[int], torch.Tensor], num_frames: int,
         if seed is not None:
             torch.manual_seed(int(seed) * 100003 + f)
         fit = make_probe(None)
-        fit.train_iters(get_frame(f), iters_key)
+        loss = _fit_all(fit, get_frame(f), iters_key)
         state = fit.frame_state() if hasattr(fit, "frame_state") else fit.state_dict()
-        return {k: v.detach().clone() for k, v in state.items()}, fit.loss()
+        return {k: v.detach().clone() for k, v in state.items()}, loss
 
     prev = fresh(a - 1)[0] if (a > 0 and b > a) else None          # the halo
     for f in range(a, b):
@@ -249,8 +258,7 @@ def keyframe_scores(get_frame: Callable[[int], torch.Tensor], num_frames: int,
             local[f] = 0.0                                          # :324-326
         else:
             p = make_probe(prev)
-            p.train_iters(get_frame(f), iters_pred)
-            local[f] = p.loss() - loss_k
+            local[f] = _fit_all(p, get_frame(f), iters_pred) - loss_k
         prev = cur
     if not distributed:
         return [local[f] for f in range(num_frames)]

@@ -25,6 +25,15 @@ class Options:
     #: not bound (rasterize_sum.py:147-150, ext.cpp:4-24).  True: 1..32 channels are rendered, with
     #: no per-tile limit (the reference's N-channel kernel has none, forward.cu:664).
     nd_channels: bool = False
+    #: "ranked": rasterize_gaussians_sum bins by per-tile counts + scatter and orders a tile's batch by
+    #: Gaussian id inside the tile kernels (three kernels, nothing the host waits for, CUDA-graph
+    #: capturable).  "onesweep": the step-by-step chain scan -> map -> custom onesweep radix sort ->
+    #: bin edges, which materialises the sorted key / id arrays like the reference does.  Same results.
+    binning: str = "ranked"
+    #: True: a forward never waits for the device; its intersection count is read later from pinned
+    #: memory (gsvc_b200.rasterize_sum module docstring: capacity, lazy overflow check).  False: every
+    #: forward waits for its own count before it returns, like the reference's .item() (utils.py:117).
+    sync_free: bool = True
 
     @contextmanager
     def override(self, **kw):

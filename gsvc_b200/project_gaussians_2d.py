@@ -20,7 +20,7 @@ def project_gaussians_2d(means2d: Tensor, L_elements: Tensor, img_height: int, i
     out = _ProjectGaussians2d.apply(means2d.contiguous(), L_elements.contiguous(), img_height, img_width,
                                     tile_bounds, clip_thresh)
     # depths are identically zero here (foward2d.cu:66-67): lets the rasteriser sort on tile id only
-    out[1]._gs2d_zero_depth = True
+    out[1]._gs2d_zero_depth = out[1]._version   # void once somebody writes into it
     return out
 
 

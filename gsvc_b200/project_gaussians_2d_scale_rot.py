@@ -18,7 +18,7 @@ def project_gaussians_2d_scale_rot(means2d: Tensor, scales2d: Tensor, rotation: 
     project_gaussians_2d; differentiable w.r.t. means2d, scales2d and rotation."""
     out = _ProjectGaussians2dScaleRot.apply(means2d.contiguous(), scales2d.contiguous(), rotation.contiguous(),
                                             img_height, img_width, tile_bounds, clip_thresh)
-    out[1]._gs2d_zero_depth = True
+    out[1]._gs2d_zero_depth = out[1]._version   # void once somebody writes into it
     return out
 
 

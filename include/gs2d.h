@@ -178,6 +178,38 @@ int gs2d_rasterize_sum_bwd_binned(int n, int num_intersects, const int32_t* gaus
                                   const int32_t* final_idx, const float* v_out, float* grads, void* scratch,
                                   size_t scratch_bytes, gs2d_stream_t stream);
 
+/* Sync-free, CUDA-graph-capturable forward / backward of rasterize_gaussians_sum on count / scatter
+ * binning (the default of the Python operator; same results as gs2d_rasterize_sum_fwd / _bwd).
+ * Replaces the same reference code (rasterize_sum.py:93-254, utils.py:99-167, forward.cu:100-163,
+ * 512-627, backward.cu:696-862) but orders a tile's Gaussians inside the tile kernels instead of
+ * sorting (tile, id) keys: per-tile counts by atomics + a last-block scan give the reference's
+ * tile_bins, a scatter fills each range in arbitrary order, and the forward / backward kernels put
+ * a tile's batch into ascending Gaussian-id order -- the order of the reference's torch.sort on
+ * tile|depth keys when depths are zero, which is what both projections emit -- while
+ * staging it into shared memory.  Three kernels (count+scan, scatter-pack, tiles) chained with
+ * programmatic dependent launch instead of five, no key / id arrays, and nothing the host has to
+ * wait for: the intersection count stays on the device.
+ *   state       gs2d_opstate_bytes(cap, H, W) bytes, 256-byte aligned, kept for the backward;
+ *               [0, zero) is cleared here (one memset);
+ *   background  fp32[3] or NULL: with no intersection at all the image is the background colour,
+ *               as rasterize_sum.py:121-129 returns it (decided on the device);
+ *   mail_host   PINNED int32[8] or NULL: {num_intersects, overflow (num_intersects > cap),
+ *               max per tile, 0, mail_seq} written by the scan's last block, mail_seq last.  The
+ *               host reads it whenever it next cares (capacity hint, lazy overflow check);
+ *   overflow    when num_intersects > cap nothing is scattered or rendered (out_img is left
+ *               untouched) and the backward writes zero gradients: the caller must regrow and redo.
+ * Depths are taken to be zero (callers with non-zero depths use the step-by-step path).  The
+ * N-channel / untruncated options stay on gs2d_rasterize_sum_nd_*. */
+size_t gs2d_opstate_bytes(int cap, int img_h, int img_w);
+/* byte offsets of tile_off (int32[tiles+1]), the packed records and the status words inside it */
+int gs2d_opstate_ranges(int cap, int img_h, int img_w, size_t* off_tile_off, size_t* off_packed, size_t* off_status);
+int gs2d_rasterize_sum_fwd_ranked(int n, const float* xys, const int32_t* radii, const float* conics,
+                                  const float* colors, const float* opacities, const float* background, int img_h,
+                                  int img_w, int cap, void* state, size_t state_bytes, float* out_img,
+                                  int32_t* final_idx, int32_t* mail_host, int mail_seq, gs2d_stream_t stream);
+int gs2d_rasterize_sum_bwd_ranked(int n, int img_h, int img_w, int cap, const void* state, size_t state_bytes,
+                                  const int32_t* final_idx, const float* v_out, float* grads, gs2d_stream_t stream);
+
 /* N-channel and / or untruncated accumulated-sum rasteriser.  The reference's Python
  * dispatches colours with channels != 3 to nd_rasterize_sum_forward / _backward (rasterize_sum.py:
  * 147-150, 218-221), which its extension never binds although the kernels exist
@@ -389,6 +421,18 @@ int gs2d_fit_step_band(int n, int cap, int img_h, int img_w, float* xyz_raw, flo
                        const gs2d_grad_exchange* exchange, const gs2d_fit_options* options, float* out_img,
                        float* param_grads_out, int32_t* ids_sorted_out, gs2d_fit_report* report_host,
                        gs2d_stream_t stream);
+/* The Adan step of the operator loop as one kernel over all parameter tensors (replaces the ~20
+ * torch._foreach_* launches of _multi_tensor_adan, optimizer.py:296-362; defaults of :65-74;
+ * the reference anticipates an external fused kernel at :365-395).  Per element, g the gradient:
+ *   diff = g - prev (0 when `first`);  m = b1 m + (1-b1) g;  d = b2 d + (1-b2) diff;
+ *   u = g + b2 diff;  n = b3 n + (1-b3) u^2;  denom = sqrt(n)/sqrt(1-b3^step) + eps;
+ *   p = (p - lr/(1-b1^step) m/denom - lr b2/(1-b2^step) d/denom) / (1 + lr wd);  prev = g
+ * The six tables are HOST arrays of num_tensors DEVICE pointers (fp32, contiguous, counts[i]
+ * elements each); `first` != 0 at the optimizer's first step (optimizer.py:183-185). */
+int gs2d_adan_step(int num_tensors, float* const* params, const float* const* grads, float* const* exp_avg,
+                   float* const* exp_avg_sq, float* const* exp_avg_diff, float* const* prev_grad, const int* counts,
+                   float lr, float beta1, float beta2, float beta3, float eps, float weight_decay, int step, int first,
+                   gs2d_stream_t stream);
 /* The reference's prune (GaussianSplats_Represent.py:98-128, :147-171): drop the `remove_count`
  * Gaussians with the smallest |rgb_w| (torch.norm over dim 1 of an [N,1] tensor, then torch.sort,
  * :103-104 / :146-147; ties -- which torch.sort leaves unspecified -- go lowest index first) and

@@ -96,3 +96,25 @@ def test_optimizer_clock():
     assert c.lr_frozen
     assert c.begin(Action("prune", 2, True)) == (1, True, True)    # rebuilt and replaced: its first step sees no grads
     assert c.begin(Action()) == (2, True, False)
+
+
+def test_adan_takes_the_reference_constructor_arguments_and_refuses_what_it_lacks():
+    """optimizer.py:65-74 of the reference: Adan(params, lr, betas, eps, weight_decay, max_grad_norm,
+    no_prox, foreach, fused)"""
+    import pytest
+    import torch
+    from gsvc_b200.adan import Adan
+    p = [torch.nn.Parameter(torch.zeros(4, 2))]
+    Adan(p, lr=1e-3, betas=(0.98, 0.92, 0.99), eps=1e-8, weight_decay=0.0, max_grad_norm=0.0, no_prox=False,
+         foreach=True, fused=False)
+    with pytest.raises(NotImplementedError):
+        Adan(p, max_grad_norm=1.0)
+    with pytest.raises(NotImplementedError):
+        Adan(p, no_prox=True)
+    opt = Adan(p, fused=True)
+    p[0].grad = torch.ones(4, 2)
+    with pytest.raises(RuntimeError):
+        opt.step()                      # fused=True insists on CUDA tensors
+    opt = Adan(p)                       # default: decides per step -> foreach on the CPU
+    opt.step()
+    assert torch.allclose(p[0], torch.full((4, 2), -1e-3), atol=1e-6)

@@ -78,19 +78,167 @@ def test_argument_errors():
         G.rasterize_gaussians_sum(*[t.cpu() for t in p], x["colors"].cpu(), x["opacity"].cpu(), H, W)
 
 
-def test_capacity_overflow_regrows_and_matches():
+def _reset_capacity(H, W, cap=None):
+    from gsvc_b200 import rasterize_sum as RS
+    dctx = RS._device_ctx(cuda)
+    torch.cuda.synchronize()
+    try:
+        dctx.poll()
+    except RS.CapacityOverflow:
+        pass
+    dctx.cap.pop((H, W), None)
+    if cap is not None:
+        dctx.cap[(H, W)] = cap
+    return dctx
+
+
+@pytest.mark.parametrize("binning", ["ranked", "onesweep"])
+def test_capacity_overflow_regrows_and_matches(binning):
+    """options.sync_free = False (and the step-by-step chain): a call whose intersections outgrow the
+    buffer is redone with a larger one before it returns"""
+    import gsvc_b200
     from gsvc_b200 import rasterize_sum as RS
     x = _x(20_000, trained=True)
     H, W = 256, 256
-    dctx = RS._device_ctx(cuda)
-    dctx.cap[(H, W)] = RS._CAP_QUANTUM   # far too small on purpose
-    p, out_small = _render(x, H, W)
-    assert dctx.cap[(H, W)] > RS._CAP_QUANTUM
-    p2, out_again = _render(x, H, W)
+    with gsvc_b200.options.override(binning=binning, sync_free=False):
+        dctx = _reset_capacity(H, W, RS._CAP_QUANTUM)   # far too small on purpose
+        p, out_small = _render(x, H, W)
+        assert dctx.cap[(H, W)] > RS._CAP_QUANTUM
+        p2, out_again = _render(x, H, W)
     assert torch.equal(out_small, out_again)
     if ref_gpu.available():
         r = ref_gpu.pipeline(x["means2d"], x["L"], x["colors"], x["opacity"], H, W)
         assert (out_small - r["out_img"]).abs().max().item() <= 1e-5 * max(1.0, r["out_img"].abs().max().item())
+
+
+def test_sync_free_overflow_is_loud_then_recovers():
+    """default (sync-free): the first call of an image size learns the count; a later call that still
+    outgrows its buffer gets a NaN image, the next call raises CapacityOverflow with the buffer
+    regrown, and the call after that is right again"""
+    from gsvc_b200 import rasterize_sum as RS
+    small, big = _x(2_000), _x(20_000, trained=True)
+    H, W = 256, 256
+    _reset_capacity(H, W)
+    _, ok = _render(small, H, W)                 # first call: waits once, sizes the buffer for `small`
+    assert torch.isfinite(ok).all()
+    dctx = RS._device_ctx(cuda)
+    dctx.cap[(H, W)] = RS._CAP_QUANTUM           # pretend the hint is stale and far too small
+    _, bad = _render(big, H, W)                  # outgrows it: nothing waits, so nothing can be redone
+    torch.cuda.synchronize()
+    assert torch.isnan(bad).all()
+    with pytest.raises(RS.CapacityOverflow):
+        _render(big, H, W)
+    _, good = _render(big, H, W)
+    torch.cuda.synchronize()
+    RS.check_overflow(cuda)
+    if ref_gpu.available():
+        r = ref_gpu.pipeline(big["means2d"], big["L"], big["colors"], big["opacity"], H, W)
+        assert (good - r["out_img"]).abs().max().item() <= 1e-5 * max(1.0, r["out_img"].abs().max().item())
+
+
+def test_sync_free_forward_never_synchronises_the_host():
+    """after the first call of a size, a forward must return while the device is still busy with
+    work queued BEFORE it (the reference blocks on .item(), utils.py:117)"""
+    x = _x(10_000)
+    H, W = 256, 256
+    _reset_capacity(H, W)
+    _render(x, H, W)
+    torch.cuda.synchronize()
+    spin = torch.empty(1 << 28, dtype=torch.uint8, device=cuda)
+    done = torch.cuda.Event()
+    for _ in range(20):
+        spin.zero_()                               # ~20 x 40 us of device work ahead of the forward
+    _render(x, H, W)
+    done.record()
+    assert not done.query(), "the forward waited for the device"
+    torch.cuda.synchronize()
+
+
+def test_ranked_and_onesweep_binning_agree_bit_for_bit():
+    import gsvc_b200
+    H, W = 200, 328
+    for trained in (False, True):
+        x = _x(6_000, trained=trained)
+        for k in x:
+            x[k].requires_grad_(k != "opacity")
+        res = {}
+        for binning in ("ranked", "onesweep"):
+            with gsvc_b200.options.override(binning=binning):
+                _reset_capacity(H, W)
+                _, out = _render(x, H, W)
+                v = torch.linspace(-1, 1, out.numel(), device=cuda).view_as(out)
+                g = torch.autograd.grad(out, [x["means2d"], x["L"], x["colors"]], v)
+                res[binning] = (out.detach(), g)
+        assert torch.equal(res["ranked"][0], res["onesweep"][0])
+        for a, b in zip(res["ranked"][1], res["onesweep"][1]):
+            assert (a - b).abs().max().item() <= 1e-4 * max(b.abs().max().item(), 1e-30)
+
+
+def test_forward_backward_capture_in_a_cuda_graph():
+    """project_gaussians_2d -> rasterize_gaussians_sum -> backward captured once and replayed: same
+    bits as the eager call (gradients: same up to the order of the atomics)"""
+    import gsvc_b200 as G
+    from gsvc_b200 import rasterize_sum as RS
+    H, W, n = 256, 256, 10_000
+    tb = (16, 16, 1)
+    x = _x(n)
+    for k in ("means2d", "L", "colors"):
+        x[k].requires_grad_(True)
+    gt = synth.target_frame(H, W)[0].permute(1, 2, 0).contiguous().to(cuda)
+    _reset_capacity(H, W)
+
+    def step():
+        p = G.project_gaussians_2d(x["means2d"], x["L"], H, W, tb)
+        out = G.rasterize_gaussians_sum(*p, x["colors"], x["opacity"], H, W, 16, 16)
+        loss = ((out.clamp(0, 1) - gt) ** 2).mean()
+        grads = torch.autograd.grad(loss, [x["means2d"], x["L"], x["colors"]])
+        return out, loss, grads
+
+    out_e, loss_e, grads_e = step()               # eager (also sizes the buffer)
+    torch.cuda.synchronize()
+    side = torch.cuda.Stream()
+    side.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(side):
+        step()                                    # warm-up on the capture stream
+    torch.cuda.current_stream().wait_stream(side)
+    graph = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(graph):
+        out_g, loss_g, grads_g = step()
+    for _ in range(3):
+        graph.replay()
+    torch.cuda.synchronize()
+    RS.check_overflow(cuda)
+    assert torch.equal(out_g, out_e.detach())
+    assert loss_g.item() == pytest.approx(loss_e.item(), rel=1e-6)
+    for a, b in zip(grads_g, grads_e):
+        assert (a - b).abs().max().item() <= 1e-4 * max(b.abs().max().item(), 1e-30)
+    # new inputs, same graph: the replay renders them
+    with torch.no_grad():
+        x["colors"].mul_(0.5)
+    graph.replay()
+    torch.cuda.synchronize()
+    with torch.no_grad():
+        p = G.project_gaussians_2d(x["means2d"], x["L"], H, W, tb)
+        ref = G.rasterize_gaussians_sum(*p, x["colors"], x["opacity"], H, W, 16, 16)
+    assert torch.equal(out_g, ref)
+
+
+def test_edited_depths_are_not_taken_for_zero():
+    """the zero-depth shortcut is void once somebody writes into the depths tensor"""
+    import gsvc_b200 as G
+    x = _x(3_000, trained=True)
+    H, W = 128, 128
+    tb = (8, 8, 1)
+    xys, depths, radii, conics, nth = G.project_gaussians_2d(x["means2d"], x["L"], H, W, tb)
+    a = G.rasterize_gaussians_sum(xys, depths, radii, conics, nth, x["colors"], x["opacity"], H, W)
+    depths.add_(torch.rand_like(depths) + 0.1)    # in place: same tensor object, new version
+    b = G.rasterize_gaussians_sum(xys, depths, radii, conics, nth, x["colors"], x["opacity"], H, W)
+    if ref_gpu.available():
+        r = ref_gpu.bin_and_sort(3_000, xys, depths, radii, nth, tb)
+        ro, _, _ = ref_gpu.rasterize_sum_forward(H, W, r["gaussian_ids_sorted"], r["tile_bins"], xys, conics,
+                                                 x["colors"], x["opacity"])
+        assert (b - ro).abs().max().item() <= 1e-5 * max(1.0, ro.abs().max().item())
+    assert a.shape == b.shape
 
 
 def test_nonzero_depths_take_the_64bit_key_path():
