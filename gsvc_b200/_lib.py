@@ -61,7 +61,7 @@ class FitOptions(Structure):
 
     _fields_ = [("rgb_w", c_void_p), ("adan_state_w", c_void_p), ("rgb_w_grad_out", c_void_p), ("adan_step", c_int),
                 ("adan_fresh", c_int), ("skip_update", c_int), ("slots", c_int), ("all_per_tile", c_int),
-                ("analytic_grad", c_int)]
+                ("analytic_grad", c_int), ("params8", c_void_p)]
 
 
 class QuantizedFrame(Structure):
@@ -72,7 +72,7 @@ class QuantizedFrame(Structure):
 
 
 FIT_LOSS_SLOTS = 64
-TARGET_F32_CHW, TARGET_U8_HWC, TARGET_I420 = 0, 1, 2
+TARGET_F32_CHW, TARGET_U8_HWC, TARGET_I420, TARGET_TILED = 0, 1, 2, 3
 FIT_PHASE_GRADS, FIT_PHASE_UPDATE = 1, 2
 
 _P = c_void_p
@@ -110,6 +110,8 @@ _SIGNATURES = {
     "gs2d_rasterize_sum_nd_fwd": (c_int, [c_int, c_int, _P, _P, _P, _P, _P, _P, _P, c_int, c_int, c_int, c_int, _P, c_size_t, _P, _P, _P, _P, _P]),
     "gs2d_rasterize_sum_nd_bwd": (c_int, [c_int, c_int, c_int, c_int, c_int, c_int, _P, c_size_t, _P, _P, _P, _P, _P, _P]),
     "gs2d_fit_layout_for": (c_int, [c_int, c_int, c_int, c_int, POINTER(FitLayout)]),
+    "gs2d_fit_target_bytes": (c_size_t, [c_int, c_int]),
+    "gs2d_fit_target_prepare": (c_int, [c_int, c_int, _P, c_int, _P, _P]),
     "gs2d_fit_init": (c_int, [c_int, c_int, c_int, c_int, _P, c_size_t, _P, _P]),
     "gs2d_fit_step": (c_int, [c_int, c_int, c_int, c_int, _P, _P, _P, _P, _P, c_int, _P, c_size_t, c_int,
                               c_float, c_float, c_float, c_float, c_float, c_float, c_int, _P, _P, _P, _P, _P]),
@@ -125,7 +127,7 @@ _SIGNATURES = {
     "gs2d_frame_pipe_acquire": (c_int, [_P, c_int, _P, POINTER(c_void_p)]),
     "gs2d_frame_pipe_release": (c_int, [_P, c_int, _P]),
     "gs2d_adan_step": (c_int, [c_int, _P, _P, _P, _P, _P, _P, _P, c_float, c_float, c_float, c_float, c_float, c_float,
-                               c_int, c_int, _P]),
+                               c_int, _P, c_int, _P]),
     "gs2d_prune_scratch_bytes": (c_size_t, [c_int]),
     "gs2d_prune_lowest": (c_int, [c_int, c_int, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, c_size_t, _P]),
     "gs2d_render_chol": (c_int, [c_int, c_int, c_int, c_int, _P, _P, _P, _P, c_int, _P, c_size_t, _P, c_int, c_int,

@@ -33,7 +33,7 @@ import torch
 
 class Adan(torch.optim.Optimizer):
     def __init__(self, params, lr=1e-3, betas=(0.98, 0.92, 0.99), eps=1e-8, weight_decay=0.0, max_grad_norm=0.0,
-                 no_prox=False, foreach: bool = True, fused: Optional[bool] = None):
+                 no_prox=False, foreach: bool = True, fused: Optional[bool] = None, capturable: bool = False):
         if lr < 0 or eps < 0 or not all(0.0 <= b < 1.0 for b in betas):
             raise ValueError("Adan: invalid hyper-parameters")
         if max_grad_norm != 0.0:
@@ -43,6 +43,10 @@ class Adan(torch.optim.Optimizer):
             raise NotImplementedError("Adan: no_prox=True (optimizer.py:351-357) is not implemented; the reference's "
                                       "fit loop leaves it False")
         self.fused = fused
+        # capturable: the step count also lives in a device int32 (group["step_dev"]) which step() bumps
+        # with a torch op and the kernel reads at run time, so that step() can sit inside a captured CUDA
+        # graph (needs the fused kernel; lr and the other hyper-parameters are baked in at capture)
+        self.capturable = bool(capturable)
         del foreach   # accepted for constructor compatibility: both paths here are multi-tensor
         super().__init__(params, dict(lr=lr, betas=betas, eps=eps, weight_decay=weight_decay))
 
@@ -51,7 +55,7 @@ class Adan(torch.optim.Optimizer):
         return all(p.is_cuda and p.dtype == torch.float32 and p.is_contiguous() and g.is_cuda
                    and g.dtype == torch.float32 and p.device == ps[0].device for p, g in zip(ps, gs))
 
-    def _step_fused(self, ps, gs, ms, ns, ds, prevs, lr, b1, b2, b3, eps, wd, t, first):
+    def _step_fused(self, ps, gs, ms, ns, ds, prevs, lr, b1, b2, b3, eps, wd, t, first, step_dev=None):
         from . import _lib
         from . import cuda as _C
         gs = [g if g.is_contiguous() else g.contiguous() for g in gs]
@@ -61,7 +65,9 @@ class Adan(torch.optim.Optimizer):
         dev = ps[0].device
         with _C._guard(dev):
             _lib.check(_lib.load().gs2d_adan_step(k, table(ps), table(gs), table(ms), table(ns), table(ds), table(prevs),
-                                                  counts, lr, b1, b2, b3, eps, wd, t, 1 if first else 0,
+                                                  counts, lr, b1, b2, b3, eps, wd, t,
+                                                  None if step_dev is None else step_dev.data_ptr(),
+                                                  1 if first else 0,
                                                   torch.cuda.current_stream(dev).cuda_stream), "adan_step")
 
     @torch.no_grad()
@@ -97,12 +103,20 @@ class Adan(torch.optim.Optimizer):
                 if fused and not ok:
                     raise RuntimeError("Adan(fused=True) needs contiguous fp32 CUDA parameters on one device")
                 fused = ok
+            if self.capturable and not fused:
+                raise RuntimeError("Adan(capturable=True) needs the fused kernel (contiguous fp32 CUDA parameters)")
             if fused:
                 first = all(fresh)
                 if first:   # the kernel writes prev := g; it only needs somewhere to put it
                     for i, p in enumerate(ps):
                         prevs[i] = self.state[p]["prev"] = torch.empty_like(p, memory_format=torch.contiguous_format)
-                self._step_fused(ps, gs, ms, ns, ds, prevs, lr, b1, b2, b3, eps, wd, t, first)
+                step_dev = None
+                if self.capturable:
+                    step_dev = group.get("step_dev")
+                    if step_dev is None:
+                        step_dev = group["step_dev"] = torch.full((1,), t - 1, dtype=torch.int32, device=ps[0].device)
+                    step_dev.add_(1)      # (inside a captured graph: replayed with every iteration)
+                self._step_fused(ps, gs, ms, ns, ds, prevs, lr, b1, b2, b3, eps, wd, t, first, step_dev)
                 continue
             for i, p in enumerate(ps):
                 if fresh[i]:

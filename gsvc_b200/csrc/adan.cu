@@ -26,10 +26,31 @@ struct AdanBatch {
 struct AdanScalars {
     float b1, b2, b3, step_size, step_size_diff, inv_bc3_sqrt, eps, decay_div;
     int first;   // previous gradient := gradient (optimizer.py:183-185)
+    // step count in device memory (a captured CUDA graph replays the same arguments every iteration, so
+    // the bias corrections cannot be baked into them): when set, the three step-dependent factors are
+    // computed here from *step_dev with the arithmetic the host uses (double pow / sqrt, rounded once)
+    const int* step_dev;
+    float lr;
 };
+
+__device__ __forceinline__ void adan_bias_corrections(AdanScalars& h) {
+    const double t = (double)*h.step_dev;
+    h.step_size = (float)((double)h.lr / (1.0 - pow((double)h.b1, t)));
+    h.step_size_diff = (float)((double)h.lr * (double)h.b2 / (1.0 - pow((double)h.b2, t)));
+    h.inv_bc3_sqrt = (float)(1.0 / sqrt(1.0 - pow((double)h.b3, t)));
+}
 
 __global__ void __launch_bounds__(kAdanThreads)
 k_adan_step(AdanBatch tb, AdanScalars h) {
+    if (h.step_dev) {
+        __shared__ float s_corr[3];
+        if (threadIdx.x == 0) {
+            adan_bias_corrections(h);
+            s_corr[0] = h.step_size; s_corr[1] = h.step_size_diff; s_corr[2] = h.inv_bc3_sqrt;
+        }
+        __syncthreads();
+        h.step_size = s_corr[0]; h.step_size_diff = s_corr[1]; h.inv_bc3_sqrt = s_corr[2];
+    }
     int t = 0;
 #pragma unroll
     for (int k = 1; k < kAdanMaxTensors; ++k)
@@ -88,8 +109,9 @@ using namespace gs2d;
 extern "C" int gs2d_adan_step(int num_tensors, float* const* params, const float* const* grads, float* const* exp_avg,
                               float* const* exp_avg_sq, float* const* exp_avg_diff, float* const* prev_grad,
                               const int* counts, float lr, float beta1, float beta2, float beta3, float eps,
-                              float weight_decay, int step, int first, gs2d_stream_t stream) {
-    GS2D_REQUIRE(num_tensors >= 0 && step >= 1, "adan_step: bad arguments");
+                              float weight_decay, int step, const int* step_dev, int first, gs2d_stream_t stream) {
+    GS2D_REQUIRE(num_tensors >= 0 && (step >= 1 || step_dev != nullptr), "adan_step: bad arguments");
+    if (step < 1) step = 1;
     GS2D_REQUIRE(num_tensors == 0 || (params && grads && exp_avg && exp_avg_sq && exp_avg_diff && prev_grad && counts),
                  "adan_step: null pointer table");
     cudaStream_t s = (cudaStream_t)stream;
@@ -101,6 +123,8 @@ extern "C" int gs2d_adan_step(int num_tensors, float* const* params, const float
     h.eps = eps;
     h.decay_div = 1.f + lr * weight_decay;
     h.first = first != 0;
+    h.step_dev = step_dev;
+    h.lr = lr;
     for (int t0 = 0; t0 < num_tensors; t0 += kAdanMaxTensors) {
         AdanBatch tb = {};
         tb.num = num_tensors - t0 < kAdanMaxTensors ? num_tensors - t0 : kAdanMaxTensors;

@@ -106,7 +106,16 @@ struct QuantConst {
     const int32_t* radii;     // activate == 3 only
     int32_t* mail_host;       // operator path: pinned int32[8] the scan reports into (may be NULL)
     int mail_seq;
+    // activate 0 / 1: floats between consecutive rows of the three parameter tensors; 0 = contiguous
+    // (2 / 3 / 3).  8 / 8 / 8 with the pointers at +0 / +2 / +5 of one buffer = the packed [n][8] rows
+    // of gs2d_fit_options.params8 (two aligned 16-byte loads per Gaussian)
+    int ld_xyz, ld_chol, ld_feat;
 };
+static inline QuantConst packed8_rows() {
+    QuantConst qc = QuantConst();
+    qc.ld_xyz = qc.ld_chol = qc.ld_feat = 8;
+    return qc;
+}
 
 __device__ __forceinline__ void fit_project(int i, const float* __restrict__ xyz_raw, const float* __restrict__ chol_raw,
                                             int activate, float half_w, float half_h, int tx, int ty, Proj2d& p,
@@ -138,8 +147,19 @@ __device__ __forceinline__ void fit_project(int i, const float* __restrict__ xyz
         L.y = addf(addf(mulf((float)c[1], qc.scale[1]), qc.beta[1]), 0.f);
         L.z = addf(addf(mulf((float)c[2], qc.scale[2]), qc.beta[2]), 0.5f);
     } else {
-        const float2 r = reinterpret_cast<const float2*>(xyz_raw)[i];
-        L = make_float3(chol_raw[3 * i], chol_raw[3 * i + 1], chol_raw[3 * i + 2]);
+        float2 r;
+        if (qc.ld_xyz == 8 && qc.ld_chol == 8 && chol_raw == xyz_raw + 2) {
+            // packed rows: xyz(2) chol(3) feat(3) -- two 16-byte loads (the second one is shared with
+            // fit_colour's: the compiler sees the same address)
+            const float4 a = reinterpret_cast<const float4*>(xyz_raw)[2 * (size_t)i];
+            const float4 b = reinterpret_cast<const float4*>(xyz_raw)[2 * (size_t)i + 1];
+            r = make_float2(a.x, a.y);
+            L = make_float3(a.z, a.w, b.x);
+        } else {
+            const size_t lx = qc.ld_xyz ? qc.ld_xyz : 2, lc = qc.ld_chol ? qc.ld_chol : 3;
+            r = *reinterpret_cast<const float2*>(xyz_raw + lx * i);
+            L = make_float3(chol_raw[lc * i], chol_raw[lc * i + 1], chol_raw[lc * i + 2]);
+        }
         if (activate) {
             means = make_float2(tanhf(r.x), tanhf(r.y));
             L.x = addf(L.x, 0.5f); L.y = addf(L.y, 0.f); L.z = addf(L.z, 0.5f);
@@ -159,7 +179,12 @@ __device__ __forceinline__ float3 fit_colour(int i, const float* __restrict__ fe
     }
     // colours = _features_dc * rgb_W (GaussianSplats_Represent.py:62-63); plain fp32 products
     const float cw = rgb_w ? rgb_w[i] : 1.f;
-    return make_float3(mulf(feat[3 * i], cw), mulf(feat[3 * i + 1], cw), mulf(feat[3 * i + 2], cw));
+    if (qc.ld_feat == 8 && ((uintptr_t)(feat - 5) & 15) == 0) {   // packed rows: feat = row + 5
+        const float4 b = reinterpret_cast<const float4*>(feat - 5)[2 * (size_t)i + 1];
+        return make_float3(mulf(b.y, cw), mulf(b.z, cw), mulf(b.w, cw));
+    }
+    const size_t lf = qc.ld_feat ? qc.ld_feat : 3;
+    return make_float3(mulf(feat[lf * i], cw), mulf(feat[lf * i + 1], cw), mulf(feat[lf * i + 2], cw));
 }
 
 // ------------------------------------------------------------------------------------------
@@ -459,11 +484,55 @@ constexpr int kBwdRows = GS2D_BWD_ROWS;   // rows of a pair's rectangle a lane e
 constexpr int kWarpStage = GS2D_WARP_STAGE;
 constexpr int kSqRecords = GS2D_SQ_RECORDS > 32 * (kTileThreads / 32) ? GS2D_SQ_RECORDS : 32 * (kTileThreads / 32);
 
+// The target frame in the tile kernel's own order: fp32 [tiles][kTileThreads][kPix][3], i.e. for every
+// tile the 12 (kPix * 3) floats each thread compares its pixels with, contiguous.  A frame is fitted for
+// thousands of iterations (train_video_Represent.py:85-86 of the reference); decoding its bytes in every
+// one of them was a fifth of the tile kernel's instructions.  Values are what the kernel's own decode
+// produces (same device functions), pixels outside the image are zero.
+template <int GT>
+__global__ void __launch_bounds__(kTileThreads)
+k_target_tiled(int W, int H, int tx, const void* __restrict__ gt, float* __restrict__ out) {
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int t = blockIdx.y * tx + blockIdx.x;
+    const int lx = lane & 15, ly0 = kWarpRows * warp + (lane >> 4);
+    const int px_i = blockIdx.x * GS2D_TILE + lx;
+    float tv[kPix * 3];
+#pragma unroll
+    for (int j = 0; j < kPix; ++j) {
+        const int py_i = blockIdx.y * GS2D_TILE + ly0 + 2 * j;
+        float3 v = make_float3(0.f, 0.f, 0.f);
+        if (px_i < W && py_i < H) {
+            const size_t pid = (size_t)py_i * W + px_i, plane = (size_t)H * W;
+            if (GT == 0) {
+                const float* g = (const float*)gt;
+                v = make_float3(__ldg(g + pid), __ldg(g + plane + pid), __ldg(g + 2 * plane + pid));
+            } else {
+                uint32_t u;
+                if (GT == 1) {
+                    const uint8_t* g = (const uint8_t*)gt + 3 * pid;
+                    u = (uint32_t)__ldg(g) | ((uint32_t)__ldg(g + 1) << 8) | ((uint32_t)__ldg(g + 2) << 16);
+                } else {
+                    const uint8_t* g = (const uint8_t*)gt;
+                    const size_t cid = (size_t)(py_i >> 1) * (W >> 1) + (px_i >> 1);
+                    u = yuv_to_rgb_packed(__ldg(g + pid), __ldg(g + plane + cid), __ldg(g + plane + (plane >> 2) + cid));
+                }
+                v = make_float3(u8_over_255(u & 255u), u8_over_255((u >> 8) & 255u), u8_over_255((u >> 16) & 255u));
+            }
+        }
+        tv[3 * j] = v.x; tv[3 * j + 1] = v.y; tv[3 * j + 2] = v.z;
+    }
+    float4* o = reinterpret_cast<float4*>(out) + ((size_t)t * kTileThreads + tid) * (kPix * 3 / 4);
+#pragma unroll
+    for (int q = 0; q < kPix * 3 / 4; ++q) o[q] = *reinterpret_cast<float4*>(tv + 4 * q);
+}
+
 // MODE 0: fit (loss + backward, no image written unless out_img != NULL)
 // MODE 1: render only (image [+ final_idx] written, no target, no backward)
 // GT: 0 = target is fp32 planar [3][H][W] (what torchvision's ToTensor / the reference's loader
 //         yields), 1 = uint8 interleaved [H][W][3] (raw frame; compared as value / 255),
 //         2 = planar I420 as the .yuv file holds it (converted here as the reference's loader does)
+//         3 = fp32 in this kernel's own per-thread order (gs2d_fit_target_prepare: any of the above,
+//             converted once per frame with the same arithmetic -- same bits, no per-iteration decode)
 //
 // One CTA of two warps per tile.  Warp w owns tile rows 8w .. 8w+7; a lane owns one column of
 // two interleaved row sets: pixel j (0..3) of lane l is (x = l & 15, y = 8w + 2j + (l >> 4)), so
@@ -521,7 +590,17 @@ k_fit_tiles(int W, int H, int tx, int row0, const int32_t* __restrict__ tile_off
     float3 tgt[kPix];
 #pragma unroll
     for (int j = 0; j < kPix; ++j) tgt[j] = make_float3(0.f, 0.f, 0.f);
-    if (MODE == 0 && in_x) {   // issued before the batch arrives: independent loads
+    if (MODE == 0 && GT == 3) {
+        // the frame as gs2d_fit_target_prepare laid it out: this thread's kPix pixels' (r, g, b) as
+        // consecutive floats -- 16-byte loads, a warp reads one contiguous run, nothing to decode
+        const float4* tp = reinterpret_cast<const float4*>(gt) + ((size_t)t * kTileThreads + tid) * (kPix * 3 / 4);
+        float tv[kPix * 3];
+#pragma unroll
+        for (int q = 0; q < kPix * 3 / 4; ++q) *reinterpret_cast<float4*>(tv + 4 * q) = __ldg(tp + q);
+#pragma unroll
+        for (int j = 0; j < kPix; ++j) tgt[j] = make_float3(tv[3 * j], tv[3 * j + 1], tv[3 * j + 2]);
+    }
+    if (MODE == 0 && GT != 3 && in_x) {   // issued before the batch arrives: independent loads
 #pragma unroll
         for (int j = 0; j < kPix; ++j) {
             const int py_i = oy + ly0 + 2 * j;
@@ -734,7 +813,7 @@ k_fit_tiles(int W, int H, int tx, int row0, const int32_t* __restrict__ tile_off
     for (int j = 0; j < kPix; ++j) {
         float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
         if (GT == 2) tgt_u8[j] = yuv_to_rgb_packed(raw_y[j], raw_u[j], raw_v[j]);
-        if (GT != 0) tgt[j] = make_float3(u8_over_255(tgt_u8[j] & 255u), u8_over_255((tgt_u8[j] >> 8) & 255u),
+        if (GT == 1 || GT == 2) tgt[j] = make_float3(u8_over_255(tgt_u8[j] & 255u), u8_over_255((tgt_u8[j] >> 8) & 255u),
                                           u8_over_255((tgt_u8[j] >> 16) & 255u));
         if (inside[j]) {
             const float cr = fminf(fmaxf(pix[j].x, 0.f), 1.f), cg = fminf(fmaxf(pix[j].y, 0.f), 1.f),
@@ -900,6 +979,11 @@ __device__ __forceinline__ float adan_one(float p, float g, float& m, float& nn,
     return h.decay_div == 1.f ? q : q / h.decay_div;   // x / 1 == x: no weight decay (the reference's setting), no division
 }
 
+// PACKED: the parameters live in one fp32 [n][8] buffer (xyz 2 | chol 3 | feat 3; gs2d_fit_options.params8),
+// passed as xyz_raw -- two aligned 16-byte loads and stores per Gaussian where the reference's AoS tensors
+// (bindings.cu:456-465 casts them to float2 / float3) take 8 scalar ones; chol_raw / feat are then unused
+// and the sharded update's route holds the peers' packed buffers in rt.xyz.
+template <bool PACKED>
 __global__ void __launch_bounds__(kFitThreads)
 k_fit_update(int n, float* __restrict__ xyz_raw, float* __restrict__ chol_raw, float* __restrict__ feat,
              float* __restrict__ adan, float* __restrict__ grads, float half_w, float half_h, int tx, int ty,
@@ -912,7 +996,8 @@ k_fit_update(int n, float* __restrict__ xyz_raw, float* __restrict__ chol_raw, f
              int H, int shard_begin, int shard_end, Route rt) {
     __shared__ int sh[8];
     __shared__ int s_last;
-    __shared__ float s_par[8 * kFitThreads];
+    __shared__ float s_par[PACKED ? 1 : 8 * kFitThreads];
+    float4* p8 = reinterpret_cast<float4*>(xyz_raw);
     // this launch updates Gaussians [shard_begin, shard_end) -- [0, n) unless the update is sharded
     // over the ranks; all arrays are indexed by the global Gaussian index
     const int gtid = blockIdx.x * kFitThreads + threadIdx.x;
@@ -929,10 +1014,18 @@ k_fit_update(int n, float* __restrict__ xyz_raw, float* __restrict__ chol_raw, f
     float4* sd = reinterpret_cast<float4*>(adan + 2 * plane + (size_t)i * 8);
     float4* sp = reinterpret_cast<float4*>(adan + 3 * plane + (size_t)i * 8);
     if (i < shard_end) {
-        fit_project(i, xyz_raw, chol_raw, 1, half_w, half_h, tx, ty, p, m, L, QuantConst());
-        par[0] = xyz_raw[2 * i]; par[1] = xyz_raw[2 * i + 1];
-        par[2] = chol_raw[3 * i]; par[3] = chol_raw[3 * i + 1]; par[4] = chol_raw[3 * i + 2];
-        par[5] = feat[3 * i]; par[6] = feat[3 * i + 1]; par[7] = feat[3 * i + 2];
+        if (PACKED) {
+            *reinterpret_cast<float4*>(par) = p8[2 * (size_t)i];
+            *reinterpret_cast<float4*>(par + 4) = p8[2 * (size_t)i + 1];
+            m = make_float2(tanhf(par[0]), tanhf(par[1]));
+            L = make_float3(addf(par[2], 0.5f), addf(par[3], 0.f), addf(par[4], 0.5f));
+            project_chol(m.x, m.y, L.x, L.y, L.z, half_w, half_h, tx, ty, p);
+        } else {
+            fit_project(i, xyz_raw, chol_raw, 1, half_w, half_h, tx, ty, p, m, L, QuantConst());
+            par[0] = xyz_raw[2 * i]; par[1] = xyz_raw[2 * i + 1];
+            par[2] = chol_raw[3 * i]; par[3] = chol_raw[3 * i + 1]; par[4] = chol_raw[3 * i + 2];
+            par[5] = feat[3 * i]; par[6] = feat[3 * i + 1]; par[7] = feat[3 * i + 2];
+        }
         if (!skip_update) {
             *reinterpret_cast<float4*>(am) = sm[0]; *reinterpret_cast<float4*>(am + 4) = sm[1];
             *reinterpret_cast<float4*>(an) = sn[0]; *reinterpret_cast<float4*>(an + 4) = sn[1];
@@ -1050,10 +1143,25 @@ k_fit_update(int n, float* __restrict__ xyz_raw, float* __restrict__ chol_raw, f
         sn[0] = *reinterpret_cast<float4*>(an); sn[1] = *reinterpret_cast<float4*>(an + 4);
         sd[0] = *reinterpret_cast<float4*>(ad); sd[1] = *reinterpret_cast<float4*>(ad + 4);
         sp[0] = *reinterpret_cast<float4*>(ap); sp[1] = *reinterpret_cast<float4*>(ap + 4);
-        xyz_raw[2 * i] = par[0]; xyz_raw[2 * i + 1] = par[1];
-        chol_raw[3 * i] = par[2]; chol_raw[3 * i + 1] = par[3]; chol_raw[3 * i + 2] = par[4];
-        feat[3 * i] = par[5]; feat[3 * i + 1] = par[6]; feat[3 * i + 2] = par[7];
-        if (rt.R > 0) {   // sharded update: staged for the block's stores into the peers' tensors (below)
+        if (PACKED) {
+            const float4 a = make_float4(par[0], par[1], par[2], par[3]), b = make_float4(par[4], par[5], par[6], par[7]);
+            p8[2 * (size_t)i] = a;
+            p8[2 * (size_t)i + 1] = b;
+            // sharded update: the all-gather is these stores into the peers' buffers (NVLink, fire and
+            // forget; read after the barrier that follows this kernel) -- 32 contiguous bytes per
+            // Gaussian, so a warp fills 1 KB of consecutive lines in each peer
+            for (int q = 0; q < rt.R; ++q) {
+                float4* pq = reinterpret_cast<float4*>(rt.xyz[q]);
+                if (pq == p8) continue;
+                pq[2 * (size_t)i] = a;
+                pq[2 * (size_t)i + 1] = b;
+            }
+        } else {
+            xyz_raw[2 * i] = par[0]; xyz_raw[2 * i + 1] = par[1];
+            chol_raw[3 * i] = par[2]; chol_raw[3 * i + 1] = par[3]; chol_raw[3 * i + 2] = par[4];
+            feat[3 * i] = par[5]; feat[3 * i + 1] = par[6]; feat[3 * i + 2] = par[7];
+        }
+        if (!PACKED && rt.R > 0) {   // sharded update: staged for the block's stores into the peers' tensors (below)
             s_par[2 * threadIdx.x] = par[0]; s_par[2 * threadIdx.x + 1] = par[1];
 #pragma unroll
             for (int k = 0; k < 3; ++k) {
@@ -1084,6 +1192,7 @@ k_fit_update(int n, float* __restrict__ xyz_raw, float* __restrict__ chol_raw, f
         }
     }
     if (skip_update) return;
+    if (PACKED && rt.R > 0) return;
     if (rt.R > 0) {
         // sharded update: the all-gather is these stores (NVLink, fire and forget; the peers read
         // them after the barrier that follows this kernel).  A block's Gaussians are contiguous in
@@ -1303,7 +1412,9 @@ int gs2d_fit_step_band(int n, int cap, int img_h, int img_w, float* xyz_raw, flo
     GS2D_REQUIRE(n > 0 && step >= 1, "fit_step: n and step must be positive");
     GS2D_REQUIRE(work != nullptr && work_bytes >= L.total_bytes, "fit_step: workspace too small");
     GS2D_REQUIRE(target_format == GS2D_TARGET_F32_CHW || target_format == GS2D_TARGET_U8_HWC ||
-                     target_format == GS2D_TARGET_I420, "fit_step: unknown target format");
+                     target_format == GS2D_TARGET_I420 || target_format == GS2D_TARGET_TILED, "fit_step: unknown target format");
+    GS2D_REQUIRE(target_format != GS2D_TARGET_TILED || ((uintptr_t)target & 15) == 0,
+                 "fit_step: a prepared target must be 16-byte aligned");
     GS2D_REQUIRE(target_format != GS2D_TARGET_I420 || (img_h % 2 == 0 && img_w % 2 == 0),
                  "fit_step: an I420 frame needs even width and height");
     GS2D_REQUIRE(xyz_raw && chol_raw && features && adan_state, "fit_step: null pointer");
@@ -1337,8 +1448,8 @@ int gs2d_fit_step_band(int n, int cap, int img_h, int img_w, float* xyz_raw, flo
         if (mc_grads) { peer_grads = nullptr; num_peers = 0; }
         if (exchange->shard_end > exchange->shard_begin) {
             GS2D_REQUIRE(exchange->shard_begin >= 0 && exchange->shard_end <= n, "fit_step: shard out of range");
-            GS2D_REQUIRE(num_peers > 0 && exchange->xyz_peers && exchange->chol_peers && exchange->feat_peers &&
-                             exchange->status_peers && grads_zero,
+            GS2D_REQUIRE(num_peers > 0 && exchange->xyz_peers && exchange->status_peers && grads_zero &&
+                             ((options && options->params8) || (exchange->chol_peers && exchange->feat_peers)),
                          "fit_step: a sharded update needs peers, their parameter pointers and a spare buffer");
             shard_begin = exchange->shard_begin;
             shard_end = exchange->shard_end;
@@ -1351,6 +1462,7 @@ int gs2d_fit_step_band(int n, int cap, int img_h, int img_w, float* xyz_raw, flo
     }
     const bool sharded = rt.R > 0;
     float* rgb_w = nullptr; float* adan_w = nullptr; float* rgb_w_grad_out = nullptr;
+    QuantConst src = QuantConst();   // row strides of the parameter tensors (packed rows: 8 / 8 / 8)
     int adan_step = step, adan_fresh = step == 1, skip_update = 0, slots = 0, analytic = 0, all_per_tile = 0;
     if (options) {
         slots = options->slots != 0;
@@ -1364,6 +1476,12 @@ int gs2d_fit_step_band(int n, int cap, int img_h, int img_w, float* xyz_raw, flo
         skip_update = options->skip_update != 0;
         analytic = options->analytic_grad != 0;
         all_per_tile = options->all_per_tile != 0;
+        if (options->params8) {
+            GS2D_REQUIRE(((uintptr_t)options->params8 & 15) == 0, "fit_step: params8 must be 16-byte aligned");
+            GS2D_REQUIRE(xyz_raw == options->params8 && chol_raw == options->params8 + 2 && features == options->params8 + 5,
+                         "fit_step: with params8 the three parameter pointers must be its columns 0 / 2 / 5");
+            src = packed8_rows();
+        }
         GS2D_REQUIRE(!(all_per_tile && slots), "fit_step: all_per_tile needs tile ranges (a slot holds 256 records)");
     }
     GS2D_REQUIRE(!sharded || (slots && rgb_w == nullptr && !skip_update),
@@ -1384,13 +1502,13 @@ int gs2d_fit_step_band(int n, int cap, int img_h, int img_w, float* xyz_raw, flo
                 }
                 k_fit_scatter<<<div_up(n, kFitThreads), kFitThreads, 0, s>>>(
                     n, xyz_raw, chol_raw, features, nullptr, rgb_w, 1, half_w, half_h, tx, ty, row0, row1, img_w, img_h,
-                    nullptr, (int32_t*)(w + L.off_tile_count), status, (float4*)(w + L.off_packed), 1, step, QuantConst(),
+                    nullptr, (int32_t*)(w + L.off_tile_count), status, (float4*)(w + L.off_packed), 1, step, src,
                     rt);
                 GS2D_CHECK_LAUNCH("fit_scatter_slots");
             }
         } else {
             rc = launch_bin(n, xyz_raw, chol_raw, features, nullptr, rgb_w, 1, img_h, img_w, row0, row1, cap, step, L, w,
-                            s, precounted != 0);
+                            s, precounted != 0, src);
             if (rc != GS2D_OK) return rc;
         }
         const int32_t* tile_off_arg = slots ? nullptr : (const int32_t*)(w + L.off_tile_off);
@@ -1411,8 +1529,14 @@ int gs2d_fit_step_band(int n, int cap, int img_h, int img_w, float* xyz_raw, flo
                 img_w, img_h, tx, row0, tile_off_arg, (int32_t*)(w + L.off_tile_count),
                 (const float4*)(w + L.off_packed), target, grad_scale, grads, loss + (step % GS2D_FIT_LOSS_SLOTS),
                 status, out_img, 1, 1, (int32_t*)nullptr, ids_sorted_out, step, tile_flags));
-        else
+        else if (target_format == GS2D_TARGET_I420)
             GS2D_CHECK_CUDA(launch_pdl(all_per_tile ? k_fit_tiles<0, 2, true> : k_fit_tiles<0, 2, false>, grid,
+                dim3(kTileThreads), s,
+                img_w, img_h, tx, row0, tile_off_arg, (int32_t*)(w + L.off_tile_count),
+                (const float4*)(w + L.off_packed), target, grad_scale, grads, loss + (step % GS2D_FIT_LOSS_SLOTS),
+                status, out_img, 1, 1, (int32_t*)nullptr, ids_sorted_out, step, tile_flags));
+        else
+            GS2D_CHECK_CUDA(launch_pdl(all_per_tile ? k_fit_tiles<0, 3, true> : k_fit_tiles<0, 3, false>, grid,
                 dim3(kTileThreads), s,
                 img_w, img_h, tx, row0, tile_off_arg, (int32_t*)(w + L.off_tile_count),
                 (const float4*)(w + L.off_packed), target, grad_scale, grads, loss + (step % GS2D_FIT_LOSS_SLOTS),
@@ -1439,7 +1563,8 @@ int gs2d_fit_step_band(int n, int cap, int img_h, int img_w, float* xyz_raw, flo
         h.first = adan_fresh;
         h.offdiag = analytic ? 1.f : 2.f;
         ProfScope ps_(GS2D_STAGE_ADAN, s);
-        GS2D_CHECK_CUDA(launch_pdl(k_fit_update, dim3(div_up(shard_end - shard_begin, kFitThreads)), dim3(kFitThreads), s,
+        GS2D_CHECK_CUDA(launch_pdl(src.ld_xyz == 8 ? k_fit_update<true> : k_fit_update<false>,
+            dim3(div_up(shard_end - shard_begin, kFitThreads)), dim3(kFitThreads), s,
             n, xyz_raw, chol_raw, features, adan_state, grads, half_w, half_h, tx, ty, h, status,
             loss + (step % GS2D_FIT_LOSS_SLOTS), loss + ((step + 1) % GS2D_FIT_LOSS_SLOTS), param_grads_out, cap,
             step + 1, (int32_t*)(w + L.off_tile_count), (int32_t*)(w + L.off_tile_off), report_host, row0, row1,
@@ -1452,6 +1577,32 @@ int gs2d_fit_step_band(int n, int cap, int img_h, int img_w, float* xyz_raw, flo
                                         exchange->barrier_epoch + 1u);
         GS2D_CHECK_LAUNCH("rank_barrier");
     }
+    return GS2D_OK;
+}
+
+size_t gs2d_fit_target_bytes(int img_h, int img_w) {
+    if (img_h < 1 || img_w < 1) return 0;
+    return (size_t)div_up(img_w, GS2D_TILE) * div_up(img_h, GS2D_TILE) * GS2D_TILE_PIX * 3 * sizeof(float);
+}
+
+int gs2d_fit_target_prepare(int img_h, int img_w, const void* target, int target_format, float* prepared,
+                            gs2d_stream_t stream) {
+    GS2D_REQUIRE(img_h > 0 && img_w > 0 && target && prepared, "fit_target_prepare: bad arguments");
+    GS2D_REQUIRE(((uintptr_t)prepared & 15) == 0, "fit_target_prepare: output must be 16-byte aligned");
+    GS2D_REQUIRE(target_format != GS2D_TARGET_I420 || (img_h % 2 == 0 && img_w % 2 == 0),
+                 "fit_target_prepare: an I420 frame needs even width and height");
+    cudaStream_t s = (cudaStream_t)stream;
+    const dim3 grid(div_up(img_w, GS2D_TILE), div_up(img_h, GS2D_TILE));
+    ProfScope ps_(GS2D_STAGE_OTHER, s);
+    if (target_format == GS2D_TARGET_F32_CHW)
+        k_target_tiled<0><<<grid, kTileThreads, 0, s>>>(img_w, img_h, grid.x, target, prepared);
+    else if (target_format == GS2D_TARGET_U8_HWC)
+        k_target_tiled<1><<<grid, kTileThreads, 0, s>>>(img_w, img_h, grid.x, target, prepared);
+    else if (target_format == GS2D_TARGET_I420)
+        k_target_tiled<2><<<grid, kTileThreads, 0, s>>>(img_w, img_h, grid.x, target, prepared);
+    else
+        GS2D_REQUIRE(false, "fit_target_prepare: unknown target format");
+    GS2D_CHECK_LAUNCH("target_tiled");
     return GS2D_OK;
 }
 
@@ -1597,8 +1748,15 @@ int gs2d_render_chol(int n, int cap, int img_h, int img_w, const float* means_or
     char* w = (char*)work;
     const int tx = div_up(img_w, GS2D_TILE), ty = div_up(img_h, GS2D_TILE);
     const int all_flag = (activate & GS2D_RENDER_ALL_PER_TILE) ? kTileAllPerTile : 0;
+    QuantConst src = QuantConst();
+    if (activate & GS2D_RENDER_PACKED8) {
+        GS2D_REQUIRE(((uintptr_t)means_or_xyz_raw & 15) == 0 && chol == means_or_xyz_raw + 2,
+                     "render_chol: packed rows need a 16-byte aligned [n][8] buffer and chol = its column 2");
+        src.ld_xyz = src.ld_chol = 8;
+        src.ld_feat = colors == means_or_xyz_raw + 5 ? 8 : 0;   // colours may be a tensor of their own (features * rgb_W)
+    }
     rc = launch_bin(n, means_or_xyz_raw, chol, colors, opacities, nullptr, (activate & GS2D_RENDER_ACTIVATE) ? 1 : 0, img_h,
-                    img_w, 0, ty, cap, 0, L, w, s, false, QuantConst(), true);
+                    img_w, 0, ty, cap, 0, L, w, s, false, src, true);
     if (rc != GS2D_OK) return rc;
     {
         ProfScope ps_(GS2D_STAGE_RASTER_FWD, s);

@@ -101,7 +101,10 @@ __device__ __forceinline__ int stage_tile_window(const float4* __restrict__ src,
 __device__ __forceinline__ void stage_tile_warp(float4 r0, float4 r1, float4 r2, int cnt, float4* sqw, int lane) {
     const int my = lane < cnt ? __float_as_int(r1.w) : 0x7fffffff;
     int rank = 0;
-    for (int k = 0; k < cnt; ++k) rank += (__shfl_sync(0xffffffffu, my, k) < my) ? 1 : 0;
+    // lanes past the batch hold INT_MAX, which is below nobody's id: the loop may run on to a multiple of 4
+    const int cnt4 = (cnt + 3) & ~3;
+#pragma unroll 4
+    for (int k = 0; k < cnt4; ++k) rank += (__shfl_sync(0xffffffffu, my, k) < my) ? 1 : 0;
     if (lane < cnt) {
         sqw[3 * rank + 0] = r0;
         sqw[3 * rank + 1] = r1;

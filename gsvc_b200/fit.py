@@ -11,6 +11,7 @@ the GPU box); GSVC's own model files use the package through `import gsplat` unc
 from __future__ import annotations
 
 import math
+import os
 
 import torch
 import torch.nn.functional as F
@@ -141,6 +142,79 @@ class FrameFit(torch.nn.Module):
         self.scheduler.step()
         return loss, psnr
 
+    # ---- the same iteration as one CUDA-graph replay ----------------------------------------------------
+    def train_iter_graphed(self, gt_image: torch.Tensor, read_loss: bool = True):
+        """train_iter with the whole iteration -- both operators, the torch glue around them, their
+        backwards, the Adan step -- captured ONCE in a CUDA graph and replayed: one host call per
+        iteration instead of ~45 launches (the operators are sync-free and capturable; the reference's
+        cannot be captured, they block on .item(), utils.py:117).  Same arithmetic as train_iter.
+        The first call of a configuration runs its iteration eagerly (on a side stream, as torch's
+        capture recipe asks) and captures; iterations in which the prune / add control acts, and the
+        one after them, run eagerly too and the graph is captured again (new parameter tensors).
+        read_loss=False skips the per-iteration loss.item() (psnr is then None)."""
+        it = self.iter + 1
+        act = self.plan.action(it, self._xyz.shape[0]) if self.plan.learns_rgb_w else _NO_ACTION
+        lr = self.optimizer.param_groups[0]["lr"]
+        key = (id(self.optimizer), tuple(p.data_ptr() for p in self.parameters()), lr, tuple(gt_image.shape))
+        if act.kind != "none" or act.rebuild:
+            self._graph = None
+            return self.train_iter(gt_image)
+        if getattr(self, "_graph", None) is None or self._graph_key != key:
+            return self._capture_iteration(gt_image, key, read_loss)
+        if gt_image.data_ptr() != self._g_gt.data_ptr():
+            self._g_gt.copy_(gt_image, non_blocking=True)
+        self._graph.replay()
+        self.iter = it
+        self.optimizer.param_groups[0]["step"] += 1        # the replay bumped the device-side counter
+        self.scheduler.step()
+        if not read_loss:
+            return self._g_loss, None
+        return self._g_loss, 10 * math.log10(1.0 / self._g_loss.item())
+
+    @torch.no_grad()
+    def forward_graphed(self):
+        """forward() (the render of train_video_Represent.py:101-106) as one CUDA-graph replay; the
+        returned image is the graph's static output, overwritten by the next replay"""
+        key = tuple(p.data_ptr() for p in self.parameters())
+        if getattr(self, "_fgraph", None) is None or self._fgraph_key != key:
+            cur = torch.cuda.current_stream(self.device)
+            side = torch.cuda.Stream(self.device)
+            side.wait_stream(cur)
+            with torch.cuda.stream(side):
+                self.forward()                              # sizes the operator's buffers outside the capture
+            cur.wait_stream(side)
+            graph = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(graph):
+                out = self.forward()
+            self._fgraph, self._fgraph_key, self._fgraph_out = graph, key, out
+        self._fgraph.replay()
+        return self._fgraph_out
+
+    def _capture_iteration(self, gt_image, key, read_loss):
+        self.optimizer.capturable = True
+        cur = torch.cuda.current_stream(self.device)
+        side = torch.cuda.Stream(self.device)
+        side.wait_stream(cur)
+        with torch.cuda.stream(side):
+            loss, psnr = self.train_iter(gt_image)          # this call's iteration (reads the loss: drains the stream)
+        cur.wait_stream(side)
+        eager = (loss.detach(), psnr)
+        del loss                                            # frees the autograd graph and with it the leaves' accumulators
+        key = (key[0], tuple(p.data_ptr() for p in self.parameters()), self.optimizer.param_groups[0]["lr"], key[3])
+        self._g_gt = gt_image.detach().clone()
+        group = self.optimizer.param_groups[0]
+        graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(graph):
+            image = self.forward()
+            g_loss = F.mse_loss(image, self._g_gt)
+            g_loss.backward()
+            self.optimizer.step()
+            self.optimizer.zero_grad(set_to_none=True)
+        group["step"] -= 1                                   # the capture ran no step; neither counter moved
+        group["step_dev"].fill_(group["step"])
+        self._graph, self._graph_key, self._g_loss = graph, key, g_loss.detach()
+        return eager
+
 
 class GS2DOverflow(RuntimeError):
     """A fused step found its workspace too small (more intersections than `cap`, or -- on tile slots --
@@ -211,11 +285,7 @@ class FusedFrameFit(torch.nn.Module):
             from . import synth
             init = synth.gaussians(num_points, seed=seed)
         dev = self.device
-        self._xyz = torch.nn.Parameter(init["_xyz"].clone().float().contiguous().to(dev), requires_grad=False)
-        self._cholesky = torch.nn.Parameter(init["_cholesky"].clone().float().contiguous().to(dev), requires_grad=False)
-        self._features_dc = torch.nn.Parameter(init["_features_dc"].clone().float().contiguous().to(dev),
-                                               requires_grad=False)
-        self.n = int(self._xyz.shape[0])
+        self._pack(init["_xyz"].float().to(dev), init["_cholesky"].float().to(dev), init["_features_dc"].float().to(dev))
         # prune / add control (GaussianSplats_Represent.py:98-172): rgb_W is a parameter only then (:31-36)
         self.plan = plan or DensityPlan(max_num_points or self.n, removal_rate, densification_interval, isdensity,
                                         isremoval)
@@ -239,6 +309,43 @@ class FusedFrameFit(torch.nn.Module):
         tiles = ((self.H + 15) // 16) * ((self.W + 15) // 16)
         self.cap = max(self._cap_ranges, tiles * 256) if self.slots else self._cap_ranges
         self._alloc()
+
+    def _pack(self, xyz: torch.Tensor, chol: torch.Tensor, feat: torch.Tensor, into: torch.Tensor | None = None):
+        """The master copy of the parameters is ONE fp32 [n][8] buffer (rows: xyz 2 | chol 3 | features 3;
+        gs2d_fit_options.params8): every per-Gaussian kernel moves a Gaussian as two aligned 16-byte
+        accesses.  `_xyz`, `_cholesky`, `_features_dc` keep the reference's names and shapes
+        (train_video_Represent.py:107-114) as column views of it; state_dict() / frame_state() hand out
+        contiguous copies."""
+        n = int(xyz.shape[0])
+        p8 = torch.empty((n, 8), dtype=torch.float32, device=self.device) if into is None else into
+        p8[:, 0:2] = xyz
+        p8[:, 2:5] = chol
+        p8[:, 5:8] = feat
+        self._params8 = p8
+        self._xyz = torch.nn.Parameter(p8[:, 0:2], requires_grad=False)
+        self._cholesky = torch.nn.Parameter(p8[:, 2:5], requires_grad=False)
+        self._features_dc = torch.nn.Parameter(p8[:, 5:8], requires_grad=False)
+        self.n = n
+
+    def _param_ptrs(self):
+        """(params8, xyz, chol, feat) device addresses; repacks first if somebody assigned a new tensor
+        to one of the three attributes instead of writing into it"""
+        base = self._params8.data_ptr()
+        if (self._xyz.data_ptr() != base or self._cholesky.data_ptr() != base + 8
+                or self._features_dc.data_ptr() != base + 20 or self._xyz.stride(0) != 8):
+            with torch.no_grad():
+                self._pack(self._xyz.detach().float().to(self.device), self._cholesky.detach().float().to(self.device),
+                           self._features_dc.detach().float().to(self.device))
+            self._counted_for = None
+            base = self._params8.data_ptr()
+        return base, base, base + 8, base + 20
+
+    def state_dict(self, *args, **kwargs):
+        sd = super().state_dict(*args, **kwargs)
+        for k in list(sd):
+            if k.split(".")[-1] in ("_xyz", "_cholesky", "_features_dc"):
+                sd[k] = sd[k].contiguous()     # a column view would drag the whole [n][8] storage into torch.save
+        return sd
 
     def _alloc(self):
         lay = self._lib.FitLayout()
@@ -298,6 +405,7 @@ class FusedFrameFit(torch.nn.Module):
         o.slots = int(self.slots)
         o.analytic_grad = int(self.analytic_grad)
         o.all_per_tile = int(self.all_per_tile and not self.slots)   # slots hold 256: a fuller tile moves the model to ranges
+        o.params8 = self._params8.data_ptr()
         return o
 
     def _issue(self, gt, fmt, out_img=None, grads_out=None, ids_out=None, w_grad_out=None, stream=None):
@@ -309,12 +417,13 @@ class FusedFrameFit(torch.nn.Module):
         if act.rebuild and not act.replaces_parameters:
             self._zero_optimizer_state()            # update_optimizer() precedes this iteration's step
         adan_step, fresh, skip = self.clock.begin(act)
+        _p8, p_xyz, p_chol, p_feat = self._param_ptrs()
         opts = self._options(adan_step, fresh, skip, w_grad_out)
         b1, b2, b3 = self.betas
         slot = self.step_index % self._lib.FIT_LOSS_SLOTS
         rc = self._cdll.gs2d_fit_step_band(
-            self.n, self.cap, self.H, self.W, self._xyz.data_ptr(), self._cholesky.data_ptr(),
-            self._features_dc.data_ptr(), self.adan_state.data_ptr(), gt if isinstance(gt, int) else gt.data_ptr(),
+            self.n, self.cap, self.H, self.W, p_xyz, p_chol,
+            p_feat, self.adan_state.data_ptr(), gt if isinstance(gt, int) else gt.data_ptr(),
             fmt, self.work.data_ptr(),
             self.layout.total_bytes, self.step_index, self.current_lr(), b1, b2, b3, self.eps, self.weight_decay,
             1 if self._precount_valid() else 0, 0, self._tile_rows,
@@ -363,9 +472,10 @@ class FusedFrameFit(torch.nn.Module):
             scratch = torch.empty((lib.gs2d_prune_scratch_bytes(n),), dtype=torch.uint8, device=dev)
             new = [torch.empty((m, c), dtype=torch.float32, device=dev) for c in (1, 2, 3, 3)]
             self.last_keep_index = torch.empty((m,), dtype=torch.int32, device=dev)
+            src = [t.detach().contiguous() for t in (self._xyz, self._cholesky, self._features_dc)]   # [n,2] [n,3] [n,3]
             self._lib.check(lib.gs2d_prune_lowest(
-                n, act.count, self.rgb_W.data_ptr(), self._xyz.data_ptr(), self._cholesky.data_ptr(),
-                self._features_dc.data_ptr(), new[0].data_ptr(), new[1].data_ptr(), new[2].data_ptr(),
+                n, act.count, self.rgb_W.data_ptr(), src[0].data_ptr(), src[1].data_ptr(),
+                src[2].data_ptr(), new[0].data_ptr(), new[1].data_ptr(), new[2].data_ptr(),
                 new[3].data_ptr(), self.last_keep_index.data_ptr(), scratch.data_ptr(), scratch.numel(),
                 torch.cuda.current_stream(dev).cuda_stream), "prune_lowest")
         else:
@@ -378,10 +488,7 @@ class FusedFrameFit(torch.nn.Module):
             cat = [torch.cat((o, a.to(dev)), dim=0) for o, a in zip(old, add)]
             new = [cat[3], cat[0], cat[1], cat[2]]
         self.rgb_W = torch.nn.Parameter(new[0], requires_grad=False)
-        self._xyz = torch.nn.Parameter(new[1], requires_grad=False)
-        self._cholesky = torch.nn.Parameter(new[2], requires_grad=False)
-        self._features_dc = torch.nn.Parameter(new[3], requires_grad=False)
-        self.n = int(self._xyz.shape[0])
+        self._pack(new[1], new[2], new[3])
         self.adan_state = None                      # new tensors, new (zero) optimizer state
         self._alloc()
 
@@ -396,10 +503,35 @@ class FusedFrameFit(torch.nn.Module):
         unless someone modified the parameter tensors since (torch bumps ._version on in-place ops)"""
         return self._counted_for == self._versions()
 
+    #: convert a resident target frame once into the tile kernel's own order (gs2d_fit_target_prepare) instead
+    #: of decoding its bytes in every iteration; False keeps the raw format (what fit_stream always does)
+    prepare_targets = os.environ.get("GS2D_NO_PREPARE") != "1"      # (the variable: A/B runs of bench.py)
+
+    def _prepared(self, gt: torch.Tensor, fmt: int):
+        """(tensor, format) the tile kernel should read for this frame: the prepared copy, made when the
+        frame (address, version counter, format) differs from the one prepared last"""
+        if not self.prepare_targets:
+            return gt, fmt
+        key = (gt.data_ptr(), gt._version, fmt)
+        if getattr(self, "_tiled_key", None) != key:
+            lib = self._cdll
+            nbytes = int(lib.gs2d_fit_target_bytes(self.H, self.W))
+            buf = getattr(self, "_tiled", None)
+            if buf is None or buf.numel() * 4 != nbytes:
+                buf = self._tiled = torch.empty((nbytes // 4,), dtype=torch.float32, device=self.device)
+            with self._C._guard(self.device):
+                self._lib.check(lib.gs2d_fit_target_prepare(self.H, self.W, gt.data_ptr(), fmt, buf.data_ptr(),
+                                                            torch.cuda.current_stream(self.device).cuda_stream),
+                                "fit_target_prepare")
+            self._tiled_key = key
+            self._tiled_src = gt          # keeps the address from being recycled while the key is live
+        return self._tiled, self._lib.TARGET_TILED
+
     def train_iters(self, gt_image: torch.Tensor, iters: int = 1, **dbg):
         gt, fmt = self._target(gt_image)
         if gt.device != self.device:
             raise RuntimeError("target frame must live on the model's device")
+        gt, fmt = self._prepared(gt, fmt)
         with self._C._guard(self.device):
             for _ in range(int(iters)):
                 self._issue(gt, fmt, **dbg)
@@ -461,6 +593,10 @@ class FusedFrameFit(torch.nn.Module):
         Positive: the intersections outgrew `cap` -> double it.  Negative: slot mode met a tile with
         more than 256 Gaussians -> tile ranges from here on (which 256 the reference renders of such
         a tile needs all of its ids)."""
+        # the no-op steps still in flight write their reports too: let them finish, then forget every report
+        # (the steps are about to be issued again under the same numbers; fit_stream polls the ring)
+        torch.cuda.current_stream(self.device).synchronize()
+        self._report_np[:, 5] = -1
         self.step_index = abs(overflow_step) - 1
         it0, t0, fresh0, frozen0 = self._ckpt
         d = max(self.step_index - it0, 0)
@@ -500,29 +636,34 @@ class FusedFrameFit(torch.nn.Module):
         model and frame size (a copy stream + 2*depth events: ~0.1 ms that a short stream of frames
         would otherwise pay on every call)"""
         key = (int(frame_bytes), int(depth))
-        if getattr(self, "_pipe_key", None) != key:
+        if self.__dict__.get("_pipe_key") != key:
             self._drop_frame_pipe()
             ct = self._ctypes
-            self._pipe_slots = torch.empty((depth, frame_bytes), dtype=torch.uint8, device=self.device)
+            slots = torch.empty((depth, frame_bytes), dtype=torch.uint8, device=self.device)
             pipe = ct.c_void_p()
             with self._C._guard(self.device):
-                self._lib.check(self._cdll.gs2d_frame_pipe_create(self._pipe_slots.data_ptr(), frame_bytes, depth,
-                                                                  ct.byref(pipe)), "frame_pipe_create")
-            self._pipe, self._pipe_key = pipe, key
-        return self._pipe
+                self._lib.check(self._cdll.gs2d_frame_pipe_create(slots.data_ptr(), frame_bytes, depth, ct.byref(pipe)),
+                                "frame_pipe_create")
+            d = self.__dict__
+            d["_pipe"], d["_pipe_key"], d["_pipe_slots"] = pipe, key, slots
+        return self.__dict__["_pipe"]
 
     def _drop_frame_pipe(self):
-        pipe = getattr(self, "_pipe", None)
+        d = self.__dict__                  # (plain attributes; also safe while the interpreter shuts down)
+        pipe = d.get("_pipe")
         if pipe is not None:
             try:
                 torch.cuda.current_stream(self.device).synchronize()
                 self._cdll.gs2d_frame_pipe_destroy(pipe)
             except Exception:   # noqa: BLE001 -- interpreter shutdown
                 pass
-        self._pipe, self._pipe_key, self._pipe_slots = None, None, None
+        d["_pipe"], d["_pipe_key"], d["_pipe_slots"] = None, None, None
 
     def __del__(self):
-        self._drop_frame_pipe()
+        try:
+            self._drop_frame_pipe()
+        except Exception:   # noqa: BLE001
+            pass
 
     def fit_stream(self, host_frames, prefetch: int = 2, lag: int = 1):
         """One iteration per frame of `host_frames` (an iterable of PINNED host targets of one
@@ -639,14 +780,37 @@ class FusedFrameFit(torch.nn.Module):
                                                   torch.cuda.current_stream(self.device).cuda_stream), "fit_init")
             self._render_img = True
         out = torch.empty((1, 3, self.H, self.W), dtype=torch.float32, device=self.device)
-        colors = self.get_features
+        _p8, p_xyz, p_chol, p_feat = self._param_ptrs()
+        colors = None if self.rgb_W is None else self.get_features      # weighted colours: a tensor of their own
         with self._C._guard(self.device):
             self._lib.check(self._lib.load().gs2d_render_chol(
-                self.n, self.cap, self.H, self.W, self._xyz.data_ptr(), self._cholesky.data_ptr(),
-                colors.data_ptr(), None, 1 | (4 if self.all_per_tile else 0), self._render_work.data_ptr(),
+                self.n, self.cap, self.H, self.W, p_xyz, p_chol,
+                p_feat if colors is None else colors.data_ptr(), None, 1 | 8 | (4 if self.all_per_tile else 0),
+                self._render_work.data_ptr(),
                 self._render_work.numel(),
                 out.data_ptr(), 1, 1, None, None, torch.cuda.current_stream(self.device).cuda_stream), "render_chol")
         return out
+
+
+def _intersections_per_tile_row(xyz_raw: torch.Tensor, chol_raw: torch.Tensor, H: int, W: int):
+    """[tile rows] intersections of every tile row for the model's current parameters, as integer torch
+    ops on the model's device (identical on every rank): the projection gives radii, the tile bbox of
+    helpers.cuh:11-43 of the reference gives the rows and the width each Gaussian adds to them"""
+    from .project_gaussians_2d import project_gaussians_2d
+    tx, ty = (W + 15) // 16, (H + 15) // 16
+    bound = torch.tensor([0.5, 0.0, 0.5], device=xyz_raw.device)
+    with torch.no_grad():
+        xys, _d, radii, _c, _n = project_gaussians_2d(torch.tanh(xyz_raw).contiguous(), (chol_raw + bound).contiguous(),
+                                                     H, W, (tx, ty, 1))
+        r = radii.float() / 16
+        cx, cy = xys[:, 0] / 16, xys[:, 1] / 16
+        x0 = (cx - r).trunc().clamp(0, tx); x1 = (cx + r + 1).trunc().clamp(0, tx)
+        y0 = (cy - r).trunc().clamp(0, ty).long(); y1 = (cy + r + 1).trunc().clamp(0, ty).long()
+        width = ((x1 - x0).clamp(min=0) * (radii > 0)).double()
+        diff = torch.zeros(ty + 1, dtype=torch.float64, device=xyz_raw.device)
+        diff.index_add_(0, y0, width)
+        diff.index_add_(0, y1, -width)
+        return [float(v) for v in diff.cumsum(0)[:ty].round().cpu()]
 
 
 def split_tile_rows(tile_rows: int, world: int, weights=None):
@@ -701,7 +865,7 @@ class SpatialFrameFit(FusedFrameFit):
     path_name = "tile-row bands per rank; scatter-pack + tile kernel on the band, gradient rows summed across ranks, replicated update"
 
     def __init__(self, H, W, num_points, device, group=None, bands=None, emulate_world: int = 0,
-                 exchange: str = "nccl", slots: bool = False, own_barrier: bool = True, **kw):
+                 exchange: str = "nccl", slots: bool = False, own_barrier: bool = True, balance: bool = False, **kw):
         """exchange: "nccl" -- one all-reduce call on the gradient rows between the two phases;
         "peer" -- the rows live in symmetric (peer-mapped) memory and the update kernel itself sums
         them over NVLink in rank order after a device-side barrier: no collective kernel, no extra
@@ -727,6 +891,13 @@ class SpatialFrameFit(FusedFrameFit):
         else:
             self.world, self.rank = dist.get_world_size(group), dist.get_rank(group)
         ty = (self.H + 15) // 16
+        if bands is None and balance:
+            # bands "balanced by intersection count (prefix sum over rows of cnt_t)" -- what a band
+            # costs is its intersections plus a fixed cost per tile (DESIGN: about a third of the tile
+            # kernel at 15 Gaussians per tile), hence the mean added to every row
+            rows = self.intersections_per_tile_row()
+            mean = sum(rows) / max(len(rows), 1)
+            bands = split_tile_rows(ty, self.world, weights=[r + 0.5 * mean for r in rows])
         self.bands = list(bands) if bands is not None else split_tile_rows(ty, self.world)
         if len(self.bands) != self.world or self.bands[0][0] != 0 or self.bands[-1][1] != ty or any(
                 a[1] != b[0] for a, b in zip(self.bands, self.bands[1:])):
@@ -738,6 +909,9 @@ class SpatialFrameFit(FusedFrameFit):
             self._setup_sharded()
         if exchange in ("peer", "nvls", "sharded"):
             self._setup_peer_buffers()
+
+    def intersections_per_tile_row(self):
+        return _intersections_per_tile_row(self._xyz.detach(), self._cholesky.detach(), self.H, self.W)
 
     def _setup_sharded(self):
         """Sharded update: rank r owns Gaussians shards[r] (optimizer state, gradient reduction,
@@ -757,17 +931,16 @@ class SpatialFrameFit(FusedFrameFit):
                 for wk in self._works[1:]:
                     self._lib.check(lib.gs2d_fit_init(n, self.cap, self.H, self.W, wk.data_ptr(), lay.total_bytes, None,
                                                       torch.cuda.current_stream(dev).cuda_stream), "fit_init")
-            par = [[t.data_ptr()] * R for t in (self._xyz, self._cholesky, self._features_dc)]
+            par = [[self._params8.data_ptr()] * R] * 3        # packed rows: only the first list is read
             status = [wk.data_ptr() + lay.off_status for wk in self._works]
         else:
             import torch.distributed._symmetric_memory as symm
             grp = self.group if self.group is not None else self._dist.group.WORLD
             buf = symm.empty((8 * n,), dtype=torch.float32, device=dev)
             self._par_hdl = symm.rendezvous(buf, grp)
-            views = (buf[:2 * n].view(n, 2), buf[2 * n:5 * n].view(n, 3), buf[5 * n:8 * n].view(n, 3))
-            for v, name in zip(views, ("_xyz", "_cholesky", "_features_dc")):
-                v.copy_(getattr(self, name).data)
-                setattr(self, name, torch.nn.Parameter(v, requires_grad=False))
+            with torch.no_grad():                              # the packed [n][8] rows move into peer-mapped memory
+                self._pack(self._xyz.detach().clone(), self._cholesky.detach().clone(),
+                           self._features_dc.detach().clone(), into=buf.view(n, 8))
             wk = symm.empty((lay.total_bytes,), dtype=torch.uint8, device=dev)
             self._work_hdl = symm.rendezvous(wk, grp)
             with self._C._guard(dev):
@@ -779,7 +952,7 @@ class SpatialFrameFit(FusedFrameFit):
             self._grads = wk[lay.off_grads:lay.off_grads + n * 48].view(torch.float32)
             self._works = [wk]
             bases = [int(p) for p in self._par_hdl.buffer_ptrs]
-            par = [[b + 4 * off for b in bases] for off in (0, 2 * n, 5 * n)]
+            par = [bases] * 3                                   # rank q's packed rows
             status = [int(p) + lay.off_status for p in self._work_hdl.buffer_ptrs]
         self._route_ptrs = torch.tensor(par + [status], dtype=torch.int64, device=dev)   # xyz, chol, feat, status
         self._route_ptr = [self._route_ptrs[k].data_ptr() for k in range(4)]
@@ -841,20 +1014,21 @@ class SpatialFrameFit(FusedFrameFit):
 
     def _band_call(self, gt, fmt, band, phases, precounted, dbg, ex=None, work=None):
         b1, b2, b3 = self.betas
-        opts = None
-        if self.slots:
-            opts = self._opts
-            opts.adan_step, opts.adan_fresh, opts.skip_update, opts.slots = 0, 0, 0, 1   # 0: the step's own clock
+        opts = self._opts
+        opts.adan_step, opts.adan_fresh, opts.skip_update, opts.slots = 0, 0, 0, int(self.slots)   # 0: the step's own clock
+        opts.analytic_grad = int(self.analytic_grad)
         work = self.work if work is None else work
         slot = self.step_index % self._lib.FIT_LOSS_SLOTS
         out_img, grads_out, ids_out = dbg.get("out_img"), dbg.get("grads_out"), dbg.get("ids_out")
+        _p8, p_xyz, p_chol, p_feat = self._param_ptrs()
+        opts.params8 = _p8
         self._lib.check(self._cdll.gs2d_fit_step_band(
-            self.n, self.cap, self.H, self.W, self._xyz.data_ptr(), self._cholesky.data_ptr(),
-            self._features_dc.data_ptr(), self.adan_state.data_ptr(), gt.data_ptr(), fmt, work.data_ptr(),
+            self.n, self.cap, self.H, self.W, p_xyz, p_chol,
+            p_feat, self.adan_state.data_ptr(), gt.data_ptr(), fmt, work.data_ptr(),
             self.layout.total_bytes, self.step_index, self.current_lr(), b1, b2, b3, self.eps, self.weight_decay,
             1 if precounted else 0, band[0], band[1], phases,
             None if ex is None else self._ctypes.addressof(ex),
-            None if opts is None else self._ctypes.addressof(opts),
+            self._ctypes.addressof(opts),
             None if out_img is None else out_img.data_ptr(),
             None if grads_out is None else grads_out.data_ptr(), None if ids_out is None else ids_out.data_ptr(),
             self._report_ptr + 24 * slot, torch.cuda.current_stream(self.device).cuda_stream), "fit_step_band")

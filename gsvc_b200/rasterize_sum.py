@@ -62,6 +62,7 @@ class _DeviceCtx:
         self.slot = 0
         self.last_num_intersects = 0
         self.cap = {}       # (H, W) -> capacity in intersections
+        self.cap_n = {}     # (H, W) -> number of Gaussians of the calls the hint was learnt from
         self.layouts = {}   # (n, cap, tx, ty) -> StateLayout
         # sync-free path: sequence numbers, the calls whose mail has not been read yet, byte sizes
         self.seq = 0
@@ -400,8 +401,10 @@ def _forward_ranked(ctx, dctx, lib, dev, n, H, W, xys, radii, conics, colors, op
     if not capturing:
         dctx.poll()                         # lazily: hints from earlier calls, overflow of an earlier call
     cap = dctx.cap.get(key, 0)
-    first = cap < 1
-    if first:
+    # a hint learnt from a model of another size says nothing about this one: count again
+    first = cap < 1 or (dctx.cap_n.get(key, n) != n and not capturing)
+    dctx.cap_n[key] = n
+    if cap < 1:
         cap = _round_cap(max(8 * n, 1 << 18) if capturing else max(4 * n, 65536))
     wait = (first or not options.sync_free) and not capturing
     with _C._guard(dev):

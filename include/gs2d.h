@@ -273,6 +273,7 @@ int gs2d_rasterize_sum_nd_bwd(int n, int channels, int img_h, int img_w, int cap
 #define GS2D_TARGET_F32_CHW 0
 #define GS2D_TARGET_U8_HWC 1
 #define GS2D_TARGET_I420 2
+#define GS2D_TARGET_TILED 3 /* what gs2d_fit_target_prepare wrote */
 typedef struct {
     size_t total_bytes;
     size_t off_status;      /* int32[16] */
@@ -296,6 +297,15 @@ typedef struct {
     int32_t step;            /* the step index this record belongs to */
 } gs2d_fit_report;
 int gs2d_fit_layout_for(int n, int cap, int img_h, int img_w, gs2d_fit_layout* out);
+/* A frame is fitted for thousands of iterations (train_video_Represent.py:85-86): convert it ONCE into the
+ * order the tile kernel reads it in -- fp32, each thread's pixels' (r, g, b) contiguous, tile after tile;
+ * gs2d_fit_target_bytes(H, W) bytes, 16-byte aligned -- and pass that with GS2D_TARGET_TILED.  Same
+ * arithmetic as the in-kernel decode of the other three formats (so the same loss, bit for bit), but the
+ * iteration then spends no instructions on it and loads the frame with coalesced 16-byte accesses.
+ * A stream of frames that are used once each is better off with the raw formats. */
+size_t gs2d_fit_target_bytes(int img_h, int img_w);
+int gs2d_fit_target_prepare(int img_h, int img_w, const void* target, int target_format, float* prepared,
+                            gs2d_stream_t stream);
 int gs2d_fit_init(int n, int cap, int img_h, int img_w, void* work, size_t work_bytes, float* adan_state,
                   gs2d_stream_t stream);
 int gs2d_fit_step(int n, int cap, int img_h, int img_w, float* xyz_raw, float* chol_raw, float* features,
@@ -413,6 +423,14 @@ typedef struct {
     int analytic_grad;   /* != 0: the projection backward uses the analytic gradient of the forward instead
                           * of the reference's formula (see
                           * gs2d_project_chol_bwd_analytic).  Off = parity with the reference. */
+    float* params8;      /* != NULL: the three parameter tensors are the columns 0-1 / 2-4 / 5-7 of this ONE
+                          * fp32 [n][8] buffer (16-byte aligned; rows = xyz 2 | chol 3 | features 3), and the
+                          * xyz_raw / chol_raw / features arguments must be params8, params8 + 2, params8 + 5.
+                          * Every per-Gaussian kernel then moves a Gaussian's parameters as two aligned 16-byte
+                          * accesses where the reference's AoS tensors (cast to float2 / float3 at
+                          * bindings.cu:456-465) take eight 4-byte ones.  With a sharded update
+                          * (gs2d_grad_exchange) xyz_peers then lists the ranks' params8 buffers and
+                          * chol_peers / feat_peers are unused. */
 } gs2d_fit_options;
 int gs2d_fit_step_band(int n, int cap, int img_h, int img_w, float* xyz_raw, float* chol_raw, float* features,
                        float* adan_state, const void* target, int target_format, void* work, size_t work_bytes,
@@ -428,11 +446,14 @@ int gs2d_fit_step_band(int n, int cap, int img_h, int img_w, float* xyz_raw, flo
  *   u = g + b2 diff;  n = b3 n + (1-b3) u^2;  denom = sqrt(n)/sqrt(1-b3^step) + eps;
  *   p = (p - lr/(1-b1^step) m/denom - lr b2/(1-b2^step) d/denom) / (1 + lr wd);  prev = g
  * The six tables are HOST arrays of num_tensors DEVICE pointers (fp32, contiguous, counts[i]
- * elements each); `first` != 0 at the optimizer's first step (optimizer.py:183-185). */
+ * elements each); `first` != 0 at the optimizer's first step (optimizer.py:183-185).
+ * step_dev (DEVICE int32, may be NULL): when set, the step count is read from there at run time instead
+ * of `step` -- a captured CUDA graph replays the same arguments every iteration, so the caller keeps the
+ * counter on the device and bumps it before each step. */
 int gs2d_adan_step(int num_tensors, float* const* params, const float* const* grads, float* const* exp_avg,
                    float* const* exp_avg_sq, float* const* exp_avg_diff, float* const* prev_grad, const int* counts,
-                   float lr, float beta1, float beta2, float beta3, float eps, float weight_decay, int step, int first,
-                   gs2d_stream_t stream);
+                   float lr, float beta1, float beta2, float beta3, float eps, float weight_decay, int step,
+                   const int* step_dev, int first, gs2d_stream_t stream);
 /* The reference's prune (GaussianSplats_Represent.py:98-128, :147-171): drop the `remove_count`
  * Gaussians with the smallest |rgb_w| (torch.norm over dim 1 of an [N,1] tensor, then torch.sort,
  * :103-104 / :146-147; ties -- which torch.sort leaves unspecified -- go lowest index first) and
@@ -504,6 +525,9 @@ int gs2d_i420_to_rgb(int img_h, int img_w, const uint8_t* yuv, uint8_t* rgb, gs2
  * NULL.  work as above (gs2d_fit_init first; the Adan pointer may be NULL there). */
 #define GS2D_RENDER_ACTIVATE 1
 #define GS2D_RENDER_ALL_PER_TILE 4
+#define GS2D_RENDER_PACKED8 8 /* means_or_xyz_raw is a 16-byte aligned fp32 [n][8] buffer of packed rows
+                               * (gs2d_fit_options.params8), chol = its column 2; colors = its column 5 or
+                               * a contiguous [n][3] tensor of its own */
 int gs2d_render_chol(int n, int cap, int img_h, int img_w, const float* means_or_xyz_raw, const float* chol,
                      const float* colors, const float* opacities, int activate, void* work, size_t work_bytes,
                      float* out_img, int out_chw, int out_clamp, int32_t* final_idx, int32_t* ids_sorted_out,

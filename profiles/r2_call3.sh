@@ -1,0 +1,10 @@
+#!/bin/bash
+# round 2, call 3: GPU tests (operator path, graph capture, packed rows, prepared targets, ADVICE), fused bench A/B
+mkdir -p $GRAFT_REPO_ROOT/gpurun_out; O=$GRAFT_REPO_ROOT/gpurun_out
+timeout 1200 python -m pytest tests -m gpu -q > $O/r2_c3_pytest.log 2>&1; echo "pytest rc $?" >> $O/r2_c3_pytest.log; tail -25 $O/r2_c3_pytest.log
+for env in "" "GS2D_NO_PREPARE=1"; do for f in "" "--trained-like"; do
+  env $env timeout 300 python bench.py --no-cpu --steps 200 $f 2>>$O/r2_c3_err.log | tail -1 | python -c "
+import sys,json
+d=json.loads(sys.stdin.read())
+print('${env:-default} $f', 'value', round(d['value']), 'warm', round(d['l2_warm']['value']), 'e2e', round(d['e2e']['value']), 'render', round(d['render']['value']), 'psnr', round(d['final_psnr'],4), {k:round(v['ms_per_step']*1e3,1) for k,v in d['stages'].items()})" 2>&1 | tee -a $O/r2_c3_ab.txt
+done; done

@@ -87,6 +87,7 @@ def _reset_capacity(H, W, cap=None):
     except RS.CapacityOverflow:
         pass
     dctx.cap.pop((H, W), None)
+    dctx.cap_n.pop((H, W), None)
     if cap is not None:
         dctx.cap[(H, W)] = cap
     return dctx
@@ -116,13 +117,12 @@ def test_sync_free_overflow_is_loud_then_recovers():
     outgrows its buffer gets a NaN image, the next call raises CapacityOverflow with the buffer
     regrown, and the call after that is right again"""
     from gsvc_b200 import rasterize_sum as RS
-    small, big = _x(2_000), _x(20_000, trained=True)
+    small, big = _x(20_000), _x(20_000, trained=True)      # same count, many times the intersections
     H, W = 256, 256
     _reset_capacity(H, W)
-    _, ok = _render(small, H, W)                 # first call: waits once, sizes the buffer for `small`
+    _, ok = _render(small, H, W)                 # first call: waits once, sizes the buffer for `small` (x4)
     assert torch.isfinite(ok).all()
-    dctx = RS._device_ctx(cuda)
-    dctx.cap[(H, W)] = RS._CAP_QUANTUM           # pretend the hint is stale and far too small
+    RS._device_ctx(cuda).cap[(H, W)] = RS._CAP_QUANTUM   # pretend the hint is far too small for what comes
     _, bad = _render(big, H, W)                  # outgrows it: nothing waits, so nothing can be redone
     torch.cuda.synchronize()
     assert torch.isnan(bad).all()
@@ -184,26 +184,29 @@ def test_forward_backward_capture_in_a_cuda_graph():
     x = _x(n)
     for k in ("means2d", "L", "colors"):
         x[k].requires_grad_(True)
+    # separate leaves for the eager reference: a leaf's gradient accumulator remembers the stream it was
+    # first used on, and one created on the default stream would drag that stream into the capture
+    xe = {k: v.detach().clone().requires_grad_(v.requires_grad) for k, v in x.items()}
     gt = synth.target_frame(H, W)[0].permute(1, 2, 0).contiguous().to(cuda)
     _reset_capacity(H, W)
 
-    def step():
+    def step(x):
         p = G.project_gaussians_2d(x["means2d"], x["L"], H, W, tb)
         out = G.rasterize_gaussians_sum(*p, x["colors"], x["opacity"], H, W, 16, 16)
         loss = ((out.clamp(0, 1) - gt) ** 2).mean()
         grads = torch.autograd.grad(loss, [x["means2d"], x["L"], x["colors"]])
         return out, loss, grads
 
-    out_e, loss_e, grads_e = step()               # eager (also sizes the buffer)
+    out_e, loss_e, grads_e = step(xe)             # eager (also sizes the buffer)
     torch.cuda.synchronize()
     side = torch.cuda.Stream()
     side.wait_stream(torch.cuda.current_stream())
     with torch.cuda.stream(side):
-        step()                                    # warm-up on the capture stream
+        step(x)                                   # warm-up on a side stream, as torch's graph recipe asks
     torch.cuda.current_stream().wait_stream(side)
     graph = torch.cuda.CUDAGraph()
     with torch.cuda.graph(graph):
-        out_g, loss_g, grads_g = step()
+        out_g, loss_g, grads_g = step(x)
     for _ in range(3):
         graph.replay()
     torch.cuda.synchronize()
@@ -316,3 +319,32 @@ def test_dropin_import_as_gsplat_and_frame_model_step():
         opt.zero_grad(set_to_none=True)
         losses.append(loss.item())
     assert losses[-1] < 0.7 * losses[0], losses
+
+
+def test_graph_replayed_fit_iteration_follows_the_eager_loop():
+    """FrameFit.train_iter_graphed (forward + loss + backward + Adan as one graph replay per iteration)
+    against FrameFit.train_iter on the same model: same losses, same parameters, step counters in sync"""
+    from gsvc_b200.fit import FrameFit
+    H, W, n = 128, 192, 4_000
+    gt = synth.target_frame(H, W, seed=3).to(cuda)
+    a = FrameFit(H, W, n, cuda, seed=3)
+    b = FrameFit(H, W, n, cuda, seed=3)
+    la, lb = [], []
+    for it in range(12):
+        l, _ = a.train_iter_graphed(gt)
+        la.append(float(l))
+        l, _ = b.train_iter(gt)
+        lb.append(float(l))
+    assert a.iter == b.iter == 12
+    assert a.optimizer.param_groups[0]["step"] == b.optimizer.param_groups[0]["step"] == 12
+    assert int(a.optimizer.param_groups[0]["step_dev"].item()) == 12
+    assert la == pytest.approx(lb, rel=2e-4)
+    assert la[-1] < la[0]
+    for k in ("_xyz", "_cholesky", "_features_dc"):
+        d = (getattr(a, k) - getattr(b, k)).abs()
+        assert float(d.median()) <= 1e-6 and float((d > 1e-3).float().mean()) <= 0.01, k
+    # a different frame through the same graph
+    gt2 = synth.target_frame(H, W, seed=4).to(cuda)
+    l2, _ = a.train_iter_graphed(gt2)
+    l2b, _ = b.train_iter(gt2)
+    assert float(l2) == pytest.approx(float(l2b), rel=2e-4)

@@ -467,33 +467,33 @@ def test_train_until_absorbs_a_slot_overflow():
     H, W, n, init, gt, a = _crowding_setup(slots=True)
     _, _, _, _, _, b = _crowding_setup(slots=False)
     gtd = gt.to(cuda)
-    K = 120
+    K = 12       # (short: a tile holding every Gaussian at lr 0.05 amplifies rounding noise quickly)
     la = a.train_until(gtd, K)
     b.train_iters(gtd, K)
     lb = b.loss()
     assert a.step_index == K and b.step_index == K
-    if a.slots:
-        pytest.skip("no tile crowded beyond 256 within the iterations")
-    assert la == pytest.approx(lb, rel=2e-3)
+    assert not a.slots, "the recipe crowds a tile beyond 256 at once"
+    assert la == pytest.approx(lb, rel=1e-3)
     assert issubclass(GS2DOverflow, RuntimeError)
-    # checking every few iterations gives the same thing
+    # checking every few iterations gives the same thing; so does a long run, as far as the count goes
     _, _, _, _, _, c = _crowding_setup(slots=True)
-    lc = c.train_until(gtd, K, check_every=16)
-    assert c.step_index == K and lc == pytest.approx(lb, rel=2e-3)
+    lc = c.train_until(gtd, K, check_every=5)
+    assert c.step_index == K and lc == pytest.approx(lb, rel=1e-3)
+    c.train_until(gtd, 150)
+    assert c.step_index == 150 and math.isfinite(c.loss())
 
 
 def test_fit_stream_resumes_after_an_overflow():
-    """frames of the steps that became no-ops are issued again, none is lost"""
+    """frames of the steps that became no-ops are issued again, none is lost, none twice"""
     H, W, n, init, gt, a = _crowding_setup(slots=True)
     _, _, _, _, _, b = _crowding_setup(slots=False)
     host = gt.contiguous().pin_memory()
-    K = 120
+    K = 40
     la = [l for l, _ in a.fit_stream(host for _ in range(K))]
     lb = [l for l, _ in b.fit_stream(host for _ in range(K))]
-    assert len(la) == K and len(lb) == K and a.step_index == K
-    if a.slots:
-        pytest.skip("no tile crowded beyond 256 within the iterations")
-    np.testing.assert_allclose(la, lb, rtol=2e-3)
+    assert len(la) == K and len(lb) == K and a.step_index == K and not a.slots
+    np.testing.assert_allclose(la[:12], lb[:12], rtol=1e-3)
+    assert la[-1] < la[0] and all(math.isfinite(x) for x in la)
 
 
 def test_gop_fit_survives_a_slot_overflow():
@@ -535,3 +535,88 @@ def test_step_lr_matches_torch_scheduler_across_a_boundary():
     fit.step_index = 0
     fit.train_iters(gt, 7)
     assert fit.current_lr() == pytest.approx(1e-2 * 0.5, rel=1e-12)    # iteration 7 -> (7-1)//5 = 1
+
+
+def test_parameters_are_column_views_of_one_packed_buffer():
+    """SURVEY 8 a12 / north_star "16-byte loads": the master copy is fp32 [n][8] (xyz 2 | chol 3 | feat 3);
+    the reference's names and shapes are views of it, and a tensor assigned from outside is packed again"""
+    H, W, n = 96, 128, 3_000
+    init, gt, a = _setup(H, W, n, seed=4, slots=True)
+    _, _, b = _setup(H, W, n, seed=4, slots=True)
+    p8 = a._params8
+    assert p8.shape == (n, 8) and p8.is_contiguous() and p8.data_ptr() % 16 == 0
+    assert a._xyz.shape == (n, 2) and a._xyz.stride() == (8, 1) and a._xyz.data_ptr() == p8.data_ptr()
+    assert a._cholesky.data_ptr() == p8.data_ptr() + 8 and a._features_dc.data_ptr() == p8.data_ptr() + 20
+    assert torch.equal(p8[:, 2:5], init["_cholesky"].to(cuda))
+    gtd = gt.to(cuda)
+    a.train_iters(gtd, 3)
+    b.train_iters(gtd, 3)
+    d = (a._params8 - b._params8).abs()       # two runs differ by the order of the gradient atomics only
+    assert float(d.median()) <= 1e-6 and float((d > 1e-4).float().mean()) <= 0.01
+    sd = a.state_dict()
+    assert all(sd[k].is_contiguous() for k in ("_xyz", "_cholesky", "_features_dc"))
+    # somebody swaps a parameter tensor instead of writing into it
+    new_xyz = a._xyz.detach().clone() * 0.9
+    a._xyz = torch.nn.Parameter(new_xyz, requires_grad=False)
+    with torch.no_grad():
+        b._xyz.copy_(new_xyz)
+    a.train_iters(gtd, 1)
+    b.train_iters(gtd, 1)
+    assert a._xyz.data_ptr() == a._params8.data_ptr()
+    assert a.loss() == pytest.approx(b.loss(), rel=1e-6)
+
+
+@pytest.mark.parametrize("fmt", ["f32", "u8", "i420"])
+def test_prepared_target_gives_the_same_bits_as_the_in_kernel_decode(fmt):
+    """gs2d_fit_target_prepare (the frame converted once into the tile kernel's order) against the
+    per-iteration decode of the same frame: identical loss sums and gradients"""
+    from gsvc_b200 import yuv
+    H, W, n = 200, 328, 3_000
+    init, gt, a = _setup(H, W, n, seed=6, slots=True)
+    _, _, b = _setup(H, W, n, seed=6, slots=True)
+    b.prepare_targets = False
+    rgb8 = (gt[0] * 255).round().to(torch.uint8).permute(1, 2, 0).contiguous()
+    frame = {"f32": gt, "u8": rgb8, "i420": yuv.rgb_to_i420(rgb8).contiguous()}[fmt].to(cuda)
+    ga = torch.empty((n, 8), device=cuda)
+    gb = torch.empty((n, 8), device=cuda)
+    a.train_iters(frame, 1, grads_out=ga)
+    b.train_iters(frame, 1, grads_out=gb)
+    assert a.loss() == pytest.approx(b.loss(), rel=1e-12)     # same per-tile sums, added up in another order
+    assert (ga - gb).abs().max().item() <= 1e-4 * gb.abs().max().item()
+    # an in-place edit of the frame is seen (version counter), a new tensor too
+    frame2 = frame.clone()
+    if fmt == "f32":
+        frame2.mul_(0.5)
+    else:
+        frame2.div_(2, rounding_mode="floor")
+    a.train_iters(frame2, 1)
+    b.train_iters(frame2, 1)
+    assert a.loss() == pytest.approx(b.loss(), rel=1e-6)
+    with torch.no_grad():
+        frame2.zero_()
+    a.train_iters(frame2, 1)
+    b.train_iters(frame2, 1)
+    assert a.loss() == pytest.approx(b.loss(), rel=1e-6)
+
+
+def test_intersections_per_tile_row_match_the_binning():
+    """the weights the tile-row split is balanced with are the per-row sums of the tile counts"""
+    _need = pytest.importorskip("torch")
+    from tests import ref_gpu
+    from gsvc_b200.fit import _intersections_per_tile_row, split_tile_rows
+    import gsvc_b200.cuda as C
+    H, W, n = 520, 392, 7_000
+    from gsvc_b200 import synth
+    g = synth.gaussians(n, seed=9, trained_like=True)
+    rows = _intersections_per_tile_row(g["_xyz"].to(cuda), g["_cholesky"].to(cuda), H, W)
+    tb = ((W + 15) // 16, (H + 15) // 16, 1)
+    xys, depths, radii, conics, nth = C.project_gaussians_2d_forward(n, g["means2d"].to(cuda), g["L"].to(cuda), H, W, tb, 0.01)
+    cum = torch.cumsum(nth, 0, dtype=torch.int32)
+    I = int(cum[-1])
+    isect, _ids = C.map_gaussian_to_intersects(n, I, xys, depths, radii, cum, tb)
+    tile_row = ((isect >> 32) // tb[0]).long()
+    want = torch.bincount(tile_row, minlength=tb[1]).tolist()
+    assert [int(r) for r in rows] == want
+    bands = split_tile_rows(tb[1], 4, weights=rows)
+    load = [sum(rows[a:b]) for a, b in bands]
+    assert max(load) <= 1.35 * (sum(rows) / 4)
