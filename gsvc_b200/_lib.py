@@ -53,6 +53,7 @@ class GradExchange(Structure):
     _fields_ = [("accumulate", c_void_p), ("peers", c_void_p), ("num_peers", c_int), ("zero", c_void_p),
                 ("multicast", c_void_p), ("shard_begin", c_int), ("shard_end", c_int), ("xyz_peers", c_void_p),
                 ("chol_peers", c_void_p), ("feat_peers", c_void_p), ("status_peers", c_void_p),
+                ("work_peers", c_void_p), ("band_edges", c_void_p),
                 ("barrier_pads", c_void_p), ("rank", c_int), ("barrier_epoch", c_uint32)]
 
 
@@ -123,6 +124,7 @@ _SIGNATURES = {
     "gs2d_dequantize": (c_int, [c_int, _P, _P, _P, _P, _P]),
     "gs2d_frame_pipe_create": (c_int, [_P, c_size_t, c_int, POINTER(c_void_p)]),
     "gs2d_frame_pipe_destroy": (c_int, [_P]),
+    "gs2d_frame_pipe_set_prepare": (c_int, [_P, c_int, c_int, c_int, _P]),
     "gs2d_frame_pipe_push": (c_int, [_P, _P, POINTER(c_int)]),
     "gs2d_frame_pipe_acquire": (c_int, [_P, c_int, _P, POINTER(c_void_p)]),
     "gs2d_frame_pipe_release": (c_int, [_P, c_int, _P]),

@@ -4,9 +4,23 @@
 #include <mutex>
 #include <vector>
 
+#include <cstdlib>
+#include <nvtx3/nvToolsExt.h>
+
 #include "gs2d_host.h"
 
 namespace gs2d {
+
+// ---- NVTX ranges per stage (GS2D_NVTX=1) ------------------------------------------------------
+static const char* const kStageNames[GS2D_NUM_STAGES] = {
+    "gs2d:project_fwd", "gs2d:memset", "gs2d:scan_map", "gs2d:sort", "gs2d:edges_pack", "gs2d:raster_fwd",
+    "gs2d:raster_bwd", "gs2d:project_bwd", "gs2d:fit_tiles", "gs2d:adan", "gs2d:other"};
+bool nvtx_enabled() {
+    static const bool on = [] { const char* e = getenv("GS2D_NVTX"); return e && e[0] == '1'; }();
+    return on;
+}
+void nvtx_push(int stage) { nvtxRangePushA(stage >= 0 && stage < GS2D_NUM_STAGES ? kStageNames[stage] : "gs2d"); }
+void nvtx_pop() { nvtxRangePop(); }
 
 static thread_local char g_err[512] = "";
 

@@ -334,6 +334,12 @@ struct Route {
     float* const* feat;
     int32_t* const* status;
     int R;
+    // remote scatter (gs2d_grad_exchange.work_peers): the ranks' workspaces, all of one layout, and the
+    // tile-row edges of their bands -- the update kernel writes the NEXT step's records of every Gaussian
+    // of its shard straight into the slots of the rank that rasterises the tile (NVLink atomics + stores)
+    char* const* work;
+    size_t off_tile_count, off_packed;
+    const int32_t* band_edges;   // [R + 1]
 };
 
 template <bool SLOT>
@@ -347,6 +353,7 @@ __device__ __forceinline__ int scatter_records(const Proj2d& p, int i, float o, 
     const int nt = (yb - ya) * bw;
     if (nt <= 0) return 0;
     int x = p.x0, y = ya;
+    const PairExtent ext = pair_extent(p.cx, p.cy, o, p.conic.x, p.conic.y, p.conic.z);   // once per Gaussian, not per tile
     for (int base = 0; base < nt; base += kScatterBatch) {
         int pos[kScatterBatch];
         const int xs = x, ys = y;
@@ -374,16 +381,65 @@ __device__ __forceinline__ int scatter_records(const Proj2d& p, int i, float o, 
                     at = (size_t)t * kSlotStride + pos[k];
                 } else {
                     at = (size_t)tile_off[t] + pos[k];
+                    GS2D_ASSERT(pos[k] >= 0 && at < (size_t)tile_off[t + 1]);   // the count kernel saw the same projection
                 }
                 if (ok) {
-                    const uint32_t rect = pair_rect(p.cx, p.cy, o, p.conic.x, p.conic.y, p.conic.z, xr * GS2D_TILE,
-                                                    yr * GS2D_TILE, W, H);
+                    const uint32_t rect = pair_rect_of(p.cx, p.cy, ext, xr * GS2D_TILE, yr * GS2D_TILE, W, H);
                     // the diagonal conic terms are stored HALVED: sigma = 0.5*(cx dx^2 + cz dy^2) + cy dx dy is
                     // then fma(dy, cy*dx, fma(dx, (cx/2)*dx, ((cz/2)*dy)*dy)) with no separate multiply by 0.5 per
                     // pixel; halving is exact, so every rounding is the reference's
                     packed[3 * at + 0] = make_float4(p.cx, p.cy, 0.5f * p.conic.x, p.conic.y);
                     packed[3 * at + 1] = make_float4(0.5f * p.conic.z, o, __uint_as_float(rect), __int_as_float(i));
                     packed[3 * at + 2] = make_float4(r, g, b, __uint_as_float((uint32_t)t));
+                }
+                if (++xr == p.x1) { xr = p.x0; ++yr; }
+            }
+        }
+    }
+    return nt;
+}
+
+// scatter_records<true> across ranks: tile (x, y) belongs to the rank whose band holds row y; its fill
+// counter and its slots are addressed in that rank's workspace (peer-mapped memory).  The claims are
+// system-scope atomics over NVLink, up to kScatterBatch of them in flight per thread, the records plain
+// stores that the cross-rank barrier after the update kernel publishes.  Returns the tiles claimed.
+__device__ __forceinline__ int scatter_records_remote(const Proj2d& p, int i, float o, float r, float g, float b, int tx,
+                                                      int W, int H, int32_t* status, int flag_step, const Route& rt) {
+    if (p.nth <= 0) return 0;
+    const int bw = p.x1 - p.x0;
+    const int nt = (p.y1 - p.y0) * bw;
+    if (nt <= 0) return 0;
+    const PairExtent ext = pair_extent(p.cx, p.cy, o, p.conic.x, p.conic.y, p.conic.z);
+    int x = p.x0, y = p.y0, q = 0;
+    for (int base = 0; base < nt; base += kScatterBatch) {
+        int pos[kScatterBatch];
+        const int xs = x, ys = y, qs = q;
+#pragma unroll
+        for (int k = 0; k < kScatterBatch; ++k) {
+            if (base + k < nt) {
+                while (y >= rt.band_edges[q + 1]) ++q;     // rows only grow: the owner is found incrementally
+                int32_t* fill = reinterpret_cast<int32_t*>(rt.work[q] + rt.off_tile_count);
+                pos[k] = atomicAdd_system(&fill[y * tx + x], 1);
+                if (++x == p.x1) { x = p.x0; ++y; }
+            }
+        }
+        int xr = xs, yr = ys, qr = qs;
+#pragma unroll
+        for (int k = 0; k < kScatterBatch; ++k) {
+            if (base + k < nt) {
+                while (yr >= rt.band_edges[qr + 1]) ++qr;
+                const int t = yr * tx + xr;
+                if (pos[k] < kSlotStride) {
+                    float4* packed = reinterpret_cast<float4*>(rt.work[qr] + rt.off_packed);
+                    const size_t at = (size_t)t * kSlotStride + pos[k];
+                    const uint32_t rect = pair_rect_of(p.cx, p.cy, ext, xr * GS2D_TILE, yr * GS2D_TILE, W, H);
+                    packed[3 * at + 0] = make_float4(p.cx, p.cy, 0.5f * p.conic.x, p.conic.y);
+                    packed[3 * at + 1] = make_float4(0.5f * p.conic.z, o, __uint_as_float(rect), __int_as_float(i));
+                    packed[3 * at + 2] = make_float4(r, g, b, __uint_as_float((uint32_t)t));
+                } else {
+                    atomicCAS(&status[kStOverflow], 0, -flag_step);
+                    for (int z = 0; z < rt.R; ++z)   // every rank must stop at this step
+                        if (rt.status[z] != status) atomicCAS_system(&rt.status[z][kStOverflow], 0, -flag_step);
                 }
                 if (++xr == p.x1) { xr = p.x0; ++yr; }
             }
@@ -671,6 +727,7 @@ k_fit_tiles(int W, int H, int tx, int row0, const int32_t* __restrict__ tile_off
     // forward walks the batches in rank order, the backward walks them again; one batch otherwise
     const bool all = ALL && cnt > GS2D_MAX_PER_TILE;
     const int nbat = all ? (cnt + GS2D_MAX_PER_TILE - 1) / GS2D_MAX_PER_TILE : 1;
+    GS2D_ASSERT(cnt >= 0 && lo >= 0 && (!slot || cnt <= kSlotStride));
     const bool per_warp = kWarpStage && cnt <= 32;     // uniform over the CTA
     float4* sq = sq_all + (per_warp ? warp * (32 * 3) : 0);
     int nb;
@@ -862,6 +919,8 @@ k_fit_tiles(int W, int H, int tx, int row0, const int32_t* __restrict__ tile_off
         const uint32_t rect = __float_as_uint(q1.z);
         const int rx0 = rect & 255, rx1 = (rect >> 8) & 255, ry0 = (rect >> 16) & 255, ry1 = rect >> 24;
         const bool live = (r0 + sub < nb) && ry1 >= ry0;
+        GS2D_ASSERT(!live || (rx0 <= rx1 && rx1 < GS2D_TILE && ry1 < GS2D_TILE));   // the row walk stays inside sv's 32 rows
+        GS2D_ASSERT(!live || (__float_as_int(q1.w) >= 0));
         const int h = live ? ry1 - ry0 + 1 : 0;
         const int ncol = live ? ((rx1 - rx0) >> 3) + 1 : 0;          // column blocks of 8: 1 or 2
         const int iters = h * ncol;
@@ -1077,6 +1136,7 @@ k_fit_update(int n, float* __restrict__ xyz_raw, float* __restrict__ chol_raw, f
         for (size_t q = gtid; q < (size_t)n * 3; q += (size_t)gridDim.x * kFitThreads) zb[q] = z;
     }
     int claimed = 0;
+    GS2D_ASSERT(shard_begin >= 0 && shard_end <= n);
     if (i < shard_end) {
         float4 g0, g1;   // v_xy(2) v_conic(3) v_rgb(3) | v_opacity(1) pad(3) unused here
         if (mc_grads) {
@@ -1177,6 +1237,15 @@ k_fit_update(int n, float* __restrict__ xyz_raw, float* __restrict__ chol_raw, f
         // the next iteration's binning starts here: project the updated parameters and count tiles
         // (same arithmetic as k_fit_count / k_fit_scatter, so the ranges match what scatter fills);
         // not when the update is sharded: each rank bins its band from the gathered parameters
+        if (rt.R > 0 && rt.work) {
+            // sharded update with remote scatter: the records of this Gaussian go straight to the ranks
+            // whose bands it touches
+            Proj2d pn;
+            project_chol(tanhf(par[0]), tanhf(par[1]), addf(par[2], 0.5f), addf(par[3], 0.f), addf(par[4], 0.5f),
+                         half_w, half_h, tx, ty, pn);
+            claimed = scatter_records_remote(pn, i, 1.f, mulf(par[5], cw), mulf(par[6], cw), mulf(par[7], cw), tx, W, H,
+                                             status, next_step, rt);
+        }
         if (rt.R == 0) {
             Proj2d pn;
             project_chol(tanhf(par[0]), tanhf(par[1]), addf(par[2], 0.5f), addf(par[3], 0.f), addf(par[4], 0.5f),
@@ -1192,6 +1261,10 @@ k_fit_update(int n, float* __restrict__ xyz_raw, float* __restrict__ chol_raw, f
         }
     }
     if (skip_update) return;
+    if (rt.R > 0 && rt.work) {
+        block_add(claimed, &status[kStSlotIsect + (next_step & 1)], sh);   // (this shard's pairs, over all bands)
+        if (PACKED) return;
+    }
     if (PACKED && rt.R > 0) return;
     if (rt.R > 0) {
         // sharded update: the all-gather is these stores (NVLink, fire and forget; the peers read
@@ -1226,6 +1299,10 @@ k_fit_update(int n, float* __restrict__ xyz_raw, float* __restrict__ chol_raw, f
 // follows may be launched programmatically: its prologue runs under the wait.
 __global__ void __launch_bounds__(32)
 k_rank_barrier(uint32_t* const* __restrict__ pads, int R, int rank, uint32_t epoch) {
+    // launched programmatically itself: the warp is already resident when the kernel before it drains
+    // (its launch latency is off the step's critical path); nothing is signalled before that kernel's
+    // writes are complete and visible
+    pdl_wait();
     pdl_release();
     const int q = threadIdx.x;
     if (q >= R) return;
@@ -1458,6 +1535,13 @@ int gs2d_fit_step_band(int n, int cap, int img_h, int img_w, float* xyz_raw, flo
             rt.feat = exchange->feat_peers;
             rt.status = exchange->status_peers;
             rt.R = num_peers;
+            if (exchange->work_peers) {
+                GS2D_REQUIRE(exchange->band_edges != nullptr, "fit_step: remote scatter needs the band edges");
+                rt.work = (char* const*)exchange->work_peers;
+                rt.off_tile_count = L.off_tile_count;
+                rt.off_packed = L.off_packed;
+                rt.band_edges = exchange->band_edges;
+            }
         }
     }
     const bool sharded = rt.R > 0;
@@ -1493,7 +1577,7 @@ int gs2d_fit_step_band(int n, int cap, int img_h, int img_w, float* xyz_raw, flo
             // modified).  A sharded update never scatters: the band's records are written here, every
             // step, from the parameters the ranks stored into this rank's tensors (the fill levels
             // are zero already: the previous tile kernel left them so)
-            if (!precounted || sharded) {
+            if (!precounted || (sharded && !rt.work)) {   // (remote scatter: the peers' update kernels filled the slots)
                 ProfScope ps_(GS2D_STAGE_EDGES_PACK, s);
                 if (!precounted) {
                     k_fit_reset_slots<<<div_up(L.tiles, kFitThreads), kFitThreads, 0, s>>>(
@@ -1517,30 +1601,22 @@ int gs2d_fit_step_band(int n, int cap, int img_h, int img_w, float* xyz_raw, flo
                                               row1 - row0);
         ProfScope ps_(GS2D_STAGE_FIT_TILES, s);
         const dim3 grid = tile_grid(tx, row1 - row0);
+        auto launch = [&](auto kernel) {
+            return launch_pdl(kernel, grid, dim3(kTileThreads), s, img_w, img_h, tx, row0, tile_off_arg,
+                              (int32_t*)(w + L.off_tile_count), (const float4*)(w + L.off_packed), target, grad_scale, grads,
+                              loss + (step % GS2D_FIT_LOSS_SLOTS), status, out_img, 1, 1, (int32_t*)nullptr, ids_sorted_out,
+                              step, tile_flags);
+        };
+        cudaError_t le;
         if (target_format == GS2D_TARGET_F32_CHW)
-            GS2D_CHECK_CUDA(launch_pdl(all_per_tile ? k_fit_tiles<0, 0, true> : k_fit_tiles<0, 0, false>, grid,
-                dim3(kTileThreads), s,
-                img_w, img_h, tx, row0, tile_off_arg, (int32_t*)(w + L.off_tile_count),
-                (const float4*)(w + L.off_packed), target, grad_scale, grads, loss + (step % GS2D_FIT_LOSS_SLOTS),
-                status, out_img, 1, 1, (int32_t*)nullptr, ids_sorted_out, step, tile_flags));
+            le = all_per_tile ? launch(k_fit_tiles<0, 0, true>) : launch(k_fit_tiles<0, 0, false>);
         else if (target_format == GS2D_TARGET_U8_HWC)
-            GS2D_CHECK_CUDA(launch_pdl(all_per_tile ? k_fit_tiles<0, 1, true> : k_fit_tiles<0, 1, false>, grid,
-                dim3(kTileThreads), s,
-                img_w, img_h, tx, row0, tile_off_arg, (int32_t*)(w + L.off_tile_count),
-                (const float4*)(w + L.off_packed), target, grad_scale, grads, loss + (step % GS2D_FIT_LOSS_SLOTS),
-                status, out_img, 1, 1, (int32_t*)nullptr, ids_sorted_out, step, tile_flags));
+            le = all_per_tile ? launch(k_fit_tiles<0, 1, true>) : launch(k_fit_tiles<0, 1, false>);
         else if (target_format == GS2D_TARGET_I420)
-            GS2D_CHECK_CUDA(launch_pdl(all_per_tile ? k_fit_tiles<0, 2, true> : k_fit_tiles<0, 2, false>, grid,
-                dim3(kTileThreads), s,
-                img_w, img_h, tx, row0, tile_off_arg, (int32_t*)(w + L.off_tile_count),
-                (const float4*)(w + L.off_packed), target, grad_scale, grads, loss + (step % GS2D_FIT_LOSS_SLOTS),
-                status, out_img, 1, 1, (int32_t*)nullptr, ids_sorted_out, step, tile_flags));
+            le = all_per_tile ? launch(k_fit_tiles<0, 2, true>) : launch(k_fit_tiles<0, 2, false>);
         else
-            GS2D_CHECK_CUDA(launch_pdl(all_per_tile ? k_fit_tiles<0, 3, true> : k_fit_tiles<0, 3, false>, grid,
-                dim3(kTileThreads), s,
-                img_w, img_h, tx, row0, tile_off_arg, (int32_t*)(w + L.off_tile_count),
-                (const float4*)(w + L.off_packed), target, grad_scale, grads, loss + (step % GS2D_FIT_LOSS_SLOTS),
-                status, out_img, 1, 1, (int32_t*)nullptr, ids_sorted_out, step, tile_flags));
+            le = all_per_tile ? launch(k_fit_tiles<0, 3, true>) : launch(k_fit_tiles<0, 3, false>);
+        GS2D_CHECK_CUDA(le);
         GS2D_CHECK_LAUNCH("fit_tiles");
     }
     const bool own_barrier = exchange && exchange->barrier_pads &&
@@ -1548,8 +1624,8 @@ int gs2d_fit_step_band(int n, int cap, int img_h, int img_w, float* xyz_raw, flo
     if (own_barrier) {
         GS2D_REQUIRE(exchange->num_peers > 0 && exchange->num_peers <= 32 && exchange->rank >= 0 &&
                          exchange->rank < exchange->num_peers, "fit_step: bad barrier description");
-        k_rank_barrier<<<1, 32, 0, s>>>(exchange->barrier_pads, exchange->num_peers, exchange->rank,
-                                        exchange->barrier_epoch);
+        GS2D_CHECK_CUDA(launch_pdl(k_rank_barrier, dim3(1), dim3(32), s, exchange->barrier_pads, exchange->num_peers,
+                                   exchange->rank, exchange->barrier_epoch));
         GS2D_CHECK_LAUNCH("rank_barrier");
     }
     if (phases & GS2D_FIT_PHASE_UPDATE) {
@@ -1573,8 +1649,8 @@ int gs2d_fit_step_band(int n, int cap, int img_h, int img_w, float* xyz_raw, flo
         GS2D_CHECK_LAUNCH("fit_update");
     }
     if (own_barrier && sharded) {   // the peers' stores into this rank's parameters precede its next scatter
-        k_rank_barrier<<<1, 32, 0, s>>>(exchange->barrier_pads, exchange->num_peers, exchange->rank,
-                                        exchange->barrier_epoch + 1u);
+        GS2D_CHECK_CUDA(launch_pdl(k_rank_barrier, dim3(1), dim3(32), s, exchange->barrier_pads, exchange->num_peers,
+                                   exchange->rank, exchange->barrier_epoch + 1u));
         GS2D_CHECK_LAUNCH("rank_barrier");
     }
     return GS2D_OK;

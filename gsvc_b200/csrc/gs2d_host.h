@@ -22,15 +22,24 @@ void prof_end(int stage, cudaStream_t s);
 
 // Brackets the launches of one stage with an event pair on the launching stream when
 // profiling is on (gs2d_prof_enable); a single predictable branch when it is off.
+// With GS2D_NVTX=1 in the environment every stage is also an NVTX range (named after the stage) on the
+// calling thread, so that a timeline profiler shows the library's stages between the caller's own ranges
+// (the reference has no tracing hooks at all).
+bool nvtx_enabled();
+void nvtx_push(int stage);
+void nvtx_pop();
+
 struct ProfScope {
     int stage;
     cudaStream_t s;
-    bool on;
-    ProfScope(int stage_, cudaStream_t s_) : stage(stage_), s(s_), on(prof_enabled()) {
+    bool on, nvtx;
+    ProfScope(int stage_, cudaStream_t s_) : stage(stage_), s(s_), on(prof_enabled()), nvtx(nvtx_enabled()) {
+        if (nvtx) nvtx_push(stage);
         if (on) prof_begin(stage, s);
     }
     ~ProfScope() {
         if (on) prof_end(stage, s);
+        if (nvtx) nvtx_pop();
     }
 };
 

@@ -44,6 +44,7 @@ __device__ __forceinline__ int stage_tile_sorted(const float4* __restrict__ src,
                 r1 = __ldg(&src[3 * (size_t)j + 1]);
                 r2 = __ldg(&src[3 * (size_t)j + 2]);
             }
+            GS2D_ASSERT(rank >= 0 && rank < cnt);
             sq[3 * rank + 0] = r0;
             sq[3 * rank + 1] = r1;
             sq[3 * rank + 2] = r2;
@@ -105,7 +106,9 @@ __device__ __forceinline__ void stage_tile_warp(float4 r0, float4 r1, float4 r2,
     const int cnt4 = (cnt + 3) & ~3;
 #pragma unroll 4
     for (int k = 0; k < cnt4; ++k) rank += (__shfl_sync(0xffffffffu, my, k) < my) ? 1 : 0;
+    GS2D_ASSERT(cnt >= 0 && cnt <= 32);
     if (lane < cnt) {
+        GS2D_ASSERT(rank >= 0 && rank < cnt);      // ids within a tile are distinct: ranks are a permutation
         sqw[3 * rank + 0] = r0;
         sqw[3 * rank + 1] = r1;
         sqw[3 * rank + 2] = r2;

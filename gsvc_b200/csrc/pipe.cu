@@ -17,6 +17,13 @@ struct gs2d_frame_pipe {
     cudaEvent_t copied[GS2D_PIPE_MAX_DEPTH];
     cudaEvent_t freed[GS2D_PIPE_MAX_DEPTH];
     bool has_consumer[GS2D_PIPE_MAX_DEPTH];
+    // optional: every frame is also converted into the tile kernel's own order (gs2d_fit_target_prepare)
+    // on the copy stream, right behind its copy -- under the previous frame's fit step like the copy itself
+    float* prepared;
+    size_t prepared_bytes;
+    int img_h, img_w, target_format;
+    cudaStream_t prep_stream;                       // the conversion: a third stage of the pipe, behind the copy
+    cudaEvent_t arrived[GS2D_PIPE_MAX_DEPTH];       // raw bytes of the slot are on the device
 };
 
 using namespace gs2d;
@@ -34,10 +41,14 @@ int gs2d_frame_pipe_create(void* device_slots, size_t frame_bytes, int depth, gs
     p->frame_bytes = frame_bytes;
     p->depth = depth;
     p->next = 0;
+    p->prepared = nullptr;
+    p->prepared_bytes = 0;
     cudaError_t e = cudaStreamCreateWithFlags(&p->copy_stream, cudaStreamNonBlocking);
+    if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&p->prep_stream, cudaStreamNonBlocking);
     for (int i = 0; i < depth && e == cudaSuccess; ++i) {
         p->has_consumer[i] = false;
-        e = cudaEventCreateWithFlags(&p->copied[i], cudaEventDisableTiming);
+        e = cudaEventCreateWithFlags(&p->arrived[i], cudaEventDisableTiming);
+        if (e == cudaSuccess) e = cudaEventCreateWithFlags(&p->copied[i], cudaEventDisableTiming);
         if (e == cudaSuccess) e = cudaEventCreateWithFlags(&p->freed[i], cudaEventDisableTiming);
     }
     if (e != cudaSuccess) {
@@ -52,11 +63,14 @@ int gs2d_frame_pipe_create(void* device_slots, size_t frame_bytes, int depth, gs
 int gs2d_frame_pipe_destroy(gs2d_frame_pipe* p) {
     if (!p) return GS2D_OK;
     cudaStreamSynchronize(p->copy_stream);
+    cudaStreamSynchronize(p->prep_stream);
     for (int i = 0; i < p->depth; ++i) {
+        cudaEventDestroy(p->arrived[i]);
         cudaEventDestroy(p->copied[i]);
         cudaEventDestroy(p->freed[i]);
     }
     cudaStreamDestroy(p->copy_stream);
+    cudaStreamDestroy(p->prep_stream);
     delete p;
     return GS2D_OK;
 }
@@ -68,15 +82,40 @@ int gs2d_frame_pipe_push(gs2d_frame_pipe* p, const void* host_frame, int* slot_o
     if (p->has_consumer[b]) GS2D_CHECK_CUDA(cudaStreamWaitEvent(p->copy_stream, p->freed[b], 0));
     GS2D_CHECK_CUDA(cudaMemcpyAsync(p->slots + (size_t)b * p->frame_bytes, host_frame, p->frame_bytes,
                                     cudaMemcpyHostToDevice, p->copy_stream));
-    GS2D_CHECK_CUDA(cudaEventRecord(p->copied[b], p->copy_stream));
+    if (p->prepared) {
+        // third stage: the copy stream goes straight on to the next frame while this one is converted
+        // (copy of frame i+2 | conversion of frame i+1 | fit step of frame i)
+        GS2D_CHECK_CUDA(cudaEventRecord(p->arrived[b], p->copy_stream));
+        GS2D_CHECK_CUDA(cudaStreamWaitEvent(p->prep_stream, p->arrived[b], 0));
+        const int rc = gs2d_fit_target_prepare(p->img_h, p->img_w, p->slots + (size_t)b * p->frame_bytes, p->target_format,
+                                               (float*)((char*)p->prepared + (size_t)b * p->prepared_bytes),
+                                               (gs2d_stream_t)p->prep_stream);
+        if (rc != GS2D_OK) return rc;
+        GS2D_CHECK_CUDA(cudaEventRecord(p->copied[b], p->prep_stream));
+    } else {
+        GS2D_CHECK_CUDA(cudaEventRecord(p->copied[b], p->copy_stream));
+    }
     *slot_out = b;
+    return GS2D_OK;
+}
+
+int gs2d_frame_pipe_set_prepare(gs2d_frame_pipe* p, int img_h, int img_w, int target_format, float* prepared_slots) {
+    GS2D_REQUIRE(p != nullptr, "frame_pipe_set_prepare: null pipe");
+    if (prepared_slots == nullptr) { p->prepared = nullptr; return GS2D_OK; }
+    GS2D_REQUIRE(img_h > 0 && img_w > 0 && ((uintptr_t)prepared_slots & 15) == 0, "frame_pipe_set_prepare: bad arguments");
+    GS2D_REQUIRE(target_format == GS2D_TARGET_F32_CHW || target_format == GS2D_TARGET_U8_HWC ||
+                     target_format == GS2D_TARGET_I420, "frame_pipe_set_prepare: unknown frame format");
+    p->prepared = prepared_slots;
+    p->prepared_bytes = gs2d_fit_target_bytes(img_h, img_w);
+    p->img_h = img_h; p->img_w = img_w; p->target_format = target_format;
     return GS2D_OK;
 }
 
 int gs2d_frame_pipe_acquire(gs2d_frame_pipe* p, int slot, gs2d_stream_t stream, void** device_frame) {
     GS2D_REQUIRE(p && device_frame && slot >= 0 && slot < p->depth, "frame_pipe_acquire: bad argument");
     GS2D_CHECK_CUDA(cudaStreamWaitEvent((cudaStream_t)stream, p->copied[slot], 0));
-    *device_frame = p->slots + (size_t)slot * p->frame_bytes;
+    *device_frame = p->prepared ? (void*)((char*)p->prepared + (size_t)slot * p->prepared_bytes)
+                                : (void*)(p->slots + (size_t)slot * p->frame_bytes);
     return GS2D_OK;
 }
 

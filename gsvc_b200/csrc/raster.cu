@@ -222,6 +222,7 @@ k_raster_bwd_tiles(int W, int H, int tx, const int32_t* __restrict__ tile_bins, 
         const uint32_t rect = __float_as_uint(q1.z);
         const int rx0 = rect & 255, rx1 = (rect >> 8) & 255, ry0 = (rect >> 16) & 255, ry1 = rect >> 24;
         const bool live = (r0 + sub < nb) && ry1 >= ry0;
+        GS2D_ASSERT(!live || (rx0 <= rx1 && rx1 < GS2D_TILE && ry1 < GS2D_TILE));
         const int h = live ? ry1 - ry0 + 1 : 0;
         const int ncol = live ? ((rx1 - rx0) >> 3) + 1 : 0;   // column blocks of 8: 1 or 2
         int max_iters = h * ncol;

@@ -631,11 +631,12 @@ class FusedFrameFit(torch.nn.Module):
                 if rec[5] != step:
                     raise RuntimeError(f"step {step} finished without reporting")
 
-    def _frame_pipe(self, frame_bytes: int, depth: int):
+    def _frame_pipe(self, frame_bytes: int, depth: int, fmt: int | None = None):
         """the library's frame pipe (include/gs2d.h) and its ring of device slots, created once per
         model and frame size (a copy stream + 2*depth events: ~0.1 ms that a short stream of frames
         would otherwise pay on every call)"""
-        key = (int(frame_bytes), int(depth))
+        prep = fmt if (fmt is not None and self.prepare_targets) else None
+        key = (int(frame_bytes), int(depth), prep)
         if self.__dict__.get("_pipe_key") != key:
             self._drop_frame_pipe()
             ct = self._ctypes
@@ -646,6 +647,12 @@ class FusedFrameFit(torch.nn.Module):
                                 "frame_pipe_create")
             d = self.__dict__
             d["_pipe"], d["_pipe_key"], d["_pipe_slots"] = pipe, key, slots
+            if prep is not None:
+                # the frames are converted into the tile kernel's own order on the copy stream as well
+                nb = int(self._cdll.gs2d_fit_target_bytes(self.H, self.W))
+                d["_pipe_prepared"] = torch.empty((depth, nb // 4), dtype=torch.float32, device=self.device)
+                self._lib.check(self._cdll.gs2d_frame_pipe_set_prepare(pipe, self.H, self.W, prep,
+                                                                        d["_pipe_prepared"].data_ptr()), "frame_pipe_set_prepare")
         return self.__dict__["_pipe"]
 
     def _drop_frame_pipe(self):
@@ -657,7 +664,7 @@ class FusedFrameFit(torch.nn.Module):
                 self._cdll.gs2d_frame_pipe_destroy(pipe)
             except Exception:   # noqa: BLE001 -- interpreter shutdown
                 pass
-        d["_pipe"], d["_pipe_key"], d["_pipe_slots"] = None, None, None
+        d["_pipe"], d["_pipe_key"], d["_pipe_slots"], d["_pipe_prepared"] = None, None, None, None
 
     def __del__(self):
         try:
@@ -665,7 +672,7 @@ class FusedFrameFit(torch.nn.Module):
         except Exception:   # noqa: BLE001
             pass
 
-    def fit_stream(self, host_frames, prefetch: int = 2, lag: int = 1):
+    def fit_stream(self, host_frames, prefetch: int = 3, lag: int = 1):
         """One iteration per frame of `host_frames` (an iterable of PINNED host targets of one
         format: raw I420 [H*3/2,W], uint8 RGB [H,W,3] or fp32 [1,3,H,W]); yields (loss, psnr) of
         every step, in order.  Frames travel through the library's frame pipe (include/gs2d.h):
@@ -688,7 +695,11 @@ class FusedFrameFit(torch.nn.Module):
         fmt = self._target(first)[1]
         frame_bytes = first.numel() * first.element_size()
         depth = max(2, min(int(prefetch), 8))
-        pipe = self._frame_pipe(frame_bytes, depth)
+        pipe = self._frame_pipe(frame_bytes, depth, fmt)
+        if self.prepare_targets:
+            fmt_in, fmt = fmt, self._lib.TARGET_TILED       # acquire() hands out the converted copy
+        else:
+            fmt_in = fmt
         slot_out, ptr_out = ct.c_int(), ct.c_void_p()
         stream = torch.cuda.current_stream(dev).cuda_stream
         queued, inflight = [], []        # (slot, host frame) copied but not consumed; (step, host frame) issued
@@ -748,7 +759,7 @@ class FusedFrameFit(torch.nn.Module):
                 inflight.clear()
                 queued.clear()
                 self._drop_frame_pipe()
-                pipe = self._frame_pipe(frame_bytes, depth)
+                pipe = self._frame_pipe(frame_bytes, depth, fmt_in)
                 it = itertools.chain(redo, it)
                 refill()
 
@@ -865,7 +876,8 @@ class SpatialFrameFit(FusedFrameFit):
     path_name = "tile-row bands per rank; scatter-pack + tile kernel on the band, gradient rows summed across ranks, replicated update"
 
     def __init__(self, H, W, num_points, device, group=None, bands=None, emulate_world: int = 0,
-                 exchange: str = "nccl", slots: bool = False, own_barrier: bool = True, balance: bool = False, **kw):
+                 exchange: str = "nccl", slots: bool = False, own_barrier: bool = True, balance: bool = False,
+                 remote_scatter: bool = False, **kw):
         """exchange: "nccl" -- one all-reduce call on the gradient rows between the two phases;
         "peer" -- the rows live in symmetric (peer-mapped) memory and the update kernel itself sums
         them over NVLink in rank order after a device-side barrier: no collective kernel, no extra
@@ -880,6 +892,10 @@ class SpatialFrameFit(FusedFrameFit):
             raise NotImplementedError("the prune / add control is not wired into the tile-row split yet")
         self.group = group
         self.own_barrier = bool(own_barrier)     # False: torch's symmetric-memory barrier between two host calls
+        # sharded update only: the update kernel writes the next step's records straight into the slots of
+        # the rank that rasterises each tile (gs2d_grad_exchange.work_peers) instead of every rank
+        # re-projecting all Gaussians to find its band's
+        self.remote_scatter = bool(remote_scatter)
         self.emulate_world = int(emulate_world)
         if exchange not in ("nccl", "peer", "nvls", "sharded"):
             raise ValueError("exchange must be 'nccl', 'peer', 'nvls' or 'sharded'")
@@ -954,8 +970,10 @@ class SpatialFrameFit(FusedFrameFit):
             bases = [int(p) for p in self._par_hdl.buffer_ptrs]
             par = [bases] * 3                                   # rank q's packed rows
             status = [int(p) + lay.off_status for p in self._work_hdl.buffer_ptrs]
-        self._route_ptrs = torch.tensor(par + [status], dtype=torch.int64, device=dev)   # xyz, chol, feat, status
-        self._route_ptr = [self._route_ptrs[k].data_ptr() for k in range(4)]
+        works = [wk.data_ptr() for wk in self._works] if self.emulate_world else [int(p) for p in self._work_hdl.buffer_ptrs]
+        self._route_ptrs = torch.tensor(par + [status, works], dtype=torch.int64, device=dev)   # xyz, chol, feat, status, work
+        self._route_ptr = [self._route_ptrs[k].data_ptr() for k in range(5)]
+        self._band_edges = torch.tensor([b[0] for b in self.bands] + [self.bands[-1][1]], dtype=torch.int32, device=dev)
 
     def _setup_peer_buffers(self):
         dev, n = self.device, self.n
@@ -1002,7 +1020,9 @@ class SpatialFrameFit(FusedFrameFit):
         if self.exchange == "sharded":
             ex.peers, ex.num_peers = self._peer_list_ptr[x], self.world
             ex.shard_begin, ex.shard_end = self.shards[rank_slot if self.emulate_world else self.rank]
-            ex.xyz_peers, ex.chol_peers, ex.feat_peers, ex.status_peers = self._route_ptr
+            ex.xyz_peers, ex.chol_peers, ex.feat_peers, ex.status_peers = self._route_ptr[:4]
+            if self.remote_scatter:
+                ex.work_peers, ex.band_edges = self._route_ptr[4], self._band_edges.data_ptr()
         return ex
 
     def _with_barrier(self, ex):

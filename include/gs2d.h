@@ -364,6 +364,18 @@ typedef struct {
     float* const* chol_peers;
     float* const* feat_peers;
     int32_t* const* status_peers;
+    /* ---- remote scatter (optional, with a sharded update) -----------------------------------------
+     * Without it every rank re-projects ALL Gaussians each step to find the ones that touch its band (the
+     * part of a step that does not shrink with the number of ranks).  With it the update kernel, which
+     * has its shard's new parameters in registers, writes the next step's packed records straight into
+     * the slots of the rank that rasterises each tile: the exchange of the records is an all-to-all fused
+     * into the update kernel (system-scope atomics for the slot claims, plain NVLink stores for the 48-byte
+     * records), and a steady-state step has no scatter kernel at all.
+     *   work_peers   DEVICE array of num_peers pointers: rank q's workspace (all of one layout)
+     *   band_edges   DEVICE int32[num_peers + 1]: rank q rasterises tile rows [band_edges[q], band_edges[q+1])
+     * The report's num_intersects then counts the pairs of this rank's SHARD (over all bands). */
+    void* const* work_peers;
+    const int32_t* band_edges;
     /* ---- cross-rank barrier issued by the library (optional; any peer exchange) -------------------
      * With `barrier_pads` set and both phases in one call, the barrier between GRADS and UPDATE (and,
      * for a sharded update, the one after UPDATE) is a one-warp kernel of this library on the same
@@ -508,6 +520,11 @@ int gs2d_dequantize(int n, const gs2d_quantized_frame* frame, float* xyz_raw, fl
 typedef struct gs2d_frame_pipe gs2d_frame_pipe;
 int gs2d_frame_pipe_create(void* device_slots, size_t frame_bytes, int depth, gs2d_frame_pipe** out);
 int gs2d_frame_pipe_destroy(gs2d_frame_pipe* pipe);
+/* Optional: every pushed frame (of `target_format`: GS2D_TARGET_F32_CHW / _U8_HWC / _I420, img_h x img_w) is
+ * also converted on the copy stream, right behind its copy, into the tile kernel's own order
+ * (gs2d_fit_target_prepare) -- prepared_slots: depth * gs2d_fit_target_bytes(H, W) bytes, caller-owned --
+ * and acquire() then hands out that copy, to be passed with GS2D_TARGET_TILED.  NULL switches it off. */
+int gs2d_frame_pipe_set_prepare(gs2d_frame_pipe* pipe, int img_h, int img_w, int target_format, float* prepared_slots);
 int gs2d_frame_pipe_push(gs2d_frame_pipe* pipe, const void* host_frame, int* slot_out);
 int gs2d_frame_pipe_acquire(gs2d_frame_pipe* pipe, int slot, gs2d_stream_t stream, void** device_frame);
 int gs2d_frame_pipe_release(gs2d_frame_pipe* pipe, int slot, gs2d_stream_t stream);
