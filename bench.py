@@ -645,13 +645,14 @@ def run_spatial(args, rank: int, world: int, dev, flush):
     gt = (synth.target_frame(h, w)[0] * 255).round().to(torch.uint8).permute(1, 2, 0).contiguous().to(dev)
     out = {"workload": f"C5: 3840x2160 synthetic frame, 200k Cholesky Gaussians, tile-row split over {world} GPUs",
            "world": world, "steps": K}
-    # sharded: reduce-scatter of the gradient rows, Adan on the rank's shard, all-gather of the parameters AND the
-    # all-to-all of the next step's records (remote scatter) inside the update kernel; sharded_local_scatter:
-    # the same without the remote scatter (every rank re-projects all Gaussians for its band: what round 1
-    # measured); nccl: replicated update behind one NCCL all-reduce of the gradient rows
-    for exchange in ("sharded", "sharded_local_scatter", "nccl"):
+    # sharded: reduce-scatter of the gradient rows, Adan on the rank's shard and all-gather of the parameters
+    # inside the update kernel over NVLink, every rank scatters its band's records from its local copy;
+    # sharded_remote_scatter: the update kernel also writes the next step's records straight into the owning
+    # rank's slots (an all-to-all by NVLink atomics + stores: measured slower, kept as an option);
+    # nccl: replicated update behind one NCCL all-reduce of the gradient rows
+    for exchange in ("sharded", "sharded_remote_scatter", "nccl"):
         fit = SpatialFrameFit(h, w, n, dev, init=init, exchange=exchange.split("_")[0], balance=True,
-                              remote_scatter=exchange == "sharded")
+                              remote_scatter=exchange == "sharded_remote_scatter")
         fit.train_iters(gt, Wm)
         dist.barrier(); torch.cuda.synchronize(dev)
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -685,12 +686,12 @@ def run_spatial(args, rank: int, world: int, dev, flush):
         d = (ref._params8 - keep._params8).abs()
         out["single_gpu_ms_per_iter"] = ref_ms
         out["loss_single_gpu"] = ref_loss
-        for exchange in ("sharded", "sharded_local_scatter", "nccl"):
+        for exchange in ("sharded", "sharded_remote_scatter", "nccl"):
             out[exchange]["speedup_vs_single_gpu"] = ref_ms / out[exchange]["ms_per_iter"]
             out[exchange]["loss_rel_diff_vs_single_gpu"] = abs(out[exchange]["loss"] - ref_loss) / ref_loss
         out["median_abs_param_diff_vs_single_gpu"] = float(d.median())
         out["parity_ok"] = bool(all(out[x]["params_identical_across_ranks"] and out[x]["loss_rel_diff_vs_single_gpu"] <= 2e-3
-                                    for x in ("sharded", "sharded_local_scatter", "nccl")))
+                                    for x in ("sharded", "sharded_remote_scatter", "nccl")))
     dist.barrier()
     return out if rank == 0 else None
 
