@@ -93,6 +93,7 @@ _SIGNATURES = {
     "gs2d_cov2d_bounds": (c_int, [c_int, _P, _P, _P, _P]),
     "gs2d_scan_scratch_bytes": (c_size_t, [c_int]),
     "gs2d_cumsum_tiles_hit": (c_int, [c_int, _P, _P, _P, _P, _P, c_size_t, _P]),
+    "gs2d_cumsum_tiles_hit_static": (c_int, [c_int, _P, _P, _P, _P, _P]),
     "gs2d_map_intersects": (c_int, [c_int, c_int, _P, _P, _P, _P, c_int, c_int, _P, _P, _P]),
     "gs2d_sort_scratch_bytes": (c_size_t, [c_int]),
     "gs2d_sort_pairs": (c_int, [c_int, _P, _P, _P, _P, c_int, c_int, _P, c_size_t, _P]),

@@ -418,6 +418,8 @@ k_edges_pack(const int32_t* __restrict__ n_dev, int n_static, const uint32_t* __
 // ==========================================================================================
 // host side
 // ==========================================================================================
+#include <mutex>
+
 #include "gs2d_internal.h"
 
 namespace gs2d {
@@ -594,6 +596,63 @@ int gs2d_cumsum_tiles_hit(int n, const int32_t* nth, int32_t* cum, int32_t* tota
                                                                total_host);
     }
     GS2D_CHECK_LAUNCH("cumsum");
+    return GS2D_OK;
+}
+
+// ---- the same scan with its scratch in a file-scope device array: allocates nothing -----------------------
+// (no counterpart in the reference).  The look-back state of
+// k_cumsum -- one 8-byte word per block of 256 values -- lives in g_scan_scratch instead of caller memory:
+// GS2D_CUMSUM_STATIC_MAX_N values at most = 16 384 words = 128 KB, held by every GPU that loads the library
+// until exit.  In host code `g_scan_scratch` is only a stand-in for the symbol, NOT a device address: the
+// address is fetched once per device, with that device current, by cudaGetSymbolAddress.
+constexpr int kStaticScanMaxN = GS2D_CUMSUM_STATIC_MAX_N;
+constexpr int kStaticScanWords = (kStaticScanMaxN + kScanThreads - 1) / kScanThreads;
+static __device__ __align__(256) unsigned long long g_scan_scratch[kStaticScanWords];
+
+constexpr int kMaxDevices = 64;
+static unsigned long long* g_scan_scratch_ptr[kMaxDevices] = {};   // device address of the array, per device
+static std::mutex g_scan_scratch_mu;
+
+static int static_scan_scratch(unsigned long long** out) {
+    int dev = -1;
+    GS2D_CHECK_CUDA(cudaGetDevice(&dev));
+    GS2D_REQUIRE(dev >= 0 && dev < kMaxDevices, "cumsum_static: device index out of range");
+    std::lock_guard<std::mutex> lk(g_scan_scratch_mu);
+    if (g_scan_scratch_ptr[dev] == nullptr) {
+        void* p = nullptr;
+        GS2D_CHECK_CUDA(cudaGetSymbolAddress(&p, g_scan_scratch));   // this device's copy: `dev` is current
+        GS2D_REQUIRE(p != nullptr, "cumsum_static: no address for the scratch symbol");
+        g_scan_scratch_ptr[dev] = (unsigned long long*)p;
+    }
+    *out = g_scan_scratch_ptr[dev];
+    return GS2D_OK;
+}
+
+int gs2d_cumsum_tiles_hit_static(int n, const int32_t* nth, int32_t* cum, int32_t* total_out, int32_t* total_host,
+                                 gs2d_stream_t stream) {
+    GS2D_REQUIRE(n >= 0, "cumsum_static: bad size");
+    if (n > kStaticScanMaxN) {
+        set_error("cumsum_static: n = %d exceeds the built-in scratch (GS2D_CUMSUM_STATIC_MAX_N = %d values); "
+                  "use gs2d_cumsum_tiles_hit with caller-owned scratch", n, kStaticScanMaxN);
+        return GS2D_ERR_ARG;
+    }
+    cudaStream_t s = (cudaStream_t)stream;
+    if (n == 0) {
+        if (total_out) GS2D_CHECK_CUDA(cudaMemsetAsync(total_out, 0, sizeof(int32_t), s));
+        return GS2D_OK;
+    }
+    GS2D_REQUIRE(nth != nullptr && cum != nullptr, "cumsum_static: null pointer");
+    unsigned long long* state = nullptr;
+    const int rc = static_scan_scratch(&state);
+    if (rc != GS2D_OK) return rc;
+    const int blocks = div_up(n, kScanThreads);
+    // the array keeps the previous call's flags: the words this call uses must start at zero
+    GS2D_CHECK_CUDA(cudaMemsetAsync(state, 0, (size_t)blocks * sizeof(unsigned long long), s));
+    {
+        ProfScope ps_(GS2D_STAGE_SCAN_MAP, s);
+        k_cumsum<<<blocks, kScanThreads, 0, s>>>(n, nth, cum, state, total_out, total_host);
+    }
+    GS2D_CHECK_LAUNCH("cumsum_static");
     return GS2D_OK;
 }
 

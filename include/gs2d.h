@@ -103,6 +103,19 @@ int gs2d_cov2d_bounds(int n, const float* cov2d, float* conics, float* radii, gs
 size_t gs2d_scan_scratch_bytes(int n);
 int gs2d_cumsum_tiles_hit(int n, const int32_t* num_tiles_hit, int32_t* cum_tiles_hit, int32_t* total_out,
                           int32_t* total_host, void* scratch, size_t scratch_bytes, gs2d_stream_t stream);
+/* gs2d_cumsum_tiles_hit WITHOUT caller scratch and without any allocation.  No counterpart in the reference:
+ * added for callers that cannot allocate (CUDA graph capture, tight
+ * serving loops, harnesses that forbid cudaMalloc).  The scan's look-back state lives in a file-scope
+ * `static __device__` array of the library (128 KB, held by every GPU that loads the library until exit),
+ * which bounds the size: n <= GS2D_CUMSUM_STATIC_MAX_N, larger n is rejected with GS2D_ERR_ARG and a
+ * clear message.  The entry point calls no cudaMalloc / cudaFree / allocating library routine; it clears
+ * the part of the array it uses (stream-ordered memset) and launches the same kernel as
+ * gs2d_cumsum_tiles_hit, so the results are identical.  ALL calls on a device share the one array:
+ * calls that may overlap on the GPU (different streams without ordering between them) race -- serialise
+ * them, or use gs2d_cumsum_tiles_hit with scratch of your own for the concurrent ones. */
+#define GS2D_CUMSUM_STATIC_MAX_N (1 << 22)
+int gs2d_cumsum_tiles_hit_static(int n, const int32_t* num_tiles_hit, int32_t* cum_tiles_hit, int32_t* total_out,
+                                 int32_t* total_host, gs2d_stream_t stream);
 /* replaces map_gaussian_to_intersects_tensor, bindings.cu:274-313 (forward.cu:100-136).
  * Key = (tile_id << 32) | sign-extended depth bits.  Slots of Gaussians with radii <= 0 are
  * written as zero, matching the reference's zero-initialised outputs. */
