@@ -563,7 +563,12 @@ def main_gpu(args, rank: int, world: int, local_rank: int):
             line["roofline"] = {"kernel": top, "bound": "hbm", "achieved": alg / dur_s / 1e9, "peak": peak,
                                 "unit": "GB/s", "frac": alg / dur_s / 1e9 / peak, "traffic": ncu_capture(top),
                                 "algorithmic_bytes": alg, "avg_launch_us": dur_s * 1e6,
-                                "peak_source": "MEASURED_PEAKS.json hbm_gbs (measured)" if peaks else "fallback 6650"}
+                                "peak_source": "MEASURED_PEAKS.json hbm_gbs (measured)" if peaks else "fallback 6650",
+                                "traffic_note": "algorithmic bytes count the frame at its information content (I420, 1.5 B/pixel); "
+                                                "the resident frame is deliberately kept as prepared fp32 (12 B/pixel = 24.9 MB "
+                                                "of the measured traffic) to take its decode out of every iteration: "
+                                                "bytes traded for instructions on a kernel at ~10 % of HBM bandwidth"
+                                if (top == "fit_tiles" and getattr(fit, "prepare_targets", False)) else None}
             # what actually bounds this kernel: warp instructions issued per second
             # against 4 schedulers x SMs x clock -- instruction count from the committed ncu capture, time live
             inst = ncu_capture(top, "smsp__inst_executed.sum")
