@@ -342,11 +342,22 @@ struct Route {
     const int32_t* band_edges;   // [R + 1]
 };
 
+// Slot mode's per-tile counter packs two counts into its 32 bits: bits 16.. = all (Gaussian, tile) pairs
+// claimed for the tile -- the reference's count: a 257th flags the step, and it is what max_per_tile
+// reports -- and bits 0..15 = the records actually STORED.  With `cull` the pairs whose pixel rectangle
+// inside the tile is empty (pair_rect: no pixel of the tile can pass the alpha test, so the pair adds
+// nothing to the image and gets no gradient; 23 % of the pairs at 1080p / 50k as initialised) are counted
+// but not stored: the tile kernel stages, ranks and walks a quarter fewer records.  While every tile has at
+// most 256 pairs all of them are rendered, so dropping the empty ones cannot change which are -- same results.
+constexpr uint32_t kFillAll = 0x10000u;      // one more pair
+constexpr uint32_t kFillStored = 0x1u;       // ... that also takes a slot
+__device__ __forceinline__ bool rect_is_empty(uint32_t rect) { return (rect >> 24) < ((rect >> 16) & 255u); }
+
 template <bool SLOT>
 __device__ __forceinline__ int scatter_records(const Proj2d& p, int i, float o, float r, float g, float b, int tx,
                                                int row0, int row1, int W, int H, const int32_t* __restrict__ tile_off,
                                                int32_t* tile_fill, float4* __restrict__ packed, int32_t* status,
-                                               int flag_step, const Route& rt = Route()) {
+                                               int flag_step, const Route& rt = Route(), bool cull = false) {
     if (p.nth <= 0) return 0;
     const int ya = max(p.y0, row0), yb = min(p.y1, row1);
     const int bw = p.x1 - p.x0;
@@ -356,11 +367,21 @@ __device__ __forceinline__ int scatter_records(const Proj2d& p, int i, float o, 
     const PairExtent ext = pair_extent(p.cx, p.cy, o, p.conic.x, p.conic.y, p.conic.z);   // once per Gaussian, not per tile
     for (int base = 0; base < nt; base += kScatterBatch) {
         int pos[kScatterBatch];
+        uint32_t rect[kScatterBatch];
         const int xs = x, ys = y;
 #pragma unroll
         for (int k = 0; k < kScatterBatch; ++k) {
             if (base + k < nt) {
-                pos[k] = atomicAdd(&tile_fill[y * tx + x], 1);
+                rect[k] = pair_rect_of(p.cx, p.cy, ext, x * GS2D_TILE, y * GS2D_TILE, W, H);
+                if (SLOT) {
+                    const bool store = !(cull && rect_is_empty(rect[k]));
+                    const uint32_t old = atomicAdd(reinterpret_cast<uint32_t*>(&tile_fill[y * tx + x]),
+                                                   store ? kFillAll + kFillStored : kFillAll);
+                    // (all pairs so far) in the high half decides the overflow; a dropped pair gets position -1
+                    pos[k] = (old >> 16) >= (uint32_t)kSlotStride ? kSlotStride : (store ? (int)(old & 0xffffu) : -1);
+                } else {
+                    pos[k] = atomicAdd(&tile_fill[y * tx + x], 1);
+                }
                 if (++x == p.x1) { x = p.x0; ++y; }
             }
         }
@@ -372,24 +393,23 @@ __device__ __forceinline__ int scatter_records(const Proj2d& p, int i, float o, 
                 size_t at;
                 bool ok = true;
                 if (SLOT) {
-                    ok = pos[k] < kSlotStride;
-                    if (!ok) {
+                    ok = pos[k] >= 0 && pos[k] < kSlotStride;
+                    if (pos[k] >= kSlotStride) {
                         atomicCAS(&status[kStOverflow], 0, -flag_step);
                         for (int q = 0; q < rt.R; ++q)   // sharded update: every rank must stop at this step
                             if (rt.status[q] != status) atomicCAS_system(&rt.status[q][kStOverflow], 0, -flag_step);
                     }
-                    at = (size_t)t * kSlotStride + pos[k];
+                    at = (size_t)t * kSlotStride + (ok ? pos[k] : 0);
                 } else {
                     at = (size_t)tile_off[t] + pos[k];
                     GS2D_ASSERT(pos[k] >= 0 && at < (size_t)tile_off[t + 1]);   // the count kernel saw the same projection
                 }
                 if (ok) {
-                    const uint32_t rect = pair_rect_of(p.cx, p.cy, ext, xr * GS2D_TILE, yr * GS2D_TILE, W, H);
                     // the diagonal conic terms are stored HALVED: sigma = 0.5*(cx dx^2 + cz dy^2) + cy dx dy is
                     // then fma(dy, cy*dx, fma(dx, (cx/2)*dx, ((cz/2)*dy)*dy)) with no separate multiply by 0.5 per
                     // pixel; halving is exact, so every rounding is the reference's
                     packed[3 * at + 0] = make_float4(p.cx, p.cy, 0.5f * p.conic.x, p.conic.y);
-                    packed[3 * at + 1] = make_float4(0.5f * p.conic.z, o, __uint_as_float(rect), __int_as_float(i));
+                    packed[3 * at + 1] = make_float4(0.5f * p.conic.z, o, __uint_as_float(rect[k]), __int_as_float(i));
                     packed[3 * at + 2] = make_float4(r, g, b, __uint_as_float((uint32_t)t));
                 }
                 if (++xr == p.x1) { xr = p.x0; ++yr; }
@@ -413,13 +433,17 @@ __device__ __forceinline__ int scatter_records_remote(const Proj2d& p, int i, fl
     int x = p.x0, y = p.y0, q = 0;
     for (int base = 0; base < nt; base += kScatterBatch) {
         int pos[kScatterBatch];
+        uint32_t rect[kScatterBatch];
         const int xs = x, ys = y, qs = q;
 #pragma unroll
         for (int k = 0; k < kScatterBatch; ++k) {
             if (base + k < nt) {
                 while (y >= rt.band_edges[q + 1]) ++q;     // rows only grow: the owner is found incrementally
-                int32_t* fill = reinterpret_cast<int32_t*>(rt.work[q] + rt.off_tile_count);
-                pos[k] = atomicAdd_system(&fill[y * tx + x], 1);
+                uint32_t* fill = reinterpret_cast<uint32_t*>(rt.work[q] + rt.off_tile_count);
+                rect[k] = pair_rect_of(p.cx, p.cy, ext, x * GS2D_TILE, y * GS2D_TILE, W, H);
+                const bool store = !rect_is_empty(rect[k]);
+                const uint32_t old = atomicAdd_system(&fill[y * tx + x], store ? kFillAll + kFillStored : kFillAll);
+                pos[k] = (old >> 16) >= (uint32_t)kSlotStride ? kSlotStride : (store ? (int)(old & 0xffffu) : -1);
                 if (++x == p.x1) { x = p.x0; ++y; }
             }
         }
@@ -429,12 +453,13 @@ __device__ __forceinline__ int scatter_records_remote(const Proj2d& p, int i, fl
             if (base + k < nt) {
                 while (yr >= rt.band_edges[qr + 1]) ++qr;
                 const int t = yr * tx + xr;
-                if (pos[k] < kSlotStride) {
+                if (pos[k] < 0) {
+                    // empty rectangle: counted, not stored
+                } else if (pos[k] < kSlotStride) {
                     float4* packed = reinterpret_cast<float4*>(rt.work[qr] + rt.off_packed);
                     const size_t at = (size_t)t * kSlotStride + pos[k];
-                    const uint32_t rect = pair_rect_of(p.cx, p.cy, ext, xr * GS2D_TILE, yr * GS2D_TILE, W, H);
                     packed[3 * at + 0] = make_float4(p.cx, p.cy, 0.5f * p.conic.x, p.conic.y);
-                    packed[3 * at + 1] = make_float4(0.5f * p.conic.z, o, __uint_as_float(rect), __int_as_float(i));
+                    packed[3 * at + 1] = make_float4(0.5f * p.conic.z, o, __uint_as_float(rect[k]), __int_as_float(i));
                     packed[3 * at + 2] = make_float4(r, g, b, __uint_as_float((uint32_t)t));
                 } else {
                     atomicCAS(&status[kStOverflow], 0, -flag_step);
@@ -490,7 +515,8 @@ k_fit_scatter(int n, const float* __restrict__ xyz_raw, const float* __restrict_
     if (i < n && !dead) {
         const float r = col.x, g = col.y, b = col.z;
         if (slots)
-            claimed = scatter_records<true>(p, i, o, r, g, b, tx, row0, row1, W, H, nullptr, tile_fill, packed, status, step, rt);
+            claimed = scatter_records<true>(p, i, o, r, g, b, tx, row0, row1, W, H, nullptr, tile_fill, packed, status, step, rt,
+                                            (slots & 2) != 0);
         else
             scatter_records<false>(p, i, o, r, g, b, tx, row0, row1, W, H, tile_off, tile_fill, packed, status, step);
     }
@@ -702,7 +728,8 @@ k_fit_tiles(int W, int H, int tx, int row0, const int32_t* __restrict__ tile_off
     }
     const int of = status[kStOverflow];
     const int lo = slot ? t * kSlotStride : tile_off[t];
-    const int cnt = slot ? tile_fill[t] : tile_off[t + 1] - lo;
+    const uint32_t fill = slot ? (uint32_t)tile_fill[t] : 0u;          // slots: all pairs << 16 | stored records
+    const int cnt = slot ? (int)(fill & 0xffffu) : tile_off[t + 1] - lo;
     if (of != 0) {
         // the workspace overflowed: the step is a no-op.  A render must not hand back stale memory as
         // an image: it is filled with NaN (the operator path reports the overflow lazily)
@@ -747,7 +774,7 @@ k_fit_tiles(int W, int H, int tx, int row0, const int32_t* __restrict__ tile_off
     const bool reset_late = per_warp;
     if (tid == 0 && !reset_late) tile_fill[t] = 0;
     if (tid == 0 && !tile_off && MODE == 0) {
-        atomicMax(&status[kStSlotMax], cnt);   // result unused: a reduction the CTA never waits for
+        atomicMax(&status[kStSlotMax], (int)(fill >> 16));   // result unused: a reduction the CTA never waits for
         if (bx == 0 && by == 0)                                    // the update kernel counts the next step into it
             status[kStSlotIsect + ((step + 1) & 1)] = 0;
     }
@@ -791,7 +818,7 @@ k_fit_tiles(int W, int H, int tx, int row0, const int32_t* __restrict__ tile_off
         if (r_lane < nb) {
             const uint32_t rect = __float_as_uint(sq[3 * r_lane + 1].z);
             const int y0 = (rect >> 16) & 255, y1 = rect >> 24;
-            touch = (y1 >= wrow_lo) && (y0 <= wrow_hi);
+            touch = (y1 >= wrow_lo) && (y0 <= wrow_hi) && (y1 >= y0);   // (an empty rectangle is y0 = 1, y1 = 0)
         }
         unsigned m = __ballot_sync(0xffffffffu, touch);
         while (m) {
@@ -1254,7 +1281,8 @@ k_fit_update(int n, float* __restrict__ xyz_raw, float* __restrict__ chol_raw, f
                 // ... and with fixed slots per tile there is nothing to count or scan first: the records
                 // of the next iteration are written right here (tile_count is the tiles' fill level)
                 claimed = scatter_records<true>(pn, i, 1.f, mulf(par[5], cw), mulf(par[6], cw), mulf(par[7], cw), tx,
-                                                row0, row1, W, H, nullptr, tile_count, packed, status, next_step);
+                                                row0, row1, W, H, nullptr, tile_count, packed, status, next_step, Route(),
+                                                (slots & 2) != 0);
             } else {
                 count_tiles(pn, tx, row0, row1, tile_count);
             }
@@ -1545,6 +1573,11 @@ int gs2d_fit_step_band(int n, int cap, int img_h, int img_w, float* xyz_raw, flo
         }
     }
     const bool sharded = rt.R > 0;
+    // slot mode drops the pairs whose pixel rectangle in the tile is empty (scatter_records); a call that asks
+    // for the rendering order (ids_sorted_out: parity tests) and scatters itself keeps them, so that the list
+    // is the reference's.  GS2D_NO_CULL=1: A/B runs.
+    static const bool no_cull = [] { const char* e = getenv("GS2D_NO_CULL"); return e && e[0] == '1'; }();
+    const int cull_bit = no_cull ? 0 : 2;
     float* rgb_w = nullptr; float* adan_w = nullptr; float* rgb_w_grad_out = nullptr;
     QuantConst src = QuantConst();   // row strides of the parameter tensors (packed rows: 8 / 8 / 8)
     int adan_step = step, adan_fresh = step == 1, skip_update = 0, slots = 0, analytic = 0, all_per_tile = 0;
@@ -1586,8 +1619,8 @@ int gs2d_fit_step_band(int n, int cap, int img_h, int img_w, float* xyz_raw, flo
                 }
                 k_fit_scatter<<<div_up(n, kFitThreads), kFitThreads, 0, s>>>(
                     n, xyz_raw, chol_raw, features, nullptr, rgb_w, 1, half_w, half_h, tx, ty, row0, row1, img_w, img_h,
-                    nullptr, (int32_t*)(w + L.off_tile_count), status, (float4*)(w + L.off_packed), 1, step, src,
-                    rt);
+                    nullptr, (int32_t*)(w + L.off_tile_count), status, (float4*)(w + L.off_packed),
+                    1 | (ids_sorted_out ? 0 : cull_bit), step, src, rt);
                 GS2D_CHECK_LAUNCH("fit_scatter_slots");
             }
         } else {
@@ -1645,7 +1678,7 @@ int gs2d_fit_step_band(int n, int cap, int img_h, int img_w, float* xyz_raw, flo
             loss + (step % GS2D_FIT_LOSS_SLOTS), loss + ((step + 1) % GS2D_FIT_LOSS_SLOTS), param_grads_out, cap,
             step + 1, (int32_t*)(w + L.off_tile_count), (int32_t*)(w + L.off_tile_off), report_host, row0, row1,
             banded ? 1 : 0, peer_grads, num_peers, grads_zero, rgb_w, adan_w, rgb_w_grad_out, skip_update,
-            mc_grads, slots, (float4*)(w + L.off_packed), img_w, img_h, shard_begin, shard_end, rt));
+            mc_grads, slots ? (1 | cull_bit) : 0, (float4*)(w + L.off_packed), img_w, img_h, shard_begin, shard_end, rt));
         GS2D_CHECK_LAUNCH("fit_update");
     }
     if (own_barrier && sharded) {   // the peers' stores into this rank's parameters precede its next scatter

@@ -63,7 +63,7 @@ k_raster_fwd(int W, int H, int tx, const int32_t* __restrict__ tile_bins, const 
         if (k_lane < nb) {
             const uint32_t rect = __float_as_uint(sq[3 * k_lane + 1].z);
             const int y0 = (rect >> 16) & 255, y1 = rect >> 24;
-            touch = (y1 >= row_lo) && (y0 <= row_hi);
+            touch = (y1 >= row_lo) && (y0 <= row_hi) && (y1 >= y0);   // (empty rectangle: y0 = 1, y1 = 0)
         }
         unsigned m = __ballot_sync(0xffffffffu, touch);
         while (m) {
@@ -348,7 +348,7 @@ k_raster_nd_fwd(int W, int H, int tx, int C, int max_tile, const int32_t* __rest
             if (k_lane < nb) {
                 const uint32_t rect = __float_as_uint(sq[3 * k_lane + 1].z);
                 const int y0 = (rect >> 16) & 255, y1 = rect >> 24;
-                touch = (y1 >= row_lo) && (y0 <= row_hi);
+                touch = (y1 >= row_lo) && (y0 <= row_hi) && (y1 >= y0);   // (empty rectangle: y0 = 1, y1 = 0)
             }
             unsigned m = __ballot_sync(0xffffffffu, touch);
             while (m) {

@@ -433,7 +433,13 @@ typedef struct {
  *                        record makes the step a no-op like a cap overflow, reported as a NEGATIVE
  *                        overflow_step: re-initialise the workspace and continue with slots = 0
  *                        (only ranges can tell WHICH 256 ids a fuller tile renders).  ids_sorted_out
- *                        is then indexed by slot (t*256 + rank). */
+ *                        is then indexed by slot (t*256 + rank).  Pairs whose pixel rectangle inside the
+ *                        tile is empty (no pixel of the tile can pass the alpha test: they add nothing to
+ *                        the image and get no gradient) are counted -- num_intersects, max_per_tile and the
+ *                        257th-pair rule see every pair, like the reference -- but take no slot: the tile
+ *                        kernel walks a quarter fewer records, same results.  Only a call that scatters
+ *                        itself (precounted == 0) AND passes ids_sorted_out stores them all, so that the
+ *                        list it returns is the reference's. */
 typedef struct {
     float* rgb_w;
     float* adan_state_w;
