@@ -23,6 +23,7 @@
 //
 // The count/scatter/tile kernels without the loss and backward are the render-only path.
 #include <cuda_fp16.h>
+#include <type_traits>
 
 #include "gs2d_internal.h"
 #include "gs2d_math.cuh"
@@ -192,10 +193,17 @@ __device__ __forceinline__ float3 fit_colour(int i, const float* __restrict__ fe
 // ------------------------------------------------------------------------------------------
 // [row0, row1): the band of tile rows this rank rasterises (the whole frame unless the frame is
 // split across GPUs by tile rows, SURVEY 8e spatial mode)
-__device__ __forceinline__ void count_tiles(const Proj2d& p, int tx, int row0, int row1, int32_t* tile_count) {
-    if (p.nth > 0)
-        for (int y = max(p.y0, row0); y < min(p.y1, row1); ++y)
-            for (int x = p.x0; x < p.x1; ++x) atomicAdd(&tile_count[y * tx + x], 1);
+// (first, stride): the tiles of the Gaussian's bbox are numbered row by row; this call takes numbers first,
+// first + stride, ... -- several lanes can share one Gaussian's tiles
+__device__ __forceinline__ void count_tiles(const Proj2d& p, int tx, int row0, int row1, int32_t* tile_count,
+                                            int first = 0, int stride = 1) {
+    if (p.nth <= 0) return;
+    const int ya = max(p.y0, row0), yb = min(p.y1, row1), bw = p.x1 - p.x0;
+    const int nt = (yb - ya) * bw;
+    for (int j = first; j < nt; j += stride) {
+        const int dy = j / bw;
+        atomicAdd(&tile_count[(ya + dy) * tx + p.x0 + (j - dy * bw)], 1);
+    }
 }
 
 // Called by every thread of every block after its count_tiles(): the last block to arrive turns
@@ -353,43 +361,47 @@ constexpr uint32_t kFillAll = 0x10000u;      // one more pair
 constexpr uint32_t kFillStored = 0x1u;       // ... that also takes a slot
 __device__ __forceinline__ bool rect_is_empty(uint32_t rect) { return (rect >> 24) < ((rect >> 16) & 255u); }
 
-template <bool SLOT>
+template <bool SLOT, int BATCH = kScatterBatch>
 __device__ __forceinline__ int scatter_records(const Proj2d& p, int i, float o, float r, float g, float b, int tx,
                                                int row0, int row1, int W, int H, const int32_t* __restrict__ tile_off,
                                                int32_t* tile_fill, float4* __restrict__ packed, int32_t* status,
-                                               int flag_step, const Route& rt = Route(), bool cull = false) {
+                                               int flag_step, const Route& rt = Route(), bool cull = false,
+                                               int first = 0, int stride = 1) {
+    // (first, stride): as count_tiles -- this call handles the bbox's tiles number first, first + stride, ...
     if (p.nth <= 0) return 0;
     const int ya = max(p.y0, row0), yb = min(p.y1, row1);
     const int bw = p.x1 - p.x0;
     const int nt = (yb - ya) * bw;
-    if (nt <= 0) return 0;
-    int x = p.x0, y = ya;
+    if (nt <= first) return 0;
+    int mine = 0;
     const PairExtent ext = pair_extent(p.cx, p.cy, o, p.conic.x, p.conic.y, p.conic.z);   // once per Gaussian, not per tile
-    for (int base = 0; base < nt; base += kScatterBatch) {
-        int pos[kScatterBatch];
-        uint32_t rect[kScatterBatch];
-        const int xs = x, ys = y;
+    for (int base = first; base < nt; base += BATCH * stride) {
+        int pos[BATCH], tid_[BATCH];
+        uint32_t rect[BATCH];
 #pragma unroll
-        for (int k = 0; k < kScatterBatch; ++k) {
-            if (base + k < nt) {
+        for (int k = 0; k < BATCH; ++k) {
+            const int j = base + k * stride;
+            if (j < nt) {
+                const int dy = j / bw;
+                const int x = p.x0 + (j - dy * bw), y = ya + dy;
+                tid_[k] = y * tx + x;
+                ++mine;
                 rect[k] = pair_rect_of(p.cx, p.cy, ext, x * GS2D_TILE, y * GS2D_TILE, W, H);
                 if (SLOT) {
                     const bool store = !(cull && rect_is_empty(rect[k]));
-                    const uint32_t old = atomicAdd(reinterpret_cast<uint32_t*>(&tile_fill[y * tx + x]),
+                    const uint32_t old = atomicAdd(reinterpret_cast<uint32_t*>(&tile_fill[tid_[k]]),
                                                    store ? kFillAll + kFillStored : kFillAll);
                     // (all pairs so far) in the high half decides the overflow; a dropped pair gets position -1
                     pos[k] = (old >> 16) >= (uint32_t)kSlotStride ? kSlotStride : (store ? (int)(old & 0xffffu) : -1);
                 } else {
-                    pos[k] = atomicAdd(&tile_fill[y * tx + x], 1);
+                    pos[k] = atomicAdd(&tile_fill[tid_[k]], 1);
                 }
-                if (++x == p.x1) { x = p.x0; ++y; }
             }
         }
-        int xr = xs, yr = ys;
 #pragma unroll
-        for (int k = 0; k < kScatterBatch; ++k) {
-            if (base + k < nt) {
-                const int t = yr * tx + xr;
+        for (int k = 0; k < BATCH; ++k) {
+            if (base + k * stride < nt) {
+                const int t = tid_[k];
                 size_t at;
                 bool ok = true;
                 if (SLOT) {
@@ -412,11 +424,10 @@ __device__ __forceinline__ int scatter_records(const Proj2d& p, int i, float o, 
                     packed[3 * at + 1] = make_float4(0.5f * p.conic.z, o, __uint_as_float(rect[k]), __int_as_float(i));
                     packed[3 * at + 2] = make_float4(r, g, b, __uint_as_float((uint32_t)t));
                 }
-                if (++xr == p.x1) { xr = p.x0; ++yr; }
             }
         }
     }
-    return nt;
+    return mine;
 }
 
 // scatter_records<true> across ranks: tile (x, y) belongs to the rank whose band holds row y; its fill
@@ -1320,6 +1331,226 @@ k_fit_update(int n, float* __restrict__ xyz_raw, float* __restrict__ chol_raw, f
     scan_tiles_by_last_block(tx, ty, cap, next_step, tile_count, tile_off, status, sh, &s_last);
 }
 
+// The same update with FOUR lanes per Gaussian (packed [n][8] rows only).  One thread per Gaussian is one
+// dependent chain of ~1 500 instructions on ~10 warps per SM: latency-bound (round 1: 22 % issue-active).
+// Here lane q of a quad runs Adan on parameters 2q, 2q+1 (their state rows are read and written as float2:
+// four lanes cover a Gaussian's 32 bytes), every lane recomputes the cheap shared parts (projection of the
+// old parameters for the backward, of the new ones for the binning), the new parameters are exchanged by
+// shuffles inside the quad, and the next step's tiles are shared out over the four lanes (tile j goes to
+// lane j mod 4) so that the slot claims of a Gaussian are in flight together.  Same arithmetic per element,
+// hence the same bits as k_fit_update<true>; the learnable colour weight rides on lane 0.
+__device__ __forceinline__ float pick4(int q, float a, float b, float c, float d) {
+    return q == 0 ? a : (q == 1 ? b : (q == 2 ? c : d));
+}
+
+#ifndef GS2D_UPDATE_LANES
+#define GS2D_UPDATE_LANES 2   // measured at C2 (adan stage): 1 lane 18.4 us, 4 lanes 16.1, 2 lanes 14.8 (one wave at 85 registers)
+#endif
+constexpr int kUpdateLanes = GS2D_UPDATE_LANES;
+#ifndef GS2D_QUAD_MIN_BLOCKS
+#define GS2D_QUAD_MIN_BLOCKS 6   // 85 registers: 24 warps per SM (measured: 16.6 us against 18.8 at the compiler's own 96)
+#endif
+// MULTI = false: the single-GPU instantiation carries none of the cross-rank paths (peer / switch reads of the
+// gradient rows, parameter stores into peers, remote scatter).  The kernel executes every instruction once
+// per warp, so its time is instruction FETCH as much as anything (round 2: 44 % of the one-thread kernel's
+// stall samples were "no instruction", 7 300 SASS instructions): less code is less time.
+// LANES = 4 or 2 lanes per Gaussian: lane q owns parameters [q*K, q*K + K), K = 8 / LANES
+template <bool MULTI, int LANES>
+__global__ void __launch_bounds__(kFitThreads, GS2D_QUAD_MIN_BLOCKS)
+k_fit_update_quad(int n, float* __restrict__ params8, float* __restrict__ adan, float* __restrict__ grads, float half_w,
+                  float half_h, int tx, int ty, AdanHyper h, int32_t* status, const double* loss_this, double* loss_next,
+                  float* __restrict__ grads_out, int cap, int next_step, int32_t* tile_count,
+                  int32_t* __restrict__ tile_off, gs2d_fit_report* report_host, int row0, int row1, int loss_in_grads,
+                  const float* const* __restrict__ peer_grads, int num_peers, float* __restrict__ grads_zero,
+                  float* __restrict__ rgb_w, float* __restrict__ adan_w, float* __restrict__ rgb_w_grad_out,
+                  int skip_update, const float* __restrict__ mc_grads, int slots, float4* __restrict__ packed, int W,
+                  int H, int shard_begin, int shard_end, Route rt) {
+    __shared__ int sh[8];
+    __shared__ int s_last;
+    const int gtid = blockIdx.x * kFitThreads + threadIdx.x;
+    constexpr int K = 8 / LANES;                  // parameters per lane
+    static_assert(LANES == 2 || LANES == 4, "two or four lanes per Gaussian");
+    const int q = gtid & (LANES - 1);             // lane of the group: parameters q*K .. q*K + K - 1
+    const int i = shard_begin + gtid / LANES;
+    const bool act = i < shard_end;
+    const unsigned full = 0xffffffffu;
+    const float4* p8 = reinterpret_cast<const float4*>(params8);
+    // ---- prologue (runs under the tile kernel's tail, see k_fit_update) ----------------------------
+    Proj2d p; float2 m = make_float2(0.f, 0.f); float3 L = make_float3(1.f, 0.f, 1.f);
+    float par[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    __align__(16) float am[K] = {}, an[K] = {}, ad[K] = {}, ap[K] = {};
+    typedef typename std::conditional<K == 2, float2, float4>::type VecK;   // a lane's K floats as one access
+    float cw = 1.f, wm = 0.f, wn = 0.f, wd = 0.f, wp = 0.f;
+    const size_t plane = (size_t)n * 8;
+    const size_t so = (size_t)(act ? i : 0) * 8 + K * q;   // this lane's share of a state / parameter row
+    p.ok = false; p.radius = 0.f; p.nth = 0; p.conic = make_float3(0.f, 0.f, 0.f);
+    if (act) {
+        *reinterpret_cast<float4*>(par) = p8[2 * (size_t)i];
+        *reinterpret_cast<float4*>(par + 4) = p8[2 * (size_t)i + 1];
+        m = make_float2(tanhf(par[0]), tanhf(par[1]));
+        L = make_float3(addf(par[2], 0.5f), addf(par[3], 0.f), addf(par[4], 0.5f));
+        project_chol(m.x, m.y, L.x, L.y, L.z, half_w, half_h, tx, ty, p);
+        if (!skip_update) {
+            *reinterpret_cast<VecK*>(am) = *reinterpret_cast<const VecK*>(adan + so);
+            *reinterpret_cast<VecK*>(an) = *reinterpret_cast<const VecK*>(adan + plane + so);
+            *reinterpret_cast<VecK*>(ad) = *reinterpret_cast<const VecK*>(adan + 2 * plane + so);
+            *reinterpret_cast<VecK*>(ap) = *reinterpret_cast<const VecK*>(adan + 3 * plane + so);
+        }
+        if (rgb_w) {
+            cw = rgb_w[i];
+            if (!skip_update && q == 0) { wm = adan_w[i]; wn = adan_w[(size_t)n + i]; wd = adan_w[2 * (size_t)n + i]; wp = adan_w[3 * (size_t)n + i]; }
+        }
+    }
+    pdl_wait();
+    pdl_release();
+    // the local gradient row is requested together with the status word (one round trip, not two)
+    float4 g0 = make_float4(0.f, 0.f, 0.f, 0.f), g1 = g0;   // v_xy(2) v_conic(3) v_rgb(3) | v_opacity(1) pad(3)
+    const bool local_row = !MULTI || (!mc_grads && num_peers == 0);
+    if (act && local_row) {
+        const float4* grow = reinterpret_cast<const float4*>(grads + (size_t)i * 12);
+        g0 = grow[0]; g1 = grow[1];
+    }
+    const int of = status[kStOverflow];
+    const bool dead = of != 0 && abs(of) < next_step;
+    if (gtid == 0 && report_host) {
+        double ls = *loss_this;
+        if (loss_in_grads) {
+            if (MULTI && mc_grads) {
+                ls = (double)multimem_sum1(mc_grads + 9);
+            } else if (MULTI && num_peers > 0) {
+                float acc = 0.f;
+                for (int r = 0; r < num_peers; ++r) acc += __ldcg(peer_grads[r] + 9);
+                ls = (double)acc;
+            } else {
+                ls = (double)grads[9];
+            }
+        }
+        report_host->loss_sum = ls;
+        report_host->num_intersects = slots ? status[kStSlotIsect + ((next_step - 1) & 1)] : status[kStNumIntersects];
+        report_host->overflow_step = of;
+        report_host->max_per_tile = slots ? status[kStSlotMax] : status[kStMaxPerTile];
+        if (slots) status[kStSlotMax] = 0;
+        __threadfence_system();
+        report_host->step = next_step - 1;
+        __threadfence_system();
+    }
+    if (dead) return;                              // uniform over the grid (see k_fit_update)
+    if (gtid == 0 && loss_next) *loss_next = 0.0;
+    if (MULTI && rt.R > 0 && grads_zero) {
+        const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
+        float4* zb = reinterpret_cast<float4*>(grads_zero);
+        for (size_t k = gtid; k < (size_t)n * 3; k += (size_t)gridDim.x * kFitThreads) zb[k] = z;
+    }
+    int claimed = 0;
+    float g[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    float gw = 0.f;
+    if (act) {
+        if (MULTI && mc_grads) {   // (the group's lanes read the same row)
+            g0 = multimem_sum4(mc_grads + (size_t)i * 12);
+            g1 = multimem_sum4(mc_grads + (size_t)i * 12 + 4);
+        } else if (MULTI && num_peers > 0) {
+            g0 = make_float4(0.f, 0.f, 0.f, 0.f);
+            g1 = g0;
+            for (int r0 = 0; r0 < num_peers; r0 += 4) {
+                float4 a[4], b[4];
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                    if (r0 + k < num_peers) {
+                        const float4* prow = reinterpret_cast<const float4*>(peer_grads[r0 + k] + (size_t)i * 12);
+                        a[k] = __ldcg(prow); b[k] = __ldcg(prow + 1);
+                    }
+                }
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                    if (r0 + k < num_peers) {
+                        g0.x += a[k].x; g0.y += a[k].y; g0.z += a[k].z; g0.w += a[k].w;
+                        g1.x += b[k].x; g1.y += b[k].y; g1.z += b[k].z; g1.w += b[k].w;
+                    }
+                }
+            }
+        }
+        g[5] = g1.y; g[6] = g1.z; g[7] = g1.w;
+        if (rgb_w) {
+            gw = g1.y * par[5] + g1.z * par[6] + g1.w * par[7];
+            g[5] = g1.y * cw; g[6] = g1.z * cw; g[7] = g1.w * cw;
+            if (rgb_w_grad_out && q == 0) rgb_w_grad_out[i] = gw;
+        }
+        if (p.ok && (int)p.radius > 0) {   // backward2d.cu:23-25
+            const float3 vc = conic_vjp(p.conic, make_float3(g0.z, g0.w, g1.x));
+            const float3 vl = chol_vjp(L.x, L.y, L.z, vc, h.offdiag);
+            const float vmx = g0.x * half_w, vmy = g0.y * half_h;            // backward2d.cu:48-49
+            g[0] = vmx * (1.f - m.x * m.x);                                   // d tanh
+            g[1] = vmy * (1.f - m.y * m.y);
+            g[2] = vl.x; g[3] = vl.y; g[4] = vl.z;
+        }
+    }
+    // every lane of the warp has loaded its row: now the row may be re-zeroed (16 bytes per lane).
+    // The barrier orders the group's loads before the stores, whichever lane is ahead.
+    __syncwarp();
+    if (act && (!MULTI || rt.R == 0)) {
+        float4* zrow = reinterpret_cast<float4*>((grads_zero ? grads_zero : grads) + (size_t)i * 12);
+        const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (LANES == 4) { if (q < 3) zrow[q] = z; }
+        else { zrow[q] = z; if (q == 0) zrow[2] = z; }
+    }
+    __align__(16) float gm[K], pm[K];              // this lane's gradients and parameters
+#pragma unroll
+    for (int k = 0; k < K; ++k) {
+        gm[k] = LANES == 4 ? pick4(q, g[k], g[K + k], g[2 * K + k], g[3 * K + k]) : (q == 0 ? g[k] : g[K + k]);
+        pm[k] = LANES == 4 ? pick4(q, par[k], par[K + k], par[2 * K + k], par[3 * K + k]) : (q == 0 ? par[k] : par[K + k]);
+    }
+    if (act && grads_out) *reinterpret_cast<VecK*>(grads_out + (size_t)i * 8 + K * q) = *reinterpret_cast<VecK*>(gm);
+    if (skip_update) return;                       // uniform over the grid
+    if (act) {
+#pragma unroll
+        for (int k = 0; k < K; ++k) pm[k] = adan_one(pm[k], gm[k], am[k], an[k], ad[k], ap[k], h);
+        *reinterpret_cast<VecK*>(adan + so) = *reinterpret_cast<VecK*>(am);
+        *reinterpret_cast<VecK*>(adan + plane + so) = *reinterpret_cast<VecK*>(an);
+        *reinterpret_cast<VecK*>(adan + 2 * plane + so) = *reinterpret_cast<VecK*>(ad);
+        *reinterpret_cast<VecK*>(adan + 3 * plane + so) = *reinterpret_cast<VecK*>(ap);
+        *reinterpret_cast<VecK*>(params8 + so) = *reinterpret_cast<VecK*>(pm);
+        for (int z = 0; MULTI && z < rt.R; ++z) {  // sharded update: the all-gather is these NVLink stores
+            float* pq = rt.xyz[z];
+            if (pq != params8) *reinterpret_cast<VecK*>(pq + so) = *reinterpret_cast<VecK*>(pm);
+        }
+        if (rgb_w && q == 0) {
+            cw = adan_one(cw, gw, wm, wn, wd, wp, h);
+            rgb_w[i] = cw;
+            adan_w[i] = wm; adan_w[(size_t)n + i] = wn; adan_w[2 * (size_t)n + i] = wd; adan_w[3 * (size_t)n + i] = wp;
+        }
+    }
+    // the quad's eight new parameters (and the new colour weight) to every lane of it
+    float np[8];
+#pragma unroll
+    for (int l = 0; l < LANES; ++l)
+#pragma unroll
+        for (int k = 0; k < K; ++k) np[l * K + k] = __shfl_sync(full, pm[k], l, LANES);
+    cw = __shfl_sync(full, cw, 0, LANES);
+    if (act && (!MULTI || rt.R == 0 || rt.work)) {
+        Proj2d pn;
+        project_chol(tanhf(np[0]), tanhf(np[1]), addf(np[2], 0.5f), addf(np[3], 0.f), addf(np[4], 0.5f), half_w, half_h,
+                     tx, ty, pn);
+        const float cr = mulf(np[5], cw), cg = mulf(np[6], cw), cb = mulf(np[7], cw);
+        if (MULTI && rt.R > 0) {                   // remote scatter (option): one lane walks the owners in order
+            if (q == 0) claimed = scatter_records_remote(pn, i, 1.f, cr, cg, cb, tx, W, H, status, next_step, rt);
+        } else if (slots) {
+            claimed = scatter_records<true, 8 / LANES>(pn, i, 1.f, cr, cg, cb, tx, row0, row1, W, H, nullptr, tile_count,
+                                                       packed, status, next_step, Route(), (slots & 2) != 0, q, LANES);
+        } else {
+            count_tiles(pn, tx, row0, row1, tile_count, q, LANES);
+        }
+    }
+    if (MULTI && rt.R > 0) {
+        if (rt.work) block_add(claimed, &status[kStSlotIsect + (next_step & 1)], sh);
+        return;
+    }
+    if (slots) {
+        block_add(claimed, &status[kStSlotIsect + (next_step & 1)], sh);
+        return;
+    }
+    scan_tiles_by_last_block(tx, ty, cap, next_step, tile_count, tile_off, status, sh, &s_last);
+}
+
 // Cross-rank barrier on the stream (include/gs2d.h, gs2d_grad_exchange.barrier_pads): one warp, lane
 // q signals rank q and waits for rank q.  The kernels before it on this stream have completed, so
 // their writes (local REDs, stores into peer memory) precede the fence; the release / acquire pair
@@ -1672,6 +1903,16 @@ int gs2d_fit_step_band(int n, int cap, int img_h, int img_w, float* xyz_raw, flo
         h.first = adan_fresh;
         h.offdiag = analytic ? 1.f : 2.f;
         ProfScope ps_(GS2D_STAGE_ADAN, s);
+        static const bool no_quad = [] { const char* e = getenv("GS2D_NO_QUAD"); return e && e[0] == '1'; }();   // A/B runs
+        if (src.ld_xyz == 8 && !no_quad)
+            GS2D_CHECK_CUDA(launch_pdl((exchange || rt.R > 0) ? k_fit_update_quad<true, kUpdateLanes> : k_fit_update_quad<false, kUpdateLanes>,
+                dim3(div_up((long long)kUpdateLanes * (shard_end - shard_begin), kFitThreads)),
+                dim3(kFitThreads), s, n, xyz_raw, adan_state, grads, half_w, half_h, tx, ty, h, status,
+                loss + (step % GS2D_FIT_LOSS_SLOTS), loss + ((step + 1) % GS2D_FIT_LOSS_SLOTS), param_grads_out, cap,
+                step + 1, (int32_t*)(w + L.off_tile_count), (int32_t*)(w + L.off_tile_off), report_host, row0, row1,
+                banded ? 1 : 0, peer_grads, num_peers, grads_zero, rgb_w, adan_w, rgb_w_grad_out, skip_update,
+                mc_grads, slots ? (1 | cull_bit) : 0, (float4*)(w + L.off_packed), img_w, img_h, shard_begin, shard_end, rt));
+        else
         GS2D_CHECK_CUDA(launch_pdl(src.ld_xyz == 8 ? k_fit_update<true> : k_fit_update<false>,
             dim3(div_up(shard_end - shard_begin, kFitThreads)), dim3(kFitThreads), s,
             n, xyz_raw, chol_raw, features, adan_state, grads, half_w, half_h, tx, ty, h, status,
