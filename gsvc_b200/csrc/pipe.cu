@@ -13,7 +13,11 @@ struct gs2d_frame_pipe {
     size_t frame_bytes;
     int depth;
     int next;
-    cudaStream_t copy_stream;
+    unsigned pushes;
+    // two copy streams, used alternately: the set-up of one frame's DMA runs under the other's transfer
+    // (a 3 MB frame is ~58 us of PCIe time and ~5 us of per-copy latency that back-to-back copies on ONE
+    // stream expose: the link, not the GPU, bounds a stream of 1080p frames)
+    cudaStream_t copy_streams[2];
     cudaEvent_t copied[GS2D_PIPE_MAX_DEPTH];
     cudaEvent_t freed[GS2D_PIPE_MAX_DEPTH];
     bool has_consumer[GS2D_PIPE_MAX_DEPTH];
@@ -41,9 +45,11 @@ int gs2d_frame_pipe_create(void* device_slots, size_t frame_bytes, int depth, gs
     p->frame_bytes = frame_bytes;
     p->depth = depth;
     p->next = 0;
+    p->pushes = 0;
     p->prepared = nullptr;
     p->prepared_bytes = 0;
-    cudaError_t e = cudaStreamCreateWithFlags(&p->copy_stream, cudaStreamNonBlocking);
+    cudaError_t e = cudaStreamCreateWithFlags(&p->copy_streams[0], cudaStreamNonBlocking);
+    if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&p->copy_streams[1], cudaStreamNonBlocking);
     if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&p->prep_stream, cudaStreamNonBlocking);
     for (int i = 0; i < depth && e == cudaSuccess; ++i) {
         p->has_consumer[i] = false;
@@ -62,14 +68,16 @@ int gs2d_frame_pipe_create(void* device_slots, size_t frame_bytes, int depth, gs
 
 int gs2d_frame_pipe_destroy(gs2d_frame_pipe* p) {
     if (!p) return GS2D_OK;
-    cudaStreamSynchronize(p->copy_stream);
+    cudaStreamSynchronize(p->copy_streams[0]);
+    cudaStreamSynchronize(p->copy_streams[1]);
     cudaStreamSynchronize(p->prep_stream);
     for (int i = 0; i < p->depth; ++i) {
         cudaEventDestroy(p->arrived[i]);
         cudaEventDestroy(p->copied[i]);
         cudaEventDestroy(p->freed[i]);
     }
-    cudaStreamDestroy(p->copy_stream);
+    cudaStreamDestroy(p->copy_streams[0]);
+    cudaStreamDestroy(p->copy_streams[1]);
     cudaStreamDestroy(p->prep_stream);
     delete p;
     return GS2D_OK;
@@ -79,13 +87,14 @@ int gs2d_frame_pipe_push(gs2d_frame_pipe* p, const void* host_frame, int* slot_o
     GS2D_REQUIRE(p && host_frame && slot_out, "frame_pipe_push: null argument");
     const int b = p->next;
     p->next = (b + 1) % p->depth;
-    if (p->has_consumer[b]) GS2D_CHECK_CUDA(cudaStreamWaitEvent(p->copy_stream, p->freed[b], 0));
+    cudaStream_t cs = p->copy_streams[p->pushes++ & 1];
+    if (p->has_consumer[b]) GS2D_CHECK_CUDA(cudaStreamWaitEvent(cs, p->freed[b], 0));
     GS2D_CHECK_CUDA(cudaMemcpyAsync(p->slots + (size_t)b * p->frame_bytes, host_frame, p->frame_bytes,
-                                    cudaMemcpyHostToDevice, p->copy_stream));
+                                    cudaMemcpyHostToDevice, cs));
     if (p->prepared) {
         // third stage: the copy stream goes straight on to the next frame while this one is converted
         // (copy of frame i+2 | conversion of frame i+1 | fit step of frame i)
-        GS2D_CHECK_CUDA(cudaEventRecord(p->arrived[b], p->copy_stream));
+        GS2D_CHECK_CUDA(cudaEventRecord(p->arrived[b], cs));
         GS2D_CHECK_CUDA(cudaStreamWaitEvent(p->prep_stream, p->arrived[b], 0));
         const int rc = gs2d_fit_target_prepare(p->img_h, p->img_w, p->slots + (size_t)b * p->frame_bytes, p->target_format,
                                                (float*)((char*)p->prepared + (size_t)b * p->prepared_bytes),
@@ -93,7 +102,7 @@ int gs2d_frame_pipe_push(gs2d_frame_pipe* p, const void* host_frame, int* slot_o
         if (rc != GS2D_OK) return rc;
         GS2D_CHECK_CUDA(cudaEventRecord(p->copied[b], p->prep_stream));
     } else {
-        GS2D_CHECK_CUDA(cudaEventRecord(p->copied[b], p->copy_stream));
+        GS2D_CHECK_CUDA(cudaEventRecord(p->copied[b], cs));
     }
     *slot_out = b;
     return GS2D_OK;

@@ -672,14 +672,18 @@ class FusedFrameFit(torch.nn.Module):
         except Exception:   # noqa: BLE001
             pass
 
-    def fit_stream(self, host_frames, prefetch: int = 3, lag: int = 1):
+    def fit_stream(self, host_frames, prefetch: int = 6, lag: int = 2):
         """One iteration per frame of `host_frames` (an iterable of PINNED host targets of one
         format: raw I420 [H*3/2,W], uint8 RGB [H,W,3] or fp32 [1,3,H,W]); yields (loss, psnr) of
         every step, in order.  Frames travel through the library's frame pipe (include/gs2d.h):
         the copy of frame i+1 runs on the pipe's stream under step i, and a step's loss arrives in
         pinned memory with the step itself.  lag: how many steps may be in flight when a result is
-        handed back -- lag=1 (default) issues step i+1 before waiting for step i, so the host's
-        work on the next step hides under the device's; lag=0 is strictly synchronous.
+        handed back -- lag=2 (default) keeps two steps queued behind the one whose result is awaited, so the
+        host's work hides under the device's; lag=0 is strictly synchronous.  prefetch: frames copied ahead
+        (device slots of the pipe).  A 1080p I420 frame is 3.1 MB = 60 us of PCIe time, more than a fit step
+        takes: the stream is bound by the host link, and the defaults (6 / 2) are what keeps the link busy
+        (measured at C2: 2/1 79.9, 3/1 71.1, 4/2 67.3, 6/2 62.9 us per step against 59.9 us for the copy alone;
+        profiles/r2_e2e_sweep.txt).
         A workspace overflow (GS2DOverflow: a tile beyond its 256 slots, more intersections than the
         capacity) is absorbed: the model rewinds, and the frames of the steps that became no-ops --
         still referenced here -- are issued again on the regrown / switched workspace, in order."""
