@@ -354,6 +354,35 @@ def c5_leg(dev, K: int, Wm: int, flush, peak_gbs: float) -> dict:
     return out
 
 
+def bind_to_gpu_cores(dev, local_rank: int, world: int) -> dict:
+    """Pin this rank to host cores near its GPU BEFORE any pinned memory is allocated (first touch decides the
+    NUMA node of the pages the copy engine will read): the GPU's PCI device in sysfs names its NUMA node and
+    the node's cpu list; the ranks that share a node split that list evenly.  -> what was done, for the line."""
+    import torch
+    info = {"numa_node": None, "cpus": None, "bound": False}
+    try:
+        pr = torch.cuda.get_device_properties(dev)
+        bdf = f"{pr.pci_domain_id:04x}:{pr.pci_bus_id:02x}:{pr.pci_device_id:02x}.0"
+        base = f"/sys/bus/pci/devices/{bdf}"
+        node = int(open(base + "/numa_node").read().strip())
+        cpulist = open(base + "/local_cpulist").read().strip()
+        cpus = []
+        for part in cpulist.split(","):
+            a, _, b = part.partition("-")
+            cpus.extend(range(int(a), int(b or a) + 1))
+        allowed = sorted(set(cpus) & set(os.sched_getaffinity(0)))
+        info.update(numa_node=node, pci=bdf, node_cpus=len(cpus), allowed_cpus=len(allowed))
+        if allowed and world > 1:
+            # ranks are spread over the node's cpus by their local index (every rank computes the same split)
+            share = max(1, len(allowed) // max(world, 1))
+            mine = allowed[(local_rank * share) % len(allowed):][:share] or allowed
+            os.sched_setaffinity(0, mine)
+            info.update(cpus=f"{mine[0]}-{mine[-1]}", bound=True)
+    except (OSError, ValueError, AttributeError) as e:
+        info["error"] = f"{type(e).__name__}: {e}"[:120]
+    return info
+
+
 def main_gpu(args, rank: int, world: int, local_rank: int):
     import torch
     import torch.distributed as dist
@@ -361,6 +390,7 @@ def main_gpu(args, rank: int, world: int, local_rank: int):
 
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
+    host_binding = bind_to_gpu_cores(dev, local_rank, world)      # before the first pin_memory()
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
 
@@ -505,6 +535,18 @@ def main_gpu(args, rank: int, world: int, local_rank: int):
         prof = _lib.prof_read()
         stages = {k: {"ms_per_step": v[0] / K, "launches_per_step": v[1] / K} for k, v in prof.items() if v[1]}
 
+    # ---- per-rank figures that explain e2e at N > 1: each rank's own copy bandwidth and e2e time ----------
+    per_rank = None
+    if world > 1:
+        mine_t = torch.tensor([h2d_ms, e2e_ms, float(host_binding.get("numa_node") if host_binding.get("numa_node") is not None else -1)],
+                              dtype=torch.float64, device=dev)
+        allr = [torch.zeros_like(mine_t) for _ in range(world)]
+        dist.all_gather(allr, mine_t)
+        fb = gt_host.numel() * gt_host.element_size()
+        per_rank = {"h2d_copy_alone_gbs": [round(fb / (float(x[0]) * 1e-3) / 1e9, 1) for x in allr],
+                    "e2e_ms_per_step": [round(float(x[1]), 4) for x in allr],
+                    "numa_node": [int(x[2]) for x in allr]}
+
     # ---- max over ranks ----------------------------------------------------------------------
     t = torch.tensor([step_ms, warm_ms, e2e_ms, render_ms, renderq_ms or 0.0], dtype=torch.float64, device=dev)
     if world > 1:
@@ -527,6 +569,7 @@ def main_gpu(args, rank: int, world: int, local_rank: int):
                     "d2h_bytes_per_step": 24 if fused else 4, "ms_per_step": e2e_ms,
                     "h2d_copy_alone_ms": h2d_ms,
                     "h2d_copy_alone_gbs": gt_host.numel() * gt_host.element_size() / (h2d_ms * 1e-3) / 1e9},
+            "host_binding": host_binding, "per_rank": per_rank,
             "gpu_launches": launches,
             "l2_warm": {"value": world * 1e3 / warm_ms, "unit": UNIT, "ms_per_step": warm_ms},
             "render": {"value": world * 1e3 / render_ms, "unit": "frames/s", "ms_per_frame": render_ms},
