@@ -208,6 +208,7 @@ __device__ __forceinline__ void count_tiles(const Proj2d& p, int tx, int row0, i
 
 // Called by every thread of every block after its count_tiles(): the last block to arrive turns
 // the per-tile counts into tile ranges.  sh: 8 ints, s_last: 1 int of shared memory.
+constexpr int kScanPerThread = 64;   // tiles a thread of the scanning block owns per pass
 __device__ __forceinline__ void scan_tiles_by_last_block(int tx, int ty, int cap, int step, int32_t* tile_count,
                                                          int32_t* __restrict__ tile_off, int32_t* status, int* sh,
                                                          int* s_last, int32_t* mail_host = nullptr, int mail_seq = 0) {
@@ -218,17 +219,17 @@ __device__ __forceinline__ void scan_tiles_by_last_block(int tx, int ty, int cap
     if (!*s_last) return;
     __threadfence();
     // exclusive scan of tile_count over all tiles by this one block; counts are re-zeroed so the
-    // scatter kernel can use the same array as its per-tile fill counters.  Each thread owns 32
-    // consecutive tiles per pass and keeps them in registers: eight 16-byte loads in flight at
-    // once (one L2 round trip per 8192 tiles instead of one per tile).
+    // scatter kernel can use the same array as its per-tile fill counters.  Each thread owns 64
+    // consecutive tiles per pass and keeps them in registers: sixteen 16-byte loads in flight at
+    // once -- the 8 160 tiles of a 1080p frame are ONE pass, i.e. one L2 round trip, of this one block.
     const int tiles = tx * ty;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     int carry = 0, mx = 0;
-    for (int base = 0; base < tiles; base += kFitThreads * 32) {
-        const int t0 = base + threadIdx.x * 32;
-        int v[32];
+    for (int base = 0; base < tiles; base += kFitThreads * kScanPerThread) {
+        const int t0 = base + threadIdx.x * kScanPerThread;
+        int v[kScanPerThread];
 #pragma unroll
-        for (int k = 0; k < 8; ++k) {
+        for (int k = 0; k < kScanPerThread / 4; ++k) {
             const int t = t0 + 4 * k;
             if (t + 3 < tiles) {
                 const int4 q = __ldcg(reinterpret_cast<const int4*>(tile_count + t));
@@ -240,7 +241,7 @@ __device__ __forceinline__ void scan_tiles_by_last_block(int tx, int ty, int cap
         }
         int sum = 0;
 #pragma unroll
-        for (int j = 0; j < 32; ++j) {
+        for (int j = 0; j < kScanPerThread; ++j) {
             const int c = v[j];
             mx = max(mx, c);
             v[j] = sum;      // exclusive within the thread
@@ -265,7 +266,7 @@ __device__ __forceinline__ void scan_tiles_by_last_block(int tx, int ty, int cap
         const int excl = carry + wexcl + incl - sum;
         const int4 z = make_int4(0, 0, 0, 0);
 #pragma unroll
-        for (int k = 0; k < 8; ++k) {
+        for (int k = 0; k < kScanPerThread / 4; ++k) {
             const int t = t0 + 4 * k;
             if (t + 3 < tiles) {
                 *reinterpret_cast<int4*>(tile_off + t) =
@@ -498,6 +499,9 @@ __device__ __forceinline__ void block_add(int v, int32_t* dst, int* sh) {
     }
 }
 
+// MULTI = false: no cross-rank overflow signalling compiled in (single GPU: the common case; these
+// per-Gaussian kernels run every instruction once per warp, so code size is time)
+template <bool MULTI>
 __global__ void __launch_bounds__(kFitThreads)
 k_fit_scatter(int n, const float* __restrict__ xyz_raw, const float* __restrict__ chol_raw,
               const float* __restrict__ feat, const float* __restrict__ opac, const float* __restrict__ rgb_w,
@@ -526,10 +530,10 @@ k_fit_scatter(int n, const float* __restrict__ xyz_raw, const float* __restrict_
     if (i < n && !dead) {
         const float r = col.x, g = col.y, b = col.z;
         if (slots)
-            claimed = scatter_records<true>(p, i, o, r, g, b, tx, row0, row1, W, H, nullptr, tile_fill, packed, status, step, rt,
-                                            (slots & 2) != 0);
+            claimed = scatter_records<true, 4>(p, i, o, r, g, b, tx, row0, row1, W, H, nullptr, tile_fill, packed, status, step,
+                                               MULTI ? rt : Route(), (slots & 2) != 0);
         else
-            scatter_records<false>(p, i, o, r, g, b, tx, row0, row1, W, H, tile_off, tile_fill, packed, status, step);
+            scatter_records<false, 4>(p, i, o, r, g, b, tx, row0, row1, W, H, tile_off, tile_fill, packed, status, step);
     }
     if (slots) block_add(claimed, &status[kStSlotIsect + (step & 1)], sh);
 }
@@ -1722,11 +1726,11 @@ static int launch_bin(int n, const float* xyz, const float* chol, const float* f
     {
         ProfScope ps_(GS2D_STAGE_EDGES_PACK, s);
         if (pdl && !precounted)   // render chain: count -> scatter -> tiles, each under its predecessor's tail
-            GS2D_CHECK_CUDA(launch_pdl(k_fit_scatter, dim3(blocks), dim3(kFitThreads), s, n, xyz, chol, feat, opac, rgb_w,
+            GS2D_CHECK_CUDA(launch_pdl(k_fit_scatter<false>, dim3(blocks), dim3(kFitThreads), s, n, xyz, chol, feat, opac, rgb_w,
                                        activate, half_w, half_h, tx, ty, row0, row1, img_w, img_h, (const int32_t*)tile_off,
                                        tile_count, status, (float4*)(w + L.off_packed), 0, step, qc, Route()));
         else
-            k_fit_scatter<<<blocks, kFitThreads, 0, s>>>(n, xyz, chol, feat, opac, rgb_w, activate, half_w, half_h, tx, ty,
+            k_fit_scatter<false><<<blocks, kFitThreads, 0, s>>>(n, xyz, chol, feat, opac, rgb_w, activate, half_w, half_h, tx, ty,
                                                          row0, row1, img_w, img_h, tile_off, tile_count, status,
                                                          (float4*)(w + L.off_packed), 0, step, qc, Route());
         GS2D_CHECK_LAUNCH("fit_scatter");
@@ -1848,7 +1852,7 @@ int gs2d_fit_step_band(int n, int cap, int img_h, int img_w, float* xyz_raw, flo
                         L.tiles, (int32_t*)(w + L.off_tile_count), status);
                     GS2D_CHECK_LAUNCH("fit_reset_slots");
                 }
-                k_fit_scatter<<<div_up(n, kFitThreads), kFitThreads, 0, s>>>(
+                (rt.R > 0 ? k_fit_scatter<true> : k_fit_scatter<false>)<<<div_up(n, kFitThreads), kFitThreads, 0, s>>>(
                     n, xyz_raw, chol_raw, features, nullptr, rgb_w, 1, half_w, half_h, tx, ty, row0, row1, img_w, img_h,
                     nullptr, (int32_t*)(w + L.off_tile_count), status, (float4*)(w + L.off_packed),
                     1 | (ids_sorted_out ? 0 : cull_bit), step, src, rt);
