@@ -698,9 +698,19 @@ def run_spatial(args, rank: int, world: int, dev, flush):
     # sharded_remote_scatter: the update kernel also writes the next step's records straight into the owning
     # rank's slots (an all-to-all by NVLink atomics + stores: measured slower, kept as an option);
     # nccl: replicated update behind one NCCL all-reduce of the gradient rows
-    for exchange in ("sharded", "sharded_remote_scatter", "nccl"):
+    # (sharded_pull: the update kernel reads every rank's gradient rows instead of the tile kernels pushing them)
+    def exchange_bytes(exchange, fit):
+        """bytes a rank moves over NVLink per step (algorithmic)"""
+        if exchange == "nccl":
+            return n * 48 * 2                                          # all-reduce: reduce-scatter + all-gather
+        gather = (n // world) * 32 * (world - 1)                      # the shard's new rows stored into every peer
+        if exchange == "sharded":                                      # pushed: 32 bytes per pair of the band, remote owners
+            return int(fit.status()[0] * 32 * (world - 1) / world) + gather
+        return (n // world) * 48 * (world - 1) + gather                # pulled: the shard's rows read from every peer
+
+    for exchange in ("sharded", "sharded_pull", "sharded_remote_scatter", "nccl"):
         fit = SpatialFrameFit(h, w, n, dev, init=init, exchange=exchange.split("_")[0], balance=True,
-                              remote_scatter=exchange == "sharded_remote_scatter")
+                              remote_scatter=exchange == "sharded_remote_scatter", push=exchange != "sharded_pull")
         fit.train_iters(gt, Wm)
         dist.barrier(); torch.cuda.synchronize(dev)
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -716,7 +726,7 @@ def run_spatial(args, rank: int, world: int, dev, flush):
         dist.all_reduce(lo, op=dist.ReduceOp.MIN); dist.all_reduce(hi, op=dist.ReduceOp.MAX)
         out[exchange] = {"ms_per_iter": float(ms), "iters_per_s": 1e3 / float(ms), "loss": loss, "bands": fit.bands,
                          "params_identical_across_ranks": bool(torch.equal(lo, hi)),
-                         "exchange_bytes_per_rank_per_iter": n * 48 + n * 32 if exchange.startswith("sharded") else n * 48 * 2}
+                         "exchange_bytes_per_rank_per_iter": exchange_bytes(exchange, fit)}
         if exchange == "sharded":
             keep = fit
         else:
@@ -734,12 +744,12 @@ def run_spatial(args, rank: int, world: int, dev, flush):
         d = (ref._params8 - keep._params8).abs()
         out["single_gpu_ms_per_iter"] = ref_ms
         out["loss_single_gpu"] = ref_loss
-        for exchange in ("sharded", "sharded_remote_scatter", "nccl"):
+        for exchange in ("sharded", "sharded_pull", "sharded_remote_scatter", "nccl"):
             out[exchange]["speedup_vs_single_gpu"] = ref_ms / out[exchange]["ms_per_iter"]
             out[exchange]["loss_rel_diff_vs_single_gpu"] = abs(out[exchange]["loss"] - ref_loss) / ref_loss
         out["median_abs_param_diff_vs_single_gpu"] = float(d.median())
         out["parity_ok"] = bool(all(out[x]["params_identical_across_ranks"] and out[x]["loss_rel_diff_vs_single_gpu"] <= 2e-3
-                                    for x in ("sharded", "sharded_remote_scatter", "nccl")))
+                                    for x in ("sharded", "sharded_pull", "sharded_remote_scatter", "nccl")))
     dist.barrier()
     return out if rank == 0 else None
 

@@ -639,18 +639,18 @@ k_target_tiled(int W, int H, int tx, const void* __restrict__ gt, float* __restr
 #ifndef GS2D_TILE_MIN_BLOCKS
 #define GS2D_TILE_MIN_BLOCKS 1
 #endif
-constexpr int kTileLossInGrads = 1;   // flags: spatial mode, the tile's loss also rides in the gradient buffer
 constexpr int kTileAllPerTile = 2;    //        every Gaussian of a tile is rendered, in batches of 256 (ranges only)
 // ALL: the instantiation that walks a fuller tile in batches (kTileAllPerTile); a run-time switch in the one
 // kernel cost the common case 42 registers and 12 % (58.9 -> 66.2 us), so it is a kernel of its own.
-template <int MODE, int GT, bool ALL = false>
+// PUSH: the instantiation of the pushed reduce-scatter (push_peers; the single-GPU kernel keeps its code).
+template <int MODE, int GT, bool ALL = false, bool PUSH = false>
 __global__ void __launch_bounds__(kTileThreads, GS2D_TILE_MIN_BLOCKS)
 k_fit_tiles(int W, int H, int tx, int row0, const int32_t* __restrict__ tile_off, int32_t* tile_fill,
             const float4* __restrict__ packed, const void* __restrict__ gt, float grad_scale,
             float* __restrict__ grads, double* loss_acc, int32_t* __restrict__ status,
             float* __restrict__ out_img, int out_chw, int out_clamp, int32_t* __restrict__ final_idx,
-            int32_t* __restrict__ ids_sorted_dbg, int step, int flags) {
-    const int loss_in_grads = flags & kTileLossInGrads;
+            int32_t* __restrict__ ids_sorted_dbg, int step, int flags, float* const* __restrict__ push_peers,
+            int push_per, float* __restrict__ loss_pad) {
     __shared__ float4 sq_all[kSqRecords * 3];
     // v_out of the tile (rows 0..15; before that, the id chunk of the staging) + 16 rows of zeros:
     // the backward's row walk may run past the tile for lanes whose pair has a shorter rectangle
@@ -939,8 +939,8 @@ k_fit_tiles(int W, int H, int tx, int row0, const int32_t* __restrict__ tile_off
         if (s != 0.f) {
             atomicAdd(loss_acc, (double)s);
             // spatial mode: the loss rides in the pad of gradient row 0 so that one all-reduce of the
-            // gradient buffer also sums the ranks' partial losses
-            if (loss_in_grads) atomicAdd(grads + 9, s);
+            // gradient buffer also sums the ranks' partial losses (pushed reduction: in a word past the rows)
+            if (loss_pad) atomicAdd(loss_pad, s);
         }
     }
 
@@ -1030,7 +1030,12 @@ k_fit_tiles(int W, int H, int tx, int row0, const int32_t* __restrict__ tile_off
             acc[5] += cr; acc[6] += cg; acc[7] += cbl;
         }
         const float tot = group8_reduce8_t(acc, lane);
-        float* row = grads + (size_t)__float_as_int(q1.w) * 12;
+        const int gid = __float_as_int(q1.w);
+        // pushed reduce-scatter (spatial mode, sharded update): the pair's 32 bytes go straight into the gradient
+        // buffer of the rank that OWNS the Gaussian (a reduction without return value: fire and forget over NVLink)
+        float* gbase = PUSH ? reinterpret_cast<float*>(__ldg(reinterpret_cast<const unsigned long long*>(push_peers) +
+                                                                   (live ? gid / push_per : 0))) : grads;
+        float* row = gbase + (size_t)gid * 12;
         if (live && tot != 0.f) atomicAdd(row + l8, tot);   // 4 pairs x 8 consecutive floats
     }
     }   // batches
@@ -1409,7 +1414,8 @@ k_fit_update_quad(int n, float* __restrict__ params8, float* __restrict__ adan, 
     pdl_release();
     // the local gradient row is requested together with the status word (one round trip, not two)
     float4 g0 = make_float4(0.f, 0.f, 0.f, 0.f), g1 = g0;   // v_xy(2) v_conic(3) v_rgb(3) | v_opacity(1) pad(3)
-    const bool local_row = !MULTI || (!mc_grads && num_peers == 0);
+    const bool push = MULTI && (loss_in_grads & 2);          // the peers' tile kernels added into THIS rank's rows
+    const bool local_row = !MULTI || push || (!mc_grads && num_peers == 0);
     if (act && local_row) {
         const float4* grow = reinterpret_cast<const float4*>(grads + (size_t)i * 12);
         g0 = grow[0]; g1 = grow[1];
@@ -1418,12 +1424,14 @@ k_fit_update_quad(int n, float* __restrict__ params8, float* __restrict__ adan, 
     const bool dead = of != 0 && abs(of) < next_step;
     if (gtid == 0 && report_host) {
         double ls = *loss_this;
-        if (loss_in_grads) {
+        if (loss_in_grads & 1) {
             if (MULTI && mc_grads) {
                 ls = (double)multimem_sum1(mc_grads + 9);
             } else if (MULTI && num_peers > 0) {
+                // pushed reduction: the ranks' partial losses sit past the rows, in one of two words by step parity
+                const size_t pad = push ? (size_t)n * 12 + 16 * ((next_step - 1) & 1) : 9;
                 float acc = 0.f;
-                for (int r = 0; r < num_peers; ++r) acc += __ldcg(peer_grads[r] + 9);
+                for (int r = 0; r < num_peers; ++r) acc += __ldcg(peer_grads[r] + pad);
                 ls = (double)acc;
             } else {
                 ls = (double)grads[9];
@@ -1440,7 +1448,9 @@ k_fit_update_quad(int n, float* __restrict__ params8, float* __restrict__ adan, 
     }
     if (dead) return;                              // uniform over the grid (see k_fit_update)
     if (gtid == 0 && loss_next) *loss_next = 0.0;
-    if (MULTI && rt.R > 0 && grads_zero) {
+    // (the next step's loss word: its last readers were the update kernels of the step before this one)
+    if (push && gtid == 0) grads[(size_t)n * 12 + 16 * (next_step & 1)] = 0.f;
+    if (MULTI && rt.R > 0 && grads_zero && !push) {
         const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
         float4* zb = reinterpret_cast<float4*>(grads_zero);
         for (size_t k = gtid; k < (size_t)n * 3; k += (size_t)gridDim.x * kFitThreads) zb[k] = z;
@@ -1452,7 +1462,7 @@ k_fit_update_quad(int n, float* __restrict__ params8, float* __restrict__ adan, 
         if (MULTI && mc_grads) {   // (the group's lanes read the same row)
             g0 = multimem_sum4(mc_grads + (size_t)i * 12);
             g1 = multimem_sum4(mc_grads + (size_t)i * 12 + 4);
-        } else if (MULTI && num_peers > 0) {
+        } else if (MULTI && num_peers > 0 && !push) {
             g0 = make_float4(0.f, 0.f, 0.f, 0.f);
             g1 = g0;
             for (int r0 = 0; r0 < num_peers; r0 += 4) {
@@ -1491,8 +1501,8 @@ k_fit_update_quad(int n, float* __restrict__ params8, float* __restrict__ adan, 
     // every lane of the warp has loaded its row: now the row may be re-zeroed (16 bytes per lane).
     // The barrier orders the group's loads before the stores, whichever lane is ahead.
     __syncwarp();
-    if (act && (!MULTI || rt.R == 0)) {
-        float4* zrow = reinterpret_cast<float4*>((grads_zero ? grads_zero : grads) + (size_t)i * 12);
+    if (act && (!MULTI || rt.R == 0 || push)) {
+        float4* zrow = reinterpret_cast<float4*>(((grads_zero && !push) ? grads_zero : grads) + (size_t)i * 12);
         const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
         if (LANES == 4) { if (q < 3) zrow[q] = z; }
         else { zrow[q] = z; if (q == 0) zrow[2] = z; }
@@ -1775,6 +1785,8 @@ int gs2d_fit_step_band(int n, int cap, int img_h, int img_w, float* xyz_raw, flo
     float* grads_zero = nullptr;
     const float* mc_grads = nullptr;
     Route rt = Route();
+    float* const* push_peers = nullptr;
+    int push_per = 1;
     int shard_begin = 0, shard_end = n;
     if (exchange) {
         GS2D_REQUIRE(exchange->accumulate != nullptr, "fit_step: exchange without an accumulate buffer");
@@ -1786,11 +1798,17 @@ int gs2d_fit_step_band(int n, int cap, int img_h, int img_w, float* xyz_raw, flo
         grads_zero = exchange->zero;
         mc_grads = exchange->multicast;
         if (mc_grads) { peer_grads = nullptr; num_peers = 0; }
+        if (exchange->push_per > 0) {
+            GS2D_REQUIRE(exchange->shard_end > exchange->shard_begin && exchange->peers != nullptr && !mc_grads,
+                         "fit_step: a pushed reduction needs a sharded update and the peers' buffers");
+            push_peers = (float* const*)exchange->peers;
+            push_per = exchange->push_per;
+        }
         if (exchange->shard_end > exchange->shard_begin) {
             GS2D_REQUIRE(exchange->shard_begin >= 0 && exchange->shard_end <= n, "fit_step: shard out of range");
-            GS2D_REQUIRE(num_peers > 0 && exchange->xyz_peers && exchange->status_peers && grads_zero &&
+            GS2D_REQUIRE(num_peers > 0 && exchange->xyz_peers && exchange->status_peers && (grads_zero || push_peers) &&
                              ((options && options->params8) || (exchange->chol_peers && exchange->feat_peers)),
-                         "fit_step: a sharded update needs peers, their parameter pointers and a spare buffer");
+                         "fit_step: a sharded update needs peers, their parameter pointers and (pulled reduction) a spare buffer");
             shard_begin = exchange->shard_begin;
             shard_end = exchange->shard_end;
             rt.xyz = exchange->xyz_peers;
@@ -1865,18 +1883,26 @@ int gs2d_fit_step_band(int n, int cap, int img_h, int img_w, float* xyz_raw, flo
         }
         const int32_t* tile_off_arg = slots ? nullptr : (const int32_t*)(w + L.off_tile_off);
         const float grad_scale = (float)(2.0 / (3.0 * (double)img_h * (double)img_w));   // the WHOLE frame's mean
-        const int tile_flags = tile_flags_for((banded ? kTileLossInGrads : 0) | (all_per_tile ? kTileAllPerTile : 0),
+        const int tile_flags = tile_flags_for(all_per_tile ? kTileAllPerTile : 0,
                                               row1 - row0);
         ProfScope ps_(GS2D_STAGE_FIT_TILES, s);
         const dim3 grid = tile_grid(tx, row1 - row0);
+        // where the band's loss also goes: the pad of gradient row 0, or (pushed reduction, where row 0 belongs to
+        // rank 0 alone) one of two words past the rows, by step parity (gs2d.h, push_per)
+        float* loss_pad = !banded ? nullptr : push_peers ? grads + (size_t)n * 12 + 16 * (step & 1) : grads + 9;
         auto launch = [&](auto kernel) {
             return launch_pdl(kernel, grid, dim3(kTileThreads), s, img_w, img_h, tx, row0, tile_off_arg,
                               (int32_t*)(w + L.off_tile_count), (const float4*)(w + L.off_packed), target, grad_scale, grads,
                               loss + (step % GS2D_FIT_LOSS_SLOTS), status, out_img, 1, 1, (int32_t*)nullptr, ids_sorted_out,
-                              step, tile_flags);
+                              step, tile_flags, push_peers, push_per, loss_pad);
         };
         cudaError_t le;
-        if (target_format == GS2D_TARGET_F32_CHW)
+        if (push_peers) {   // (slots only: checked above)
+            le = target_format == GS2D_TARGET_F32_CHW  ? launch(k_fit_tiles<0, 0, false, true>)
+                 : target_format == GS2D_TARGET_U8_HWC ? launch(k_fit_tiles<0, 1, false, true>)
+                 : target_format == GS2D_TARGET_I420   ? launch(k_fit_tiles<0, 2, false, true>)
+                                                       : launch(k_fit_tiles<0, 3, false, true>);
+        } else if (target_format == GS2D_TARGET_F32_CHW)
             le = all_per_tile ? launch(k_fit_tiles<0, 0, true>) : launch(k_fit_tiles<0, 0, false>);
         else if (target_format == GS2D_TARGET_U8_HWC)
             le = all_per_tile ? launch(k_fit_tiles<0, 1, true>) : launch(k_fit_tiles<0, 1, false>);
@@ -1908,14 +1934,16 @@ int gs2d_fit_step_band(int n, int cap, int img_h, int img_w, float* xyz_raw, flo
         h.offdiag = analytic ? 1.f : 2.f;
         ProfScope ps_(GS2D_STAGE_ADAN, s);
         static const bool no_quad = [] { const char* e = getenv("GS2D_NO_QUAD"); return e && e[0] == '1'; }();   // A/B runs
+        GS2D_REQUIRE(!push_peers || (src.ld_xyz == 8 && !no_quad), "fit_step: a pushed reduction needs the packed parameter rows");
         if (src.ld_xyz == 8 && !no_quad)
             GS2D_CHECK_CUDA(launch_pdl((exchange || rt.R > 0) ? k_fit_update_quad<true, kUpdateLanes> : k_fit_update_quad<false, kUpdateLanes>,
                 dim3(div_up((long long)kUpdateLanes * (shard_end - shard_begin), kFitThreads)),
                 dim3(kFitThreads), s, n, xyz_raw, adan_state, grads, half_w, half_h, tx, ty, h, status,
                 loss + (step % GS2D_FIT_LOSS_SLOTS), loss + ((step + 1) % GS2D_FIT_LOSS_SLOTS), param_grads_out, cap,
                 step + 1, (int32_t*)(w + L.off_tile_count), (int32_t*)(w + L.off_tile_off), report_host, row0, row1,
-                banded ? 1 : 0, peer_grads, num_peers, grads_zero, rgb_w, adan_w, rgb_w_grad_out, skip_update,
-                mc_grads, slots ? (1 | cull_bit) : 0, (float4*)(w + L.off_packed), img_w, img_h, shard_begin, shard_end, rt));
+                (banded ? 1 : 0) | (push_peers ? 2 : 0), peer_grads, num_peers, grads_zero, rgb_w, adan_w, rgb_w_grad_out,
+                skip_update, mc_grads, slots ? (1 | cull_bit) : 0, (float4*)(w + L.off_packed), img_w, img_h, shard_begin,
+                shard_end, rt));
         else
         GS2D_CHECK_CUDA(launch_pdl(src.ld_xyz == 8 ? k_fit_update<true> : k_fit_update<false>,
             dim3(div_up(shard_end - shard_begin, kFitThreads)), dim3(kFitThreads), s,
@@ -2005,7 +2033,7 @@ int gs2d_render_quantized(int n, int cap, int img_h, int img_w, const gs2d_quant
             img_w, img_h, tx, 0, (const int32_t*)(w + L.off_tile_off), (int32_t*)(w + L.off_tile_count),
             (const float4*)(w + L.off_packed), (const void*)nullptr, 0.f, (float*)nullptr, (double*)nullptr,
             (int32_t*)(w + L.off_status), out_img, out_chw, out_clamp, final_idx, ids_sorted_out, 0,
-            tile_flags_for(0, ty)));
+            tile_flags_for(0, ty), (float* const*)nullptr, 1, (float*)nullptr));
         GS2D_CHECK_LAUNCH("render_tiles");
     }
     return GS2D_OK;
@@ -2072,7 +2100,8 @@ int gs2d_rasterize_sum_fwd_ranked(int n, const float* xys, const int32_t* radii,
         GS2D_CHECK_CUDA(launch_pdl(k_fit_tiles<1, 0, false>, tile_grid(tx, ty), dim3(kTileThreads), s,
             img_w, img_h, tx, 0, (const int32_t*)(w + L.off_tile_off), (int32_t*)(w + L.off_tile_count),
             (const float4*)(w + L.off_packed), (const void*)background, 0.f, (float*)nullptr, (double*)nullptr,
-            (int32_t*)(w + L.off_status), out_img, 0, 0, final_idx, (int32_t*)nullptr, 0, tile_flags_for(0, ty)));
+            (int32_t*)(w + L.off_status), out_img, 0, 0, final_idx, (int32_t*)nullptr, 0, tile_flags_for(0, ty),
+            (float* const*)nullptr, 1, (float*)nullptr));
         GS2D_CHECK_LAUNCH("raster_fwd_ranked");
     }
     return GS2D_OK;
@@ -2119,7 +2148,7 @@ int gs2d_render_chol(int n, int cap, int img_h, int img_w, const float* means_or
             img_w, img_h, tx, 0, (const int32_t*)(w + L.off_tile_off), (int32_t*)(w + L.off_tile_count),
             (const float4*)(w + L.off_packed), (const void*)nullptr, 0.f, (float*)nullptr, (double*)nullptr,
             (int32_t*)(w + L.off_status), out_img, out_chw, out_clamp, final_idx, ids_sorted_out, 0,
-            tile_flags_for(all_flag, ty)));
+            tile_flags_for(all_flag, ty), (float* const*)nullptr, 1, (float*)nullptr));
         GS2D_CHECK_LAUNCH("render_tiles");
     }
     return GS2D_OK;

@@ -881,7 +881,7 @@ class SpatialFrameFit(FusedFrameFit):
 
     def __init__(self, H, W, num_points, device, group=None, bands=None, emulate_world: int = 0,
                  exchange: str = "nccl", slots: bool = False, own_barrier: bool = True, balance: bool = False,
-                 remote_scatter: bool = False, **kw):
+                 remote_scatter: bool = False, push: bool = True, **kw):
         """exchange: "nccl" -- one all-reduce call on the gradient rows between the two phases;
         "peer" -- the rows live in symmetric (peer-mapped) memory and the update kernel itself sums
         them over NVLink in rank order after a device-side barrier: no collective kernel, no extra
@@ -900,6 +900,9 @@ class SpatialFrameFit(FusedFrameFit):
         # the rank that rasterises each tile (gs2d_grad_exchange.work_peers) instead of every rank
         # re-projecting all Gaussians to find its band's
         self.remote_scatter = bool(remote_scatter)
+        # sharded update only: the tile kernels add every pair's gradient straight into the OWNER rank's buffer
+        # (gs2d_grad_exchange.push_per) instead of the update kernel reading every rank's rows
+        self.push = bool(push) and os.environ.get("GS2D_NO_PUSH") != "1"
         self.emulate_world = int(emulate_world)
         if exchange not in ("nccl", "peer", "nvls", "sharded"):
             raise ValueError("exchange must be 'nccl', 'peer', 'nvls' or 'sharded'")
@@ -939,8 +942,10 @@ class SpatialFrameFit(FusedFrameFit):
         rank's parameter tensors, and a tile that outgrows its slots is flagged in every rank's
         status words: both move into symmetric (peer-mapped) memory."""
         dev, n, lay, R = self.device, self.n, self.layout, self.world
-        edges = [round(r * n / R) for r in range(R + 1)]
-        self.shards = [(edges[r], edges[r + 1]) for r in range(R)]
+        # uniform shards: Gaussian i belongs to rank i // per (the tile kernels of a pushed reduction compute the owner)
+        per = -(-n // R)
+        self._shard_per = per
+        self.shards = [(r * per, min((r + 1) * per, n)) for r in range(R)]
         if any(b <= a for a, b in self.shards):
             raise ValueError("need at least one Gaussian per rank")
         lib = self._lib.load()
@@ -1022,6 +1027,9 @@ class SpatialFrameFit(FusedFrameFit):
         ex.zero = self._own[rank_slot][1 - x]
         ex.multicast = (self._mc + x * self.n * 48) if (with_peers and self.exchange == "nvls") else None
         if self.exchange == "sharded":
+            if self.push:      # one buffer: a row is re-zeroed by its owner right after it was read (see gs2d.h)
+                x = 0
+                ex.accumulate, ex.zero, ex.push_per = self._own[rank_slot][0], None, self._shard_per
             ex.peers, ex.num_peers = self._peer_list_ptr[x], self.world
             ex.shard_begin, ex.shard_end = self.shards[rank_slot if self.emulate_world else self.rank]
             ex.xyz_peers, ex.chol_peers, ex.feat_peers, ex.status_peers = self._route_ptr[:4]

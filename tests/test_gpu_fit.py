@@ -417,7 +417,7 @@ def test_fit_stream_equals_resident_loop(fmt, lag, prefetch):
     assert a.step_index == K
 
 
-@pytest.mark.parametrize("exchange", ["nccl", "peer", "sharded", "sharded-local-scatter"])
+@pytest.mark.parametrize("exchange", ["nccl", "peer", "sharded", "sharded-pull", "sharded-remote-scatter"])
 @pytest.mark.parametrize("H,W,n,world", [(256, 256, 10_000, 2), (200, 328, 3_000, 3), (1080, 1920, 50_000, 4)])
 def test_tile_row_bands_sum_to_the_whole_frame(H, W, n, world, exchange):
     """spatial mode on ONE GPU: every band's gradients (and loss) added into the same buffer in
@@ -431,8 +431,11 @@ def test_tile_row_bands_sum_to_the_whole_frame(H, W, n, world, exchange):
     # records into the tile slots of the rank that owns each tile row (one workspace per rank)
     # (default: the update kernel scatters the next records into the owning rank's slots itself;
     # "-local-scatter": every rank re-projects all Gaussians for its band instead); bands balanced by work
+    # "sharded" = pushed reduce-scatter (the tile kernels add into the owner's buffer); "-pull": the update kernel
+    # reads every rank's rows instead; "-remote-scatter": it also writes the next records into the owners' slots
     banded = SpatialFrameFit(H, W, n, cuda, init=init, emulate_world=world, exchange=exchange.split("-")[0],
-                             remote_scatter=not exchange.endswith("local-scatter"), balance=(world == 3))
+                             remote_scatter=exchange.endswith("remote-scatter"), push=not exchange.endswith("pull"),
+                             balance=(world == 3))
     gtd = gt.to(cuda)
     ga = torch.empty((n, 8), device=cuda)
     gb = torch.empty((n, 8), device=cuda)
