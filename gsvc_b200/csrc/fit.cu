@@ -579,6 +579,31 @@ constexpr int kBwdRows = GS2D_BWD_ROWS;   // rows of a pair's rectangle a lane e
 #define GS2D_SQ_RECORDS GS2D_MAX_PER_TILE   // experiments only: a smaller batch buffer (tiles beyond it are then truncated)
 #endif
 constexpr int kWarpStage = GS2D_WARP_STAGE;
+// experiment (VERDICT r1 #3e; profiles/r2_ab_bulk_stage.txt): slot mode, the tile's first 32 records arrive by ONE
+// bulk asynchronous copy (cp.async.bulk, the 1-D form of TMA) into shared memory, completion on an mbarrier; the
+// warps then rank out of shared memory.  Measured against the lanes' own 16-byte loads: see the file.  Off.
+#ifndef GS2D_STAGE_BULK
+#define GS2D_STAGE_BULK 0
+#endif
+#if GS2D_STAGE_BULK
+__device__ __forceinline__ void mbar_init(unsigned long long* bar, int count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"((uint32_t)__cvta_generic_to_shared(bar)), "r"(count));
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void bulk_load_expect(void* dst, const void* src, uint32_t bytes, unsigned long long* bar) {
+    const uint32_t b = (uint32_t)__cvta_generic_to_shared(bar), d = (uint32_t)__cvta_generic_to_shared(dst);
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(b), "r"(bytes) : "memory");
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(d), "l"(src), "r"(bytes), "r"(b) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(unsigned long long* bar, uint32_t parity) {
+    const uint32_t b = (uint32_t)__cvta_generic_to_shared(bar);
+    asm volatile(
+        "{\n.reg .pred p;\nWAIT_%=:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra DONE_%=;\nbra WAIT_%=;\nDONE_%=:\n}" ::"r"(b), "r"(parity) : "memory");
+}
+#endif
 constexpr int kSqRecords = GS2D_SQ_RECORDS > 32 * (kTileThreads / 32) ? GS2D_SQ_RECORDS : 32 * (kTileThreads / 32);
 
 // The target frame in the tile kernel's own order: fp32 [tiles][kTileThreads][kPix][3], i.e. for every
@@ -677,6 +702,12 @@ k_fit_tiles(int W, int H, int tx, int row0, const int32_t* __restrict__ tile_off
         for (int j = 0; j < GS2D_TILE_PIX / kTileThreads; ++j)
             sv[GS2D_TILE_PIX + j * kTileThreads + tid] = make_float4(0.f, 0.f, 0.f, 0.f);
     }
+#if GS2D_STAGE_BULK
+    __shared__ __align__(128) float4 sraw[32 * 3];
+    __shared__ __align__(8) unsigned long long sbar;
+    if (tid == 0) mbar_init(&sbar, 1);
+    __syncthreads();   // (in the prologue: before the wait for the previous kernel)
+#endif
 
     const int lx = lane & 15, ly0 = kWarpRows * warp + (lane >> 4);   // pixel j: (lx, ly0 + 2j)
     const int ox = bx * GS2D_TILE, oy = tile_y * GS2D_TILE;
@@ -737,14 +768,22 @@ k_fit_tiles(int W, int H, int tx, int row0, const int32_t* __restrict__ tile_off
     // with the flag and the count -- one round trip to L2 instead of two.  (Requesting 64 per warp
     // was measured in round 1: no gain, 25 MB per step of never-written slots pulled from DRAM.)
     float4 w0 = make_float4(0.f, 0.f, 0.f, 0.f), w1 = w0, w2 = w0;
+#if GS2D_STAGE_BULK
+    if (kWarpStage && slot && tid == 0)
+        bulk_load_expect(sraw, packed + 3 * ((size_t)t * kSlotStride), 32 * 48, &sbar);
+#else
     if (kWarpStage && slot) {
         const float4* rec = packed + 3 * ((size_t)t * kSlotStride + lane);
         w0 = __ldg(rec); w1 = __ldg(rec + 1); w2 = __ldg(rec + 2);
     }
+#endif
     const int of = status[kStOverflow];
     const int lo = slot ? t * kSlotStride : tile_off[t];
     const uint32_t fill = slot ? (uint32_t)tile_fill[t] : 0u;          // slots: all pairs << 16 | stored records
     const int cnt = slot ? (int)(fill & 0xffffu) : tile_off[t + 1] - lo;
+#if GS2D_STAGE_BULK
+    if (kWarpStage && slot) mbar_wait(&sbar, 0);   // every thread passes here once (phase 0), also before an early return
+#endif
     if (of != 0) {
         // the workspace overflowed: the step is a no-op.  A render must not hand back stale memory as
         // an image: it is filled with NaN (the operator path reports the overflow lazily)
@@ -773,6 +812,9 @@ k_fit_tiles(int W, int H, int tx, int row0, const int32_t* __restrict__ tile_off
     const bool per_warp = kWarpStage && cnt <= 32;     // uniform over the CTA
     float4* sq = sq_all + (per_warp ? warp * (32 * 3) : 0);
     int nb;
+#if GS2D_STAGE_BULK
+    if (kWarpStage && slot && per_warp) { w0 = sraw[3 * lane]; w1 = sraw[3 * lane + 1]; w2 = sraw[3 * lane + 2]; }
+#endif
     if (per_warp) {
         if (!slot && lane < cnt) {
             const float4* rec = packed + 3 * ((size_t)lo + lane);
