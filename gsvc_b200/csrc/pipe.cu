@@ -4,6 +4,7 @@
 // the same plumbing through a Python tensor library costs more host time per frame than the
 // whole fit step takes on the device.
 #include <cstdint>
+#include <cstdlib>
 #include <new>
 
 #include "gs2d_host.h"
@@ -14,9 +15,10 @@ struct gs2d_frame_pipe {
     int depth;
     int next;
     unsigned pushes;
-    // two copy streams, used alternately: the set-up of one frame's DMA runs under the other's transfer
-    // (a 3 MB frame is ~58 us of PCIe time and ~5 us of per-copy latency that back-to-back copies on ONE
-    // stream expose: the link, not the GPU, bounds a stream of 1080p frames)
+    // One copy stream carries the frames in order.  (GS2D_PIPE_STREAMS=2 alternates between two, so that the
+    // set-up of one frame's DMA runs under the other's transfer: measured again late in round 2,
+    // profiles/r2_e2e_fill_probe.txt -- no faster in steady state, 62.8 vs 63.4 us per 1080p frame, and the first
+    // frames of a stream then share the link and arrive later: 68.9 vs 73.5 us per step over a 20-frame stream.)
     cudaStream_t copy_streams[2];
     cudaEvent_t copied[GS2D_PIPE_MAX_DEPTH];
     cudaEvent_t freed[GS2D_PIPE_MAX_DEPTH];
@@ -87,7 +89,8 @@ int gs2d_frame_pipe_push(gs2d_frame_pipe* p, const void* host_frame, int* slot_o
     GS2D_REQUIRE(p && host_frame && slot_out, "frame_pipe_push: null argument");
     const int b = p->next;
     p->next = (b + 1) % p->depth;
-    cudaStream_t cs = p->copy_streams[p->pushes++ & 1];
+    static const bool two_streams = [] { const char* e = getenv("GS2D_PIPE_STREAMS"); return e && e[0] == '2'; }();   // A/B runs
+    cudaStream_t cs = p->copy_streams[two_streams ? (p->pushes++ & 1) : 0];
     if (p->has_consumer[b]) GS2D_CHECK_CUDA(cudaStreamWaitEvent(cs, p->freed[b], 0));
     GS2D_CHECK_CUDA(cudaMemcpyAsync(p->slots + (size_t)b * p->frame_bytes, host_frame, p->frame_bytes,
                                     cudaMemcpyHostToDevice, cs));
