@@ -195,14 +195,27 @@ __device__ __forceinline__ float3 fit_colour(int i, const float* __restrict__ fe
 // split across GPUs by tile rows, SURVEY 8e spatial mode)
 // (first, stride): the tiles of the Gaussian's bbox are numbered row by row; this call takes numbers first,
 // first + stride, ... -- several lanes can share one Gaussian's tiles
+// j / bw for the tile numbering of a bbox (0 <= j, 1 <= bw, both far below 2^23): one multiply by the
+// reciprocal and a one-step correction instead of the ~20 instructions of an integer division by a variable;
+// exact whatever the rounding of the reciprocal (the quotient estimate is off by at most one).
+__device__ __forceinline__ int div_small(int j, int bw, float inv_bw, int& rem) {
+    int dy = (int)((float)j * inv_bw);
+    rem = j - dy * bw;
+    if (rem < 0) { --dy; rem += bw; }
+    else if (rem >= bw) { ++dy; rem -= bw; }
+    return dy;
+}
+
 __device__ __forceinline__ void count_tiles(const Proj2d& p, int tx, int row0, int row1, int32_t* tile_count,
                                             int first = 0, int stride = 1) {
     if (p.nth <= 0) return;
     const int ya = max(p.y0, row0), yb = min(p.y1, row1), bw = p.x1 - p.x0;
     const int nt = (yb - ya) * bw;
+    const float inv_bw = __fdividef(1.f, (float)bw);
     for (int j = first; j < nt; j += stride) {
-        const int dy = j / bw;
-        atomicAdd(&tile_count[(ya + dy) * tx + p.x0 + (j - dy * bw)], 1);
+        int dx;
+        const int dy = div_small(j, bw, inv_bw, dx);
+        atomicAdd(&tile_count[(ya + dy) * tx + p.x0 + dx], 1);
     }
 }
 
@@ -376,6 +389,7 @@ __device__ __forceinline__ int scatter_records(const Proj2d& p, int i, float o, 
     if (nt <= first) return 0;
     int mine = 0;
     const PairExtent ext = pair_extent(p.cx, p.cy, o, p.conic.x, p.conic.y, p.conic.z);   // once per Gaussian, not per tile
+    const float inv_bw = __fdividef(1.f, (float)bw);
     for (int base = first; base < nt; base += BATCH * stride) {
         int pos[BATCH], tid_[BATCH];
         uint32_t rect[BATCH];
@@ -383,8 +397,9 @@ __device__ __forceinline__ int scatter_records(const Proj2d& p, int i, float o, 
         for (int k = 0; k < BATCH; ++k) {
             const int j = base + k * stride;
             if (j < nt) {
-                const int dy = j / bw;
-                const int x = p.x0 + (j - dy * bw), y = ya + dy;
+                int dx;
+                const int dy = div_small(j, bw, inv_bw, dx);
+                const int x = p.x0 + dx, y = ya + dy;
                 tid_[k] = y * tx + x;
                 ++mine;
                 rect[k] = pair_rect_of(p.cx, p.cy, ext, x * GS2D_TILE, y * GS2D_TILE, W, H);
@@ -1123,8 +1138,15 @@ __device__ __forceinline__ float adan_one(float p, float g, float& m, float& nn,
     nn = nn * h.b3 + (1.f - h.b3) * u * u;
     const float denom = sqrtf(nn) * h.inv_bc3_sqrt + h.eps;
     prev = g;
-    const float q = p - h.step_size * (m / denom) - h.step_size_diff * (d / denom);
-    return h.decay_div == 1.f ? q : q / h.decay_div;   // x / 1 == x: no weight decay (the reference's setting), no division
+    float q = p - h.step_size * (m / denom) - h.step_size_diff * (d / denom);
+    // x / 1 == x: no weight decay (the reference's setting), no division.  The empty asm keeps the compiler from
+    // turning the (uniform) branch into a select that computes the IEEE division anyway -- it did: 4 % of the
+    // update kernel's instructions (profiles/r2_fit_update_hotspots.txt)
+    if (h.decay_div != 1.f) {
+        asm volatile("" ::: "memory");
+        q = q / h.decay_div;
+    }
+    return q;
 }
 
 // PACKED: the parameters live in one fp32 [n][8] buffer (xyz 2 | chol 3 | feat 3; gs2d_fit_options.params8),
