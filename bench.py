@@ -704,13 +704,18 @@ def run_spatial(args, rank: int, world: int, dev, flush):
         if exchange == "nccl":
             return n * 48 * 2                                          # all-reduce: reduce-scatter + all-gather
         gather = (n // world) * 32 * (world - 1)                      # the shard's new rows stored into every peer
-        if exchange == "sharded":                                      # pushed: 32 bytes per pair of the band, remote owners
+        if getattr(fit, "push", False):                                # pushed: 32 bytes per pair of the band, remote owners
             return int(fit.status()[0] * 32 * (world - 1) / world) + gather
         return (n // world) * 48 * (world - 1) + gather                # pulled: the shard's rows read from every peer
 
-    for exchange in ("sharded", "sharded_pull", "sharded_remote_scatter", "nccl"):
+    # "sharded" is the default a user gets: pushed from three ranks up, pulled at two (measured); the other of the
+    # two reductions runs beside it
+    other = "sharded_pull" if world >= 3 else "sharded_push"
+    variants = ("sharded", other, "sharded_remote_scatter", "nccl")
+    for exchange in variants:
         fit = SpatialFrameFit(h, w, n, dev, init=init, exchange=exchange.split("_")[0], balance=True,
-                              remote_scatter=exchange == "sharded_remote_scatter", push=exchange != "sharded_pull")
+                              remote_scatter=exchange == "sharded_remote_scatter",
+                              push={"sharded_pull": False, "sharded_push": True}.get(exchange))
         fit.train_iters(gt, Wm)
         dist.barrier(); torch.cuda.synchronize(dev)
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -726,6 +731,7 @@ def run_spatial(args, rank: int, world: int, dev, flush):
         dist.all_reduce(lo, op=dist.ReduceOp.MIN); dist.all_reduce(hi, op=dist.ReduceOp.MAX)
         out[exchange] = {"ms_per_iter": float(ms), "iters_per_s": 1e3 / float(ms), "loss": loss, "bands": fit.bands,
                          "params_identical_across_ranks": bool(torch.equal(lo, hi)),
+                         "reduction": ("push" if fit.push else "pull") if exchange.startswith("sharded") else "all-reduce",
                          "exchange_bytes_per_rank_per_iter": exchange_bytes(exchange, fit)}
         if exchange == "sharded":
             keep = fit
@@ -744,12 +750,12 @@ def run_spatial(args, rank: int, world: int, dev, flush):
         d = (ref._params8 - keep._params8).abs()
         out["single_gpu_ms_per_iter"] = ref_ms
         out["loss_single_gpu"] = ref_loss
-        for exchange in ("sharded", "sharded_pull", "sharded_remote_scatter", "nccl"):
+        for exchange in variants:
             out[exchange]["speedup_vs_single_gpu"] = ref_ms / out[exchange]["ms_per_iter"]
             out[exchange]["loss_rel_diff_vs_single_gpu"] = abs(out[exchange]["loss"] - ref_loss) / ref_loss
         out["median_abs_param_diff_vs_single_gpu"] = float(d.median())
         out["parity_ok"] = bool(all(out[x]["params_identical_across_ranks"] and out[x]["loss_rel_diff_vs_single_gpu"] <= 2e-3
-                                    for x in ("sharded", "sharded_pull", "sharded_remote_scatter", "nccl")))
+                                    for x in variants))
     dist.barrier()
     return out if rank == 0 else None
 

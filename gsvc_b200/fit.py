@@ -12,6 +12,7 @@ from __future__ import annotations
 
 import math
 import os
+from typing import Optional
 
 import torch
 import torch.nn.functional as F
@@ -881,7 +882,7 @@ class SpatialFrameFit(FusedFrameFit):
 
     def __init__(self, H, W, num_points, device, group=None, bands=None, emulate_world: int = 0,
                  exchange: str = "nccl", slots: bool = False, own_barrier: bool = True, balance: bool = False,
-                 remote_scatter: bool = False, push: bool = True, **kw):
+                 remote_scatter: bool = False, push: Optional[bool] = None, **kw):
         """exchange: "nccl" -- one all-reduce call on the gradient rows between the two phases;
         "peer" -- the rows live in symmetric (peer-mapped) memory and the update kernel itself sums
         them over NVLink in rank order after a device-side barrier: no collective kernel, no extra
@@ -902,7 +903,11 @@ class SpatialFrameFit(FusedFrameFit):
         self.remote_scatter = bool(remote_scatter)
         # sharded update only: the tile kernels add every pair's gradient straight into the OWNER rank's buffer
         # (gs2d_grad_exchange.push_per) instead of the update kernel reading every rank's rows
-        self.push = bool(push) and os.environ.get("GS2D_NO_PUSH") != "1"
+        # Default (None): from three ranks up.  Measured on C5 (profiles/r2_mg{2,4,8}_bench.json): the remote
+        # reductions cost the tile kernel more than the update kernel saves at 2 GPUs (0.143 vs 0.135 ms), and
+        # win at 4 (0.104 vs 0.116) and 8 (0.087 vs 0.110).
+        self.push = bool(push) if push is not None else None
+        self._push_env_off = os.environ.get("GS2D_NO_PUSH") == "1"
         self.emulate_world = int(emulate_world)
         if exchange not in ("nccl", "peer", "nvls", "sharded"):
             raise ValueError("exchange must be 'nccl', 'peer', 'nvls' or 'sharded'")
@@ -913,6 +918,7 @@ class SpatialFrameFit(FusedFrameFit):
             self.world, self.rank = self.emulate_world, 0
         else:
             self.world, self.rank = dist.get_world_size(group), dist.get_rank(group)
+        self.push = (self.world >= 3 if self.push is None else self.push) and sharded and not self._push_env_off
         ty = (self.H + 15) // 16
         if bands is None and balance:
             # bands "balanced by intersection count (prefix sum over rows of cnt_t)" -- what a band
