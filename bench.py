@@ -584,9 +584,9 @@ def main_gpu(args, rank: int, world: int, local_rank: int):
         if args.trained_like:
             line["config"]["workload"] += " [trained-like init: informational, not the headline config]"
         if hasattr(fit, "status"):
-            line["config"]["max_per_tile"] = fit.status()[2]
-            line["config"]["intersections_last_step"] = I
-            line["config"]["target"] = ("resident frame converted once into the tile kernel's order (gs2d_fit_target_prepare), "
+            # (beside `config`, not in it: `config` carries the same keys on every arm, base_config)
+            line["workload_detail"] = {"max_per_tile": fit.status()[2], "intersections_last_step": I}
+            line["workload_detail"]["target"] = ("resident frame converted once into the tile kernel's order (gs2d_fit_target_prepare), "
                                         "12 B/pixel read per iteration; e2e: raw I420 decoded in the tile kernel"
                                         if getattr(fit, "prepare_targets", False) else "raw frame decoded in the tile kernel")
         if stages:
