@@ -597,6 +597,12 @@ constexpr int kWarpStage = GS2D_WARP_STAGE;
 // experiment (VERDICT r1 #3e; profiles/r2_ab_bulk_stage.txt): slot mode, the tile's first 32 records arrive by ONE
 // bulk asynchronous copy (cp.async.bulk, the 1-D form of TMA) into shared memory, completion on an mbarrier; the
 // warps then rank out of shared memory.  Measured against the lanes' own 16-byte loads: see the file.  Off.
+// gradient rows added by 16-byte vector reductions (REDG.E.ADD.F32x4): 0 never, 1 in the pushed-reduction
+// instantiation (the additions cross NVLink), 2 always.  Measured: profiles/r2_ab_red_v4.txt
+#ifndef GS2D_RED_V4
+#define GS2D_RED_V4 1
+#endif
+constexpr int kRedV4 = GS2D_RED_V4;
 #ifndef GS2D_STAGE_BULK
 #define GS2D_STAGE_BULK 0
 #endif
@@ -1086,14 +1092,25 @@ k_fit_tiles(int W, int H, int tx, int row0, const int32_t* __restrict__ tile_off
             acc[4] += 0.5f * S2;
             acc[5] += cr; acc[6] += cg; acc[7] += cbl;
         }
-        const float tot = group8_reduce8_t(acc, lane);
         const int gid = __float_as_int(q1.w);
         // pushed reduce-scatter (spatial mode, sharded update): the pair's 32 bytes go straight into the gradient
         // buffer of the rank that OWNS the Gaussian (a reduction without return value: fire and forget over NVLink)
         float* gbase = PUSH ? reinterpret_cast<float*>(__ldg(reinterpret_cast<const unsigned long long*>(push_peers) +
                                                                    (live ? gid / push_per : 0))) : grads;
         float* row = gbase + (size_t)gid * 12;
-        if (live && tot != 0.f) atomicAdd(row + l8, tot);   // 4 pairs x 8 consecutive floats
+        if (kRedV4 == 2 || (kRedV4 == 1 && PUSH)) {
+            // two 16-byte reductions per pair instead of eight 4-byte ones: a quarter of the packets on NVLink
+            float t4[4];
+            group8_reduce8_v4(acc, lane, t4);
+            if (live && (l8 & 3) == 0 && (t4[0] != 0.f || t4[1] != 0.f || t4[2] != 0.f || t4[3] != 0.f))
+                red_add_v4<PUSH>(row + l8, t4);
+        } else {
+            const float tot = group8_reduce8_t(acc, lane);
+            if (live && tot != 0.f) {   // 4 pairs x 8 consecutive floats
+                if (PUSH) atomicAdd_system(row + l8, tot);
+                else atomicAdd(row + l8, tot);
+            }
+        }
     }
     }   // batches
 #if GS2D_TILE_PERSIST
