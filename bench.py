@@ -708,10 +708,8 @@ def run_spatial(args, rank: int, world: int, dev, flush):
             return int(fit.status()[0] * 32 * (world - 1) / world) + gather
         return (n // world) * 48 * (world - 1) + gather                # pulled: the shard's rows read from every peer
 
-    # "sharded" is the default a user gets: pushed from three ranks up, pulled at two (measured); the other of the
-    # two reductions runs beside it
-    other = "sharded_pull" if world >= 3 else "sharded_push"
-    variants = ("sharded", other, "sharded_remote_scatter", "nccl")
+    # "sharded" is the default a user gets (pushed reduction); the pulled one runs beside it
+    variants = ("sharded", "sharded_pull", "sharded_remote_scatter", "nccl")
     for exchange in variants:
         fit = SpatialFrameFit(h, w, n, dev, init=init, exchange=exchange.split("_")[0], balance=True,
                               remote_scatter=exchange == "sharded_remote_scatter",

@@ -903,9 +903,9 @@ class SpatialFrameFit(FusedFrameFit):
         self.remote_scatter = bool(remote_scatter)
         # sharded update only: the tile kernels add every pair's gradient straight into the OWNER rank's buffer
         # (gs2d_grad_exchange.push_per) instead of the update kernel reading every rank's rows
-        # Default (None): from three ranks up.  Measured on C5 (profiles/r2_mg{2,4,8}_bench.json): the remote
-        # reductions cost the tile kernel more than the update kernel saves at 2 GPUs (0.143 vs 0.135 ms), and
-        # win at 4 (0.104 vs 0.116) and 8 (0.087 vs 0.110).
+        # Default (None): on.  Measured on C5 (profiles/r2_mg{2,4,8}_bench.json, r2_ab_red_v4.txt): with 16-byte
+        # vector reductions over NVLink pushing wins at every rank count (2: 0.129 vs 0.135 ms, 4: 0.095 vs
+        # 0.115, 8: 0.084 vs 0.110); with scalar ones it lost at two ranks.
         self.push = bool(push) if push is not None else None
         self._push_env_off = os.environ.get("GS2D_NO_PUSH") == "1"
         self.emulate_world = int(emulate_world)
@@ -918,7 +918,7 @@ class SpatialFrameFit(FusedFrameFit):
             self.world, self.rank = self.emulate_world, 0
         else:
             self.world, self.rank = dist.get_world_size(group), dist.get_rank(group)
-        self.push = (self.world >= 3 if self.push is None else self.push) and sharded and not self._push_env_off
+        self.push = (True if self.push is None else self.push) and sharded and not self._push_env_off
         ty = (self.H + 15) // 16
         if bands is None and balance:
             # bands "balanced by intersection count (prefix sum over rows of cnt_t)" -- what a band
