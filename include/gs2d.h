@@ -393,7 +393,7 @@ typedef struct {
      * push_per > 0: Gaussian i is owned by rank i / push_per (so shard_begin / shard_end must be that rank's
      * [r * push_per, min((r + 1) * push_per, n))), and the TILE kernel adds every pair's gradient straight into
      * row i of the owner's buffer `peers[i / push_per]` -- reductions without a return value, fire and forget
-     * over NVLink, 32 bytes per (Gaussian, tile) pair.  After the barrier the update kernel finds its shard's
+     * over NVLink, 32 bytes per (Gaussian, tile) pair as two 16-byte vector reductions (red.global.add.v4.f32).  After the barrier the update kernel finds its shard's
      * rows complete in its OWN buffer (`accumulate`): no peer reads (they made the sharded update's kernel three
      * times slower than the single-GPU one), no spare buffer to clear -- it re-zeroes each row it has read, and
      * the next writes to it come after the step's second barrier.  `zero` is then ignored.
