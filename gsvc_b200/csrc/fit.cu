@@ -534,13 +534,20 @@ k_fit_scatter(int n, const float* __restrict__ xyz_raw, const float* __restrict_
     Proj2d p; float2 m; float3 L;
     float o = 1.f;
     float3 col = make_float3(0.f, 0.f, 0.f);
-    if (i < n) {
+    // (MULTI, the sharded update of the tile-row split: the parameters are what the PEERS' update kernels stored
+    // into this rank's tensors before the barrier kernel this launch depends on -- nothing is read before the wait)
+    if (!MULTI && i < n) {
         fit_project(i, xyz_raw, chol_raw, activate, half_w, half_h, tx, ty, p, m, L, qc);
         o = opac ? opac[i] : 1.f;
         col = fit_colour(i, feat, rgb_w, activate, qc);
     }
     pdl_wait();
     pdl_release();
+    if (MULTI && i < n) {
+        fit_project(i, xyz_raw, chol_raw, activate, half_w, half_h, tx, ty, p, m, L, qc);
+        o = opac ? opac[i] : 1.f;
+        col = fit_colour(i, feat, rgb_w, activate, qc);
+    }
     const bool dead = status[kStOverflow] != 0;
     if (i < n && !dead) {
         const float r = col.x, g = col.y, b = col.z;
@@ -1951,10 +1958,20 @@ int gs2d_fit_step_band(int n, int cap, int img_h, int img_w, float* xyz_raw, flo
                         L.tiles, (int32_t*)(w + L.off_tile_count), status);
                     GS2D_CHECK_LAUNCH("fit_reset_slots");
                 }
-                (rt.R > 0 ? k_fit_scatter<true> : k_fit_scatter<false>)<<<div_up(n, kFitThreads), kFitThreads, 0, s>>>(
-                    n, xyz_raw, chol_raw, features, nullptr, rgb_w, 1, half_w, half_h, tx, ty, row0, row1, img_w, img_h,
-                    nullptr, (int32_t*)(w + L.off_tile_count), status, (float4*)(w + L.off_packed),
-                    1 | (ids_sorted_out ? 0 : cull_bit), step, src, rt);
+                if (rt.R > 0) {
+                    // launched programmatically: its blocks are resident when the barrier kernel before it (the
+                    // previous step's second barrier) lets go; it reads nothing before its wait
+                    GS2D_CHECK_CUDA(launch_pdl(k_fit_scatter<true>, dim3(div_up(n, kFitThreads)), dim3(kFitThreads), s,
+                        n, (const float*)xyz_raw, (const float*)chol_raw, (const float*)features, (const float*)nullptr,
+                        (const float*)rgb_w, 1, half_w, half_h, tx, ty, row0, row1, img_w, img_h, (const int32_t*)nullptr,
+                        (int32_t*)(w + L.off_tile_count), status, (float4*)(w + L.off_packed),
+                        1 | (ids_sorted_out ? 0 : cull_bit), step, src, rt));
+                } else {
+                    k_fit_scatter<false><<<div_up(n, kFitThreads), kFitThreads, 0, s>>>(
+                        n, xyz_raw, chol_raw, features, nullptr, rgb_w, 1, half_w, half_h, tx, ty, row0, row1, img_w, img_h,
+                        nullptr, (int32_t*)(w + L.off_tile_count), status, (float4*)(w + L.off_packed),
+                        1 | (ids_sorted_out ? 0 : cull_bit), step, src, rt);
+                }
                 GS2D_CHECK_LAUNCH("fit_scatter_slots");
             }
         } else {
