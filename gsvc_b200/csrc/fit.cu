@@ -1129,6 +1129,21 @@ k_fit_tiles(int W, int H, int tx, int row0, const int32_t* __restrict__ tile_off
 // ------------------------------------------------------------------------------------------
 // K4: projection backward + tanh backward + Adan + gradient re-zeroing
 // ------------------------------------------------------------------------------------------
+// the ranks' partial losses: one word per peer, all requests in flight together (a plain `acc += load` loop
+// waits for each NVLink round trip in turn -- on the ONE thread that reports the step, which the whole kernel
+// then waits for: 2 us per peer)
+__device__ __forceinline__ float sum_peer_words(const float* const* __restrict__ peers, int num_peers, size_t at) {
+    float acc = 0.f;
+    for (int r0 = 0; r0 < num_peers; r0 += 8) {
+        float v[8];
+#pragma unroll
+        for (int k = 0; k < 8; ++k) v[k] = (r0 + k < num_peers) ? __ldcg(peers[r0 + k] + at) : 0.f;
+#pragma unroll
+        for (int k = 0; k < 8; ++k) acc += v[k];
+    }
+    return acc;
+}
+
 // one 16-byte row segment summed over all ranks by the NVLink switch (NVLS)
 __device__ __forceinline__ float4 multimem_sum4(const float* mc) {
     float4 v;
@@ -1245,9 +1260,7 @@ k_fit_update(int n, float* __restrict__ xyz_raw, float* __restrict__ chol_raw, f
             if (mc_grads) {
                 ls = (double)multimem_sum1(mc_grads + 9);
             } else if (num_peers > 0) {
-                float acc = 0.f;
-                for (int r = 0; r < num_peers; ++r) acc += __ldcg(peer_grads[r] + 9);
-                ls = (double)acc;
+                ls = (double)sum_peer_words(peer_grads, num_peers, 9);
             } else {
                 ls = (double)grads[9];
             }
@@ -1518,9 +1531,7 @@ k_fit_update_quad(int n, float* __restrict__ params8, float* __restrict__ adan, 
             } else if (MULTI && num_peers > 0) {
                 // pushed reduction: the ranks' partial losses sit past the rows, in one of two words by step parity
                 const size_t pad = push ? (size_t)n * 12 + 16 * ((next_step - 1) & 1) : 9;
-                float acc = 0.f;
-                for (int r = 0; r < num_peers; ++r) acc += __ldcg(peer_grads[r] + pad);
-                ls = (double)acc;
+                ls = (double)sum_peer_words(peer_grads, num_peers, pad);
             } else {
                 ls = (double)grads[9];
             }
