@@ -53,8 +53,8 @@ class GradExchange(Structure):
     _fields_ = [("accumulate", c_void_p), ("peers", c_void_p), ("num_peers", c_int), ("zero", c_void_p),
                 ("multicast", c_void_p), ("shard_begin", c_int), ("shard_end", c_int), ("xyz_peers", c_void_p),
                 ("chol_peers", c_void_p), ("feat_peers", c_void_p), ("status_peers", c_void_p),
-                ("work_peers", c_void_p), ("band_edges", c_void_p), ("push_per", c_int),
-                ("barrier_pads", c_void_p), ("rank", c_int), ("barrier_epoch", c_uint32)]
+                ("work_peers", c_void_p), ("band_edges", c_void_p),
+                ("barrier_pads", c_void_p), ("rank", c_int), ("barrier_epoch", c_uint32), ("push_per", c_int)]
 
 
 class FitOptions(Structure):

@@ -389,18 +389,6 @@ typedef struct {
      * The report's num_intersects then counts the pairs of this rank's SHARD (over all bands). */
     void* const* work_peers;
     const int32_t* band_edges;
-    /* ---- pushed reduce-scatter (optional, with a sharded update; needs gs2d_fit_options.params8) ----------
-     * push_per > 0: Gaussian i is owned by rank i / push_per (so shard_begin / shard_end must be that rank's
-     * [r * push_per, min((r + 1) * push_per, n))), and the TILE kernel adds every pair's gradient straight into
-     * row i of the owner's buffer `peers[i / push_per]` -- reductions without a return value, fire and forget
-     * over NVLink, 32 bytes per (Gaussian, tile) pair as two 16-byte vector reductions (red.global.add.v4.f32).  After the barrier the update kernel finds its shard's
-     * rows complete in its OWN buffer (`accumulate`): no peer reads (they made the sharded update's kernel three
-     * times slower than the single-GPU one), no spare buffer to clear -- it re-zeroes each row it has read, and
-     * the next writes to it come after the step's second barrier.  `zero` is then ignored.
-     * Every buffer must then be n * 12 + 32 floats long (zero before the first step): row 0 belongs to rank 0
-     * alone, so a rank's partial loss goes into word n * 12 + 16 * (step & 1) of its OWN buffer instead of row
-     * 0's pad; the update kernels sum that word over `peers` and clear the other parity's for the next step. */
-    int push_per;
     /* ---- cross-rank barrier issued by the library (optional; any peer exchange) -------------------
      * With `barrier_pads` set and both phases in one call, the barrier between GRADS and UPDATE (and,
      * for a sharded update, the one after UPDATE) is a one-warp kernel of this library on the same
@@ -416,6 +404,20 @@ typedef struct {
     uint32_t* const* barrier_pads;
     int rank;
     uint32_t barrier_epoch;
+    /* ---- pushed reduce-scatter (optional, with a sharded update; needs gs2d_fit_options.params8; the newest
+     * field, hence last: the layout before it is as it was) ----------
+     * push_per > 0: Gaussian i is owned by rank i / push_per (so shard_begin / shard_end must be that rank's
+     * [r * push_per, min((r + 1) * push_per, n))), and the TILE kernel adds every pair's gradient straight into
+     * row i of the owner's buffer `peers[i / push_per]` -- reductions without a return value, fire and forget
+     * over NVLink, 32 bytes per (Gaussian, tile) pair as two 16-byte vector reductions
+     * (red.global.add.v4.f32).  After the barrier the update kernel finds its shard's rows complete in its OWN
+     * buffer (`accumulate`): no peer reads (they made the sharded update's kernel three times slower than the
+     * single-GPU one), no spare buffer to clear -- it re-zeroes each row it has read, and the next writes to
+     * it come after the step's second barrier.  `zero` is then ignored.
+     * Every buffer must then be n * 12 + 32 floats long (zero before the first step): row 0 belongs to rank 0
+     * alone, so a rank's partial loss goes into word n * 12 + 16 * (step & 1) of its OWN buffer instead of row
+     * 0's pad; the update kernels sum that word over `peers` and clear the other parity's for the next step. */
+    int push_per;
 } gs2d_grad_exchange;
 /* Optional extras of a step: the learnable colour weight and the optimizer bookkeeping that the
  * reference's prune / add control needs (GaussianSplats_Represent.py:31-36 rgb_W, :62-67
