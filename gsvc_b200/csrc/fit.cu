@@ -1054,7 +1054,7 @@ k_fit_tiles(int W, int H, int tx, int row0, const int32_t* __restrict__ tile_off
             const float dx = subf(gx, (float)(ox + lxp));
             const float t1 = mulf(cxh, dx), t3 = mulf(cy, dx);
             // Straight-line inner loop: a pixel that fails the reference's test contributes vis = alpha
-            // = 0, and so does a lane whose column lies outside its pair's rectangle (col_ok).  Rows are
+            // = 0; a lane whose column lies outside its pair's rectangle (col_ok) drops its sums after the walk.  Rows are
             // not masked: the four pairs of a pass walk max_h rows, and a row past a pair's own ry1 is
             // either inside the tile, where the rectangle guarantees that the test fails
             // (gs2d_math.cuh:pair_rect), or past the tile, where v_out reads the zero rows.
@@ -1076,9 +1076,16 @@ k_fit_tiles(int W, int H, int tx, int row0, const int32_t* __restrict__ tile_off
                     const float sg = fmaf_(dy, t3, fmaf_(dx, t1, mulf(mulf(czh, dy), dy)));
                     const float vis = gauss_vis(sg);
                     const float oa = mulf(opac, vis);                                 // alpha before the clamp at 1
-                    const float al = minf(oa, 1.f);
-                    const bool ok = col_ok && gauss_pass(sg, al);
-                    const float oak = ok ? oa : 0.f, alk = ok ? al : 0.f;
+                    // gauss_pass(sg, min(oa, 1)) ? oa : 0.  min(oa, 1) < 1/255 <=> oa < 1/255, so the test looks at oa
+                    // and ONE select serves the clamped and the unclamped alpha (min(0, 1) = 0); written as two
+                    // chained predicate sets + a select (the compiler made it two compare/select pairs).  A lane
+                    // outside its pair's columns is not masked per pixel: what it accumulates is dropped after the
+                    // column.  28 -> 26 instructions per pixel: 47.9 -> 46.9 us at C2, 121.1 -> 116.0 us with
+                    // trained-like Gaussians, same values (profiles/r2_ab_bwd_lean.txt).
+                    float oak;
+                    asm("{\n.reg .pred p;\nsetp.geu.f32 p, %1, 0f00000000;\nsetp.geu.and.f32 p, %2, 0f3B808081, p;\n"
+                        "selp.f32 %0, %2, 0f00000000, p;\n}" : "=f"(oak) : "f"(sg), "f"(oa));   // 0f3B808081 = 1/255 as gauss_pass has it
+                    const float alk = minf(oak, 1.f);
                     const float4 vo = svc[(ry + u) * GS2D_TILE];          // rows past the tile read the zero rows
                     const float v_alpha = q2.x * vo.x + q2.y * vo.y + q2.z * vo.z;   // backward.cu:821-825
                     const float v_sigma = -oak * v_alpha;                             // :827  (-opac * vis * v_alpha)
@@ -1092,6 +1099,7 @@ k_fit_tiles(int W, int H, int tx, int row0, const int32_t* __restrict__ tile_off
                 }
                 dy0 -= (float)kBwdRows;
             }
+            if (!col_ok) { S0 = 0.f; S1 = 0.f; S2 = 0.f; cr = 0.f; cg = 0.f; cbl = 0.f; }   // (not a multiply: NaN-proof)
             acc[0] += cx * dx * S0 + cy * S1;                                         // v_xy     :831-832
             acc[1] += cy * dx * S0 + cz * S1;
             acc[2] += 0.5f * dx * dx * S0;                                            // v_conic  :828-830

@@ -247,9 +247,10 @@ k_raster_bwd_tiles(int W, int H, int tx, const int32_t* __restrict__ tile_bins, 
             const int lxs = min(lxp, GS2D_TILE - 1);
             const float dx = subf(gx, (float)(ox + lxp));
             const float t1 = mulf(cxh, dx), t3 = mulf(cy, dx);
-            float S0 = 0.f, S1 = 0.f, S2 = 0.f, cr = 0.f, cg = 0.f, cbl = 0.f;
+            float S0 = 0.f, S1 = 0.f, S2 = 0.f, cr = 0.f, cg = 0.f, cbl = 0.f, op = 0.f;
             float dy0 = subf(gy, (float)(oy + ry0));   // exact, and so is stepping it by whole rows
             const float4* svc = sv + ry0 * GS2D_TILE + lxs;
+            // (a lane outside its pair's columns is not masked per pixel: its sums are dropped after the walk)
 #pragma unroll 1
             for (int ry = 0; ry < max_h; ry += 2) {
 #pragma unroll
@@ -259,12 +260,12 @@ k_raster_bwd_tiles(int W, int H, int tx, const int32_t* __restrict__ tile_bins, 
                     const float vis = gauss_vis(sg);
                     const float al = minf(mulf(opac, vis), 1.f);
                     const float4 vo = svc[(ry + u) * GS2D_TILE];
-                    const bool ok = col_ok && gidx <= __float_as_int(vo.w) && gauss_pass(sg, al);
+                    const bool ok = gidx <= __float_as_int(vo.w) && gauss_pass(sg, al);
                     const float visk = ok ? vis : 0.f, alk = ok ? al : 0.f;
                     const float va = visk * (q2.x * vo.x + q2.y * vo.y + q2.z * vo.z);   // vis * v_alpha  (backward.cu:821-825)
                     const float v_sigma = -opac * va;                                      // :827
                     const float tt = v_sigma * dy;
-                    acc_op += va;                                                          // v_opacity :833
+                    op += va;                                                              // v_opacity :833
                     S0 += v_sigma;
                     S1 += tt;
                     S2 = fmaf(tt, dy, S2);
@@ -274,6 +275,8 @@ k_raster_bwd_tiles(int W, int H, int tx, const int32_t* __restrict__ tile_bins, 
                 }
                 dy0 -= 2.f;
             }
+            if (!col_ok) { S0 = 0.f; S1 = 0.f; S2 = 0.f; cr = 0.f; cg = 0.f; cbl = 0.f; op = 0.f; }
+            acc_op += op;
             acc[0] += cx * dx * S0 + cy * S1;          // v_xy     :831-832
             acc[1] += cy * dx * S0 + cz * S1;
             acc[2] += 0.5f * dx * dx * S0;             // v_conic  :828-830
