@@ -882,13 +882,16 @@ k_fit_tiles(int W, int H, int tx, int row0, const int32_t* __restrict__ tile_off
     // the same single-rounding operations per pixel as the scalar form (bit-identical results),
     // half the issue slots for the arithmetic (measured: fit +2.9 %, trained-like +4.2 %, render
     // +3.7..7 %; the same packing of the backward's row pairs cost 31 registers and was 8 % slower).
-    // A pixel that fails the test accumulates alpha = 0.
-    f32x2 py2[kPix / 2], pr[kPix / 2], pg[kPix / 2], pb[kPix / 2];
+    // A pixel that fails the test accumulates alpha = 0.  Round 2, late (profiles/r2_ab_fwd_lean.txt): the
+    // colours are accumulated by scalar FFMAs again -- the packed accumulators' register pairs were copied at the
+    // reconvergence of the row-block branch, six moves per block -- the pass test is two chained predicate sets and
+    // one select on the unclamped alpha (gauss_alpha_if_pass), and pixels past the frame's edge are no longer
+    // masked per pixel (nothing of theirs is used): 82 -> 74 instructions per record, 46.8 -> 46.0 us at C2,
+    // render 23.4 k -> 24.3 k fps.
+    f32x2 py2[kPix / 2];
 #pragma unroll
-    for (int P = 0; P < kPix / 2; ++P) {
-        py2[P] = pk2(py[2 * P], py[2 * P + 1]);
-        pr[P] = pg[P] = pb[P] = pk2(0.f, 0.f);
-    }
+    for (int P = 0; P < kPix / 2; ++P) py2[P] = pk2(py[2 * P], py[2 * P + 1]);
+    float sr[kPix] = {}, sg_[kPix] = {}, sb[kPix] = {};   // the pixels' accumulated colours
     for (int bat = 0; bat < nbat; ++bat) {
     if (bat) {
         __syncthreads();   // everyone is done with the previous batch
@@ -926,16 +929,17 @@ k_fit_tiles(int W, int H, int tx, int row0, const int32_t* __restrict__ tile_off
                 const f32x2 sg = fma2(dy, bc2(t3), q);
                 const f32x2 e = mul2(sg, bc2(-1.4426950216293334961f));
                 const f32x2 al = mul2(bc2(q1.y), pk2(ex2_approx(lo2(e)), ex2_approx(hi2(e))));
-                const float a0 = minf(lo2(al), 1.f), a1 = minf(hi2(al), 1.f);
-                const bool ok0 = inside[2 * P] && gauss_pass(lo2(sg), a0);
-                const bool ok1 = inside[2 * P + 1] && gauss_pass(hi2(sg), a1);
-                const f32x2 ak = pk2(ok0 ? a0 : 0.f, ok1 ? a1 : 0.f);
-                pr[P] = fma2(ak, bc2(q2.x), pr[P]);
-                pg[P] = fma2(ak, bc2(q2.y), pg[P]);
-                pb[P] = fma2(ak, bc2(q2.z), pb[P]);
-                if (MODE == 1) {
-                    if (ok0) cur_idx[2 * P] = lob + k;
-                    if (ok1) cur_idx[2 * P + 1] = lob + k;
+                // (pixels past the frame's edge are not masked here: nothing of theirs is ever used)
+                const float k0 = minf(gauss_alpha_if_pass(lo2(sg), lo2(al)), 1.f);
+                const float k1 = minf(gauss_alpha_if_pass(hi2(sg), hi2(al)), 1.f);
+                // scalar accumulation (same single roundings): the packed form's register pairs were copied at
+                // the reconvergence of the row-block branch, six moves per block
+                sr[2 * P] = fmaf_(k0, q2.x, sr[2 * P]); sr[2 * P + 1] = fmaf_(k1, q2.x, sr[2 * P + 1]);
+                sg_[2 * P] = fmaf_(k0, q2.y, sg_[2 * P]); sg_[2 * P + 1] = fmaf_(k1, q2.y, sg_[2 * P + 1]);
+                sb[2 * P] = fmaf_(k0, q2.z, sb[2 * P]); sb[2 * P + 1] = fmaf_(k1, q2.z, sb[2 * P + 1]);
+                if (MODE == 1) {   // a pixel that passed has alpha >= 1/255 (or NaN -> 1 after the min)
+                    if (k0 > 0.f) cur_idx[2 * P] = lob + k;
+                    if (k1 > 0.f) cur_idx[2 * P + 1] = lob + k;
                 }
             }
         }
@@ -943,8 +947,8 @@ k_fit_tiles(int W, int H, int tx, int row0, const int32_t* __restrict__ tile_off
     }   // batches
 #pragma unroll
     for (int P = 0; P < kPix / 2; ++P) {
-        pix[2 * P] = make_float3(lo2(pr[P]), lo2(pg[P]), lo2(pb[P]));
-        pix[2 * P + 1] = make_float3(hi2(pr[P]), hi2(pg[P]), hi2(pb[P]));
+        pix[2 * P] = make_float3(sr[2 * P], sg_[2 * P], sb[2 * P]);
+        pix[2 * P + 1] = make_float3(sr[2 * P + 1], sg_[2 * P + 1], sb[2 * P + 1]);
     }
     if (out_img || final_idx) {
         // operator path (MODE 1, gt = background colour): with no intersection at all the reference
@@ -1082,9 +1086,7 @@ k_fit_tiles(int W, int H, int tx, int row0, const int32_t* __restrict__ tile_off
                     // outside its pair's columns is not masked per pixel: what it accumulates is dropped after the
                     // column.  28 -> 26 instructions per pixel: 47.9 -> 46.9 us at C2, 121.1 -> 116.0 us with
                     // trained-like Gaussians, same values (profiles/r2_ab_bwd_lean.txt).
-                    float oak;
-                    asm("{\n.reg .pred p;\nsetp.geu.f32 p, %1, 0f00000000;\nsetp.geu.and.f32 p, %2, 0f3B808081, p;\n"
-                        "selp.f32 %0, %2, 0f00000000, p;\n}" : "=f"(oak) : "f"(sg), "f"(oa));   // 0f3B808081 = 1/255 as gauss_pass has it
+                    const float oak = gauss_alpha_if_pass(sg, oa);
                     const float alk = minf(oak, 1.f);
                     const float4 vo = svc[(ry + u) * GS2D_TILE];          // rows past the tile read the zero rows
                     const float v_alpha = q2.x * vo.x + q2.y * vo.y + q2.z * vo.z;   // backward.cu:821-825
