@@ -150,20 +150,50 @@ _STATE_KEYS = ("_xyz", "_cholesky", "_features_dc")
 _STATE_COLS = (2, 3, 3)
 
 
-def _gather_states(local: Dict[int, dict], rank: int, world: int, group) -> Optional[Dict[int, dict]]:
-    """rank 0 <- every rank's frames: the small per-frame records (psnr, iterations, Gaussian count) as objects
-    over `group`, the parameters as one flat fp32 tensor per rank (per frame: xyz [n,2] | cholesky [n,3] |
-    features [n,3], frames in order) by one all-gather of the default NCCL group; rank 0 hands out CPU views of it."""
+def _pack_states(local: Dict[int, dict]):
+    """frame -> result  =>  (one flat fp32 tensor: per frame in order xyz [n,2] | cholesky [n,3] | features [n,3];
+    {frame: the result's small fields + "rows": n})"""
     frames = sorted(local)
-    dev = torch.device("cuda", torch.cuda.current_device())
     meta = {f: {k: v for k, v in local[f].items() if k != "state"} for f in frames}
     for f in frames:
         meta[f]["rows"] = int(local[f]["state"]["_xyz"].shape[0])
-    pack = (torch.cat([local[f]["state"][k].reshape(-1) for f in frames for k in _STATE_KEYS])
-            if frames else torch.empty((0,), dtype=torch.float32, device=dev))
-    digest = int(pack.view(torch.int32).to(torch.int64).sum()) if pack.numel() else 0   # of the bits: order-free, exact
+    if not frames:
+        return torch.empty((0,), dtype=torch.float32), meta
+    return torch.cat([local[f]["state"][k].reshape(-1) for f in frames for k in _STATE_KEYS]), meta
+
+
+def _unpack_states(flat: torch.Tensor, meta: Dict[int, dict]) -> Dict[int, dict]:
+    """inverse of _pack_states: the states are contiguous views of `flat`"""
+    want = 8 * sum(int(m["rows"]) for m in meta.values())
+    if flat.numel() != want:
+        raise ValueError(f"GOP gather: {flat.numel()} packed values for frames that need {want}")
+    out: Dict[int, dict] = {}
+    at = 0
+    for f in sorted(meta):
+        m = dict(meta[f])
+        n = m.pop("rows")
+        m["state"] = {}
+        for k, c in zip(_STATE_KEYS, _STATE_COLS):
+            m["state"][k] = flat[at:at + n * c].view(n, c)
+            at += n * c
+        out[f] = m
+    return out
+
+
+def _bit_digest(t: torch.Tensor) -> int:
+    """sum of the tensor's 32-bit words as integers: order-free and exact"""
+    return int(t.contiguous().view(torch.int32).to(torch.int64).sum()) if t.numel() else 0
+
+
+def _gather_states(local: Dict[int, dict], rank: int, world: int, group) -> Optional[Dict[int, dict]]:
+    """rank 0 <- every rank's frames: the small per-frame records (psnr, iterations, Gaussian count) as objects
+    over `group`, the parameters as one flat fp32 tensor per rank (_pack_states) by one all-gather of the
+    default NCCL group; rank 0 hands out CPU views of it."""
+    dev = torch.device("cuda", torch.cuda.current_device())
+    pack, meta = _pack_states(local)
+    pack = pack.to(dev)
     both = [None] * world
-    dist.all_gather_object(both, (meta, digest), group=group)
+    dist.all_gather_object(both, (meta, _bit_digest(pack)), group=group)
     metas, digests = [b[0] for b in both], [b[1] for b in both]
     # ONE all-gather of the job's own NCCL communicator, every rank's share padded to the longest.  Not a gather
     # to rank 0 and not send / recv: NCCL sets up point-to-point connections on their first use, which cost an
@@ -177,23 +207,13 @@ def _gather_states(local: Dict[int, dict], rank: int, world: int, group) -> Opti
     dist.all_gather_into_tensor(everything, padded)
     if rank != 0:
         return None
-    parts = [everything[r * longest:(r + 1) * longest] for r in range(world)]
     merged: Dict[int, dict] = {}
     for r in range(world):
-        buf = parts[r][:elems_of[r]]
-        got = int(buf.view(torch.int32).to(torch.int64).sum()) if buf.numel() else 0
+        buf = everything[r * longest:r * longest + elems_of[r]]
+        got = _bit_digest(buf)
         if got != digests[r]:
             raise RuntimeError(f"GOP gather: rank {r}'s parameters arrived damaged (digest {got} != {digests[r]})")
-        host = buf.cpu()
-        at = 0
-        for f in sorted(metas[r]):
-            m = dict(metas[r][f])
-            n = m.pop("rows")
-            m["state"] = {}
-            for k, c in zip(_STATE_KEYS, _STATE_COLS):
-                m["state"][k] = host[at:at + n * c].view(n, c)      # contiguous views of the rank's buffer
-                at += n * c
-            merged[f] = m
+        merged.update(_unpack_states(buf.cpu(), metas[r]))
     return merged
 
 

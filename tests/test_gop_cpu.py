@@ -256,3 +256,30 @@ def test_keyframe_scores_world_size_3_gloo_with_halo():
     assert res[0][0] == list(range(0, 8))                               # block [0, 8)
     assert res[1][0] == list(range(7, 16))                              # block [8, 16) + the frame before it
     assert res[2][0] == list(range(15, 24))
+
+
+def test_pack_and_unpack_of_a_rank_s_frames_round_trip():
+    """the packing behind the multi-GPU gather (gop._gather_states): frames with different Gaussian counts, out
+    of order in the dict, come back bit for bit, as contiguous views of the flat buffer; the digest is order-free"""
+    from gsvc_b200 import gop
+    g = torch.Generator().manual_seed(3)
+    local = {}
+    for f, n in ((7, 5), (3, 1), (12, 9)):
+        local[f] = {"state": {"_xyz": torch.randn(n, 2, generator=g), "_cholesky": torch.randn(n, 3, generator=g),
+                              "_features_dc": torch.randn(n, 3, generator=g)},
+                    "psnr": 30.0 + f, "iters": 100 * f, "num_points": n}
+    flat, meta = gop._pack_states(local)
+    assert flat.dtype == torch.float32 and flat.numel() == 8 * (5 + 1 + 9)
+    assert sorted(meta) == [3, 7, 12] and [meta[f]["rows"] for f in sorted(meta)] == [1, 5, 9]
+    assert "state" not in meta[7] and meta[7]["psnr"] == 37.0
+    back = gop._unpack_states(flat.clone(), meta)
+    assert sorted(back) == [3, 7, 12]
+    for f in local:
+        assert back[f]["psnr"] == local[f]["psnr"] and back[f]["iters"] == local[f]["iters"] and "rows" not in back[f]
+        for k in ("_xyz", "_cholesky", "_features_dc"):
+            assert back[f]["state"][k].is_contiguous() and torch.equal(back[f]["state"][k], local[f]["state"][k])
+    assert gop._bit_digest(flat) == gop._bit_digest(flat.flip(0)) != gop._bit_digest(flat + 1)
+    empty, meta0 = gop._pack_states({})
+    assert empty.numel() == 0 and meta0 == {} and gop._unpack_states(empty, meta0) == {} and gop._bit_digest(empty) == 0
+    with pytest.raises(ValueError):
+        gop._unpack_states(flat[:-1], meta)
