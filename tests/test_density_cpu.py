@@ -118,3 +118,26 @@ def test_adan_takes_the_reference_constructor_arguments_and_refuses_what_it_lack
     opt = Adan(p)                       # default: decides per step -> foreach on the CPU
     opt.step()
     assert torch.allclose(p[0], torch.full((4, 2), -1e-3), atol=1e-6)
+
+
+def test_step_lr_formula_matches_torch_scheduler_on_cpu():
+    """FusedFrameFit.current_lr() against torch.optim.lr_scheduler.StepLR across boundaries, without a GPU
+    (the method only reads the step index, the schedule and the optimizer clock: called unbound on a stand-in).
+    Iteration `it` runs optimizer.step() BEFORE the it-th scheduler.step() (GaussianSplats_Represent.py:52, 203-206)."""
+    from types import SimpleNamespace
+
+    import torch
+
+    from gsvc_b200.fit import FusedFrameFit
+    for step_size, gamma in ((5, 0.5), (3, 0.1), (20000, 0.5)):
+        stub = SimpleNamespace(lr=1e-2, lr_gamma=gamma, lr_step_size=step_size, step_index=0,
+                               clock=SimpleNamespace(lr_frozen=False))
+        opt = torch.optim.SGD([torch.nn.Parameter(torch.zeros(1))], lr=1e-2)
+        sch = torch.optim.lr_scheduler.StepLR(opt, step_size=step_size, gamma=gamma)
+        for it in range(1, 4 * min(step_size, 10) + 2):
+            stub.step_index = it                      # as _issue has it while iteration `it` is being issued
+            assert FusedFrameFit.current_lr(stub) == pytest.approx(opt.param_groups[0]["lr"], rel=1e-12), (step_size, it)
+            opt.step()
+            sch.step()
+        stub.clock.lr_frozen = True                   # update_optimizer() rebuilt the optimizer without a scheduler (:93-97)
+        assert FusedFrameFit.current_lr(stub) == 1e-2
